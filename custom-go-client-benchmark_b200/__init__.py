@@ -1,0 +1,9 @@
+"""B200-native CRC-32C verification and latency reduction: the data-parallel hot path of
+tritone/custom-go-client-benchmark behind a C ABI (include/b200crc.h).
+
+    crc32c   — Go hash/crc32-shaped surface (New/Update/Checksum/VerifyObjects/Combine)
+    latency  — README histogram, OpenCensus distribution, ssd_test percentiles
+The CUDA library is required; nothing here computes on the CPU.
+"""
+from . import _lib, crc32c, latency  # noqa: F401
+from ._lib import B200Error  # noqa: F401

@@ -1,0 +1,962 @@
+// C ABI of libb200crc.so (declared in include/b200crc.h).  Host-side plumbing only: contexts, plans,
+// staging, streams.  Every message byte is hashed on the GPU; the only CRC arithmetic done here is
+// GF(2) combination of finished per-shard / per-chunk CRCs (b200_crc32c_combine).
+#include "b200crc.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <new>
+#include <vector>
+
+#include "crc_kernels.h"
+#include "lat_kernels.h"
+
+using namespace b200;
+
+namespace {
+
+thread_local char g_err[512] = "";
+
+int fail_cuda(cudaError_t e, const char* what) {
+    snprintf(g_err, sizeof g_err, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+    cudaGetLastError();  // clear sticky-less error state
+    return B200_ERR_CUDA;
+}
+int fail(int code, const char* what) {
+    snprintf(g_err, sizeof g_err, "%s", what);
+    return code;
+}
+#define CU(call)                                             \
+    do {                                                     \
+        cudaError_t e_ = (call);                             \
+        if (e_ != cudaSuccess) return fail_cuda(e_, #call);  \
+    } while (0)
+
+constexpr size_t kStageBytes = 32u << 20;   // staging slab for pageable host input
+constexpr int kSingleSlots = 8192;          // result slots for chunked single-object work
+
+struct DevState {
+    int dev = 0;
+    int grid = 148;
+    cudaStream_t stream = nullptr;       // compute
+    cudaStream_t copy_stream = nullptr;  // H2D
+    DeviceTables tabs{};
+    std::mutex mu;                  // guards the streams and scratch of this device
+    std::recursive_mutex stage_mu;  // guards the staging slabs (held across whole host-input calls)
+    std::map<uint32_t, uint32_t*> adv_seg;  // rows_per_seg -> device [4][256]
+    uint32_t* seg_raw = nullptr;            // scratch for single-object runs
+    size_t seg_raw_cap = 0;
+    uint32_t* d_got = nullptr;              // [kSingleSlots]
+    uint8_t* d_ok = nullptr;                // [1]
+    unsigned long long* d_nbad = nullptr;   // [1]
+    uint8_t* d_stage[2] = {nullptr, nullptr};
+    size_t d_stage_cap = 0;
+    uint8_t* h_stage[2] = {nullptr, nullptr};
+    uint32_t* h_got = nullptr;  // pinned [kSingleSlots]
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    LatScratch lat{};
+};
+
+}  // namespace
+
+struct b200_ctx {
+    std::vector<DevState*> devs;
+};
+
+namespace {
+
+DevState* get_dev(b200_ctx* ctx, int dev) {
+    if (!ctx) return nullptr;
+    for (DevState* d : ctx->devs)
+        if (d->dev == dev) return d;
+    return nullptr;
+}
+
+int upload(uint32_t** dst, const uint32_t* src, size_t n) {
+    CU(cudaMalloc(dst, n * sizeof(uint32_t)));
+    CU(cudaMemcpy(*dst, src, n * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int get_adv_seg(DevState* d, uint32_t rows_per_seg, const uint32_t** out) {
+    auto it = d->adv_seg.find(rows_per_seg);
+    if (it == d->adv_seg.end()) {
+        uint32_t tab[1024];
+        host_build_adv_table((uint64_t)rows_per_seg * kRowBytes, tab);
+        uint32_t* dp = nullptr;
+        if (int rc = upload(&dp, tab, 1024)) return rc;
+        it = d->adv_seg.emplace(rows_per_seg, dp).first;
+    }
+    *out = it->second;
+    return 0;
+}
+
+uint32_t env_rows_per_seg() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200_ROWS_PER_SEG");
+        v = e ? atoi(e) : 0;
+    }
+    return (uint32_t)v;
+}
+
+// Segment length: a power of two number of rows such that every warp of the persistent grid gets
+// several segments, but segments stay long enough to amortise the per-segment column fold.
+uint32_t choose_rows_per_seg(uint64_t total_rows, int grid) {
+    if (uint32_t e = env_rows_per_seg()) return e;
+    uint64_t target = total_rows / ((uint64_t)grid * kRowsWarps * 6);
+    uint32_t r = 16;
+    while ((uint64_t)r * 2 <= target && r < 1024) r *= 2;
+    return r;
+}
+
+int ensure_seg_raw(DevState* d, size_t ntasks) {
+    if (ntasks <= d->seg_raw_cap) return 0;
+    if (d->seg_raw) cudaFree(d->seg_raw);
+    d->seg_raw = nullptr;
+    d->seg_raw_cap = 0;
+    size_t cap = std::max<size_t>(ntasks, 1 << 16);
+    CU(cudaMalloc(&d->seg_raw, cap * sizeof(uint32_t)));
+    d->seg_raw_cap = cap;
+    return 0;
+}
+
+int ensure_stage(DevState* d, size_t bytes) {
+    if (bytes <= d->d_stage_cap) return 0;
+    for (int i = 0; i < 2; i++) {
+        if (d->d_stage[i]) cudaFree(d->d_stage[i]);
+        d->d_stage[i] = nullptr;
+    }
+    d->d_stage_cap = 0;
+    for (int i = 0; i < 2; i++) CU(cudaMalloc(&d->d_stage[i], bytes));
+    d->d_stage_cap = bytes;
+    return 0;
+}
+
+// Enqueue CRC of one device buffer on d->stream; result lands in d->d_got[slot].  Caller holds d->mu.
+int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc, int slot) {
+    uintptr_t addr = (uintptr_t)dptr;
+    uintptr_t base = addr & ~(uintptr_t)15;
+    BatchArgs a{};
+    a.base = (const uint8_t*)base;
+    a.single_off = addr - base;
+    a.single_len = n;
+    ObjectCut cut = cut_object(addr, n);
+    a.rows_per_seg = choose_rows_per_seg(cut.rows, d->grid);
+    uint64_t ntasks = (cut.rows + a.rows_per_seg - 1) / a.rows_per_seg;
+    while (ntasks > (1u << 30)) {
+        a.rows_per_seg *= 2;
+        ntasks = (cut.rows + a.rows_per_seg - 1) / a.rows_per_seg;
+    }
+    if (int rc = ensure_seg_raw(d, ntasks)) return rc;
+    if (int rc = get_adv_seg(d, a.rows_per_seg, &a.adv_seg)) return rc;
+    a.nobj = 1;
+    a.ntasks = (uint32_t)ntasks;
+    a.seg_raw = d->seg_raw;
+    a.got = d->d_got + slot;
+    a.ok = d->d_ok;
+    a.nbad = d->d_nbad;
+    a.init_crc = init_crc;
+    CU(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr));
+    return 0;
+}
+
+bool is_pinned(const void* p) {
+    cudaPointerAttributes at{};
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return at.type == cudaMemoryTypeHost;
+}
+
+// CRC of n host bytes, chunked and double buffered: H2D of chunk k+1 overlaps the kernels of chunk k.
+// Chunk CRCs (each a fresh checksum) are folded on the host with GF(2) combine.  Caller holds d->mu.
+int stream_host_locked(DevState* d, uint32_t crc, const uint8_t* host, size_t n, size_t chunk, uint32_t* out) {
+    if (n == 0) {
+        *out = crc;
+        return 0;
+    }
+    if (chunk == 0) chunk = kStageBytes;
+    chunk = (chunk + 511) & ~(size_t)511;
+    const bool pinned = is_pinned(host);
+    if (!pinned && chunk > kStageBytes) chunk = kStageBytes;
+    size_t nchunks = (n + chunk - 1) / chunk;
+    while (nchunks > (size_t)kSingleSlots) {  // keep within the result slots: larger chunks (pinned only)
+        if (!pinned) break;
+        chunk *= 2;
+        nchunks = (n + chunk - 1) / chunk;
+    }
+    if (int rc = ensure_stage(d, std::min(chunk, (n + 511) & ~(size_t)511))) return rc;
+    size_t done_chunks = 0;
+    uint32_t acc = crc;
+    while (done_chunks < nchunks) {
+        size_t batch = std::min(nchunks - done_chunks, (size_t)kSingleSlots);
+        for (size_t k = 0; k < batch; k++) {
+            size_t idx = done_chunks + k;
+            int b = (int)(idx & 1);
+            size_t o = idx * chunk;
+            size_t len = std::min(chunk, n - o);
+            if (idx >= 2) CU(cudaStreamWaitEvent(d->copy_stream, d->ev_done[b], 0));
+            const uint8_t* src = host + o;
+            if (!pinned) {
+                if (idx >= 2) CU(cudaEventSynchronize(d->ev_copied[b]));  // pinned slab free again
+                memcpy(d->h_stage[b], src, len);
+                src = d->h_stage[b];
+            }
+            CU(cudaMemcpyAsync(d->d_stage[b], src, len, cudaMemcpyHostToDevice, d->copy_stream));
+            CU(cudaEventRecord(d->ev_copied[b], d->copy_stream));
+            CU(cudaStreamWaitEvent(d->stream, d->ev_copied[b], 0));
+            if (int rc = enqueue_single(d, d->d_stage[b], len, 0, (int)k)) return rc;
+            CU(cudaEventRecord(d->ev_done[b], d->stream));
+        }
+        CU(cudaMemcpyAsync(d->h_got, d->d_got, batch * sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+        for (size_t k = 0; k < batch; k++) {
+            size_t idx = done_chunks + k;
+            size_t len = std::min(chunk, n - idx * chunk);
+            acc = b200_crc32c_combine(acc, d->h_got[k], len);
+        }
+        done_chunks += batch;
+    }
+    *out = acc;
+    return 0;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------------
+
+extern "C" {
+
+const char* b200_strerror(int status) {
+    switch (status) {
+        case B200_OK: return "ok";
+        case B200_ERR_INVALID: return "invalid argument";
+        case B200_ERR_CUDA: return "CUDA error";
+        case B200_ERR_NOMEM: return "out of memory";
+        case B200_ERR_EMPTY: return "empty sample set";
+        case B200_ERR_TOO_LARGE: return "size beyond fixed capacity";
+        default: return "unknown status";
+    }
+}
+
+const char* b200_last_error(void) { return g_err; }
+
+int b200_device_count(int* n) {
+    if (!n) return fail(B200_ERR_INVALID, "n is null");
+    CU(cudaGetDeviceCount(n));
+    return 0;
+}
+
+int b200_init(int ndev, const int* devs, b200_ctx** out) {
+    if (!out || ndev < 1) return fail(B200_ERR_INVALID, "b200_init: ndev < 1 or out is null");
+    int have = 0;
+    CU(cudaGetDeviceCount(&have));
+    b200_ctx* ctx = new (std::nothrow) b200_ctx;
+    if (!ctx) return fail(B200_ERR_NOMEM, "b200_init");
+    uint32_t adv_row[1024], col_k[128], xsq[64], byte_tab[256];
+    host_build_adv_table(kRowBytes, adv_row);
+    host_build_col_k(col_k);
+    host_build_xpow8_sq(xsq);
+    host_build_byte_tab(byte_tab);
+    for (int i = 0; i < ndev; i++) {
+        int dev = devs ? devs[i] : i;
+        if (dev < 0 || dev >= have) {
+            b200_shutdown(ctx);
+            return fail(B200_ERR_INVALID, "b200_init: no such device");
+        }
+        DevState* d = new (std::nothrow) DevState;
+        if (!d) {
+            b200_shutdown(ctx);
+            return fail(B200_ERR_NOMEM, "b200_init");
+        }
+        d->dev = dev;
+        ctx->devs.push_back(d);
+        cudaError_t e = cudaSetDevice(dev);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking);
+        for (int b = 0; b < 2 && e == cudaSuccess; b++) {
+            e = cudaEventCreateWithFlags(&d->ev_copied[b], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_done[b], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaHostAlloc(&d->h_stage[b], kStageBytes, cudaHostAllocDefault);
+        }
+        if (e == cudaSuccess) e = cudaHostAlloc(&d->h_got, kSingleSlots * sizeof(uint32_t), cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaMalloc(&d->d_got, kSingleSlots * sizeof(uint32_t));
+        if (e == cudaSuccess) e = cudaMalloc(&d->d_ok, 16);
+        if (e == cudaSuccess) e = cudaMalloc(&d->d_nbad, sizeof(unsigned long long));
+        if (e != cudaSuccess) {
+            b200_shutdown(ctx);
+            return fail_cuda(e, "b200_init: device setup");
+        }
+        d->grid = rows_kernel_grid(dev);
+        int rc = upload(&d->tabs.adv_row, adv_row, 1024);
+        if (!rc) rc = upload(&d->tabs.col_k, col_k, 128);
+        if (!rc) rc = upload(&d->tabs.xpow8_sq, xsq, 64);
+        if (!rc) rc = upload(&d->tabs.byte_tab, byte_tab, 256);
+        if (!rc) rc = lat_scratch_init(&d->lat) == cudaSuccess ? 0 : fail(B200_ERR_CUDA, "latency scratch");
+        if (rc) {
+            b200_shutdown(ctx);
+            return rc;
+        }
+    }
+    *out = ctx;
+    return 0;
+}
+
+int b200_shutdown(b200_ctx* ctx) {
+    if (!ctx) return 0;
+    for (DevState* d : ctx->devs) {
+        cudaSetDevice(d->dev);
+        if (d->stream) cudaStreamSynchronize(d->stream);
+        if (d->copy_stream) cudaStreamSynchronize(d->copy_stream);
+        for (auto& kv : d->adv_seg) cudaFree(kv.second);
+        cudaFree(d->tabs.adv_row);
+        cudaFree(d->tabs.col_k);
+        cudaFree(d->tabs.xpow8_sq);
+        cudaFree(d->tabs.byte_tab);
+        cudaFree(d->seg_raw);
+        cudaFree(d->d_got);
+        cudaFree(d->d_ok);
+        cudaFree(d->d_nbad);
+        cudaFreeHost(d->h_got);
+        lat_scratch_free(&d->lat);
+        for (int b = 0; b < 2; b++) {
+            cudaFree(d->d_stage[b]);
+            cudaFreeHost(d->h_stage[b]);
+            if (d->ev_copied[b]) cudaEventDestroy(d->ev_copied[b]);
+            if (d->ev_done[b]) cudaEventDestroy(d->ev_done[b]);
+        }
+        if (d->stream) cudaStreamDestroy(d->stream);
+        if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
+        delete d;
+    }
+    cudaGetLastError();
+    delete ctx;
+    return 0;
+}
+
+int b200_ctx_ndev(const b200_ctx* ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+
+int b200_alloc_pinned(b200_ctx* ctx, size_t n, void** host) {
+    if (!ctx || !host) return fail(B200_ERR_INVALID, "b200_alloc_pinned");
+    CU(cudaSetDevice(ctx->devs[0]->dev));
+    cudaError_t e = cudaHostAlloc(host, n ? n : 1, cudaHostAllocPortable);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        return fail(B200_ERR_NOMEM, "cudaHostAlloc");
+    }
+    CU(e);
+    return 0;
+}
+
+int b200_free_pinned(b200_ctx* ctx, void* host) {
+    if (!ctx) return fail(B200_ERR_INVALID, "b200_free_pinned");
+    if (host) CU(cudaFreeHost(host));
+    return 0;
+}
+
+int b200_alloc_device(b200_ctx* ctx, int dev, size_t n, void** dptr) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !dptr) return fail(B200_ERR_INVALID, "b200_alloc_device: unknown device or null out");
+    CU(cudaSetDevice(dev));
+    cudaError_t e = cudaMalloc(dptr, n ? n : 1);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        return fail(B200_ERR_NOMEM, "cudaMalloc");
+    }
+    CU(e);
+    return 0;
+}
+
+int b200_free_device(b200_ctx* ctx, int dev, void* dptr) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d) return fail(B200_ERR_INVALID, "b200_free_device: unknown device");
+    CU(cudaSetDevice(dev));
+    if (dptr) CU(cudaFree(dptr));
+    return 0;
+}
+
+int b200_memcpy_h2d(b200_ctx* ctx, int dev, void* dptr, const void* host, size_t n) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || (n && (!dptr || !host))) return fail(B200_ERR_INVALID, "b200_memcpy_h2d");
+    CU(cudaSetDevice(dev));
+    CU(cudaMemcpy(dptr, host, n, cudaMemcpyHostToDevice));
+    return 0;
+}
+
+int b200_memcpy_d2h(b200_ctx* ctx, int dev, void* host, const void* dptr, size_t n) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || (n && (!dptr || !host))) return fail(B200_ERR_INVALID, "b200_memcpy_d2h");
+    CU(cudaSetDevice(dev));
+    CU(cudaMemcpy(host, dptr, n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+uint32_t b200_crc32c_combine(uint32_t crc1, uint32_t crc2, uint64_t len2) {
+    return gf2_mul(host_xpow8(len2), crc1) ^ crc2;
+}
+
+int b200_crc32c_update_device(b200_ctx* ctx, int dev, uint32_t crc, const void* dptr, size_t n, uint32_t* out) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !out || (n && !dptr)) return fail(B200_ERR_INVALID, "b200_crc32c_update_device");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    if (int rc = enqueue_single(d, dptr, n, crc, 0)) return rc;
+    CU(cudaMemcpyAsync(d->h_got, d->d_got, sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    *out = d->h_got[0];
+    return 0;
+}
+
+int b200_crc32c_stream_host(b200_ctx* ctx, int dev, uint32_t crc, const void* host, size_t n, size_t chunk,
+                            uint32_t* out) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !out || (n && !host)) return fail(B200_ERR_INVALID, "b200_crc32c_stream_host");
+    std::lock_guard<std::recursive_mutex> slk(d->stage_mu);
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    return stream_host_locked(d, crc, (const uint8_t*)host, n, chunk, out);
+}
+
+int b200_crc32c_update_host(b200_ctx* ctx, int dev, uint32_t crc, const void* p, size_t n, uint32_t* out) {
+    return b200_crc32c_stream_host(ctx, dev, crc, p, n, 0, out);
+}
+
+int b200_crc32c_sharded(b200_ctx* ctx, const void* const* dptr_per_dev, const uint64_t* len_per_dev, int ndev,
+                        uint32_t* out) {
+    if (!ctx || !dptr_per_dev || !len_per_dev || !out || ndev < 1 || ndev > (int)ctx->devs.size())
+        return fail(B200_ERR_INVALID, "b200_crc32c_sharded");
+    // enqueue on every device first, then collect: the shards run concurrently
+    for (int i = 0; i < ndev; i++) {
+        DevState* d = ctx->devs[i];
+        d->mu.lock();
+    }
+    int rc = 0;
+    for (int i = 0; i < ndev && !rc; i++) {
+        DevState* d = ctx->devs[i];
+        cudaError_t e = cudaSetDevice(d->dev);
+        if (e != cudaSuccess) { rc = fail_cuda(e, "cudaSetDevice"); break; }
+        rc = enqueue_single(d, dptr_per_dev[i], len_per_dev[i], 0, 0);
+        if (!rc) {
+            e = cudaMemcpyAsync(d->h_got, d->d_got, sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream);
+            if (e != cudaSuccess) rc = fail_cuda(e, "cudaMemcpyAsync");
+        }
+    }
+    uint32_t acc = 0;
+    for (int i = 0; i < ndev; i++) {
+        DevState* d = ctx->devs[i];
+        if (!rc) {
+            cudaSetDevice(d->dev);
+            cudaError_t e = cudaStreamSynchronize(d->stream);
+            if (e != cudaSuccess) rc = fail_cuda(e, "cudaStreamSynchronize");
+            else acc = b200_crc32c_combine(acc, d->h_got[0], len_per_dev[i]);
+        }
+    }
+    for (int i = 0; i < ndev; i++) ctx->devs[i]->mu.unlock();
+    if (!rc) *out = acc;
+    return rc;
+}
+
+int b200_fill_payload_device(b200_ctx* ctx, int dev, void* dptr, uint64_t first_word, size_t nwords, uint64_t seed) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || (nwords && !dptr) || ((uintptr_t)dptr & 7)) return fail(B200_ERR_INVALID, "b200_fill_payload_device");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    CU(launch_fill_payload((uint64_t*)dptr, first_word, nwords, seed, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
+int b200_fill_latency_ns_device(b200_ctx* ctx, int dev, int64_t* dptr, uint64_t first, size_t n, uint64_t seed) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || (n && !dptr)) return fail(B200_ERR_INVALID, "b200_fill_latency_ns_device");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    CU(launch_fill_latency(dptr, first, n, seed, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
+}  // extern "C"
+
+// ---- prepared batches -------------------------------------------------------------------------------
+
+struct b200_batch {
+    DevState* d = nullptr;
+    size_t nobj = 0;
+    uint64_t* d_off = nullptr;
+    uint64_t* d_len = nullptr;
+    uint32_t* d_seg_start = nullptr;
+    uint32_t* d_want = nullptr;
+    uint32_t* d_seg_raw = nullptr;
+    uint32_t* d_got = nullptr;
+    uint8_t* d_ok = nullptr;
+    unsigned long long* d_nbad = nullptr;
+    const uint32_t* adv_seg = nullptr;
+    uint32_t ntasks = 0, rows_per_seg = 0;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;  // begin, rows kernel end, all end
+    bool ran = false;
+};
+
+extern "C" {
+
+int b200_batch_free(b200_batch* b) {
+    if (!b) return 0;
+    if (b->d) cudaSetDevice(b->d->dev);
+    cudaFree(b->d_off);
+    cudaFree(b->d_len);
+    cudaFree(b->d_seg_start);
+    cudaFree(b->d_want);
+    cudaFree(b->d_seg_raw);
+    cudaFree(b->d_got);
+    cudaFree(b->d_ok);
+    cudaFree(b->d_nbad);
+    if (b->ev0) cudaEventDestroy(b->ev0);
+    if (b->ev1) cudaEventDestroy(b->ev1);
+    if (b->ev2) cudaEventDestroy(b->ev2);
+    cudaGetLastError();
+    delete b;
+    return 0;
+}
+
+int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_t* len, size_t nobj,
+                      const uint32_t* want, b200_batch** out) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !out || (nobj && (!off || !len)) || nobj > 0x7FFFFFFFu)
+        return fail(B200_ERR_INVALID, "b200_batch_create");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    b200_batch* b = new (std::nothrow) b200_batch;
+    if (!b) return fail(B200_ERR_NOMEM, "b200_batch_create");
+    b->d = d;
+    b->nobj = nobj;
+    // plan: the arena base is 16-byte aligned, so the cut of object i depends on off[i] only
+    uint64_t total_rows = 0;
+    for (size_t i = 0; i < nobj; i++) total_rows += cut_object(off[i], len[i]).rows;
+    uint32_t rps = choose_rows_per_seg(total_rows, d->grid);
+    std::vector<uint32_t> seg_start(nobj + 1);
+    for (;;) {
+        uint64_t t = 0;
+        for (size_t i = 0; i < nobj; i++) {
+            seg_start[i] = (uint32_t)t;
+            t += (cut_object(off[i], len[i]).rows + rps - 1) / rps;
+        }
+        seg_start[nobj] = (uint32_t)t;
+        if (t <= (1u << 30)) break;
+        rps *= 2;
+    }
+    b->rows_per_seg = rps;
+    b->ntasks = seg_start[nobj];
+    int rc = get_adv_seg(d, rps, &b->adv_seg);
+    auto dev_alloc = [&](void** p, size_t bytes) -> int {
+        if (rc) return rc;
+        cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
+        if (e != cudaSuccess) rc = e == cudaErrorMemoryAllocation ? fail(B200_ERR_NOMEM, "cudaMalloc")
+                                                                  : fail_cuda(e, "cudaMalloc");
+        return rc;
+    };
+    dev_alloc((void**)&b->d_off, nobj * 8);
+    dev_alloc((void**)&b->d_len, nobj * 8);
+    dev_alloc((void**)&b->d_seg_start, (nobj + 1) * 4);
+    if (want) dev_alloc((void**)&b->d_want, nobj * 4);
+    dev_alloc((void**)&b->d_seg_raw, (size_t)b->ntasks * 4);
+    dev_alloc((void**)&b->d_got, nobj * 4);
+    dev_alloc((void**)&b->d_ok, nobj);
+    dev_alloc((void**)&b->d_nbad, 8);
+    auto cu = [&](cudaError_t e, const char* what) {
+        if (!rc && e != cudaSuccess) rc = fail_cuda(e, what);
+    };
+    if (!rc && nobj) {
+        cu(cudaMemcpy(b->d_off, off, nobj * 8, cudaMemcpyHostToDevice), "upload off");
+        cu(cudaMemcpy(b->d_len, len, nobj * 8, cudaMemcpyHostToDevice), "upload len");
+        if (want) cu(cudaMemcpy(b->d_want, want, nobj * 4, cudaMemcpyHostToDevice), "upload want");
+    }
+    if (!rc) cu(cudaMemcpy(b->d_seg_start, seg_start.data(), (nobj + 1) * 4, cudaMemcpyHostToDevice), "upload plan");
+    if (!rc) cu(cudaEventCreate(&b->ev0), "event");
+    if (!rc) cu(cudaEventCreate(&b->ev1), "event");
+    if (!rc) cu(cudaEventCreate(&b->ev2), "event");
+    if (rc) {
+        b200_batch_free(b);
+        return rc;
+    }
+    *out = b;
+    return 0;
+}
+
+int b200_batch_run_async(b200_batch* b, const void* base) {
+    if (!b || (b->nobj && !base) || ((uintptr_t)base & 15))
+        return fail(B200_ERR_INVALID, "b200_batch_run: arena base must be a 16-byte aligned device pointer");
+    DevState* d = b->d;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(d->dev));
+    BatchArgs a{};
+    a.base = (const uint8_t*)base;
+    a.off = b->d_off;
+    a.len = b->d_len;
+    a.seg_start = b->d_seg_start;
+    a.want = b->d_want;
+    a.seg_raw = b->d_seg_raw;
+    a.got = b->d_got;
+    a.ok = b->d_ok;
+    a.nbad = b->d_nbad;
+    a.adv_seg = b->adv_seg;
+    a.nobj = (uint32_t)b->nobj;
+    a.ntasks = b->ntasks;
+    a.rows_per_seg = b->rows_per_seg;
+    a.init_crc = 0;
+    CU(launch_batch(a, d->tabs, d->grid, d->stream, b->ev0, b->ev1));
+    CU(cudaEventRecord(b->ev2, d->stream));
+    b->ran = true;
+    return 0;
+}
+
+int b200_batch_wait(b200_batch* b) {
+    if (!b) return fail(B200_ERR_INVALID, "b200_batch_wait");
+    CU(cudaSetDevice(b->d->dev));
+    CU(cudaStreamSynchronize(b->d->stream));
+    return 0;
+}
+
+int b200_batch_run(b200_batch* b, const void* base) {
+    if (int rc = b200_batch_run_async(b, base)) return rc;
+    return b200_batch_wait(b);
+}
+
+int b200_batch_results(b200_batch* b, uint32_t* got, uint8_t* ok, uint64_t* nbad) {
+    if (!b || !b->ran) return fail(B200_ERR_INVALID, "b200_batch_results: batch has not run");
+    CU(cudaSetDevice(b->d->dev));
+    CU(cudaStreamSynchronize(b->d->stream));
+    if (got && b->nobj) CU(cudaMemcpy(got, b->d_got, b->nobj * 4, cudaMemcpyDeviceToHost));
+    if (ok && b->nobj) CU(cudaMemcpy(ok, b->d_ok, b->nobj, cudaMemcpyDeviceToHost));
+    if (nbad) {
+        unsigned long long v = 0;
+        CU(cudaMemcpy(&v, b->d_nbad, 8, cudaMemcpyDeviceToHost));
+        *nbad = v;
+    }
+    return 0;
+}
+
+int b200_batch_kernel_ms(b200_batch* b, float* total_ms, float* rows_kernel_ms) {
+    if (!b || !b->ran) return fail(B200_ERR_INVALID, "b200_batch_kernel_ms: batch has not run");
+    CU(cudaSetDevice(b->d->dev));
+    CU(cudaEventSynchronize(b->ev2));
+    if (total_ms) CU(cudaEventElapsedTime(total_ms, b->ev0, b->ev2));
+    if (rows_kernel_ms) CU(cudaEventElapsedTime(rows_kernel_ms, b->ev0, b->ev1));
+    return 0;
+}
+
+int b200_batch_launches(const b200_batch* b, int* launches_per_run) {
+    if (!b || !launches_per_run) return fail(B200_ERR_INVALID, "b200_batch_launches");
+    *launches_per_run = (b->ntasks ? 1 : 0) + (b->nobj ? 1 : 0);
+    return 0;
+}
+
+int b200_crc32c_batch_device(b200_ctx* ctx, int dev, const void* base, const uint64_t* off, const uint64_t* len,
+                             size_t nobj, const uint32_t* want, uint32_t* got, uint8_t* ok, uint64_t* nbad) {
+    b200_batch* b = nullptr;
+    if (int rc = b200_batch_create(ctx, dev, off, len, nobj, want, &b)) return rc;
+    int rc = b200_batch_run(b, base);
+    if (!rc) rc = b200_batch_results(b, got, ok, nbad);
+    b200_batch_free(b);
+    return rc;
+}
+
+int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, const uint64_t* len, size_t nobj,
+                           const uint32_t* want, uint32_t* got, uint8_t* ok, uint64_t* nbad) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || (nobj && (!bufs || !len))) return fail(B200_ERR_INVALID, "b200_crc32c_batch_host");
+    // Pack objects back to back (16-byte aligned starts) into slabs of at most kSlab bytes; each slab is
+    // one H2D copy from pinned staging and one device batch.  Slab k+1 is packed and copied while slab k
+    // is verified.  An object larger than a slab is streamed on its own.
+    const size_t kSlab = kStageBytes;
+    uint64_t bad_total = 0;
+    size_t i = 0;
+    int slot = 0;
+    b200_batch* inflight[2] = {nullptr, nullptr};
+    size_t inflight_first[2] = {0, 0}, inflight_n[2] = {0, 0};
+    int rc = 0;
+    std::lock_guard<std::recursive_mutex> slk(d->stage_mu);
+    auto collect = [&](int s) -> int {
+        if (!inflight[s]) return 0;
+        uint64_t nb = 0;
+        size_t f = inflight_first[s];
+        int r = b200_batch_results(inflight[s], got ? got + f : nullptr, ok ? ok + f : nullptr, &nb);
+        bad_total += nb;
+        b200_batch_free(inflight[s]);
+        inflight[s] = nullptr;
+        return r;
+    };
+    {
+        std::lock_guard<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(dev));
+        if (int r = ensure_stage(d, kSlab)) return r;
+    }
+    std::vector<uint64_t> offs, lens;
+    while (i < nobj && !rc) {
+        if (len[i] > kSlab) {  // a big object: stream it alone (it uses both staging slabs)
+            for (int s2 = 0; s2 < 2 && !rc; s2++) rc = collect(s2);
+            if (rc) break;
+            uint32_t c = 0;
+            rc = b200_crc32c_stream_host(ctx, dev, 0, bufs[i], len[i], 0, &c);
+            if (rc) break;
+            if (got) got[i] = c;
+            bool good = want ? c == want[i] : true;
+            if (ok) ok[i] = good;
+            bad_total += !good;
+            i++;
+            continue;
+        }
+        rc = collect(slot);  // the staging pair `slot` is free once its previous batch finished
+        if (rc) break;
+        offs.clear();
+        lens.clear();
+        size_t first = i, used = 0;
+        while (i < nobj && len[i] <= kSlab) {
+            size_t start = (used + 15) & ~(size_t)15;
+            if (start + len[i] > kSlab) break;
+            if (len[i]) memcpy(d->h_stage[slot] + start, bufs[i], len[i]);
+            offs.push_back(start);
+            lens.push_back(len[i]);
+            used = start + len[i];
+            i++;
+        }
+        b200_batch* b = nullptr;
+        rc = b200_batch_create(ctx, dev, offs.data(), lens.data(), offs.size(), want ? want + first : nullptr, &b);
+        if (rc) break;
+        {
+            std::lock_guard<std::mutex> lk(d->mu);
+            cudaSetDevice(dev);
+            cudaError_t e = cudaMemcpyAsync(d->d_stage[slot], d->h_stage[slot], used, cudaMemcpyHostToDevice,
+                                            d->copy_stream);
+            if (e == cudaSuccess) e = cudaEventRecord(d->ev_copied[slot], d->copy_stream);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(d->stream, d->ev_copied[slot], 0);
+            if (e != cudaSuccess) rc = fail_cuda(e, "slab upload");
+        }
+        if (!rc) rc = b200_batch_run_async(b, d->d_stage[slot]);
+        inflight[slot] = b;
+        inflight_first[slot] = first;
+        inflight_n[slot] = offs.size();
+        slot ^= 1;
+    }
+    for (int s = 0; s < 2; s++) {
+        int r = collect(s);
+        if (!rc) rc = r;
+    }
+    (void)inflight_n;
+    if (!rc && nbad) *nbad = bad_total;
+    return rc;
+}
+
+// ---- hash.Hash32 --------------------------------------------------------------------------------------
+
+}  // extern "C"
+
+struct b200_hasher {
+    b200_ctx* ctx = nullptr;
+    int dev = 0;
+    uint32_t crc = 0;      // CRC of everything flushed so far
+    uint8_t* buf = nullptr;  // pinned
+    size_t fill = 0, cap = 0;
+};
+
+extern "C" {
+
+int b200_hasher_new(b200_ctx* ctx, int dev, b200_hasher** out) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !out) return fail(B200_ERR_INVALID, "b200_hasher_new");
+    b200_hasher* h = new (std::nothrow) b200_hasher;
+    if (!h) return fail(B200_ERR_NOMEM, "b200_hasher_new");
+    h->ctx = ctx;
+    h->dev = dev;
+    h->cap = 8u << 20;  // four of the read loop's 2 MiB buffers (main.go:125)
+    CU(cudaSetDevice(dev));
+    cudaError_t e = cudaHostAlloc(&h->buf, h->cap, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        delete h;
+        return fail_cuda(e, "cudaHostAlloc");
+    }
+    *out = h;
+    return 0;
+}
+
+static int hasher_flush(b200_hasher* h) {
+    if (!h->fill) return 0;
+    uint32_t c = 0;
+    int rc = b200_crc32c_stream_host(h->ctx, h->dev, h->crc, h->buf, h->fill, h->cap, &c);
+    if (rc) return rc;
+    h->crc = c;
+    h->fill = 0;
+    return 0;
+}
+
+int b200_hasher_write(b200_hasher* h, const void* p, size_t n) {
+    if (!h || (n && !p)) return fail(B200_ERR_INVALID, "b200_hasher_write");
+    const uint8_t* s = (const uint8_t*)p;
+    while (n) {
+        size_t take = std::min(n, h->cap - h->fill);
+        memcpy(h->buf + h->fill, s, take);
+        h->fill += take;
+        s += take;
+        n -= take;
+        if (h->fill == h->cap)
+            if (int rc = hasher_flush(h)) return rc;
+    }
+    return 0;
+}
+
+int b200_hasher_sum32(b200_hasher* h, uint32_t* out) {
+    if (!h || !out) return fail(B200_ERR_INVALID, "b200_hasher_sum32");
+    if (int rc = hasher_flush(h)) return rc;
+    *out = h->crc;
+    return 0;
+}
+
+int b200_hasher_reset(b200_hasher* h) {
+    if (!h) return fail(B200_ERR_INVALID, "b200_hasher_reset");
+    h->crc = 0;
+    h->fill = 0;
+    return 0;
+}
+
+int b200_hasher_free(b200_hasher* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->dev);
+    cudaFreeHost(h->buf);
+    delete h;
+    return 0;
+}
+
+}  // extern "C"
+
+// ---- latency reduction ----------------------------------------------------------------------------------
+
+extern "C" {
+
+int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                    const double* edges, int nedges, int mode, uint64_t* counts, b200_lat_stats* stats) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !edges || !counts || (n && !d_samples) || ((uintptr_t)d_samples & 7) ||
+        (mode != B200_HIST_NUMPY && mode != B200_HIST_OPENCENSUS) || nedges > B200_HIST_MAX_EDGES)
+        return fail(B200_ERR_INVALID, "b200_hist_fixed");
+    HistParams P;
+    if (host_build_hist_params(edges, nedges, mode, divisor, &P))
+        return fail(B200_ERR_INVALID, "b200_hist_fixed: edges must be ascending, divisor >= 1");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
+    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1));
+    unsigned long long c[kMaxThresholds + 1];
+    LatMoments m;
+    CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    uint64_t below = 0, above = 0;
+    if (mode == B200_HIST_NUMPY) {
+        for (int i = 0; i < nedges - 1; i++) counts[i] = c[i + 1];
+        below = c[0];
+        above = c[nedges];
+    } else {
+        for (int i = 0; i <= nedges; i++) counts[i] = c[i];
+    }
+    if (stats) {
+        memset(stats, 0, sizeof *stats);
+        stats->count = m.count;
+        if (m.count) {
+            stats->min = m.min_ns / divisor;  // C division truncates toward zero, as Go's does
+            stats->max = m.max_ns / divisor;
+        }
+        stats->sum = m.sum_lo;
+        stats->sum_hi = m.sum_hi;
+        stats->sumsq_lo = m.sumsq_lo;
+        stats->sumsq_hi = m.sumsq_hi;
+        stats->dropped_below = below;
+        stats->dropped_above = above;
+    }
+    return 0;
+}
+
+int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t* mn, int64_t* mx) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !mn || !mx || (n && !d_samples)) return fail(B200_ERR_INVALID, "b200_minmax");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    CU(launch_minmax((const long long*)d_samples, n, d->lat, d->stream));
+    LatMoments m;
+    CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    *mn = m.min_ns;
+    *mx = m.max_ns;
+    return 0;
+}
+
+int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, uint64_t key_base, int shift,
+                     int top, int nk, const uint64_t* prefix, uint64_t* counts) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !counts || (n && !d_samples) || nk < 1 || nk > B200_SELECT_MAX_K || shift < 0 || top <= shift ||
+        top > 64 || top - shift > kRadixBits || (top < 64 && !prefix))
+        return fail(B200_ERR_INVALID, "b200_radix_count");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    if (top < 64)
+        CU(cudaMemcpyAsync(d->lat.d_prefix, prefix, nk * sizeof(uint64_t), cudaMemcpyHostToDevice, d->stream));
+    CU(launch_radix_pass((const long long*)d_samples, n, key_base, shift, top, nk, d->lat, d->stream));
+    CU(cudaMemcpyAsync(counts, d->lat.d_radix, (size_t)nk * kRadixBins * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                       d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
+int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
+                    int nk, int64_t* out) {
+    if (!k || !out || nk < 1 || divisor < 1) return fail(B200_ERR_INVALID, "b200_select_kth");
+    if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
+    for (int i = 0; i < nk; i++)
+        if (k[i] >= n) return fail(B200_ERR_INVALID, "b200_select_kth: k >= n");
+    int64_t mn, mx;
+    if (int rc = b200_minmax(ctx, dev, d_samples, n, &mn, &mx)) return rc;
+    const uint64_t kmin = (uint64_t)mn ^ 0x8000000000000000ull, kmax = (uint64_t)mx ^ 0x8000000000000000ull;
+    const uint64_t range = kmax - kmin;
+    int bits = 0;
+    while (bits < 64 && (range >> bits)) bits++;
+    std::vector<uint64_t> counts((size_t)kMaxSelect * kRadixBins);
+    for (int g = 0; g < nk; g += kMaxSelect) {
+        int m = std::min(kMaxSelect, nk - g);
+        uint64_t prefix[kMaxSelect] = {0, 0, 0, 0}, rank[kMaxSelect];
+        for (int i = 0; i < m; i++) rank[i] = k[g + i];
+        int top = bits;
+        bool first = true;
+        while (top > 0) {
+            int shift = std::max(top - kRadixBits, 0);
+            int width = top - shift;
+            // first pass: key' < 2^top, so every sample matches prefix 0 and one histogram serves all k
+            int rc = b200_radix_count(ctx, dev, d_samples, n, kmin, shift, top, first ? 1 : m, prefix, counts.data());
+            if (rc) return rc;
+            for (int i = 0; i < m; i++) {
+                const uint64_t* h = counts.data() + (first ? 0 : (size_t)i * kRadixBins);
+                uint64_t cum = 0;
+                int dgt = 0;
+                for (; dgt < (1 << width); dgt++) {
+                    if (rank[i] < cum + h[dgt]) break;
+                    cum += h[dgt];
+                }
+                if (dgt == (1 << width)) return fail(B200_ERR_CUDA, "b200_select_kth: inconsistent radix counts");
+                rank[i] -= cum;
+                prefix[i] = (prefix[i] << width) | (uint64_t)dgt;
+            }
+            top = shift;
+            first = false;
+        }
+        for (int i = 0; i < m; i++) {
+            int64_t ns = (int64_t)((prefix[i] + kmin) ^ 0x8000000000000000ull);
+            out[g + i] = ns / divisor;  // truncating division is monotone: k-th of v = trunc(k-th of ns / divisor)
+        }
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,281 @@
+// CRC-32C kernels for sm_100a.
+//
+// What is computed: Go's crc32.Update(crc, MakeTable(Castagnoli), p) — the per-chunk statement inside
+// storage.Reader.Read that the reference's read loop drives (main.go:140) — for a whole batch of
+// device-resident objects at once, bit-exactly.
+//
+// K1 "row kernel" (HBM-bound by design, shared-memory-lookup-bound in practice):
+//   An object body is viewed as rows of 512 bytes = 128 little-endian words.  A warp owns a segment of
+//   consecutive rows; lane l issues one coalesced 128-bit load per row and thereby owns word columns
+//   4l..4l+3.  Each column is an independent CRC register that is advanced by a whole row per step:
+//       a_c <- A^512(a_c) ^ w(r, c)          (A = "feed one zero byte", a GF(2)-linear map)
+//   A^512 on a 32-bit register is four byte-indexed lookups.  The four 256-entry tables live in shared
+//   memory replicated once per bank (entry v for lane l at byte v*256 + l*4 (+128 for the odd table of a
+//   pair)), so lane l only ever touches bank l: lookups are bank-conflict free whatever the data, and the
+//   address is a single PRMT of (state byte, lane*4).  128 KB of tables -> one 1024-thread CTA per SM.
+//   At the end of a segment the 128 column registers are folded with their in-row weights
+//   x^(32*(128-c)) and xor-reduced over the warp into one raw register per segment.
+// Finalize kernel: per object, Horner over the segment registers with the per-segment shift constant,
+//   unaligned head and sub-row tail bytes, init/final inversion, comparison with want[].
+#include "crc_kernels.h"
+
+namespace b200 {
+
+namespace {
+
+constexpr uint32_t kPairStride = 65536;  // tables {0,1} at [0,64K), {2,3} at [64K,128K)
+
+extern __shared__ __align__(1024) uint8_t smem_tab[];
+
+__device__ __forceinline__ uint32_t lds_u32(uint32_t byte_off) {
+    return *reinterpret_cast<const uint32_t*>(smem_tab + byte_off);
+}
+
+// A^512 applied to a column register.  lane4 = lane * 4 (< 128, so bytes 1..3 of it are zero).
+__device__ __forceinline__ uint32_t adv_row(uint32_t x, uint32_t lane4) {
+    uint32_t o0 = __byte_perm(x, lane4, 0x5504);  // (byte0(x) << 8) | lane4
+    uint32_t o1 = __byte_perm(x, lane4, 0x5514);
+    uint32_t o2 = __byte_perm(x, lane4, 0x5524);
+    uint32_t o3 = __byte_perm(x, lane4, 0x5534);
+    return lds_u32(o0) ^ lds_u32(o1 + 128) ^ lds_u32(o2 + kPairStride) ^ lds_u32(o3 + kPairStride + 128);
+}
+
+__device__ __forceinline__ uint4 ldg_row(const uint4* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ uint32_t find_object(const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t task) {
+    uint32_t lo = 0, hi = nobj;  // invariant: seg_start[lo] <= task < seg_start[hi]
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(seg_start + mid) <= task) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+__global__ void __launch_bounds__(kRowsThreads, 1)
+crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
+                const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
+                uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv_tab,
+                const uint32_t* __restrict__ col_k, uint32_t* __restrict__ seg_raw) {
+    // replicate the compact 4x256 table once per bank
+    {
+        uint32_t i = threadIdx.x;  // kRowsThreads == 4*256
+        uint32_t t = i >> 8, v = i & 255;
+        uint32_t val = __ldg(adv_tab + i);
+        uint4 q = make_uint4(val, val, val, val);
+        uint4* dst = reinterpret_cast<uint4*>(smem_tab + (t >> 1) * kPairStride + v * 256 + (t & 1) * 128);
+#pragma unroll
+        for (int k = 0; k < 8; k++) dst[k] = q;
+    }
+    __syncthreads();
+
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t lane4 = lane * 4;
+    const uint32_t warp = threadIdx.x >> 5;
+    const uint32_t k0 = __ldg(col_k + lane4), k1 = __ldg(col_k + lane4 + 1), k2 = __ldg(col_k + lane4 + 2),
+                   k3 = __ldg(col_k + lane4 + 3);
+    const uint32_t nwarps = gridDim.x * kRowsWarps;
+
+    for (uint32_t task = warp * gridDim.x + blockIdx.x; task < ntasks; task += nwarps) {
+        uint32_t seg = task;
+        uint64_t o = single_off, n = single_len;
+        if (off) {
+            const uint32_t obj = find_object(seg_start, nobj, task);
+            seg = task - __ldg(seg_start + obj);
+            o = __ldg(off + obj);
+            n = __ldg(len + obj);
+        }
+        const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
+        const uint64_t row0 = (uint64_t)seg * rows_per_seg;
+        uint64_t left = cut.rows - row0;
+        const uint32_t R = left < rows_per_seg ? (uint32_t)left : rows_per_seg;
+        const uint4* p = reinterpret_cast<const uint4*>(base + o + cut.head + row0 * kRowBytes) + lane;
+
+        uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        const uint4 zero = make_uint4(0, 0, 0, 0);
+        uint4 w0 = 0 < R ? ldg_row(p) : zero;
+        uint4 w1 = 1 < R ? ldg_row(p + 32) : zero;
+        uint4 w2 = 2 < R ? ldg_row(p + 64) : zero;
+        uint4 w3 = 3 < R ? ldg_row(p + 96) : zero;
+        uint32_t r = 0;
+#define B200_STEP(ROW)                         \
+    a0 = adv_row(a0, lane4) ^ (ROW).x;         \
+    a1 = adv_row(a1, lane4) ^ (ROW).y;         \
+    a2 = adv_row(a2, lane4) ^ (ROW).z;         \
+    a3 = adv_row(a3, lane4) ^ (ROW).w;
+        for (; r + 4 <= R; r += 4) {
+            const uint4* q = p + (size_t)(r + 4) * 32;
+            uint4 n0 = r + 4 < R ? ldg_row(q) : zero;
+            uint4 n1 = r + 5 < R ? ldg_row(q + 32) : zero;
+            uint4 n2 = r + 6 < R ? ldg_row(q + 64) : zero;
+            uint4 n3 = r + 7 < R ? ldg_row(q + 96) : zero;
+            B200_STEP(w0) B200_STEP(w1) B200_STEP(w2) B200_STEP(w3)
+            w0 = n0; w1 = n1; w2 = n2; w3 = n3;
+        }
+        if (r < R) { B200_STEP(w0) r++; }
+        if (r < R) { B200_STEP(w1) r++; }
+        if (r < R) { B200_STEP(w2) r++; }
+#undef B200_STEP
+        // fold the 128 columns: column c still has to pass over 4*(128-c) bytes of its row
+        uint32_t s = gf2_mul(k0, a0) ^ gf2_mul(k1, a1) ^ gf2_mul(k2, a2) ^ gf2_mul(k3, a3);
+#pragma unroll
+        for (int d = 16; d; d >>= 1) s ^= __shfl_xor_sync(0xFFFFFFFFu, s, d);
+        if (lane == 0) seg_raw[task] = s;
+    }
+}
+
+__device__ __forceinline__ uint32_t adv_tab4(const uint32_t* __restrict__ t, uint32_t s) {
+    return __ldg(t + (s & 0xFF)) ^ __ldg(t + 256 + ((s >> 8) & 0xFF)) ^ __ldg(t + 512 + ((s >> 16) & 0xFF)) ^
+           __ldg(t + 768 + (s >> 24));
+}
+
+// One CTA per object.
+__global__ void __launch_bounds__(kFinalThreads)
+crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
+                    const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ want,
+                    const uint32_t* __restrict__ seg_raw, const uint32_t* __restrict__ adv_seg,
+                    const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab, uint32_t rows_per_seg,
+                    uint32_t init_crc, uint64_t single_off, uint64_t single_len, uint32_t* __restrict__ got,
+                    uint8_t* __restrict__ ok, unsigned long long* nbad) {
+    __shared__ uint32_t red[kFinalThreads / 32];
+    const uint32_t obj = blockIdx.x;
+    const uint64_t o = off ? off[obj] : single_off;
+    const uint64_t n = off ? len[obj] : single_len;
+    const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
+    const uint32_t first = off ? seg_start[obj] : 0;
+    const uint64_t nfull = cut.rows / rows_per_seg;
+    const uint32_t last_rows = (uint32_t)(cut.rows % rows_per_seg);
+    const uint64_t seg_bytes = (uint64_t)rows_per_seg * kRowBytes;
+    const uint8_t* p = base + o;
+
+    // F = sum over full segments j of x^(8*seg_bytes*(nfull-1-j)) * raw_j
+    uint32_t F = 0;
+    if (nfull > 64) {
+        const uint64_t per = (nfull + kFinalThreads - 1) / kFinalThreads;
+        uint64_t lo = (uint64_t)threadIdx.x * per, hi = lo + per;
+        if (hi > nfull) hi = nfull;
+        uint32_t part = 0;
+        if (lo < hi) {
+            for (uint64_t j = lo; j < hi; j++) part = adv_tab4(adv_seg, part) ^ seg_raw[first + j];
+            uint64_t after = (nfull - hi) * seg_bytes;
+            if (after) part = gf2_mul(gf2_xpow8(after, xsq), part);
+        }
+#pragma unroll
+        for (int d = 16; d; d >>= 1) part ^= __shfl_xor_sync(0xFFFFFFFFu, part, d);
+        if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = part;
+        __syncthreads();
+        if (threadIdx.x == 0)
+            for (int w = 0; w < kFinalThreads / 32; w++) F ^= red[w];
+    } else if (threadIdx.x == 0) {
+        for (uint64_t j = 0; j < nfull; j++) F = adv_tab4(adv_seg, F) ^ seg_raw[first + j];
+    }
+    if (threadIdx.x != 0) return;
+
+    uint32_t s = ~init_crc;
+    for (uint32_t i = 0; i < cut.head; i++) s = (s >> 8) ^ __ldg(byte_tab + ((s ^ p[i]) & 0xFF));
+    if (nfull) s = gf2_mul(gf2_xpow8(nfull * seg_bytes, xsq), s) ^ F;
+    if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first + nfull];
+    const uint8_t* t = p + cut.head + cut.rows * kRowBytes;  // 16-byte aligned
+    uint32_t i = 0;
+    for (; i + 4 <= cut.tail; i += 4) {  // sub-row tail, a word at a time
+        uint32_t x = *reinterpret_cast<const uint32_t*>(t + i) ^ s;
+#pragma unroll
+        for (int k = 0; k < 4; k++) x = (x >> 8) ^ __ldg(byte_tab + (x & 0xFF));
+        s = x;
+    }
+    for (; i < cut.tail; i++) s = (s >> 8) ^ __ldg(byte_tab + ((s ^ t[i]) & 0xFF));
+    const uint32_t crc = ~s;
+    got[obj] = crc;
+    const bool good = want ? (crc == want[obj]) : true;
+    ok[obj] = good ? 1 : 0;
+    if (!good) atomicAdd(nbad, 1ull);
+}
+
+__device__ __forceinline__ uint64_t splitmix64_dev(uint64_t seed, uint64_t index) {
+    uint64_t z = seed + (index + 1) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    return z ^ (z >> 31);
+}
+
+__global__ void fill_payload_kernel(uint64_t* __restrict__ dst, uint64_t first_word, size_t nwords, uint64_t seed) {
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nwords; i += stride)
+        dst[i] = splitmix64_dev(seed, first_word + i);
+}
+
+__global__ void fill_latency_kernel(int64_t* __restrict__ dst, uint64_t first, size_t n, uint64_t seed) {
+    size_t stride = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        uint64_t idx = first + i;
+        uint64_t z = splitmix64_dev(seed, 2 * idx), z2 = splitmix64_dev(seed, 2 * idx + 1);
+        uint64_t s = (z & 0xFFFF) + ((z >> 16) & 0xFFFF) + ((z >> 32) & 0xFFFF) + (z >> 48);
+        uint64_t ns = 20000000ull + (s * 75000000ull) / 262141ull;
+        uint64_t q = z2 & 0xFF;
+        if (q < 64) ns = (ns / 1000000ull) * 1000000ull;
+        else if (q < 128) ns = (ns / 1000ull) * 1000ull;
+        uint64_t sel = (z2 >> 8) % 100;
+        if (sel == 0) ns = 95000000ull + (z2 >> 20) % (10000000000ull - 95000000ull);
+        else if (sel == 1) ns = (z2 >> 20) % 20000000ull;
+        dst[i] = (int64_t)ns;
+    }
+}
+
+}  // namespace
+
+size_t rows_kernel_smem() { return 4 * 256 * 32 * sizeof(uint32_t); }
+
+int rows_kernel_grid(int dev) {
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;  // persistent: one 1024-thread CTA per SM (128 KB of tables each)
+}
+
+cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream,
+                         cudaEvent_t ev_begin, cudaEvent_t ev_end) {
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(crc_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)rows_kernel_smem());
+        if (e != cudaSuccess) return e;
+        attr_dev = dev;
+    }
+    cudaError_t e = cudaMemsetAsync(a.nbad, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    if (ev_begin) cudaEventRecord(ev_begin, stream);
+    if (a.ntasks) {
+        uint32_t need = (a.ntasks + kRowsWarps - 1) / kRowsWarps;
+        int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
+        crc_rows_kernel<<<g, kRowsThreads, rows_kernel_smem(), stream>>>(a.base, a.off, a.len, a.seg_start, a.nobj,
+                                                                         a.ntasks, a.rows_per_seg, a.single_off, a.single_len,
+                                                                         t.adv_row, t.col_k, a.seg_raw);
+    }
+    if (ev_end) cudaEventRecord(ev_end, stream);
+    if (a.nobj)
+        crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, a.seg_start, a.want, a.seg_raw,
+                                                                  a.adv_seg, t.xpow8_sq, t.byte_tab, a.rows_per_seg,
+                                                                  a.init_crc, a.single_off, a.single_len, a.got, a.ok,
+                                                                  a.nbad);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fill_payload(uint64_t* dst, uint64_t first_word, size_t nwords, uint64_t seed, cudaStream_t s) {
+    if (!nwords) return cudaSuccess;
+    fill_payload_kernel<<<148 * 8, 256, 0, s>>>(dst, first_word, nwords, seed);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_fill_latency(int64_t* dst, uint64_t first, size_t n, uint64_t seed, cudaStream_t s) {
+    if (!n) return cudaSuccess;
+    fill_latency_kernel<<<148 * 8, 256, 0, s>>>(dst, first, n, seed);
+    return cudaGetLastError();
+}
+
+}  // namespace b200

@@ -1,0 +1,80 @@
+// Internal (C++) launch interface of the CRC-32C kernels.  The C ABI in api.cu is built on this.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "gf2.h"
+
+namespace b200 {
+
+constexpr int kRowBytes = 512;    // one row = one coalesced 128-bit load per lane of a warp
+constexpr int kRowWords = 128;
+constexpr int kRowsThreads = 1024;
+constexpr int kRowsWarps = kRowsThreads / 32;
+constexpr int kFinalThreads = 128;
+
+// How an object [addr, addr+len) is cut: an unaligned head (< 16 B) so the body starts on a 16-byte
+// boundary, whole 512-byte rows, and a tail (< 512 B).  Rows go to the row kernel, head and tail are
+// folded in by the finalize kernel.
+struct ObjectCut {
+    uint32_t head;
+    uint32_t tail;
+    uint64_t rows;
+};
+B200_HD ObjectCut cut_object(uint64_t addr, uint64_t len) {
+    ObjectCut c;
+    uint64_t h = (16 - (addr & 15)) & 15;
+    c.head = (uint32_t)(h < len ? h : len);
+    uint64_t body = len - c.head;
+    c.rows = body / kRowBytes;
+    c.tail = (uint32_t)(body % kRowBytes);
+    return c;
+}
+
+// Constant tables a device needs (built once per context on the host, see tables.cu).
+struct DeviceTables {
+    uint32_t* adv_row;   // [4][256] multiply-by-x^(8*512) slicing tables (compact; kernels replicate per bank)
+    uint32_t* col_k;     // [128] x^(8*4*(128-c)): weight of column c inside a row
+    uint32_t* xpow8_sq;  // [64]  x^(8*2^k)
+    uint32_t* byte_tab;  // [256] classic one-byte table
+};
+
+struct BatchArgs {
+    const uint8_t* base;        // device arena, 16-byte aligned
+    const uint64_t* off;        // [nobj] device
+    const uint64_t* len;        // [nobj] device
+    const uint32_t* seg_start;  // [nobj+1] device: first task of each object
+    const uint32_t* want;       // [nobj] device or nullptr
+    uint32_t* seg_raw;          // [ntasks] device scratch: raw CRC register of each segment
+    uint32_t* got;              // [nobj] device
+    uint8_t* ok;                // [nobj] device
+    unsigned long long* nbad;   // device scalar (zeroed by the launcher)
+    const uint32_t* adv_seg;    // [4][256] multiply-by-x^(8*512*rows_per_seg) tables (device)
+    uint32_t nobj;
+    uint32_t ntasks;
+    uint32_t rows_per_seg;
+    uint32_t init_crc;          // crc32.Update's first argument, same for every object (0 = fresh checksum)
+    // single-object mode (off == nullptr): the object is base[single_off .. single_off+single_len) and owns
+    // tasks 0..ntasks-1; no plan arrays are read.
+    uint64_t single_off;
+    uint64_t single_len;
+};
+
+int rows_kernel_grid(int dev);
+size_t rows_kernel_smem();
+// Enqueue row kernel + finalize kernel on `stream`.  ev_* may be null; when given they bracket the row kernel.
+cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream,
+                         cudaEvent_t ev_rows_begin, cudaEvent_t ev_rows_end);
+
+cudaError_t launch_fill_payload(uint64_t* dst, uint64_t first_word, size_t nwords, uint64_t seed, cudaStream_t s);
+cudaError_t launch_fill_latency(int64_t* dst, uint64_t first, size_t n, uint64_t seed, cudaStream_t s);
+
+// Host side table construction (tables.cu)
+void host_build_adv_table(uint64_t nbytes, uint32_t out[4 * 256]);
+void host_build_col_k(uint32_t out[128]);
+void host_build_xpow8_sq(uint32_t out[64]);
+void host_build_byte_tab(uint32_t out[256]);
+uint32_t host_xpow8(uint64_t nbytes);
+
+
+}  // namespace b200

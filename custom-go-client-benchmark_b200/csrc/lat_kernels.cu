@@ -1,0 +1,379 @@
+// Latency-sample reduction kernels for sm_100a: fixed-edge histogram + exact integer moments, and
+// MSD radix counting for exact order statistics.
+//
+// Reference semantics (bit-exact targets):
+//   sample      main.go:145-146  float64(time.Since(start).Milliseconds()): int64 ns / 1e6 truncating
+//   numpy bins  README.md:21-23,32  numpy.histogram(x, [20,25,..,95]): [a,b) bins, last closed, rest dropped
+//   OC buckets  metrics_exporter.go:28  first bound strictly greater than v, else overflow bucket
+//   percentiles benchmark-script/ssd_test/main.go:147-163  sorted[size/2] etc.
+// Both bin rules are monotone step functions of the raw nanosecond value, so the host turns the float
+// edges into ascending int64 nanosecond thresholds and the kernel only counts thresholds <= n; no
+// per-sample division or float compare is needed for binning.  A log-linear LUT (32 cells per power of
+// two) gives the count at the low end of the sample's cell plus the 0..few thresholds inside it.
+// All kernels are HBM-bound streams of 8 bytes per sample with 128-bit loads; counters are private per
+// (warp, lane) in shared memory so the skewed latency distribution causes no atomic contention.
+#include "lat_kernels.h"
+
+#include <cmath>
+#include <cstring>
+
+namespace b200 {
+
+namespace {
+
+constexpr int kHistThreads = 256;
+constexpr int kHistWarps = kHistThreads / 32;
+constexpr int kRadixThreads = 512;
+
+struct U128 {
+    unsigned long long lo, hi;
+};
+__device__ __forceinline__ void add128(U128& a, unsigned long long lo, unsigned long long hi) {
+    unsigned long long s = a.lo + lo;
+    a.hi += hi + (s < a.lo);
+    a.lo = s;
+}
+
+__device__ __forceinline__ unsigned long long udiv_magic(unsigned long long a, const HistParams& P) {
+    if (P.magic == 0) return a >> P.magic_shift;  // power of two divisor
+    unsigned long long t = __umul64hi(a, P.magic);
+    if (P.magic_add) t = ((a - t) >> 1) + t;
+    return t >> P.magic_shift;
+}
+
+__device__ __forceinline__ int classify(long long n, const long long* __restrict__ thr, int nthr,
+                                        const unsigned short* __restrict__ lut) {
+    int c;
+    if (n >= 0) {
+        unsigned long long u = (unsigned long long)n;
+        int idx;
+        if (u < 32) idx = (int)u;
+        else {
+            int e = 63 - __clzll((long long)u);
+            idx = (e - 4) * 32 + (int)((u >> (e - 5)) & 31);
+        }
+        unsigned cell = lut[idx];
+        c = cell >> 8;
+        int extra = cell & 0xFF;
+        int c0 = c;
+        for (int k = 0; k < extra; k++) c += (n >= thr[c0 + k]);
+    } else {
+        c = 0;
+        for (int j = 0; j < nthr; j++) c += (n >= thr[j]);
+    }
+    return c;
+}
+
+__global__ void __launch_bounds__(kHistThreads)
+hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
+            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, int want_moments) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    __shared__ HistParams P;
+    // [warp][bin][lane] private counters
+    unsigned* tbl = reinterpret_cast<unsigned*>(sm);
+    {
+        const unsigned* src = reinterpret_cast<const unsigned*>(Pg);
+        unsigned* dst = reinterpret_cast<unsigned*>(&P);
+        for (int i = threadIdx.x; i < (int)(sizeof(HistParams) / 4); i += kHistThreads) dst[i] = src[i];
+    }
+    const int nbins = Pg->nthr + 1;
+    for (int i = threadIdx.x; i < kHistWarps * nbins * 32; i += kHistThreads) tbl[i] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned* mine = tbl + (size_t)warp * nbins * 32 + lane;
+
+    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
+    U128 sum{0, 0}, sq{0, 0};
+    unsigned long long cnt = 0;
+
+    auto one = [&](long long v) {
+        int c = classify(v, P.thr, P.nthr, P.lut);
+        mine[c * 32]++;
+        if (want_moments) {
+            mn = v < mn ? v : mn;
+            mx = v > mx ? v : mx;
+            unsigned long long a = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+            unsigned long long q = udiv_magic(a, P);
+            add128(sq, q * q, __umul64hi(q, q));
+            if (v < 0) add128(sum, 0ull - q, q ? ~0ull : 0ull);
+            else add128(sum, q, 0);
+            cnt++;
+        }
+    };
+
+    // head (to 16-byte alignment), vector body, tail
+    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
+    if (head > n) head = n;
+    const size_t tid = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
+    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
+    if (tid == 0 && head) one(x[0]);
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    size_t i = tid;
+    for (; i + nthreads < npairs; i += 2 * nthreads) {  // two independent loads in flight
+        longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads);
+        one(a.x); one(a.y); one(b.x); one(b.y);
+    }
+    for (; i < npairs; i += nthreads) {
+        longlong2 a = __ldg(x2 + i);
+        one(a.x); one(a.y);
+    }
+    if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
+
+    __syncthreads();
+    for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
+        unsigned long long t = 0;
+        for (int w = 0; w < kHistWarps; w++)
+            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * nbins + b) * 32 + ((l + b) & 31)];
+        if (t) atomicAdd(counts + b, t);
+    }
+    if (want_moments) {
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
+            mn = omn < mn ? omn : mn;
+            mx = omx > mx ? omx : mx;
+            cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, d);
+            unsigned long long l1 = __shfl_xor_sync(0xFFFFFFFFu, sum.lo, d), h1 = __shfl_xor_sync(0xFFFFFFFFu, sum.hi, d);
+            add128(sum, l1, h1);
+            unsigned long long l2 = __shfl_xor_sync(0xFFFFFFFFu, sq.lo, d), h2 = __shfl_xor_sync(0xFFFFFFFFu, sq.hi, d);
+            add128(sq, l2, h2);
+        }
+        if (lane == 0 && cnt) {
+            atomicMin(&mom->min_ns, mn);
+            atomicMax(&mom->max_ns, mx);
+            atomicAdd(&mom->count, cnt);
+            unsigned long long old = atomicAdd(&mom->sum_lo, sum.lo);
+            unsigned long long carry = (old + sum.lo) < old;
+            atomicAdd(reinterpret_cast<unsigned long long*>(&mom->sum_hi), sum.hi + carry);
+            old = atomicAdd(&mom->sumsq_lo, sq.lo);
+            carry = (old + sq.lo) < old;
+            atomicAdd(&mom->sumsq_hi, sq.hi + carry);
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kHistThreads)
+minmax_kernel(const long long* __restrict__ x, size_t n, LatMoments* __restrict__ mom) {
+    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
+    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
+    for (size_t i = (size_t)blockIdx.x * kHistThreads + threadIdx.x; i < n; i += nthreads) {
+        long long v = __ldg(x + i);
+        mn = v < mn ? v : mn;
+        mx = v > mx ? v : mx;
+    }
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
+        mn = omn < mn ? omn : mn;
+        mx = omx > mx ? omx : mx;
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(&mom->min_ns, mn);
+        atomicMax(&mom->max_ns, mx);
+    }
+}
+
+__global__ void __launch_bounds__(kRadixThreads)
+radix_kernel(const long long* __restrict__ x, size_t n, unsigned long long key_base, int shift, int top, int nk,
+             const unsigned long long* __restrict__ prefix, unsigned long long* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char sm[];
+    unsigned* hist = reinterpret_cast<unsigned*>(sm);  // [nk][kRadixBins]
+    for (int i = threadIdx.x; i < nk * kRadixBins; i += kRadixThreads) hist[i] = 0;
+    __shared__ unsigned long long pf[kMaxSelect];
+    if (threadIdx.x < nk) pf[threadIdx.x] = top >= 64 ? 0 : prefix[threadIdx.x];
+    __syncthreads();
+    const unsigned mask = (top - shift >= kRadixBits) ? (kRadixBins - 1) : ((1u << (top - shift)) - 1);
+    const bool all = top >= 64;
+    const size_t nthreads = (size_t)gridDim.x * kRadixThreads;
+    auto one = [&](long long v) {
+        unsigned long long key = ((unsigned long long)v ^ 0x8000000000000000ull) - key_base;
+        unsigned dgt = (unsigned)(key >> shift) & mask;
+        unsigned long long hi = all ? 0 : key >> top;
+#pragma unroll
+        for (int k = 0; k < kMaxSelect; k++)
+            if (k < nk && hi == pf[k]) atomicAdd(hist + k * kRadixBins + dgt, 1u);
+    };
+    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
+    if (head > n) head = n;
+    const size_t tid = (size_t)blockIdx.x * kRadixThreads + threadIdx.x;
+    if (tid == 0 && head) one(x[0]);
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    size_t i = tid;
+    for (; i + nthreads < npairs; i += 2 * nthreads) {
+        longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads);
+        one(a.x); one(a.y); one(b.x); one(b.y);
+    }
+    for (; i < npairs; i += nthreads) {
+        longlong2 a = __ldg(x2 + i);
+        one(a.x); one(a.y);
+    }
+    if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
+    __syncthreads();
+    for (int i2 = threadIdx.x; i2 < nk * kRadixBins; i2 += kRadixThreads) {
+        unsigned c = hist[i2];
+        if (c) atomicAdd(out + i2, (unsigned long long)c);
+    }
+}
+
+size_t hist_smem(int nbins) { return (size_t)kHistWarps * nbins * 32 * sizeof(unsigned); }
+
+int sm_count() {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    return sms;
+}
+
+}  // namespace
+
+cudaError_t lat_scratch_init(LatScratch* s) {
+    memset(s, 0, sizeof *s);
+    cudaError_t e = cudaMalloc(&s->d_params, sizeof(HistParams));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_counts, (kMaxThresholds + 1) * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_mom, sizeof(LatMoments));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
+    return e;
+}
+
+void lat_scratch_free(LatScratch* s) {
+    cudaFree(s->d_params);
+    cudaFree(s->d_counts);
+    cudaFree(s->d_mom);
+    cudaFree(s->d_radix);
+    cudaFree(s->d_prefix);
+    memset(s, 0, sizeof *s);
+}
+
+static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
+    LatMoments init{};
+    init.min_ns = 0x7FFFFFFFFFFFFFFFll;
+    init.max_ns = (long long)0x8000000000000000ull;
+    return cudaMemcpyAsync(s.d_mom, &init, sizeof init, cudaMemcpyHostToDevice, stream);
+}
+
+cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
+                        cudaStream_t stream, int nbins) {
+    cudaError_t e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    e = reset_moments(s, stream);
+    if (e != cudaSuccess) return e;
+    if (!n) return cudaSuccess;
+    size_t smem = hist_smem(nbins);
+    e = cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem(kMaxThresholds + 1));
+    if (e != cudaSuccess) return e;
+    int per_sm = 2;
+    size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
+    int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
+    hist_kernel<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom, want_moments ? 1 : 0);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch& s, cudaStream_t stream) {
+    cudaError_t e = reset_moments(s, stream);
+    if (e != cudaSuccess || !n) return e;
+    int grid = (int)std::min<size_t>((size_t)sm_count() * 8, (n + kHistThreads - 1) / kHistThreads);
+    minmax_kernel<<<grid, kHistThreads, 0, stream>>>(d_samples, n, s.d_mom);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned long long key_base, int shift, int top,
+                              int nk, const LatScratch& s, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(s.d_radix, 0, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess || !n) return e;
+    size_t smem = (size_t)nk * kRadixBins * sizeof(unsigned);
+    e = cudaFuncSetAttribute(radix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)(kMaxSelect * kRadixBins * sizeof(unsigned)));
+    if (e != cudaSuccess) return e;
+    size_t want_ctas = (n / 2 + kRadixThreads - 1) / kRadixThreads;
+    int grid = (int)std::min<size_t>((size_t)sm_count() * 2, want_ctas ? want_ctas : 1);
+    radix_kernel<<<grid, kRadixThreads, smem, stream>>>(d_samples, n, key_base, shift, top, nk, s.d_prefix, s.d_radix);
+    return cudaGetLastError();
+}
+
+// ---- host: float edges -> int64 nanosecond thresholds --------------------------------------------------
+
+namespace {
+
+// smallest raw n with trunc(n / d) >= E   (E integer, d >= 1), saturating
+long long first_n_with_quotient_at_least(double E, long long d) {
+    const double lim = 9.2e18;
+    if (E > 0) {
+        double t = E * (double)d;
+        if (t >= lim) return 0x7FFFFFFFFFFFFFFFll;
+        return (long long)E * d;
+    }
+    double t = (E - 1) * (double)d;
+    if (t <= -lim) return (long long)0x8000000000000000ull;
+    return ((long long)E - 1) * d + 1;
+}
+
+}  // namespace
+
+int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* P) {
+    memset(P, 0, sizeof *P);
+    if (divisor < 1 || nedges < 1 || nedges > kMaxThresholds - 2) return -1;
+    for (int i = 0; i < nedges; i++) {
+        if (std::isnan(edges[i])) return -1;
+        if (i && !(edges[i] > edges[i - 1])) return -1;
+    }
+    // v = trunc(n/d) is an integer, so  v < e  <=>  v < ceil(e)  and  v <= e  <=>  v < floor(e) + 1
+    int m = 0;
+    if (mode == 0) {  // numpy: below edges[0] -> count 0 (dropped); last edge inclusive; above -> count nedges
+        if (nedges < 2) return -1;
+        for (int j = 0; j < nedges - 1; j++) P->thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
+        P->thr[m++] = first_n_with_quotient_at_least(std::floor(edges[nedges - 1]) + 1, divisor);
+    } else {  // opencensus: bucket = #{bounds <= v}
+        for (int j = 0; j < nedges; j++) P->thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
+    }
+    P->nthr = m;
+    // log-linear LUT over n >= 0
+    for (int idx = 0; idx < kLutCells; idx++) {
+        unsigned long long lo, hi;
+        if (idx < 32) lo = hi = (unsigned long long)idx;
+        else {
+            int e = idx / 32 + 4, mant = idx % 32;
+            if (e > 62) { P->lut[idx] = (unsigned short)(m << 8); continue; }
+            lo = (1ull << e) + ((unsigned long long)mant << (e - 5));
+            hi = lo + (1ull << (e - 5)) - 1;
+        }
+        int base = 0, extra = 0;
+        for (int j = 0; j < m; j++) {
+            if (P->thr[j] <= (long long)lo) base++;
+            else if (P->thr[j] <= (long long)hi) extra++;
+        }
+        P->lut[idx] = (unsigned short)((base << 8) | extra);
+    }
+    // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)
+    P->divisor = divisor;
+    unsigned long long d = (unsigned long long)divisor;
+    if ((d & (d - 1)) == 0) {
+        P->magic = 0;
+        int l = 0;
+        while ((1ull << l) < d) l++;
+        P->magic_shift = l;
+    } else {
+        int l = 63;
+        while (!((d >> l) & 1)) l--;  // floor(log2 d)
+        unsigned __int128 num = (unsigned __int128)1 << (64 + l);
+        unsigned long long q = (unsigned long long)(num / d);
+        unsigned long long rem = (unsigned long long)(num % d);
+        unsigned long long e = d - rem;
+        if (e < (1ull << l)) {
+            P->magic = q + 1;
+            P->magic_add = 0;
+            P->magic_shift = l;
+        } else {
+            unsigned long long q2 = q * 2, rem2 = rem * 2;
+            if (rem2 >= d || rem2 < rem) q2 += 1;
+            P->magic = q2 + 1;
+            P->magic_add = 1;
+            P->magic_shift = l;
+        }
+    }
+    return 0;
+}
+
+}  // namespace b200

@@ -1,0 +1,58 @@
+// Internal launch interface of the latency-reduction kernels (histogram, moments, radix select).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200 {
+
+constexpr int kMaxThresholds = 66;      // B200_HIST_MAX_EDGES + slack
+constexpr int kLutCells = 2048;         // log-linear cells: 32 per power of two
+constexpr int kRadixBits = 12;
+constexpr int kRadixBins = 1 << kRadixBits;
+constexpr int kMaxSelect = 4;           // order statistics resolved per pass
+
+// Exact integer moments of the scaled samples v = trunc(ns / divisor).
+struct LatMoments {
+    unsigned long long count;
+    long long min_ns, max_ns;           // of the raw samples (division is monotone)
+    unsigned long long sum_lo;          // 128-bit two's complement sum of v
+    long long sum_hi;
+    unsigned long long sumsq_lo, sumsq_hi;  // 128-bit sum of v*v
+};
+
+// Device-side parameter block for the histogram kernel, built on the host.
+struct HistParams {
+    long long thr[kMaxThresholds];      // thresholds in raw ns, ascending: count(n) = #{j : thr[j] <= n}
+    int nthr;
+    unsigned short lut[kLutCells];      // (base << 8) | extra for each log-linear cell of n >= 0
+    unsigned long long magic;           // division by `divisor` as multiply-high (see lat_kernels.cu)
+    int magic_shift;
+    int magic_add;
+    long long divisor;
+};
+
+struct LatScratch {
+    HistParams* d_params;
+    unsigned long long* d_counts;       // [kMaxThresholds + 1]
+    LatMoments* d_mom;
+    unsigned long long* d_radix;        // [kMaxSelect][kRadixBins]
+    unsigned long long* d_prefix;       // [kMaxSelect]
+};
+
+cudaError_t lat_scratch_init(LatScratch* s);
+void lat_scratch_free(LatScratch* s);
+
+// counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
+cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
+                        cudaStream_t stream, int nbins);
+// One MSD radix pass over key' = (ns ^ 2^63) - key_base: for each k < nk count the digit
+// (key' >> shift) & (2^(top-shift) - 1) over the samples with key' >> top == d_prefix[k] (all samples when
+// top >= 64).  top - shift <= kRadixBits.
+cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned long long key_base, int shift, int top,
+                              int nk, const LatScratch& s, cudaStream_t stream);
+cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch& s, cudaStream_t stream);
+
+// Host helper: fill thresholds / LUT / magic for (edges, mode, divisor).
+int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* out);
+
+}  // namespace b200

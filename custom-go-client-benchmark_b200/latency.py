@@ -1,0 +1,232 @@
+"""Host-side mirror of the reference's latency reduction, over the C ABI.
+
+  hist_readme      README.md:15-35   numpy.histogram(x, range(20,100,5)) of per-read milliseconds
+  hist_opencensus  metrics_exporter.go:22-34  ochttp.DefaultLatencyDistribution buckets + distribution data
+  percentiles      benchmark-script/ssd_test/main.go:147-163  avg/P20/P50/P90/p99/min/max by floor index
+Samples live on the device as int64 nanoseconds (time.Duration); `divisor` restates Duration.Milliseconds()
+(main.go:146) or .Microseconds() (ssd_test/main.go:79).  With world_size > 1 (one process per GPU) the
+bin / digit counts are summed across ranks with torch.distributed (NCCL on GPUs, gloo in CPU tests).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from fractions import Fraction
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import HIST_NUMPY, HIST_OPENCENSUS, RADIX_BINS, SELECT_MAX_K, LatStats, check
+from .crc32c import Context, default_context
+
+README_EDGES = np.array(list(range(20, 100, 5)), dtype=np.float64)  # README.md:21-23 (15 bins, 20..95)
+OC_DEFAULT_LATENCY_BOUNDS = np.array(
+    [1, 2, 3, 4, 5, 6, 8, 10, 13, 16, 20, 25, 30, 40, 50, 65, 80, 100, 130, 160, 200, 250, 300, 400, 500, 650, 800,
+     1000, 2000, 5000, 10000, 20000, 50000, 100000], dtype=np.float64)  # ochttp.DefaultLatencyDistribution
+NS_PER_MS, NS_PER_US = 1_000_000, 1_000
+_SIGN = 1 << 63
+_M64 = (1 << 64) - 1
+
+
+@dataclass
+class Distribution:
+    """Shape of OpenCensus view.DistributionData (what metrics_exporter.go:22-34 exports)."""
+    count: int
+    min: int
+    max: int
+    sum: int                 # exact integer sum of the scaled samples
+    sum_wrapped: int         # the same reduced to int64 the way Go's `sum += x` wraps
+    sumsq: int               # exact integer sum of squares
+    counts: np.ndarray
+    dropped_below: int = 0
+    dropped_above: int = 0
+
+    @property
+    def mean(self) -> float:
+        return float(Fraction(self.sum, self.count)) if self.count else 0.0
+
+    @property
+    def sum_of_squared_dev(self) -> float:
+        if not self.count:
+            return 0.0
+        return float(Fraction(self.sumsq) - Fraction(self.sum * self.sum, self.count))
+
+    @property
+    def avg_go_int(self) -> int:
+        """sum/int64(size) with Go's truncating integer division (ssd_test/main.go:157)."""
+        s = self.sum_wrapped
+        q = abs(s) // self.count
+        return q if s >= 0 else -q
+
+
+def _signed(lo: int, hi: int) -> int:
+    v = (hi << 64) | lo if hi >= 0 else ((hi + (1 << 64)) << 64) | lo
+    if hi < 0:
+        v -= 1 << 128
+    return v
+
+
+class _Reducer:
+    """Sums small integer arrays over ranks.  No-op when not distributed."""
+
+    def __init__(self, group=None, device=None):
+        self.group, self.device = group, device
+        try:
+            import torch.distributed as dist
+            self.dist = dist if dist.is_available() and dist.is_initialized() else None
+        except Exception:
+            self.dist = None
+
+    @property
+    def active(self):
+        return self.dist is not None and self.dist.get_world_size(self.group) > 1
+
+    def _run(self, arr: np.ndarray, op: str) -> np.ndarray:
+        if not self.active:
+            return arr
+        import torch
+        t = torch.from_numpy(arr.astype(np.int64, copy=True))
+        if self.device is not None:
+            t = t.to(self.device)
+        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op), group=self.group)
+        return t.cpu().numpy()
+
+    def sum_u64(self, arr: np.ndarray) -> np.ndarray:
+        # split into 32-bit halves so the int64 all-reduce cannot overflow for < 2^31 ranks
+        a = arr.astype(np.uint64)
+        lo = self._run((a & np.uint64(0xFFFFFFFF)).astype(np.int64), "SUM").astype(object)
+        hi = self._run((a >> np.uint64(32)).astype(np.int64), "SUM").astype(object)
+        return lo + hi * (1 << 32)  # python ints
+
+    def min_i64(self, v: int) -> int:
+        return int(self._run(np.array([v], dtype=np.int64), "MIN")[0])
+
+    def max_i64(self, v: int) -> int:
+        return int(self._run(np.array([v], dtype=np.int64), "MAX")[0])
+
+
+def hist_fixed(d_samples: int, n: int, divisor: int, edges, mode: int, ctx: Optional[Context] = None,
+               dev: Optional[int] = None, group=None, reduce_device=None) -> Distribution:
+    ctx = ctx or default_context()
+    edges = np.ascontiguousarray(edges, dtype=np.float64)
+    nb = edges.size - 1 if mode == HIST_NUMPY else edges.size + 1
+    counts = np.zeros(nb, dtype=np.uint64)
+    st = LatStats()
+    check(ctx._L.b200_hist_fixed(ctx._h, ctx._dev(dev), d_samples, n, divisor, edges.ctypes.data, edges.size, mode,
+                                 counts.ctypes.data, C.byref(st)))
+    total = _signed(st.sum, st.sum_hi)
+    sumsq = (st.sumsq_hi << 64) | st.sumsq_lo
+    red = _Reducer(group, reduce_device)
+    cnt, mn, mx, below, above = st.count, st.min, st.max, st.dropped_below, st.dropped_above
+    if red.active:
+        # 128-bit quantities travel as four 32-bit limbs each (sum offset to be non-negative)
+        off = 1 << 100
+        limbs = lambda v: [(v >> (32 * i)) & 0xFFFFFFFF for i in range(4)]
+        vec = np.array(list(counts) + [cnt, below, above] + limbs(total + off) + limbs(sumsq), dtype=np.uint64)
+        r = red.sum_u64(vec)
+        world = red.dist.get_world_size(group)
+        counts = np.array([int(x) for x in r[:nb]], dtype=np.uint64)
+        cnt, below, above = int(r[nb]), int(r[nb + 1]), int(r[nb + 2])
+        total = sum(int(r[nb + 3 + i]) << (32 * i) for i in range(4)) - world * off
+        sumsq = sum(int(r[nb + 7 + i]) << (32 * i) for i in range(4))
+        big = (1 << 63) - 1
+        mn = red.min_i64(mn if st.count else big)
+        mx = red.max_i64(mx if st.count else -big - 1)
+    wrapped = total & _M64
+    wrapped = wrapped - (1 << 64) if wrapped >= _SIGN else wrapped
+    return Distribution(cnt, mn, mx, total, wrapped, sumsq, counts, below, above)
+
+
+def hist_readme(d_samples_ns: int, n: int, **kw) -> Distribution:
+    """README.md:21-23,32 on per-read milliseconds (main.go:146)."""
+    return hist_fixed(d_samples_ns, n, NS_PER_MS, README_EDGES, HIST_NUMPY, **kw)
+
+
+def hist_opencensus(d_samples_ns: int, n: int, **kw) -> Distribution:
+    """metrics_exporter.go:28 distribution view on per-read milliseconds."""
+    return hist_fixed(d_samples_ns, n, NS_PER_MS, OC_DEFAULT_LATENCY_BOUNDS, HIST_OPENCENSUS, **kw)
+
+
+def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Optional[Context] = None,
+               dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None):
+    """k-th smallest (0-based) of trunc(sample/divisor) over all ranks' samples.  MSD radix select."""
+    ctx = ctx or default_context()
+    L, h, d = ctx._L, ctx._h, ctx._dev(dev)
+    red = _Reducer(group, reduce_device)
+    ks = [int(k) for k in ks]
+    if not red.active:
+        karr = np.array(ks, dtype=np.uint64)
+        out = np.zeros(len(ks), dtype=np.int64)
+        check(L.b200_select_kth(h, d, d_samples, n, divisor, karr.ctypes.data, len(ks), out.ctypes.data))
+        return [int(x) for x in out]
+    # distributed form: same loop as b200_select_kth with an all-reduce after every count
+    ntot = int(red.sum_u64(np.array([n], dtype=np.uint64))[0]) if n_global is None else n_global
+    if ntot == 0:
+        raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
+    if any(k >= ntot for k in ks):
+        raise ValueError("k >= n")
+    mn, mx = C.c_int64(), C.c_int64()
+    check(L.b200_minmax(h, d, d_samples, n, C.byref(mn), C.byref(mx)))
+    gmn, gmx = red.min_i64(mn.value), red.max_i64(mx.value)
+    kmin, kmax = (gmn + _SIGN) & _M64, (gmx + _SIGN) & _M64
+    bits = (kmax - kmin).bit_length()
+    res = []
+    for g in range(0, len(ks), SELECT_MAX_K):
+        grp = ks[g:g + SELECT_MAX_K]
+        m = len(grp)
+        prefix, rank = [0] * m, list(grp)
+        top, first = bits, True
+        while top > 0:
+            shift = max(top - 12, 0)
+            width = top - shift
+            nk = 1 if first else m
+            counts = np.zeros(nk * RADIX_BINS, dtype=np.uint64)
+            parr = np.array(prefix[:nk] if not first else [0], dtype=np.uint64)
+            check(L.b200_radix_count(h, d, d_samples, n, kmin, shift, top, nk, parr.ctypes.data,
+                                     counts.ctypes.data))
+            tot = red.sum_u64(counts)
+            for i in range(m):
+                hrow = tot[0:RADIX_BINS] if first else tot[i * RADIX_BINS:(i + 1) * RADIX_BINS]
+                cum = 0
+                for dgt in range(1 << width):
+                    c = int(hrow[dgt])
+                    if rank[i] < cum + c:
+                        break
+                    cum += c
+                else:
+                    raise RuntimeError("inconsistent radix counts")
+                rank[i] -= cum
+                prefix[i] = (prefix[i] << width) | dgt
+            top, first = shift, False
+        for i in range(m):
+            key = (prefix[i] + kmin) & _M64
+            ns = key - _SIGN  # undo the sign flip
+            q = abs(ns) // divisor
+            res.append(q if ns >= 0 else -q)
+    return res
+
+
+@dataclass
+class Percentiles:
+    """The seven lines ssd_test prints (benchmark-script/ssd_test/main.go:157-163), in sample units."""
+    avg: int
+    p20: int
+    p50: int
+    p90: int
+    p99: int
+    min: int
+    max: int
+
+
+def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Optional[Context] = None,
+                dev: Optional[int] = None, group=None, reduce_device=None) -> Percentiles:
+    dist_ = hist_fixed(d_samples_ns, n, divisor, OC_DEFAULT_LATENCY_BOUNDS, HIST_OPENCENSUS, ctx=ctx, dev=dev,
+                       group=group, reduce_device=reduce_device)
+    size = dist_.count
+    if size == 0:
+        raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
+    ks = [size // 5, size // 2, (9 * size) // 10, (99 * size) // 100]
+    p20, p50, p90, p99 = select_kth(d_samples_ns, n, divisor, ks, ctx=ctx, dev=dev, group=group,
+                                    reduce_device=reduce_device, n_global=size)
+    return Percentiles(dist_.avg_go_int, p20, p50, p90, p99, dist_.min, dist_.max)

@@ -1,0 +1,292 @@
+"""GPU parity tests for the CRC-32C path, through the C ABI, against the CPU oracle (bit-exact)."""
+import importlib
+import json
+import os
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+pkg = importlib.import_module("custom-go-client-benchmark_b200")
+crc32c = pkg.crc32c
+
+KATS = [(b"", 0), (b"a", 0xC1D04330), (b"123456789", 0xE3069283), (bytes(32), 0x8A9136AA),
+        (b"\xff" * 32, 0x62A8AB43), (bytes(range(32)), 0x46DD794E), (bytes(range(31, -1, -1)), 0x113FDB5C)]
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = crc32c.Context([0])
+    yield c
+    c.close()
+
+
+@pytest.fixture(scope="module")
+def arena(ctx):
+    """64 MiB + slack of splitmix payload on the device and on the host."""
+    n = (64 << 20) + 4096
+    host = oracle.payload(n)
+    d = ctx.alloc_device(n)
+    ctx.h2d(d, host)
+    yield host, d
+    ctx.free_device(d)
+
+
+@pytest.mark.parametrize("data,want", KATS)
+def test_known_answers_update_host(ctx, data, want):
+    assert crc32c.Checksum(data, ctx) == want
+
+
+def test_update_continuation_and_chunking(ctx):
+    d = bytes(oracle.payload(300000))
+    crc = 0
+    for i in range(0, len(d), 37 * 1024 + 5):
+        crc = crc32c.Update(crc, d[i:i + 37 * 1024 + 5], ctx)
+    assert crc == oracle.crc32c(d)
+    assert crc32c.Update(0x12345678, d[:1000], ctx) == oracle.crc32c(d[:1000], 0x12345678)
+
+
+@settings(max_examples=60, deadline=None)
+@given(st.integers(0, 4096 + 64), st.integers(0, 3 << 20), st.integers(0, 2**32 - 1))
+def test_update_device_random_offsets_and_lengths(ctx, arena, start, length, crc):
+    host, d = arena
+    assert crc32c.UpdateDevice(crc, d + start, length, ctx) == oracle.crc32c(host[start:start + length], crc)
+
+
+@pytest.mark.parametrize("length", [0, 1, 3, 15, 16, 17, 511, 512, 513, 1023, 1024, 8191, 8192, 8193, 65536,
+                                    (1 << 20) - 1, (2 << 20), (2 << 20) + 1, 8 << 20, (64 << 20) + 999])
+@pytest.mark.parametrize("start", [0, 1, 7, 15, 16, 33])
+def test_update_device_edges(ctx, arena, start, length):
+    host, d = arena
+    assert crc32c.UpdateDevice(0, d + start, length, ctx) == oracle.crc32c(host[start:start + length])
+
+
+def test_hash32_interface(ctx):
+    h = crc32c.New(ctx)
+    assert h.Size() == 4 and h.BlockSize() == 1
+    assert h.Sum32() == 0
+    d = bytes(oracle.payload(3_000_000))
+    n = h.Write(d[:10])
+    assert n == 10
+    h.Write(d[10:70000])
+    mid = h.Sum32()
+    assert mid == oracle.crc32c(d[:70000])
+    assert h.Sum32() == mid  # Sum32 does not disturb the state
+    assert h.Sum(b"ab") == b"ab" + mid.to_bytes(4, "big")
+    h.Write(d[70000:])
+    assert h.Sum32() == oracle.crc32c(d)
+    h.Reset()
+    assert h.Sum32() == 0
+    h.Write(b"123456789")
+    assert h.Sum32() == 0xE3069283
+    h.close()
+
+
+def test_hash32_many_small_writes_and_flush_boundary(ctx):
+    h = crc32c.New(ctx)
+    d = bytes(oracle.payload((8 << 20) + 12345))  # crosses the 8 MiB staging buffer
+    step = 2 << 20                                   # the read loop's buffer size (main.go:125)
+    for i in range(0, len(d), step):
+        h.Write(d[i:i + step])
+    assert h.Sum32() == oracle.crc32c(d)
+    h.close()
+
+
+def _batch_check(ctx, host, d, off, ln):
+    want, _, _ = oracle.verify_objects(host, off, ln, threads=8)
+    got, ok, nbad = crc32c.VerifyObjectsDevice(d, off, ln, want, ctx=ctx)
+    assert (got == want).all()
+    assert nbad == 0 and ok.all()
+    return want
+
+
+def test_batch_uniform_2mib_objects(ctx, arena):
+    host, d = arena
+    n = 32
+    off = np.arange(n, dtype=np.uint64) * (2 << 20)
+    ln = np.full(n, 2 << 20, dtype=np.uint64)
+    _batch_check(ctx, host, d, off, ln)
+
+
+def test_batch_ragged_unaligned(ctx, arena):
+    host, d = arena
+    rng = np.random.default_rng(7)
+    n = 300
+    ln = rng.integers(1, 400_000, size=n).astype(np.uint64)
+    off = rng.integers(0, (64 << 20) - 400_000, size=n).astype(np.uint64)  # overlapping, unaligned
+    ln[:8] = [0, 1, 15, 16, 511, 512, 513, 4 << 20]
+    _batch_check(ctx, host, d, off, ln)
+
+
+def test_batch_many_tiny_objects(ctx, arena):
+    host, d = arena
+    rng = np.random.default_rng(11)
+    n = 5000
+    ln = rng.integers(0, 700, size=n).astype(np.uint64)
+    off = rng.integers(0, 1 << 20, size=n).astype(np.uint64)
+    _batch_check(ctx, host, d, off, ln)
+
+
+def test_batch_empty(ctx, arena):
+    host, d = arena
+    got, ok, nbad = crc32c.VerifyObjectsDevice(d, np.zeros(0, np.uint64), np.zeros(0, np.uint64), None, ctx=ctx)
+    assert got.size == 0 and nbad == 0
+
+
+def test_batch_misaligned_arena_is_rejected(ctx, arena):
+    host, d = arena
+    with pytest.raises(pkg.B200Error):
+        crc32c.VerifyObjectsDevice(d + 4, np.zeros(1, np.uint64), np.full(1, 100, np.uint64), None, ctx=ctx)
+
+
+def test_batch_flags_exactly_the_corrupt_object(ctx):
+    n, size = 48, 1 << 20
+    host = oracle.payload(n * size).copy()
+    off = np.arange(n, dtype=np.uint64) * size
+    ln = np.full(n, size, dtype=np.uint64)
+    want, _, _ = oracle.verify_objects(host, off, ln, threads=8)
+    host[17 * size + 777] ^= 0x01  # one flipped bit
+    d = ctx.alloc_device(host.size)
+    ctx.h2d(d, host)
+    b = crc32c.DeviceBatch(off, ln, want, ctx)
+    b.run(d)
+    got, ok, nbad = b.results()
+    assert nbad == 1 and list(np.nonzero(~ok)[0]) == [17]
+    assert got[17] != want[17] and (np.delete(got, 17) == np.delete(want, 17)).all()
+    # plan is reusable: heal the object and re-run
+    host[17 * size + 777] ^= 0x01
+    ctx.h2d(d, host)
+    b.run(d)
+    got, ok, nbad = b.results()
+    assert nbad == 0 and (got == want).all()
+    assert b.launches() == 2
+    b.close()
+    ctx.free_device(d)
+
+
+@pytest.mark.parametrize("rps", ["16", "64", "1000"])
+def test_rows_per_segment_is_not_a_semantic_knob(rps, arena):
+    # fresh process-level knob: run in a subprocess so the env var is read
+    import subprocess, sys
+    code = (
+        "import importlib, numpy as np, oracle\n"
+        "pkg = importlib.import_module('custom-go-client-benchmark_b200')\n"
+        "c = pkg.crc32c.Context([0])\n"
+        "h = oracle.payload(5_000_000)\n"
+        "d = c.alloc_device(h.size); c.h2d(d, h)\n"
+        "assert pkg.crc32c.UpdateDevice(0, d + 5, 4_999_000, c) == oracle.crc32c(h[5:5 + 4_999_000])\n"
+        "print('ok')\n")
+    env = dict(os.environ, B200_ROWS_PER_SEG=rps)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.check_output([sys.executable, "-c", code], env=env, cwd=root, text=True)
+    assert "ok" in out
+
+
+def test_verify_objects_host_buffers(ctx):
+    rng = np.random.default_rng(3)
+    sizes = [0, 1, 100, 4096, 2 << 20, 12345, (2 << 20) + 1, 40 << 20, 7]
+    bufs = [bytes(oracle.payload(s, first_word=int(rng.integers(0, 1 << 30)))) for s in sizes]
+    want = [oracle.crc32c(b) for b in bufs]
+    bad, got = crc32c.VerifyObjects(bufs, want, ctx)
+    assert bad == [] and list(got) == want
+    want[3] ^= 1
+    want[7] ^= 0x80000000
+    bad, got = crc32c.VerifyObjects(bufs, want, ctx)
+    assert bad == [3, 7]
+
+
+def test_verify_objects_host_many(ctx):
+    # enough 2 MiB objects to cycle the staging slabs several times (config 1's object size)
+    n = 80
+    base = oracle.payload(n * (2 << 20))
+    bufs = [base[i * (2 << 20):(i + 1) * (2 << 20)] for i in range(n)]
+    off = np.arange(n, dtype=np.uint64) * (2 << 20)
+    want, _, _ = oracle.verify_objects(base, off, np.full(n, 2 << 20, np.uint64), threads=8)
+    bad, got = crc32c.VerifyObjects(bufs, want, ctx)
+    assert bad == [] and (got == want).all()
+
+
+def test_sharded_single_device(ctx, arena):
+    host, d = arena
+    n = 48 << 20
+    assert crc32c.ShardedChecksum([d], [n], ctx) == oracle.crc32c(host[:n])
+
+
+def test_sharded_emulated_split_matches_combine(ctx, arena):
+    # the multi-GPU rule on one GPU: shard CRCs folded left to right with Combine
+    host, d = arena
+    n = 60 << 20
+    for parts in (2, 4, 8):
+        bounds = [n * i // parts for i in range(parts + 1)]
+        acc = 0
+        for a, b in zip(bounds[:-1], bounds[1:]):
+            acc = crc32c.Combine(acc, crc32c.UpdateDevice(0, d + a, b - a, ctx), b - a)
+        assert acc == oracle.crc32c(host[:n])
+
+
+def test_stream_host_pinned_and_pageable(ctx):
+    n = (96 << 20) + 4321
+    src = oracle.payload(n)
+    want = oracle.crc32c(src)
+    assert crc32c.StreamChecksum(src, chunk=16 << 20, ctx=ctx) == want          # pageable: staged
+    pinned = ctx.alloc_pinned(n)
+    pinned[:] = src
+    assert crc32c.StreamChecksum(pinned, chunk=16 << 20, ctx=ctx) == want       # pinned: direct H2D
+    assert crc32c.StreamChecksum(pinned, chunk=256 << 20, ctx=ctx) == want      # config 4 chunk size
+    assert crc32c.StreamChecksum(pinned[1:], chunk=5 << 20, ctx=ctx) == oracle.crc32c(src[1:])
+    ctx.free_pinned(pinned)
+
+
+def test_device_generator_matches_oracle(ctx):
+    nw = 1 << 18
+    d = ctx.alloc_device(nw * 8)
+    ctx.fill_payload(d, nw, oracle.SEED, first_word=12345)
+    back = np.empty(nw * 8, dtype=np.uint8)
+    ctx.d2h(back, d)
+    assert (back == oracle.payload(nw * 8, first_word=12345)).all()
+    ctx.free_device(d)
+
+
+def test_golden_fixture(ctx):
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))
+    for case in g["crc"]:
+        data = oracle.payload(case["nbytes"], seed=case["seed"], first_word=case["first_word"])[case["skip"]:]
+        assert crc32c.Checksum(data, ctx) == case["crc32c"], case
+
+
+def test_full_size_config2_properties(ctx):
+    """BASELINE config 2 at full size: 4096 x 2 MiB objects = 8 GiB, generated on the device.
+    Size-independent checks: (a) a sample of objects against the oracle on regenerated payload,
+    (b) the fold of all 4096 object CRCs with Combine equals the CRC of the arena taken as ONE object,
+    (c) one flipped bit flags exactly one object."""
+    nobj, size = 4096, 2 << 20
+    total = nobj * size
+    d = ctx.alloc_device(total)
+    ctx.fill_payload(d, total // 8, oracle.SEED)
+    off = np.arange(nobj, dtype=np.uint64) * size
+    ln = np.full(nobj, size, dtype=np.uint64)
+    b = crc32c.DeviceBatch(off, ln, None, ctx)
+    b.run(d)
+    got, ok, nbad = b.results()
+    assert nbad == 0
+    for i in (0, 1, 1234, 2047, 4095):
+        assert got[i] == oracle.crc32c(oracle.payload(size, first_word=i * size // 8)), i
+    acc = 0
+    for c in got:
+        acc = crc32c.Combine(acc, int(c), size)
+    whole = crc32c.UpdateDevice(0, d, total, ctx)
+    assert acc == whole
+    # negative control: flip one bit in object 1234 on the device
+    byte = np.empty(1, dtype=np.uint8)
+    ctx.d2h(byte, d + 1234 * size + 99)
+    byte ^= 0x20
+    ctx.h2d(d + 1234 * size + 99, byte)
+    b2 = crc32c.DeviceBatch(off, ln, got, ctx)
+    b2.run(d)
+    got2, ok2, nbad2 = b2.results()
+    assert nbad2 == 1 and list(np.nonzero(~ok2)[0]) == [1234]
+    b.close(); b2.close()
+    ctx.free_device(d)

@@ -1,0 +1,203 @@
+"""GPU parity tests for the latency reduction path (histogram, distribution moments, exact percentiles)."""
+import importlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+
+pytestmark = pytest.mark.gpu
+pkg = importlib.import_module("custom-go-client-benchmark_b200")
+crc32c, lat = pkg.crc32c, pkg.latency
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    c = crc32c.Context([0])
+    yield c
+    c.close()
+
+
+def upload(ctx, a):
+    a = np.ascontiguousarray(a, dtype=np.int64)
+    d = ctx.alloc_device(max(a.nbytes, 8))
+    if a.size:
+        ctx.h2d(d, a)
+    return d
+
+
+@pytest.fixture(scope="module")
+def samples(ctx):
+    n = 1_000_003
+    d = ctx.alloc_device(n * 8)
+    ctx.fill_latency_ns(d, n, oracle.SEED)
+    yield oracle.latency_ns(n), d, n
+    ctx.free_device(d)
+
+
+def test_device_generator_matches_oracle(ctx, samples):
+    ns, d, n = samples
+    back = np.empty(n, dtype=np.int64)
+    ctx.d2h(back, d)
+    assert (back == ns).all()
+
+
+def test_readme_histogram(ctx, samples):
+    ns, d, n = samples
+    ms = oracle.ns_to_ms(ns)
+    ref, dropped = oracle.hist_numpy(ms.astype(np.float64))
+    h = lat.hist_readme(d, n, ctx=ctx)
+    assert list(h.counts) == list(ref)
+    assert h.dropped_below + h.dropped_above == dropped
+    assert h.dropped_below == int((ms < 20).sum()) and h.dropped_above == int((ms > 95).sum())
+
+
+def test_opencensus_distribution(ctx, samples):
+    ns, d, n = samples
+    ms = oracle.ns_to_ms(ns)
+    ref = oracle.hist_opencensus(ms.astype(np.float64))
+    h = lat.hist_opencensus(d, n, ctx=ctx)
+    assert list(h.counts) == list(ref)
+    s = oracle.stats_i64(ms)
+    assert (h.count, h.min, h.max) == (s.count, s.min, s.max)
+    assert h.sum == int(ms.sum()) and h.sum_wrapped == int(ms.sum())
+    assert h.sumsq == int((ms.astype(object) ** 2).sum())
+    # float views.  Ours is the exactly rounded sum/n; the reference's means are order dependent float
+    # recurrences (OpenCensus Welford, README left-to-right sum) that drift by O(n) roundings, so the
+    # tolerance is 1e-12 relative (observed ~1.6e-15 * 100 at n = 1e6).
+    assert h.mean == float(int(ms.sum()) / ms.size) or abs(h.mean - int(ms.sum()) / ms.size) <= np.spacing(h.mean)
+    assert abs(h.mean - s.mean_welford) <= 1e-12 * abs(h.mean)
+    assert abs(h.mean - s.mean_seq) <= 1e-12 * abs(h.mean)
+    assert abs(h.sum_of_squared_dev - s.sum_sq_dev) <= 1e-9 * s.sum_sq_dev
+
+
+def test_histogram_edge_values(ctx):
+    ms_vals = [19, 20, 24, 25, 90, 94, 95, 96, 100, 0, -5]
+    ns = np.array([v * 1_000_000 for v in ms_vals] + [19_999_999, 20_000_000, 24_999_999, 25_000_000,
+                                                      95_999_999, 96_000_000, -1, -999_999, -1_000_000], dtype=np.int64)
+    d = upload(ctx, ns)
+    ms = oracle.ns_to_ms(ns)
+    ref, dropped = oracle.hist_numpy(ms.astype(np.float64))
+    h = lat.hist_readme(d, ns.size, ctx=ctx)
+    assert list(h.counts) == list(ref) and h.dropped_below + h.dropped_above == dropped
+    oc = lat.hist_opencensus(d, ns.size, ctx=ctx)
+    assert list(oc.counts) == list(oracle.hist_opencensus(ms.astype(np.float64)))
+    s = oracle.stats_i64(ms)
+    assert (oc.count, oc.min, oc.max, oc.sum) == (s.count, s.min, s.max, int(ms.sum()))
+    ctx.free_device(d)
+
+
+def test_fractional_and_negative_edges(ctx):
+    rng = np.random.default_rng(5)
+    ns = rng.integers(-50_000_000, 200_000_000, size=50_001).astype(np.int64)
+    d = upload(ctx, ns)
+    for div in (1_000_000, 1000, 1, 7):
+        v = (np.abs(ns) // div) * np.sign(ns)  # Go truncation
+        edges = np.array([-30.5, -10, -0.5, 0, 0.25, 3, 19.999, 20, 20.5, 77, 1e5], dtype=np.float64)
+        h = lat.hist_fixed(d, ns.size, div, edges, pkg._lib.HIST_NUMPY, ctx=ctx)
+        ref, dropped = oracle.hist_numpy(v.astype(np.float64), edges)
+        assert list(h.counts) == list(ref), div
+        assert h.dropped_below + h.dropped_above == dropped
+        oc = lat.hist_fixed(d, ns.size, div, edges, pkg._lib.HIST_OPENCENSUS, ctx=ctx)
+        assert list(oc.counts) == list(oracle.hist_opencensus(v.astype(np.float64), edges))
+        assert oc.sum == int(v.sum()) and oc.min == v.min() and oc.max == v.max()
+    ctx.free_device(d)
+
+
+def test_histogram_unaligned_and_tiny(ctx, samples):
+    ns, d, n = samples
+    for start, cnt in [(1, 1001), (3, 2), (5, 1), (0, 0), (7, 100000)]:
+        ms = oracle.ns_to_ms(ns[start:start + cnt])
+        ref, dropped = oracle.hist_numpy(ms.astype(np.float64))
+        h = lat.hist_readme(d + 8 * start, cnt, ctx=ctx)
+        assert list(h.counts) == list(ref) and h.count == cnt
+
+
+def test_percentiles_match_reference_rule(ctx, samples):
+    ns, d, n = samples
+    us = oracle.ns_to_us(ns)
+    o = oracle.percentiles_i64(us)
+    p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)
+    assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (o.avg, o.p20, o.p50, o.p90, o.p99, o.min, o.max)
+
+
+@pytest.mark.parametrize("n", [1, 2, 5, 10, 99, 100, 101, 4097])
+def test_percentile_index_rule_small_n(ctx, n):
+    rng = np.random.default_rng(n)
+    ns = rng.integers(0, 10**10, size=n).astype(np.int64)
+    d = upload(ctx, ns)
+    o = oracle.percentiles_i64(oracle.ns_to_us(ns))
+    p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)
+    assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (o.avg, o.p20, o.p50, o.p90, o.p99, o.min, o.max)
+    ctx.free_device(d)
+
+
+def test_select_every_rank_with_duplicates_and_negatives(ctx):
+    rng = np.random.default_rng(2)
+    ns = np.concatenate([rng.integers(-1000, 1000, size=300), np.full(200, 42), np.full(50, -7),
+                         rng.integers(-2**62, 2**62, size=20)]).astype(np.int64)
+    rng.shuffle(ns)
+    d = upload(ctx, ns)
+    ks = list(range(ns.size))
+    got = lat.select_kth(d, ns.size, 1, ks, ctx=ctx)
+    assert got == [int(x) for x in np.sort(ns)]
+    got3 = lat.select_kth(d, ns.size, 3, [0, 100, 569], ctx=ctx)
+    v = np.sort((np.abs(ns.astype(object)) // 3) * np.sign(ns))
+    assert got3 == [int(v[0]), int(v[100]), int(v[569])]
+    ctx.free_device(d)
+
+
+def test_select_all_equal_and_empty(ctx):
+    ns = np.full(1000, 123456789, dtype=np.int64)
+    d = upload(ctx, ns)
+    assert lat.select_kth(d, 1000, 1000, [0, 500, 999], ctx=ctx) == [123456] * 3
+    with pytest.raises(pkg.B200Error) as e:
+        lat.select_kth(d, 0, 1, [0], ctx=ctx)
+    assert e.value.status == pkg._lib.ERR_EMPTY
+    with pytest.raises(pkg.B200Error):
+        lat.select_kth(d, 1000, 1, [1000], ctx=ctx)
+    with pytest.raises(ZeroDivisionError):
+        lat.percentiles(d, 0, ctx=ctx)
+    ctx.free_device(d)
+
+
+def test_golden_fixture(ctx):
+    g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))["latency"]
+    n = g["n"]
+    d = ctx.alloc_device(n * 8)
+    ctx.fill_latency_ns(d, n, g["seed"])
+    h = lat.hist_readme(d, n, ctx=ctx)
+    assert [int(x) for x in h.counts] == g["numpy15_counts"]
+    assert h.dropped_below + h.dropped_above == g["numpy15_dropped"]
+    assert [int(x) for x in lat.hist_opencensus(d, n, ctx=ctx).counts] == g["oc35_counts"]
+    p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)
+    assert [p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max] == g["us_percentiles"]
+    ctx.free_device(d)
+
+
+def test_large_sample_set_properties(ctx):
+    """1.25e8 samples (one GPU's share of BASELINE config 5), generated on the device.  Size-independent
+    checks: counts + dropped == n; each selected order statistic v_k satisfies
+    #(samples < v_k) <= k < #(samples <= v_k), counted by the histogram kernel with edges at v_k."""
+    n = 125_000_000
+    d = ctx.alloc_device(n * 8)
+    ctx.fill_latency_ns(d, n, oracle.SEED)
+    h = lat.hist_readme(d, n, ctx=ctx)
+    assert int(h.counts.sum()) + h.dropped_below + h.dropped_above == n and h.count == n
+    oc = lat.hist_opencensus(d, n, ctx=ctx)
+    assert int(oc.counts.sum()) == n
+    ks = [n // 5, n // 2, 9 * n // 10, 99 * n // 100]
+    vs = lat.select_kth(d, n, lat.NS_PER_US, ks, ctx=ctx)
+    for k, v in zip(ks, vs):
+        c = lat.hist_fixed(d, n, lat.NS_PER_US, np.array([v, v + 1], dtype=np.float64), pkg._lib.HIST_OPENCENSUS,
+                           ctx=ctx).counts
+        less, equal = int(c[0]), int(c[1])
+        assert less <= k < less + equal, (k, v, less, equal)
+    # prefix cross-check against the oracle on the first 2e6 samples
+    m = 2_000_000
+    ref, dropped = oracle.hist_numpy(oracle.ns_to_ms(oracle.latency_ns(m)).astype(np.float64))
+    hp = lat.hist_readme(d, m, ctx=ctx)
+    assert list(hp.counts) == list(ref)
+    ctx.free_device(d)

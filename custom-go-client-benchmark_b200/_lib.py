@@ -38,6 +38,8 @@ SIGNATURES = {
     "b200_init": (_int, [_int, C.POINTER(_int), _pp]),
     "b200_shutdown": (_int, [_vp]),
     "b200_ctx_ndev": (_int, [_vp]),
+    "b200_timer_start": (_int, [_vp, _int]),
+    "b200_timer_stop": (_int, [_vp, _int, C.POINTER(C.c_float)]),
     "b200_alloc_pinned": (_int, [_vp, _sz, _pp]),
     "b200_free_pinned": (_int, [_vp, _vp]),
     "b200_alloc_device": (_int, [_vp, _int, _sz, _pp]),

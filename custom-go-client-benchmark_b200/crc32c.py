@@ -91,6 +91,14 @@ class Context:
     def fill_latency_ns(self, dptr: int, n: int, seed: int, first: int = 0, dev: Optional[int] = None):
         check(self._L.b200_fill_latency_ns_device(self._h, self._dev(dev), dptr, first, n, seed))
 
+    def timer_start(self, dev: Optional[int] = None):
+        check(self._L.b200_timer_start(self._h, self._dev(dev)))
+
+    def timer_stop(self, dev: Optional[int] = None) -> float:
+        ms = C.c_float()
+        check(self._L.b200_timer_stop(self._h, self._dev(dev), C.byref(ms)))
+        return ms.value
+
     def _dev(self, dev):
         return self.devices[0] if dev is None else dev
 
@@ -107,8 +115,14 @@ def default_context() -> Context:
 
 def _as_bytes(p) -> np.ndarray:
     if isinstance(p, np.ndarray):
+        if p.dtype == np.uint8 and p.ndim == 1 and p.flags.c_contiguous:
+            return p
         return np.ascontiguousarray(p).view(np.uint8).reshape(-1)
     return np.frombuffer(p, dtype=np.uint8)
+
+
+def _addr(a: np.ndarray):
+    return a.__array_interface__["data"][0] if a.size else None
 
 
 def Update(crc: int, p, ctx: Optional[Context] = None, dev: Optional[int] = None) -> int:
@@ -191,7 +205,7 @@ def VerifyObjects(bufs: Sequence, want: Optional[Sequence[int]], ctx: Optional[C
     ctx = ctx or default_context()
     arrs = [_as_bytes(b) for b in bufs]
     n = len(arrs)
-    ptrs = (C.c_void_p * max(n, 1))(*[a.ctypes.data if a.size else None for a in arrs])
+    ptrs = (C.c_void_p * max(n, 1))(*[_addr(a) for a in arrs])
     lens = np.array([a.size for a in arrs], dtype=np.uint64)
     w = None if want is None else np.ascontiguousarray(want, dtype=np.uint32)
     got = np.zeros(n, dtype=np.uint32)

@@ -39,6 +39,24 @@ int fail(int code, const char* what) {
 constexpr size_t kStageBytes = 32u << 20;   // staging slab for pageable host input
 constexpr int kSingleSlots = 8192;          // result slots for chunked single-object work
 
+constexpr size_t kSlabBytes = 256u << 20;  // device slab for VerifyObjects on host buffers
+
+// Reusable plan + result buffers of one device slab (host mirrors are pinned so uploads are asynchronous).
+struct HostSlab {
+    size_t cap = 0, task_cap = 0;
+    uint64_t *d_off = nullptr, *d_len = nullptr, *h_off = nullptr, *h_len = nullptr;
+    uint32_t *d_seg = nullptr, *h_seg = nullptr, *d_want = nullptr, *h_want = nullptr;
+    uint32_t *d_got = nullptr, *h_got = nullptr, *d_seg_raw = nullptr;
+    uint8_t *d_ok = nullptr, *h_ok = nullptr;
+    unsigned long long *d_nbad = nullptr, *h_nbad = nullptr;
+    cudaEvent_t done = nullptr;
+    bool busy = false;
+    size_t first = 0, n = 0;
+    void release();
+    int reserve(size_t nobj);
+    int reserve_tasks(size_t ntasks);
+};
+
 struct DevState {
     int dev = 0;
     int grid = 148;
@@ -58,8 +76,57 @@ struct DevState {
     uint8_t* h_stage[2] = {nullptr, nullptr};
     uint32_t* h_got = nullptr;  // pinned [kSingleSlots]
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
+    cudaEvent_t ev_timer[2] = {nullptr, nullptr};
     LatScratch lat{};
+    HostSlab slab[2];
 };
+
+void HostSlab::release() {
+    cudaFree(d_off); cudaFree(d_len); cudaFree(d_seg); cudaFree(d_want); cudaFree(d_got); cudaFree(d_ok);
+    cudaFree(d_nbad); cudaFree(d_seg_raw);
+    cudaFreeHost(h_off); cudaFreeHost(h_len); cudaFreeHost(h_seg); cudaFreeHost(h_want); cudaFreeHost(h_got);
+    cudaFreeHost(h_ok); cudaFreeHost(h_nbad);
+    if (done) cudaEventDestroy(done);
+    *this = HostSlab();
+}
+
+int HostSlab::reserve(size_t nobj) {
+    if (!done) CU(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+    if (!d_nbad) {
+        CU(cudaMalloc(&d_nbad, 8));
+        CU(cudaHostAlloc(&h_nbad, 8, cudaHostAllocDefault));
+    }
+    if (nobj <= cap) return 0;
+    size_t c = std::max<size_t>(nobj * 2, 1024);
+    cudaFree(d_off); cudaFree(d_len); cudaFree(d_seg); cudaFree(d_want); cudaFree(d_got); cudaFree(d_ok);
+    cudaFreeHost(h_off); cudaFreeHost(h_len); cudaFreeHost(h_seg); cudaFreeHost(h_want); cudaFreeHost(h_got);
+    cudaFreeHost(h_ok);
+    cap = 0;
+    CU(cudaMalloc(&d_off, c * 8));
+    CU(cudaMalloc(&d_len, c * 8));
+    CU(cudaMalloc(&d_seg, (c + 1) * 4));
+    CU(cudaMalloc(&d_want, c * 4));
+    CU(cudaMalloc(&d_got, c * 4));
+    CU(cudaMalloc(&d_ok, c));
+    CU(cudaHostAlloc(&h_off, c * 8, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h_len, c * 8, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h_seg, (c + 1) * 4, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h_want, c * 4, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h_got, c * 4, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h_ok, c, cudaHostAllocDefault));
+    cap = c;
+    return 0;
+}
+
+int HostSlab::reserve_tasks(size_t ntasks) {
+    if (ntasks <= task_cap) return 0;
+    size_t c = std::max<size_t>(ntasks * 2, 1 << 16);
+    cudaFree(d_seg_raw);
+    task_cap = 0;
+    CU(cudaMalloc(&d_seg_raw, c * 4));
+    task_cap = c;
+    return 0;
+}
 
 }  // namespace
 
@@ -284,6 +351,7 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
             e = cudaEventCreateWithFlags(&d->ev_copied[b], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_done[b], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaHostAlloc(&d->h_stage[b], kStageBytes, cudaHostAllocDefault);
+            if (e == cudaSuccess) e = cudaEventCreate(&d->ev_timer[b]);
         }
         if (e == cudaSuccess) e = cudaHostAlloc(&d->h_got, kSingleSlots * sizeof(uint32_t), cudaHostAllocDefault);
         if (e == cudaSuccess) e = cudaMalloc(&d->d_got, kSingleSlots * sizeof(uint32_t));
@@ -325,11 +393,14 @@ int b200_shutdown(b200_ctx* ctx) {
         cudaFree(d->d_nbad);
         cudaFreeHost(d->h_got);
         lat_scratch_free(&d->lat);
+        d->slab[0].release();
+        d->slab[1].release();
         for (int b = 0; b < 2; b++) {
             cudaFree(d->d_stage[b]);
             cudaFreeHost(d->h_stage[b]);
             if (d->ev_copied[b]) cudaEventDestroy(d->ev_copied[b]);
             if (d->ev_done[b]) cudaEventDestroy(d->ev_done[b]);
+            if (d->ev_timer[b]) cudaEventDestroy(d->ev_timer[b]);
         }
         if (d->stream) cudaStreamDestroy(d->stream);
         if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
@@ -341,6 +412,27 @@ int b200_shutdown(b200_ctx* ctx) {
 }
 
 int b200_ctx_ndev(const b200_ctx* ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+
+int b200_timer_start(b200_ctx* ctx, int dev) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d) return fail(B200_ERR_INVALID, "b200_timer_start");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    CU(cudaStreamSynchronize(d->stream));
+    CU(cudaEventRecord(d->ev_timer[0], d->stream));
+    return 0;
+}
+
+int b200_timer_stop(b200_ctx* ctx, int dev, float* ms) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !ms) return fail(B200_ERR_INVALID, "b200_timer_stop");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    CU(cudaEventRecord(d->ev_timer[1], d->stream));
+    CU(cudaEventSynchronize(d->ev_timer[1]));
+    CU(cudaEventElapsedTime(ms, d->ev_timer[0], d->ev_timer[1]));
+    return 0;
+}
 
 int b200_alloc_pinned(b200_ctx* ctx, size_t n, void** host) {
     if (!ctx || !host) return fail(B200_ERR_INVALID, "b200_alloc_pinned");
@@ -499,7 +591,9 @@ struct b200_batch {
     unsigned long long* d_nbad = nullptr;
     const uint32_t* adv_seg = nullptr;
     uint32_t ntasks = 0, rows_per_seg = 0;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;  // begin, rows kernel end, all end
+    static constexpr int kRing = 256;  // per-run CUDA event triples: begin, row kernel end, all end
+    cudaEvent_t ev[kRing][3] = {};
+    uint64_t runs = 0, timed_from = 0;
     bool ran = false;
 };
 
@@ -516,9 +610,9 @@ int b200_batch_free(b200_batch* b) {
     cudaFree(b->d_got);
     cudaFree(b->d_ok);
     cudaFree(b->d_nbad);
-    if (b->ev0) cudaEventDestroy(b->ev0);
-    if (b->ev1) cudaEventDestroy(b->ev1);
-    if (b->ev2) cudaEventDestroy(b->ev2);
+    for (auto& t : b->ev)
+        for (cudaEvent_t e : t)
+            if (e) cudaEventDestroy(e);
     cudaGetLastError();
     delete b;
     return 0;
@@ -577,9 +671,9 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
         if (want) cu(cudaMemcpy(b->d_want, want, nobj * 4, cudaMemcpyHostToDevice), "upload want");
     }
     if (!rc) cu(cudaMemcpy(b->d_seg_start, seg_start.data(), (nobj + 1) * 4, cudaMemcpyHostToDevice), "upload plan");
-    if (!rc) cu(cudaEventCreate(&b->ev0), "event");
-    if (!rc) cu(cudaEventCreate(&b->ev1), "event");
-    if (!rc) cu(cudaEventCreate(&b->ev2), "event");
+    for (auto& t : b->ev)
+        for (cudaEvent_t& e : t)
+            if (!rc) cu(cudaEventCreate(&e), "event");
     if (rc) {
         b200_batch_free(b);
         return rc;
@@ -609,8 +703,10 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     a.ntasks = b->ntasks;
     a.rows_per_seg = b->rows_per_seg;
     a.init_crc = 0;
-    CU(launch_batch(a, d->tabs, d->grid, d->stream, b->ev0, b->ev1));
-    CU(cudaEventRecord(b->ev2, d->stream));
+    cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];
+    CU(launch_batch(a, d->tabs, d->grid, d->stream, ev[0], ev[1]));
+    CU(cudaEventRecord(ev[2], d->stream));
+    b->runs++;
     b->ran = true;
     return 0;
 }
@@ -644,9 +740,22 @@ int b200_batch_results(b200_batch* b, uint32_t* got, uint8_t* ok, uint64_t* nbad
 int b200_batch_kernel_ms(b200_batch* b, float* total_ms, float* rows_kernel_ms) {
     if (!b || !b->ran) return fail(B200_ERR_INVALID, "b200_batch_kernel_ms: batch has not run");
     CU(cudaSetDevice(b->d->dev));
-    CU(cudaEventSynchronize(b->ev2));
-    if (total_ms) CU(cudaEventElapsedTime(total_ms, b->ev0, b->ev2));
-    if (rows_kernel_ms) CU(cudaEventElapsedTime(rows_kernel_ms, b->ev0, b->ev1));
+    CU(cudaStreamSynchronize(b->d->stream));
+    uint64_t from = b->timed_from;
+    if (b->runs - from > b200_batch::kRing) from = b->runs - b200_batch::kRing;
+    double tot = 0, rows = 0;
+    for (uint64_t r = from; r < b->runs; r++) {
+        cudaEvent_t* ev = b->ev[r % b200_batch::kRing];
+        float t = 0, k = 0;
+        CU(cudaEventElapsedTime(&t, ev[0], ev[2]));
+        CU(cudaEventElapsedTime(&k, ev[0], ev[1]));
+        tot += t;
+        rows += k;
+    }
+    uint64_t n = b->runs - from;
+    if (total_ms) *total_ms = n ? (float)(tot / n) : 0.f;
+    if (rows_kernel_ms) *rows_kernel_ms = n ? (float)(rows / n) : 0.f;
+    b->timed_from = b->runs;
     return 0;
 }
 
@@ -670,35 +779,34 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
                            const uint32_t* want, uint32_t* got, uint8_t* ok, uint64_t* nbad) {
     DevState* d = get_dev(ctx, dev);
     if (!d || (nobj && (!bufs || !len))) return fail(B200_ERR_INVALID, "b200_crc32c_batch_host");
-    // Pack objects back to back (16-byte aligned starts) into slabs of at most kSlab bytes; each slab is
-    // one H2D copy from pinned staging and one device batch.  Slab k+1 is packed and copied while slab k
-    // is verified.  An object larger than a slab is streamed on its own.
-    const size_t kSlab = kStageBytes;
-    uint64_t bad_total = 0;
-    size_t i = 0;
-    int slot = 0;
-    b200_batch* inflight[2] = {nullptr, nullptr};
-    size_t inflight_first[2] = {0, 0}, inflight_n[2] = {0, 0};
-    int rc = 0;
+    // Objects are laid out back to back (16-byte aligned starts) in one of two device slabs.  Pinned
+    // buffers (b200_alloc_pinned) are copied straight from where they lie — neighbouring buffers merge into
+    // one cudaMemcpyAsync — pageable ones go through the pinned staging slab.  While slab k is verified on
+    // the compute stream, slab k+1 is being filled by the copy engine.  An object larger than a slab is
+    // streamed on its own.
     std::lock_guard<std::recursive_mutex> slk(d->stage_mu);
-    auto collect = [&](int s) -> int {
-        if (!inflight[s]) return 0;
-        uint64_t nb = 0;
-        size_t f = inflight_first[s];
-        int r = b200_batch_results(inflight[s], got ? got + f : nullptr, ok ? ok + f : nullptr, &nb);
-        bad_total += nb;
-        b200_batch_free(inflight[s]);
-        inflight[s] = nullptr;
-        return r;
-    };
     {
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
-        if (int r = ensure_stage(d, kSlab)) return r;
+        if (int r = ensure_stage(d, kSlabBytes)) return r;
     }
-    std::vector<uint64_t> offs, lens;
+    uint64_t bad_total = 0;
+    int rc = 0;
+    size_t i = 0;
+    int slot = 0;
+    auto collect = [&](int s) -> int {  // wait for slab s and hand its results to the caller
+        HostSlab& hs = d->slab[s];
+        if (!hs.busy) return 0;
+        cudaError_t e = cudaEventSynchronize(hs.done);
+        hs.busy = false;
+        if (e != cudaSuccess) return fail_cuda(e, "cudaEventSynchronize");
+        if (got) memcpy(got + hs.first, hs.h_got, hs.n * sizeof(uint32_t));
+        if (ok) memcpy(ok + hs.first, hs.h_ok, hs.n);
+        bad_total += *hs.h_nbad;
+        return 0;
+    };
     while (i < nobj && !rc) {
-        if (len[i] > kSlab) {  // a big object: stream it alone (it uses both staging slabs)
+        if (len[i] > kSlabBytes) {  // a big object: stream it alone (it uses both device slabs)
             for (int s2 = 0; s2 < 2 && !rc; s2++) rc = collect(s2);
             if (rc) break;
             uint32_t c = 0;
@@ -711,50 +819,119 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
             i++;
             continue;
         }
-        rc = collect(slot);  // the staging pair `slot` is free once its previous batch finished
+        rc = collect(slot);  // device slab `slot` and its plan buffers are free once its last batch finished
         if (rc) break;
-        offs.clear();
-        lens.clear();
-        size_t first = i, used = 0;
-        while (i < nobj && len[i] <= kSlab) {
+        HostSlab& hs = d->slab[slot];
+        // choose the objects of this slab
+        size_t first = i, used = 0, staged = 0;
+        size_t cnt = 0;
+        while (i < nobj && len[i] <= kSlabBytes) {
             size_t start = (used + 15) & ~(size_t)15;
-            if (start + len[i] > kSlab) break;
-            if (len[i]) memcpy(d->h_stage[slot] + start, bufs[i], len[i]);
-            offs.push_back(start);
-            lens.push_back(len[i]);
+            if (start + len[i] > kSlabBytes) break;
             used = start + len[i];
             i++;
+            cnt++;
         }
-        b200_batch* b = nullptr;
-        rc = b200_batch_create(ctx, dev, offs.data(), lens.data(), offs.size(), want ? want + first : nullptr, &b);
-        if (rc) break;
-        {
-            std::lock_guard<std::mutex> lk(d->mu);
-            cudaSetDevice(dev);
-            cudaError_t e = cudaMemcpyAsync(d->d_stage[slot], d->h_stage[slot], used, cudaMemcpyHostToDevice,
-                                            d->copy_stream);
-            if (e == cudaSuccess) e = cudaEventRecord(d->ev_copied[slot], d->copy_stream);
-            if (e == cudaSuccess) e = cudaStreamWaitEvent(d->stream, d->ev_copied[slot], 0);
-            if (e != cudaSuccess) rc = fail_cuda(e, "slab upload");
+        std::lock_guard<std::mutex> lk(d->mu);
+        cudaSetDevice(dev);
+        if ((rc = hs.reserve(cnt))) break;
+        // plan (the device slab is 256-byte aligned, so cuts depend on the offsets only)
+        uint64_t total_rows = 0;
+        used = 0;
+        for (size_t k = 0; k < cnt; k++) {
+            size_t start = (used + 15) & ~(size_t)15;
+            hs.h_off[k] = start;
+            hs.h_len[k] = len[first + k];
+            if (want) hs.h_want[k] = want[first + k];
+            used = start + len[first + k];
+            total_rows += cut_object(start, len[first + k]).rows;
         }
-        if (!rc) rc = b200_batch_run_async(b, d->d_stage[slot]);
-        inflight[slot] = b;
-        inflight_first[slot] = first;
-        inflight_n[slot] = offs.size();
+        uint32_t rps = choose_rows_per_seg(total_rows, d->grid);
+        uint64_t t = 0;
+        for (size_t k = 0; k < cnt; k++) {
+            hs.h_seg[k] = (uint32_t)t;
+            t += (cut_object(hs.h_off[k], hs.h_len[k]).rows + rps - 1) / rps;
+        }
+        hs.h_seg[cnt] = (uint32_t)t;
+        if ((rc = hs.reserve_tasks(t))) break;
+        const uint32_t* adv_seg = nullptr;
+        if ((rc = get_adv_seg(d, rps, &adv_seg))) break;
+        cudaError_t e = cudaSuccess;
+        auto cu = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
+        cu(cudaMemcpyAsync(hs.d_off, hs.h_off, cnt * 8, cudaMemcpyHostToDevice, d->copy_stream));
+        cu(cudaMemcpyAsync(hs.d_len, hs.h_len, cnt * 8, cudaMemcpyHostToDevice, d->copy_stream));
+        cu(cudaMemcpyAsync(hs.d_seg, hs.h_seg, (cnt + 1) * 4, cudaMemcpyHostToDevice, d->copy_stream));
+        if (want) cu(cudaMemcpyAsync(hs.d_want, hs.h_want, cnt * 4, cudaMemcpyHostToDevice, d->copy_stream));
+        // data: merge host-contiguous pinned neighbours into single copies
+        size_t k = 0;
+        while (k < cnt && e == cudaSuccess) {
+            const uint8_t* src = (const uint8_t*)bufs[first + k];
+            size_t n = hs.h_len[k];
+            if (n == 0) { k++; continue; }
+            if (is_pinned(src)) {
+                size_t run_begin = hs.h_off[k], run_bytes = n, j = k + 1;
+                while (j < cnt && (const uint8_t*)bufs[first + j] == src + (hs.h_off[j] - run_begin) &&
+                       is_pinned(bufs[first + j])) {
+                    run_bytes = hs.h_off[j] + hs.h_len[j] - run_begin;
+                    j++;
+                }
+                cu(cudaMemcpyAsync(d->d_stage[slot] + run_begin, src, run_bytes, cudaMemcpyHostToDevice, d->copy_stream));
+                k = j;
+            } else {
+                // pageable: through this slab's half of pinned staging, kStageBytes at a time
+                size_t done = 0;
+                while (done < n && e == cudaSuccess) {
+                    size_t piece = std::min(n - done, kStageBytes - staged % kStageBytes);
+                    if (staged && staged % kStageBytes == 0) cu(cudaStreamSynchronize(d->copy_stream));
+                    memcpy(d->h_stage[slot] + staged % kStageBytes, src + done, piece);
+                    cu(cudaMemcpyAsync(d->d_stage[slot] + hs.h_off[k] + done, d->h_stage[slot] + staged % kStageBytes,
+                                       piece, cudaMemcpyHostToDevice, d->copy_stream));
+                    done += piece;
+                    staged += piece;
+                }
+                k++;
+            }
+        }
+        if (staged) cu(cudaStreamSynchronize(d->copy_stream));  // pinned staging of this slot is reusable next round
+        cu(cudaEventRecord(d->ev_copied[slot], d->copy_stream));
+        cu(cudaStreamWaitEvent(d->stream, d->ev_copied[slot], 0));
+        if (e != cudaSuccess) { rc = fail_cuda(e, "slab upload"); break; }
+        BatchArgs a{};
+        a.base = d->d_stage[slot];
+        a.off = hs.d_off;
+        a.len = hs.d_len;
+        a.seg_start = hs.d_seg;
+        a.want = want ? hs.d_want : nullptr;
+        a.seg_raw = hs.d_seg_raw;
+        a.got = hs.d_got;
+        a.ok = hs.d_ok;
+        a.nbad = hs.d_nbad;
+        a.adv_seg = adv_seg;
+        a.nobj = (uint32_t)cnt;
+        a.ntasks = (uint32_t)t;
+        a.rows_per_seg = rps;
+        cu(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr));
+        cu(cudaMemcpyAsync(hs.h_got, hs.d_got, cnt * 4, cudaMemcpyDeviceToHost, d->stream));
+        cu(cudaMemcpyAsync(hs.h_ok, hs.d_ok, cnt, cudaMemcpyDeviceToHost, d->stream));
+        cu(cudaMemcpyAsync(hs.h_nbad, hs.d_nbad, 8, cudaMemcpyDeviceToHost, d->stream));
+        cu(cudaEventRecord(hs.done, d->stream));
+        if (e != cudaSuccess) { rc = fail_cuda(e, "slab verify"); break; }
+        hs.busy = true;
+        hs.first = first;
+        hs.n = cnt;
         slot ^= 1;
     }
     for (int s = 0; s < 2; s++) {
         int r = collect(s);
         if (!rc) rc = r;
     }
-    (void)inflight_n;
     if (!rc && nbad) *nbad = bad_total;
     return rc;
 }
 
-// ---- hash.Hash32 --------------------------------------------------------------------------------------
-
 }  // extern "C"
+
+// ---- hash.Hash32 --------------------------------------------------------------------------------------
 
 struct b200_hasher {
     b200_ctx* ctx = nullptr;

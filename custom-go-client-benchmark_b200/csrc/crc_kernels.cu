@@ -23,21 +23,27 @@ namespace b200 {
 
 namespace {
 
-constexpr uint32_t kPairStride = 65536;  // tables {0,1} at [0,64K), {2,3} at [64K,128K)
+// Shared memory map of the row kernel.  The replicated tables start at ABSOLUTE shared address 0x10000 so
+// that a lookup address is a pure byte permutation of (state byte, lane word): 0x00TTVVLL with
+// TT = 1 + pair, VV = state byte, LL = lane*4 (+0x80 for the odd table of a pair, as an immediate).
+constexpr uint32_t kTabAbs = 0x10000;     // absolute shared address of table pair {0,1}; {2,3} follow at +64 KB
+constexpr uint32_t kPairStride = 65536;
+constexpr uint32_t kTabBytes = 4 * 256 * 32 * 4;
 
-extern __shared__ __align__(1024) uint8_t smem_tab[];
+extern __shared__ __align__(1024) uint8_t smem_raw[];
 
-__device__ __forceinline__ uint32_t lds_u32(uint32_t byte_off) {
-    return *reinterpret_cast<const uint32_t*>(smem_tab + byte_off);
-}
-
-// A^512 applied to a column register.  lane4 = lane * 4 (< 128, so bytes 1..3 of it are zero).
-__device__ __forceinline__ uint32_t adv_row(uint32_t x, uint32_t lane4) {
-    uint32_t o0 = __byte_perm(x, lane4, 0x5504);  // (byte0(x) << 8) | lane4
-    uint32_t o1 = __byte_perm(x, lane4, 0x5514);
-    uint32_t o2 = __byte_perm(x, lane4, 0x5524);
-    uint32_t o3 = __byte_perm(x, lane4, 0x5534);
-    return lds_u32(o0) ^ lds_u32(o1 + 128) ^ lds_u32(o2 + kPairStride) ^ lds_u32(o3 + kPairStride + 128);
+// A^512 applied to a column register.  lanew = 0x00010000 | lane*4: byte 0 = lane*4, byte 2 = 1, byte 3 = 0.
+__device__ __forceinline__ uint32_t adv_row(uint32_t x, uint32_t lanew) {
+    uint32_t o0 = __byte_perm(x, lanew, 0x7604);  // [lane*4, byte0(x), 0x01, 0x00]
+    uint32_t o1 = __byte_perm(x, lanew, 0x7614);
+    uint32_t o2 = __byte_perm(x, lanew, 0x7624);
+    uint32_t o3 = __byte_perm(x, lanew, 0x7634);
+    uint32_t t0, t1, t2, t3;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t0) : "r"(o0));
+    asm volatile("ld.shared.u32 %0, [%1+128];" : "=r"(t1) : "r"(o1));
+    asm volatile("ld.shared.u32 %0, [%1+65536];" : "=r"(t2) : "r"(o2));
+    asm volatile("ld.shared.u32 %0, [%1+65664];" : "=r"(t3) : "r"(o3));
+    return t0 ^ t1 ^ t2 ^ t3;
 }
 
 __device__ __forceinline__ uint4 ldg_row(const uint4* p) {
@@ -62,20 +68,23 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
                 const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
                 uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv_tab,
                 const uint32_t* __restrict__ col_k, uint32_t* __restrict__ seg_raw) {
-    // replicate the compact 4x256 table once per bank
+    // replicate the compact 4x256 table once per bank, at absolute shared address kTabAbs
+    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     {
         uint32_t i = threadIdx.x;  // kRowsThreads == 4*256
         uint32_t t = i >> 8, v = i & 255;
         uint32_t val = __ldg(adv_tab + i);
-        uint4 q = make_uint4(val, val, val, val);
-        uint4* dst = reinterpret_cast<uint4*>(smem_tab + (t >> 1) * kPairStride + v * 256 + (t & 1) * 128);
+        uint32_t dst = kTabAbs + (t >> 1) * kPairStride + v * 256 + (t & 1) * 128;
 #pragma unroll
-        for (int k = 0; k < 8; k++) dst[k] = q;
+        for (int k = 0; k < 8; k++)
+            asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(dst + 16 * k), "r"(val));
     }
+    if (smem_base > 1024) asm volatile("trap;");  // the dynamic window must cover [0x10000, 0x30000)
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t lane4 = lane * 4;
+    const uint32_t lanew = 0x00010000u | lane4;
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t k0 = __ldg(col_k + lane4), k1 = __ldg(col_k + lane4 + 1), k2 = __ldg(col_k + lane4 + 2),
                    k3 = __ldg(col_k + lane4 + 3);
@@ -97,29 +106,31 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
         const uint4* p = reinterpret_cast<const uint4*>(base + o + cut.head + row0 * kRowBytes) + lane;
 
         uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-        const uint4 zero = make_uint4(0, 0, 0, 0);
-        uint4 w0 = 0 < R ? ldg_row(p) : zero;
-        uint4 w1 = 1 < R ? ldg_row(p + 32) : zero;
-        uint4 w2 = 2 < R ? ldg_row(p + 64) : zero;
-        uint4 w3 = 3 < R ? ldg_row(p + 96) : zero;
-        uint32_t r = 0;
 #define B200_STEP(ROW)                         \
-    a0 = adv_row(a0, lane4) ^ (ROW).x;         \
-    a1 = adv_row(a1, lane4) ^ (ROW).y;         \
-    a2 = adv_row(a2, lane4) ^ (ROW).z;         \
-    a3 = adv_row(a3, lane4) ^ (ROW).w;
-        for (; r + 4 <= R; r += 4) {
-            const uint4* q = p + (size_t)(r + 4) * 32;
-            uint4 n0 = r + 4 < R ? ldg_row(q) : zero;
-            uint4 n1 = r + 5 < R ? ldg_row(q + 32) : zero;
-            uint4 n2 = r + 6 < R ? ldg_row(q + 64) : zero;
-            uint4 n3 = r + 7 < R ? ldg_row(q + 96) : zero;
-            B200_STEP(w0) B200_STEP(w1) B200_STEP(w2) B200_STEP(w3)
-            w0 = n0; w1 = n1; w2 = n2; w3 = n3;
+    a0 = adv_row(a0, lanew) ^ (ROW).x;         \
+    a1 = adv_row(a1, lanew) ^ (ROW).y;         \
+    a2 = adv_row(a2, lanew) ^ (ROW).z;         \
+    a3 = adv_row(a3, lanew) ^ (ROW).w;
+        // Main loop: 8 rows per trip in two register sets so that four 128-bit loads are always in flight
+        // and nothing is copied.  The prefetch of the trip after the last one is clamped to valid rows.
+        uint32_t r = 0;
+        if (R >= 8) {
+            const uint32_t last = R - 4;
+            uint4 x0 = ldg_row(p), x1 = ldg_row(p + 32), x2 = ldg_row(p + 64), x3 = ldg_row(p + 96);
+            for (; r + 8 <= R; r += 8) {
+                const uint4* qb = p + (size_t)(r + 4) * 32;
+                uint4 y0 = ldg_row(qb), y1 = ldg_row(qb + 32), y2 = ldg_row(qb + 64), y3 = ldg_row(qb + 96);
+                B200_STEP(x0) B200_STEP(x1) B200_STEP(x2) B200_STEP(x3)
+                const uint32_t nx = r + 8 < last ? r + 8 : last;
+                const uint4* qa = p + (size_t)nx * 32;
+                x0 = ldg_row(qa); x1 = ldg_row(qa + 32); x2 = ldg_row(qa + 64); x3 = ldg_row(qa + 96);
+                B200_STEP(y0) B200_STEP(y1) B200_STEP(y2) B200_STEP(y3)
+            }
         }
-        if (r < R) { B200_STEP(w0) r++; }
-        if (r < R) { B200_STEP(w1) r++; }
-        if (r < R) { B200_STEP(w2) r++; }
+        for (; r < R; r++) {  // at most 7 rows (only the last segment of an object)
+            uint4 x = ldg_row(p + (size_t)r * 32);
+            B200_STEP(x)
+        }
 #undef B200_STEP
         // fold the 128 columns: column c still has to pass over 4*(128-c) bytes of its row
         uint32_t s = gf2_mul(k0, a0) ^ gf2_mul(k1, a1) ^ gf2_mul(k2, a2) ^ gf2_mul(k3, a3);
@@ -228,7 +239,9 @@ __global__ void fill_latency_kernel(int64_t* __restrict__ dst, uint64_t first, s
 
 }  // namespace
 
-size_t rows_kernel_smem() { return 4 * 256 * 32 * sizeof(uint32_t); }
+// dynamic shared memory: everything up to the end of the tables at absolute 0x10000 + 128 KB (the driver's
+// reserved 1 KB sits below the dynamic window; the kernel checks the window start at run time)
+size_t rows_kernel_smem() { return kTabAbs + kTabBytes; }
 
 int rows_kernel_grid(int dev) {
     int sms = 148;

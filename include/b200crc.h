@@ -46,6 +46,10 @@ int b200_device_count(int* n);
 int b200_init(int ndev, const int* devs, b200_ctx** out);
 int b200_shutdown(b200_ctx* ctx);
 int b200_ctx_ndev(const b200_ctx* ctx);
+/* CUDA-event stopwatch on the device's compute stream, for timing a region of enqueued work on the device:
+ * start drains the stream and records; stop records, waits and returns the elapsed milliseconds. */
+int b200_timer_start(b200_ctx* ctx, int dev);
+int b200_timer_stop(b200_ctx* ctx, int dev, float* ms);
 
 /* Library-owned memory, so that Go can view it with unsafe.Slice and C keeps no Go pointers.
  * The pinned buffer replaces ReadObject's `buf := make([]byte, 2*MB)` (main.go:125). */
@@ -89,7 +93,9 @@ int b200_batch_run(b200_batch* b, const void* base);
 int b200_batch_run_async(b200_batch* b, const void* base); /* enqueue only; pair with b200_batch_wait */
 int b200_batch_wait(b200_batch* b);
 int b200_batch_results(b200_batch* b, uint32_t* got, uint8_t* ok, uint64_t* nbad);
-int b200_batch_kernel_ms(b200_batch* b, float* total_ms, float* rows_kernel_ms); /* CUDA-event times of the last run */
+/* Mean CUDA-event duration (ms) of the runs since the previous call (at most the last 256): the whole run
+ * and its row kernel alone.  Waits for the stream. */
+int b200_batch_kernel_ms(b200_batch* b, float* total_ms, float* rows_kernel_ms);
 int b200_batch_launches(const b200_batch* b, int* launches_per_run);
 int b200_batch_free(b200_batch* b);
 /* VerifyObjects([]buf, []want) with HOST buffers (the Go-facing form): bufs[i] points at len[i] bytes.

@@ -13,6 +13,7 @@ SO_PATH = os.path.join(HERE, "libb200crc.so")
 OK, ERR_INVALID, ERR_CUDA, ERR_NOMEM, ERR_EMPTY, ERR_TOO_LARGE = 0, -1, -2, -3, -4, -5
 HIST_NUMPY, HIST_OPENCENSUS = 0, 1
 RADIX_BINS, SELECT_MAX_K = 4096, 4
+NOALLOC_MAX_BYTES = 1 << 35
 
 
 class B200Error(RuntimeError):
@@ -48,6 +49,7 @@ SIGNATURES = {
     "b200_memcpy_d2h": (_int, [_vp, _int, _vp, _vp, _sz]),
     "b200_crc32c_update_host": (_int, [_vp, _int, _u32, _vp, _sz, C.POINTER(_u32)]),
     "b200_crc32c_update_device": (_int, [_vp, _int, _u32, _vp, _sz, C.POINTER(_u32)]),
+    "b200_crc32c_update_device_noalloc": (_int, [_int, _u32, _vp, _sz, C.POINTER(_u32)]),
     "b200_hasher_new": (_int, [_vp, _int, _pp]),
     "b200_hasher_write": (_int, [_vp, _vp, _sz]),
     "b200_hasher_sum32": (_int, [_vp, C.POINTER(_u32)]),

@@ -147,6 +147,15 @@ def UpdateDevice(crc: int, dptr: int, n: int, ctx: Optional[Context] = None, dev
     return out.value
 
 
+def UpdateDeviceNoAlloc(crc: int, dptr: int, n: int, dev: int = 0) -> int:
+    """crc32.Update on a device buffer for callers that must not allocate device memory (their pool owns it
+    all, or they cannot take cudaMalloc's device-wide synchronisation).  Uses the library's fixed built-in
+    scratch: at most 32 GiB per call, calls are serialised, and the first call on a GPU does its set-up."""
+    out = C.c_uint32()
+    check(_lib.load().b200_crc32c_update_device_noalloc(dev, crc & 0xFFFFFFFF, dptr, n, C.byref(out)))
+    return out.value
+
+
 def Combine(crc1: int, crc2: int, len2: int) -> int:
     """CRC of A||B from crc(A), crc(B), len(B).  Pure GF(2) arithmetic on the host."""
     return int(_lib.load().b200_crc32c_combine(crc1 & 0xFFFFFFFF, crc2 & 0xFFFFFFFF, len2))

@@ -68,6 +68,21 @@ int b200_crc32c_update_host(b200_ctx* ctx, int dev, uint32_t crc, const void* p,
 /* Same on a device-resident buffer (16-byte alignment not required). */
 int b200_crc32c_update_device(b200_ctx* ctx, int dev, uint32_t crc, const void* dptr, size_t n, uint32_t* out);
 
+/* No counterpart in the reference.  Same result as b200_crc32c_update_device, for callers that cannot
+ * allocate device memory: processes that gave all of it to their own pool at start-up, and read loops
+ * that cannot take the device-wide synchronisation of cudaMalloc/cudaFree.  Needs no b200_ctx and calls no
+ * allocating routine: the row kernel's per-segment scratch and the constant tables live in a fixed ~266 KB
+ * array inside the library image, which every GPU that loads the library holds until exit.
+ *   - n > B200_NOALLOC_MAX_BYTES is rejected with B200_ERR_TOO_LARGE (split and b200_crc32c_combine).
+ *   - All calls share that one array per GPU; they are serialised inside the library and each waits for
+ *     its result, so they never overlap on the GPU — overlapping users of the array would race.  The array
+ *     keeps the previous call's contents; what must start at zero is cleared on every call.
+ *   - The first call on a GPU also does that GPU's one-time set-up (resolves the array's device address,
+ *     uploads the tables); make it before starting any stream capture.
+ *   - Runs on the device's legacy default stream and returns once *out (host memory) holds the CRC. */
+#define B200_NOALLOC_MAX_BYTES (1ull << 35)
+int b200_crc32c_update_device_noalloc(int dev, uint32_t crc, const void* dptr, size_t n, uint32_t* out);
+
 /* hash.Hash32 as returned by crc32.New(crc32.MakeTable(crc32.Castagnoli)): Write never fails and
  * consumes all of p; Sum32 does not disturb the state; Reset returns to the empty message. */
 int b200_hasher_new(b200_ctx* ctx, int dev, b200_hasher** out);

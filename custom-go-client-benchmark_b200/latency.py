@@ -106,6 +106,31 @@ class _Reducer:
         return int(self._run(np.array([v], dtype=np.int64), "MAX")[0])
 
 
+def merge_distribution(red: _Reducer, counts: np.ndarray, cnt: int, mn: int, mx: int, total: int, sumsq: int,
+                       below: int, above: int) -> Distribution:
+    """Combine one rank's exact integer partials with the other ranks' (sum / min / max all-reduces)."""
+    nb = counts.size
+    if red.active:
+        # 128-bit quantities travel as four 32-bit limbs each (the signed sum is offset to be non-negative)
+        off = 1 << 100
+        limbs = lambda v: [(v >> (32 * i)) & 0xFFFFFFFF for i in range(4)]
+        vec = np.array([int(c) for c in counts] + [cnt, below, above] + limbs(total + off) + limbs(sumsq),
+                       dtype=np.uint64)
+        r = red.sum_u64(vec)
+        world = red.dist.get_world_size(red.group)
+        counts = np.array([int(x) for x in r[:nb]], dtype=np.uint64)
+        had = cnt > 0
+        cnt, below, above = int(r[nb]), int(r[nb + 1]), int(r[nb + 2])
+        total = sum(int(r[nb + 3 + i]) << (32 * i) for i in range(4)) - world * off
+        sumsq = sum(int(r[nb + 7 + i]) << (32 * i) for i in range(4))
+        big = (1 << 63) - 1
+        mn = red.min_i64(mn if had else big)
+        mx = red.max_i64(mx if had else -big - 1)
+    wrapped = total & _M64
+    wrapped = wrapped - (1 << 64) if wrapped >= _SIGN else wrapped
+    return Distribution(cnt, mn, mx, total, wrapped, sumsq, counts, below, above)
+
+
 def hist_fixed(d_samples: int, n: int, divisor: int, edges, mode: int, ctx: Optional[Context] = None,
                dev: Optional[int] = None, group=None, reduce_device=None) -> Distribution:
     ctx = ctx or default_context()
@@ -117,25 +142,8 @@ def hist_fixed(d_samples: int, n: int, divisor: int, edges, mode: int, ctx: Opti
                                  counts.ctypes.data, C.byref(st)))
     total = _signed(st.sum, st.sum_hi)
     sumsq = (st.sumsq_hi << 64) | st.sumsq_lo
-    red = _Reducer(group, reduce_device)
-    cnt, mn, mx, below, above = st.count, st.min, st.max, st.dropped_below, st.dropped_above
-    if red.active:
-        # 128-bit quantities travel as four 32-bit limbs each (sum offset to be non-negative)
-        off = 1 << 100
-        limbs = lambda v: [(v >> (32 * i)) & 0xFFFFFFFF for i in range(4)]
-        vec = np.array(list(counts) + [cnt, below, above] + limbs(total + off) + limbs(sumsq), dtype=np.uint64)
-        r = red.sum_u64(vec)
-        world = red.dist.get_world_size(group)
-        counts = np.array([int(x) for x in r[:nb]], dtype=np.uint64)
-        cnt, below, above = int(r[nb]), int(r[nb + 1]), int(r[nb + 2])
-        total = sum(int(r[nb + 3 + i]) << (32 * i) for i in range(4)) - world * off
-        sumsq = sum(int(r[nb + 7 + i]) << (32 * i) for i in range(4))
-        big = (1 << 63) - 1
-        mn = red.min_i64(mn if st.count else big)
-        mx = red.max_i64(mx if st.count else -big - 1)
-    wrapped = total & _M64
-    wrapped = wrapped - (1 << 64) if wrapped >= _SIGN else wrapped
-    return Distribution(cnt, mn, mx, total, wrapped, sumsq, counts, below, above)
+    return merge_distribution(_Reducer(group, reduce_device), counts, st.count, st.min, st.max, total, sumsq,
+                              st.dropped_below, st.dropped_above)
 
 
 def hist_readme(d_samples_ns: int, n: int, **kw) -> Distribution:
@@ -148,27 +156,23 @@ def hist_opencensus(d_samples_ns: int, n: int, **kw) -> Distribution:
     return hist_fixed(d_samples_ns, n, NS_PER_MS, OC_DEFAULT_LATENCY_BOUNDS, HIST_OPENCENSUS, **kw)
 
 
-def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Optional[Context] = None,
-               dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None):
-    """k-th smallest (0-based) of trunc(sample/divisor) over all ranks' samples.  MSD radix select."""
-    ctx = ctx or default_context()
-    L, h, d = ctx._L, ctx._h, ctx._dev(dev)
-    red = _Reducer(group, reduce_device)
+def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int, ks: Sequence[int],
+                 n_global: Optional[int] = None):
+    """MSD radix select over the union of all ranks' samples.
+
+    minmax_fn() -> (min, max) of this rank's raw samples; count_fn(key_base, shift, top, prefixes) -> uint64
+    array [len(prefixes)][4096] of this rank's digit counts (b200_minmax / b200_radix_count on the GPU).
+    After every local count the histograms are summed over ranks, so every rank walks the same digits.
+    """
     ks = [int(k) for k in ks]
-    if not red.active:
-        karr = np.array(ks, dtype=np.uint64)
-        out = np.zeros(len(ks), dtype=np.int64)
-        check(L.b200_select_kth(h, d, d_samples, n, divisor, karr.ctypes.data, len(ks), out.ctypes.data))
-        return [int(x) for x in out]
-    # distributed form: same loop as b200_select_kth with an all-reduce after every count
-    ntot = int(red.sum_u64(np.array([n], dtype=np.uint64))[0]) if n_global is None else n_global
+    ntot = int(red.sum_u64(np.array([n_local], dtype=np.uint64))[0]) if (n_global is None and red.active) else (
+        n_local if n_global is None else n_global)
     if ntot == 0:
         raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
-    if any(k >= ntot for k in ks):
+    if any(k >= ntot or k < 0 for k in ks):
         raise ValueError("k >= n")
-    mn, mx = C.c_int64(), C.c_int64()
-    check(L.b200_minmax(h, d, d_samples, n, C.byref(mn), C.byref(mx)))
-    gmn, gmx = red.min_i64(mn.value), red.max_i64(mx.value)
+    mn, mx = minmax_fn()
+    gmn, gmx = red.min_i64(mn), red.max_i64(mx)
     kmin, kmax = (gmn + _SIGN) & _M64, (gmx + _SIGN) & _M64
     bits = (kmax - kmin).bit_length()
     res = []
@@ -180,17 +184,14 @@ def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Opt
         while top > 0:
             shift = max(top - 12, 0)
             width = top - shift
-            nk = 1 if first else m
-            counts = np.zeros(nk * RADIX_BINS, dtype=np.uint64)
-            parr = np.array(prefix[:nk] if not first else [0], dtype=np.uint64)
-            check(L.b200_radix_count(h, d, d_samples, n, kmin, shift, top, nk, parr.ctypes.data,
-                                     counts.ctypes.data))
-            tot = red.sum_u64(counts)
+            # first pass: key' < 2^top, so every sample matches prefix 0 and one histogram serves all k
+            pfx = [0] if first else prefix
+            tot = red.sum_u64(np.asarray(count_fn(kmin, shift, top, pfx), dtype=np.uint64).reshape(-1))
             for i in range(m):
-                hrow = tot[0:RADIX_BINS] if first else tot[i * RADIX_BINS:(i + 1) * RADIX_BINS]
+                row = tot[0:RADIX_BINS] if first else tot[i * RADIX_BINS:(i + 1) * RADIX_BINS]
                 cum = 0
                 for dgt in range(1 << width):
-                    c = int(hrow[dgt])
+                    c = int(row[dgt])
                     if rank[i] < cum + c:
                         break
                     cum += c
@@ -200,11 +201,38 @@ def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Opt
                 prefix[i] = (prefix[i] << width) | dgt
             top, first = shift, False
         for i in range(m):
-            key = (prefix[i] + kmin) & _M64
-            ns = key - _SIGN  # undo the sign flip
-            q = abs(ns) // divisor
+            ns = ((prefix[i] + kmin) & _M64) - _SIGN  # undo the sign flip
+            q = abs(ns) // divisor                    # Go's truncating division
             res.append(q if ns >= 0 else -q)
     return res
+
+
+def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Optional[Context] = None,
+               dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None):
+    """k-th smallest (0-based) of trunc(sample/divisor) over all ranks' samples (sorted[k] of
+    ssd_test/main.go:158-163) without sorting."""
+    ctx = ctx or default_context()
+    L, h, d = ctx._L, ctx._h, ctx._dev(dev)
+    red = _Reducer(group, reduce_device)
+    if not red.active:
+        karr = np.array([int(k) for k in ks], dtype=np.uint64)
+        out = np.zeros(karr.size, dtype=np.int64)
+        check(L.b200_select_kth(h, d, d_samples, n, divisor, karr.ctypes.data, karr.size, out.ctypes.data))
+        return [int(x) for x in out]
+
+    def minmax_fn():
+        mn, mx = C.c_int64(), C.c_int64()
+        check(L.b200_minmax(h, d, d_samples, n, C.byref(mn), C.byref(mx)))
+        return mn.value, mx.value
+
+    def count_fn(key_base, shift, top, prefixes):
+        counts = np.zeros(len(prefixes) * RADIX_BINS, dtype=np.uint64)
+        parr = np.array(prefixes, dtype=np.uint64)
+        check(L.b200_radix_count(h, d, d_samples, n, key_base, shift, top, len(prefixes), parr.ctypes.data,
+                                 counts.ctypes.data))
+        return counts
+
+    return radix_select(red, n, minmax_fn, count_fn, divisor, ks, n_global)
 
 
 @dataclass

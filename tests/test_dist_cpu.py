@@ -1,0 +1,134 @@
+"""world_size-2 gloo tests (CPU) of the host-side multi-rank logic: shard CRC folding, the count all-reduce
+behind the histogram, and the distributed radix-select loop.  The per-rank GPU primitives are replaced here by
+numpy stand-ins with the same contract (b200_minmax / b200_radix_count / b200_hist_fixed partials); the GPU
+primitives themselves are covered by the -m gpu tests."""
+import importlib
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+import oracle
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+pkg = importlib.import_module("custom-go-client-benchmark_b200")
+lat = pkg.latency
+SIGN, M64 = 1 << 63, (1 << 64) - 1
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _np_count_fn(samples):
+    keys = (samples.astype(np.int64).view(np.uint64) ^ np.uint64(SIGN))
+
+    def count_fn(key_base, shift, top, prefixes):
+        k = (keys - np.uint64(key_base)).astype(np.uint64)
+        out = np.zeros((len(prefixes), lat.RADIX_BINS), dtype=np.uint64)
+        width = top - shift
+        for i, p in enumerate(prefixes):
+            sel = k if top >= 64 else k[(k >> np.uint64(top)) == np.uint64(p)]
+            dg = ((sel >> np.uint64(shift)) & np.uint64((1 << width) - 1)).astype(np.int64)
+            out[i] = np.bincount(dg, minlength=lat.RADIX_BINS).astype(np.uint64)
+        return out.reshape(-1)
+    return count_fn
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # --- 1. sharded object: rank r hashes bytes [r*L/N, (r+1)*L/N); rank 0 folds (crc, len) pairs ------
+        L = 3_000_001
+        data = oracle.payload(L)
+        lo, hi = L * rank // world, L * (rank + 1) // world
+        mine = oracle.crc32c(data[lo:hi])            # stand-in for b200_crc32c_update_device on this rank
+        gathered = [None] * world
+        dist.all_gather_object(gathered, (mine, hi - lo))
+        acc = 0
+        for c, ln in gathered:
+            acc = pkg.crc32c.Combine(acc, c, ln)     # the product's host-side GF(2) fold
+        assert acc == oracle.crc32c(data)
+
+        # --- 2. histogram merge ---------------------------------------------------------------------------
+        n = 100_000
+        ns_all = oracle.latency_ns(n)
+        ns = ns_all[n * rank // world: n * (rank + 1) // world]
+        ms = oracle.ns_to_ms(ns)
+        counts, dropped = oracle.hist_numpy(ms.astype(np.float64))
+        below, above = int((ms < 20).sum()), int((ms > 95).sum())
+        red = lat._Reducer()
+        assert red.active
+        d = lat.merge_distribution(red, counts, ms.size, int(ms.min()), int(ms.max()), int(ms.sum()),
+                                   int((ms.astype(object) ** 2).sum()), below, above)
+        ms_all = oracle.ns_to_ms(ns_all)
+        ref, ref_dropped = oracle.hist_numpy(ms_all.astype(np.float64))
+        assert list(d.counts) == list(ref) and d.dropped_below + d.dropped_above == ref_dropped
+        assert (d.count, d.min, d.max, d.sum) == (n, ms_all.min(), ms_all.max(), int(ms_all.sum()))
+        assert d.sumsq == int((ms_all.astype(object) ** 2).sum())
+        s = oracle.stats_i64(ms_all)
+        assert abs(d.mean - s.mean_welford) <= 1e-12 * d.mean
+        assert abs(d.sum_of_squared_dev - s.sum_sq_dev) <= 1e-9 * s.sum_sq_dev
+
+        # --- 3. distributed radix select ------------------------------------------------------------------
+        for divisor in (1000, 1):
+            ks = [0, n // 5, n // 2, 9 * n // 10, 99 * n // 100, n - 1]
+            got = lat.radix_select(red, ns.size, lambda: (int(ns.min()), int(ns.max())), _np_count_fn(ns), divisor, ks)
+            srt = np.sort(ns_all // divisor)
+            assert got == [int(srt[k]) for k in ks], (divisor, got)
+        # negatives + duplicates + an empty rank
+        rng = np.random.default_rng(1)
+        all_v = np.concatenate([rng.integers(-5000, 5000, 900), np.full(300, -17), rng.integers(-2**62, 2**62, 10)]
+                               ).astype(np.int64)
+        part = all_v if rank == 0 else all_v[:0]
+        big = (1 << 63) - 1
+        mm = (lambda: (int(part.min()), int(part.max()))) if part.size else (lambda: (big, -big - 1))
+        got = lat.radix_select(red, part.size, mm, _np_count_fn(part), 1, [0, 600, all_v.size - 1])
+        srt = np.sort(all_v)
+        assert got == [int(srt[0]), int(srt[600]), int(srt[-1])]
+        q.put((rank, "ok"))
+    except Exception as e:  # surface the failure in the parent
+        import traceback
+        q.put((rank, traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_world_size_2_gloo():
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    results = [q.get(timeout=240) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    for rank, msg in results:
+        assert msg == "ok", f"rank {rank}: {msg}"
+
+
+def test_radix_select_single_process_matches_sort():
+    red = lat._Reducer()
+    assert not red.active
+    rng = np.random.default_rng(0)
+    v = rng.integers(0, 10**10, size=5000).astype(np.int64)
+    ks = [0, 1, 2500, 4999]
+    got = lat.radix_select(red, v.size, lambda: (int(v.min()), int(v.max())), _np_count_fn(v), 1000, ks)
+    srt = np.sort(v // 1000)
+    assert got == [int(srt[k]) for k in ks]
+    with pytest.raises(ZeroDivisionError):
+        lat.radix_select(red, 0, lambda: (0, 0), _np_count_fn(v[:0]), 1, [0])
+    with pytest.raises(ValueError):
+        lat.radix_select(red, v.size, lambda: (int(v.min()), int(v.max())), _np_count_fn(v), 1, [5000])

@@ -1088,15 +1088,13 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
     return 0;
 }
 
-int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
-                    int nk, int64_t* out) {
-    if (!k || !out || nk < 1 || divisor < 1) return fail(B200_ERR_INVALID, "b200_select_kth");
+int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, int64_t lo_ns,
+                          int64_t hi_ns, const uint64_t* k, int nk, int64_t* out) {
+    if (!k || !out || nk < 1 || divisor < 1 || lo_ns > hi_ns) return fail(B200_ERR_INVALID, "b200_select_kth");
     if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
     for (int i = 0; i < nk; i++)
         if (k[i] >= n) return fail(B200_ERR_INVALID, "b200_select_kth: k >= n");
-    int64_t mn, mx;
-    if (int rc = b200_minmax(ctx, dev, d_samples, n, &mn, &mx)) return rc;
-    const uint64_t kmin = (uint64_t)mn ^ 0x8000000000000000ull, kmax = (uint64_t)mx ^ 0x8000000000000000ull;
+    const uint64_t kmin = (uint64_t)lo_ns ^ 0x8000000000000000ull, kmax = (uint64_t)hi_ns ^ 0x8000000000000000ull;
     const uint64_t range = kmax - kmin;
     int bits = 0;
     while (bits < 64 && (range >> bits)) bits++;
@@ -1107,6 +1105,9 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         for (int i = 0; i < m; i++) rank[i] = k[g + i];
         int top = bits;
         bool first = true;
+        if (top == 0) {  // all samples equal lo_ns: nothing to resolve
+            for (int i = 0; i < m; i++) prefix[i] = 0;
+        }
         while (top > 0) {
             int shift = std::max(top - kRadixBits, 0);
             int width = top - shift;
@@ -1121,7 +1122,8 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
                     if (rank[i] < cum + h[dgt]) break;
                     cum += h[dgt];
                 }
-                if (dgt == (1 << width)) return fail(B200_ERR_CUDA, "b200_select_kth: inconsistent radix counts");
+                if (dgt == (1 << width))
+                    return fail(B200_ERR_INVALID, "b200_select_kth: samples outside the given [lo, hi] range");
                 rank[i] -= cum;
                 prefix[i] = (prefix[i] << width) | (uint64_t)dgt;
             }
@@ -1134,6 +1136,15 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         }
     }
     return 0;
+}
+
+int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
+                    int nk, int64_t* out) {
+    if (!k || !out || nk < 1 || divisor < 1) return fail(B200_ERR_INVALID, "b200_select_kth");
+    if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
+    int64_t mn, mx;
+    if (int rc = b200_minmax(ctx, dev, d_samples, n, &mn, &mx)) return rc;
+    return b200_select_kth_range(ctx, dev, d_samples, n, divisor, mn, mx, k, nk, out);
 }
 
 }  // extern "C"

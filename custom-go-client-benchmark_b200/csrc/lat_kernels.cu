@@ -64,13 +64,20 @@ __device__ __forceinline__ int classify(long long n, const long long* __restrict
     return c;
 }
 
-__global__ void __launch_bounds__(kHistThreads)
+// Per-thread running moments.  Fast path values fit 32 bits, so their squares fit 64.
+struct Moments {
+    unsigned mn32 = 0xFFFFFFFFu, mx32 = 0;                 // of fast-path samples
+    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;  // of slow-path samples
+    U128 sum{0, 0}, sq{0, 0};
+};
+
+template <bool MOMENTS>
+__global__ void __launch_bounds__(kHistThreads, 4)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
-            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, int want_moments) {
+            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom) {
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ HistParams P;
-    // [warp][bin][lane] private counters
-    unsigned* tbl = reinterpret_cast<unsigned*>(sm);
+    unsigned* tbl = reinterpret_cast<unsigned*>(sm);  // [warp][bin][lane] private counters
     {
         const unsigned* src = reinterpret_cast<const unsigned*>(Pg);
         unsigned* dst = reinterpret_cast<unsigned*>(&P);
@@ -81,23 +88,47 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned* mine = tbl + (size_t)warp * nbins * 32 + lane;
+    Moments m;
+    const unsigned magic32 = P.magic32;
+    const int shift32 = P.shift32, mode32 = P.mode32;
 
-    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
-    U128 sum{0, 0}, sq{0, 0};
-    unsigned long long cnt = 0;
-
-    auto one = [&](long long v) {
+    // generic path: any int64 sample
+    auto slow = [&](long long v) {
         int c = classify(v, P.thr, P.nthr, P.lut);
         mine[c * 32]++;
-        if (want_moments) {
-            mn = v < mn ? v : mn;
-            mx = v > mx ? v : mx;
+        if (MOMENTS) {
+            m.mn = v < m.mn ? v : m.mn;
+            m.mx = v > m.mx ? v : m.mx;
             unsigned long long a = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
             unsigned long long q = udiv_magic(a, P);
-            add128(sq, q * q, __umul64hi(q, q));
-            if (v < 0) add128(sum, 0ull - q, q ? ~0ull : 0ull);
-            else add128(sum, q, 0);
-            cnt++;
+            add128(m.sq, q * q, __umul64hi(q, q));
+            if (v < 0) add128(m.sum, 0ull - q, q ? ~0ull : 0ull);
+            else add128(m.sum, q, 0);
+        }
+    };
+    // fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), everything in 32-bit arithmetic
+    auto one = [&](long long v) {
+        const unsigned long long uv = (unsigned long long)v;
+        if (uv >> 32) { slow(v); return; }
+        const unsigned u = (unsigned)uv;
+        const int e = 31 - __clz((int)(u | 1));
+        const unsigned idx = u < 32 ? u : (unsigned)((e - 4) * 32) + ((u >> (e - 5)) & 31);
+        const unsigned cell = P.lut[idx];
+        if ((cell & 0xFF) > 1) { slow(v); return; }  // several thresholds inside this cell: rare
+        const unsigned c = (cell >> 8) + (u > P.cell_gt[idx] ? 1u : 0u);
+        mine[c * 32]++;
+        if (MOMENTS) {
+            m.mn32 = min(m.mn32, u);
+            m.mx32 = max(m.mx32, u);
+            unsigned q;
+            if (mode32 == 1) {
+                unsigned t = __umulhi(magic32, u);
+                q = (t + ((u - t) >> 1)) >> shift32;
+            } else {
+                q = mode32 == 0 ? u : 0u;
+            }
+            add128(m.sum, q, 0);
+            add128(m.sq, (unsigned long long)q * q, 0);
         }
     };
 
@@ -110,9 +141,10 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
     const size_t npairs = (n - head) / 2;
     size_t i = tid;
-    for (; i + nthreads < npairs; i += 2 * nthreads) {  // two independent loads in flight
-        longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads);
-        one(a.x); one(a.y); one(b.x); one(b.y);
+    for (; i + 3 * nthreads < npairs; i += 4 * nthreads) {  // four independent 128-bit loads in flight
+        longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads), c = __ldg(x2 + i + 2 * nthreads),
+                  d = __ldg(x2 + i + 3 * nthreads);
+        one(a.x); one(a.y); one(b.x); one(b.y); one(c.x); one(c.y); one(d.x); one(d.y);
     }
     for (; i < npairs; i += nthreads) {
         longlong2 a = __ldg(x2 + i);
@@ -127,22 +159,28 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             for (int l = 0; l < 32; l++) t += tbl[((size_t)w * nbins + b) * 32 + ((l + b) & 31)];
         if (t) atomicAdd(counts + b, t);
     }
-    if (want_moments) {
+    if (MOMENTS) {
+        long long mn = m.mn, mx = m.mx;
+        if (m.mn32 <= m.mx32) {  // this thread saw fast-path samples
+            mn = (long long)m.mn32 < mn ? (long long)m.mn32 : mn;
+            mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
+        }
+        U128 sum = m.sum, sq = m.sq;
 #pragma unroll
         for (int d = 16; d; d >>= 1) {
             long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
             mn = omn < mn ? omn : mn;
             mx = omx > mx ? omx : mx;
-            cnt += __shfl_xor_sync(0xFFFFFFFFu, cnt, d);
             unsigned long long l1 = __shfl_xor_sync(0xFFFFFFFFu, sum.lo, d), h1 = __shfl_xor_sync(0xFFFFFFFFu, sum.hi, d);
             add128(sum, l1, h1);
             unsigned long long l2 = __shfl_xor_sync(0xFFFFFFFFu, sq.lo, d), h2 = __shfl_xor_sync(0xFFFFFFFFu, sq.hi, d);
             add128(sq, l2, h2);
         }
-        if (lane == 0 && cnt) {
-            atomicMin(&mom->min_ns, mn);
-            atomicMax(&mom->max_ns, mx);
-            atomicAdd(&mom->count, cnt);
+        if (lane == 0) {
+            if (mn <= mx) {
+                atomicMin(&mom->min_ns, mn);
+                atomicMax(&mom->max_ns, mx);
+            }
             unsigned long long old = atomicAdd(&mom->sum_lo, sum.lo);
             unsigned long long carry = (old + sum.lo) < old;
             atomicAdd(reinterpret_cast<unsigned long long*>(&mom->sum_hi), sum.hi + carry);
@@ -150,6 +188,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             carry = (old + sq.lo) < old;
             atomicAdd(&mom->sumsq_hi, sq.hi + carry);
         }
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&mom->count, (unsigned long long)n);
     }
 }
 
@@ -261,13 +300,18 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     e = reset_moments(s, stream);
     if (e != cudaSuccess) return e;
     if (!n) return cudaSuccess;
-    size_t smem = hist_smem(nbins);
-    e = cudaFuncSetAttribute(hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist_smem(kMaxThresholds + 1));
+    const size_t smem = hist_smem(nbins);
+    const int max_smem = (int)hist_smem(kMaxThresholds + 1);
+    e = cudaFuncSetAttribute(hist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
-    int per_sm = 2;
+    // resident CTAs per SM: 4 by registers, fewer when the private counter tables are large
+    int per_sm = (int)std::min<size_t>(4, (200 * 1024) / (smem + sizeof(HistParams) + 1024));
+    if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
-    hist_kernel<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom, want_moments ? 1 : 0);
+    if (want_moments) hist_kernel<true><<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom);
+    else hist_kernel<false><<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom);
     return cudaGetLastError();
 }
 
@@ -344,7 +388,28 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
             if (P->thr[j] <= (long long)lo) base++;
             else if (P->thr[j] <= (long long)hi) extra++;
         }
-        P->lut[idx] = (unsigned short)((base << 8) | extra);
+        P->lut[idx] = (unsigned short)((base << 8) | (extra > 255 ? 255 : extra));
+        // thresholds inside a cell are > lo >= 0, so thr - 1 >= 0; beyond 32 bits no fast-path sample exceeds it
+        unsigned int gt = 0xFFFFFFFFu;
+        if (extra >= 1 && base < m) {
+            long long t1 = P->thr[base] - 1;
+            gt = t1 >= 0xFFFFFFFFll ? 0xFFFFFFFFu : (unsigned int)t1;
+        }
+        P->cell_gt[idx] = gt;
+    }
+    // 32-bit dividends (Granlund-Montgomery, N = 32): l = ceil(log2 d), m' = floor(2^32 (2^l - d) / d) + 1,
+    // q = (t + ((n - t) >> 1)) >> (l - 1) with t = umulhi(m', n)
+    if (divisor == 1) {
+        P->mode32 = 0;
+    } else if ((unsigned long long)divisor > 0xFFFFFFFFull) {
+        P->mode32 = 2;
+    } else {
+        unsigned long long d32 = (unsigned long long)divisor;
+        int l = 0;
+        while ((1ull << l) < d32) l++;
+        P->magic32 = (unsigned int)((((unsigned __int128)1 << 32) * ((1ull << l) - d32)) / d32 + 1);
+        P->shift32 = l - 1;
+        P->mode32 = 1;
     }
     // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)
     P->divisor = divisor;

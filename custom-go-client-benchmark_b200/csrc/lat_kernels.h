@@ -25,9 +25,14 @@ struct HistParams {
     long long thr[kMaxThresholds];      // thresholds in raw ns, ascending: count(n) = #{j : thr[j] <= n}
     int nthr;
     unsigned short lut[kLutCells];      // (base << 8) | extra for each log-linear cell of n >= 0
+    unsigned int cell_gt[kLutCells];    // fast path (0 <= n < 2^32): count = base + (n > cell_gt[cell]);
+                                        // = (first threshold inside the cell) - 1, or 0xFFFFFFFF if none
     unsigned long long magic;           // division by `divisor` as multiply-high (see lat_kernels.cu)
     int magic_shift;
     int magic_add;
+    unsigned int magic32;               // the same for 32-bit dividends: q = (t + ((n - t) >> 1)) >> shift32,
+    int shift32;                        //   t = umulhi(magic32, n); mode32: 0 = divisor 1, 1 = magic, 2 = q is 0
+    int mode32;
     long long divisor;
 };
 

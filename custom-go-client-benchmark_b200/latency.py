@@ -208,19 +208,27 @@ def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int,
 
 
 def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Optional[Context] = None,
-               dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None):
+               dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None,
+               bounds_ns: Optional[tuple] = None):
     """k-th smallest (0-based) of trunc(sample/divisor) over all ranks' samples (sorted[k] of
-    ssd_test/main.go:158-163) without sorting."""
+    ssd_test/main.go:158-163) without sorting.  bounds_ns = (lo, hi) with lo <= every sample <= hi on every
+    rank skips the min/max pass."""
     ctx = ctx or default_context()
     L, h, d = ctx._L, ctx._h, ctx._dev(dev)
     red = _Reducer(group, reduce_device)
     if not red.active:
         karr = np.array([int(k) for k in ks], dtype=np.uint64)
         out = np.zeros(karr.size, dtype=np.int64)
-        check(L.b200_select_kth(h, d, d_samples, n, divisor, karr.ctypes.data, karr.size, out.ctypes.data))
+        if bounds_ns is None:
+            check(L.b200_select_kth(h, d, d_samples, n, divisor, karr.ctypes.data, karr.size, out.ctypes.data))
+        else:
+            check(L.b200_select_kth_range(h, d, d_samples, n, divisor, int(bounds_ns[0]), int(bounds_ns[1]),
+                                          karr.ctypes.data, karr.size, out.ctypes.data))
         return [int(x) for x in out]
 
     def minmax_fn():
+        if bounds_ns is not None:
+            return int(bounds_ns[0]), int(bounds_ns[1])
         mn, mx = C.c_int64(), C.c_int64()
         check(L.b200_minmax(h, d, d_samples, n, C.byref(mn), C.byref(mx)))
         return mn.value, mx.value
@@ -255,6 +263,10 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
     if size == 0:
         raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
     ks = [size // 5, size // 2, (9 * size) // 10, (99 * size) // 100]
+    # raw-nanosecond bounds implied by the scaled min/max of the pass above (truncating division)
+    lo = dist_.min * divisor if dist_.min > 0 else (dist_.min - 1) * divisor + 1
+    hi = (dist_.max + 1) * divisor - 1 if dist_.max >= 0 else dist_.max * divisor
+    lo, hi = max(lo, -(1 << 63)), min(hi, (1 << 63) - 1)
     p20, p50, p90, p99 = select_kth(d_samples_ns, n, divisor, ks, ctx=ctx, dev=dev, group=group,
-                                    reduce_device=reduce_device, n_global=size)
+                                    reduce_device=reduce_device, n_global=size, bounds_ns=(lo, hi))
     return Percentiles(dist_.avg_go_int, p20, p50, p90, p99, dist_.min, dist_.max)

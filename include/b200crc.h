@@ -163,6 +163,10 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
  * arrays.  B200_ERR_EMPTY when n == 0 (the reference panics there). */
 int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                     const uint64_t* k, int nk, int64_t* out);
+/* The same when the caller already knows bounds lo_ns <= every sample <= hi_ns (for instance from the min/max
+ * of a previous b200_hist_fixed): saves the min/max pass.  Samples outside the bounds are an error. */
+int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, int64_t lo_ns,
+                          int64_t hi_ns, const uint64_t* k, int nk, int64_t* out);
 /* Building blocks of b200_select_kth for the one-process-per-GPU form, where the caller all-reduces the
  * results over ranks between calls (NCCL; see custom-go-client-benchmark_b200/latency.py):
  * b200_minmax: min and max raw sample on this device (INT64_MAX / INT64_MIN when n == 0).

@@ -52,6 +52,8 @@ SIGNATURES = {
     "b200_crc32c_update_device_noalloc": (_int, [_int, _u32, _vp, _sz, C.POINTER(_u32)]),
     "b200_hasher_new": (_int, [_vp, _int, _pp]),
     "b200_hasher_write": (_int, [_vp, _vp, _sz]),
+    "b200_hasher_reserve": (_int, [_vp, _pp, C.POINTER(_sz)]),
+    "b200_hasher_commit": (_int, [_vp, _sz]),
     "b200_hasher_sum32": (_int, [_vp, C.POINTER(_u32)]),
     "b200_hasher_reset": (_int, [_vp]),
     "b200_hasher_free": (_int, [_vp]),

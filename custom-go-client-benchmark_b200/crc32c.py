@@ -174,6 +174,26 @@ class Hash32:
         check(self._ctx._L.b200_hasher_write(self._h, a.ctypes.data if a.size else None, a.size))
         return a.size  # Go: n == len(p), err == nil always
 
+    def ReadFrom(self, r) -> int:
+        """io.ReaderFrom: drain `r` (anything with readinto, or read) straight into the hasher's pinned
+        staging buffer — the replacement for io.CopyBuffer(io.Discard, rc, buf) at main.go:140.  Returns the
+        number of bytes consumed (Go returns (n int64, err error); errors raise here)."""
+        L, total = self._ctx._L, 0
+        while True:
+            ptr, avail = C.c_void_p(), C.c_size_t()
+            check(L.b200_hasher_reserve(self._h, C.byref(ptr), C.byref(avail)))
+            view = memoryview((C.c_uint8 * avail.value).from_address(ptr.value)).cast("B")
+            if hasattr(r, "readinto"):
+                n = r.readinto(view)
+            else:
+                chunk = r.read(avail.value)
+                n = len(chunk)
+                view[:n] = chunk
+            if not n:
+                return total
+            check(L.b200_hasher_commit(self._h, n))
+            total += n
+
     def Sum32(self) -> int:
         out = C.c_uint32()
         check(self._ctx._L.b200_hasher_sum32(self._h, C.byref(out)))
@@ -308,3 +328,35 @@ def StreamChecksum(host: np.ndarray, chunk: int = 256 << 20, crc: int = 0, ctx: 
     check(ctx._L.b200_crc32c_stream_host(ctx._h, ctx._dev(dev), crc, a.ctypes.data if a.size else None, a.size, chunk,
                                          C.byref(out)))
     return out.value
+
+
+# ---- wire checksums: how GCS hands the expected CRC-32C to storage.Reader ----------------------
+
+def EncodeXGoogHash(crc: int) -> str:
+    """'crc32c=<base64 of the big-endian uint32>' as in the X-Goog-Hash response header (HTTP/JSON API)."""
+    import base64
+    return "crc32c=" + base64.b64encode((crc & 0xFFFFFFFF).to_bytes(4, "big")).decode()
+
+
+def DecodeXGoogHash(header: str) -> Optional[int]:
+    """Extract the CRC-32C from an X-Goog-Hash header value ('crc32c=AAAAAA==,md5=...'); None if absent."""
+    import base64
+    for part in header.split(","):
+        part = part.strip()
+        if part.startswith("crc32c="):
+            raw = base64.b64decode(part[len("crc32c="):])
+            if len(raw) != 4:
+                raise ValueError("crc32c value must decode to 4 bytes")
+            return int.from_bytes(raw, "big")
+    return None
+
+
+def DecodeFixed32(raw: bytes) -> int:
+    """gRPC ObjectChecksums.crc32c is a protobuf fixed32: four little-endian bytes on the wire."""
+    if len(raw) != 4:
+        raise ValueError("fixed32 is 4 bytes")
+    return int.from_bytes(raw, "little")
+
+
+def EncodeFixed32(crc: int) -> bytes:
+    return (crc & 0xFFFFFFFF).to_bytes(4, "little")

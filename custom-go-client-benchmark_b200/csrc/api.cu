@@ -162,6 +162,8 @@ int get_adv_seg(DevState* d, uint32_t rows_per_seg, const uint32_t** out) {
     return 0;
 }
 
+constexpr uint32_t kMaxRowsPerSeg = 2048;  // 1 MiB segments: 32 KB per lane in the fold kernel
+
 uint32_t env_rows_per_seg() {
     static int v = -1;
     if (v < 0) {
@@ -175,9 +177,12 @@ uint32_t env_rows_per_seg() {
 // several segments, but segments stay long enough to amortise the per-segment column fold.
 uint32_t choose_rows_per_seg(uint64_t total_rows, int grid) {
     if (uint32_t e = env_rows_per_seg()) return e;
-    uint64_t target = total_rows / ((uint64_t)grid * kRowsWarps * 6);
+    // large inputs: ~6 segments per warp of the fold kernel (16 warps/SM), segments of up to 1024 rows so the
+    // per-segment epilogue stays a few percent; small inputs fall back to the row kernel's finer grain
+    uint64_t target = total_rows / ((uint64_t)grid * kFoldWarps * 6);
+    if (target < kFoldMinRows || !fold_enabled(kFoldMinRows)) target = total_rows / ((uint64_t)grid * kRowsWarps * 6);
     uint32_t r = 16;
-    while ((uint64_t)r * 2 <= target && r < 1024) r *= 2;
+    while ((uint64_t)r * 2 <= target && r < kMaxRowsPerSeg) r *= 2;
     return r;
 }
 
@@ -223,6 +228,8 @@ int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc,
     if (int rc = get_adv_seg(d, a.rows_per_seg, &a.adv_seg)) return rc;
     a.nobj = 1;
     a.ntasks = (uint32_t)ntasks;
+    a.nfull_tasks = (uint32_t)(cut.rows / a.rows_per_seg);
+    a.npartial_tasks = a.ntasks - a.nfull_tasks;
     a.seg_raw = d->seg_raw;
     a.got = d->d_got + slot;
     a.ok = d->d_ok;
@@ -326,8 +333,9 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
     CU(cudaGetDeviceCount(&have));
     b200_ctx* ctx = new (std::nothrow) b200_ctx;
     if (!ctx) return fail(B200_ERR_NOMEM, "b200_init");
-    uint32_t adv_row[1024], col_k[128], xsq[64], byte_tab[256];
+    uint32_t adv_row[1024], col_k[128], xsq[64], byte_tab[256], adv4[1024];
     host_build_adv_table(kRowBytes, adv_row);
+    host_build_adv_table(4, adv4);
     host_build_col_k(col_k);
     host_build_xpow8_sq(xsq);
     host_build_byte_tab(byte_tab);
@@ -366,6 +374,7 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
         if (!rc) rc = upload(&d->tabs.col_k, col_k, 128);
         if (!rc) rc = upload(&d->tabs.xpow8_sq, xsq, 64);
         if (!rc) rc = upload(&d->tabs.byte_tab, byte_tab, 256);
+        if (!rc) rc = upload(&d->tabs.adv4, adv4, 1024);
         if (!rc) rc = lat_scratch_init(&d->lat) == cudaSuccess ? 0 : fail(B200_ERR_CUDA, "latency scratch");
         if (rc) {
             b200_shutdown(ctx);
@@ -387,6 +396,7 @@ int b200_shutdown(b200_ctx* ctx) {
         cudaFree(d->tabs.col_k);
         cudaFree(d->tabs.xpow8_sq);
         cudaFree(d->tabs.byte_tab);
+        cudaFree(d->tabs.adv4);
         cudaFree(d->seg_raw);
         cudaFree(d->d_got);
         cudaFree(d->d_ok);
@@ -590,7 +600,7 @@ struct b200_batch {
     uint8_t* d_ok = nullptr;
     unsigned long long* d_nbad = nullptr;
     const uint32_t* adv_seg = nullptr;
-    uint32_t ntasks = 0, rows_per_seg = 0;
+    uint32_t ntasks = 0, rows_per_seg = 0, nfull = 0;
     static constexpr int kRing = 256;  // per-run CUDA event triples: begin, row kernel end, all end
     cudaEvent_t ev[kRing][3] = {};
     uint64_t runs = 0, timed_from = 0;
@@ -646,6 +656,7 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     }
     b->rows_per_seg = rps;
     b->ntasks = seg_start[nobj];
+    for (size_t i = 0; i < nobj; i++) b->nfull += (uint32_t)(cut_object(off[i], len[i]).rows / rps);
     int rc = get_adv_seg(d, rps, &b->adv_seg);
     auto dev_alloc = [&](void** p, size_t bytes) -> int {
         if (rc) return rc;
@@ -701,6 +712,8 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     a.adv_seg = b->adv_seg;
     a.nobj = (uint32_t)b->nobj;
     a.ntasks = b->ntasks;
+    a.nfull_tasks = b->nfull;
+    a.npartial_tasks = b->ntasks - b->nfull;
     a.rows_per_seg = b->rows_per_seg;
     a.init_crc = 0;
     cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];
@@ -761,7 +774,8 @@ int b200_batch_kernel_ms(b200_batch* b, float* total_ms, float* rows_kernel_ms) 
 
 int b200_batch_launches(const b200_batch* b, int* launches_per_run) {
     if (!b || !launches_per_run) return fail(B200_ERR_INVALID, "b200_batch_launches");
-    *launches_per_run = (b->ntasks ? 1 : 0) + (b->nobj ? 1 : 0);
+    const bool fold = fold_enabled(b->rows_per_seg) && b->nfull > 0;
+    *launches_per_run = (fold ? 1 : 0) + ((b->ntasks && (!fold || b->ntasks > b->nfull)) ? 1 : 0) + (b->nobj ? 1 : 0);
     return 0;
 }
 
@@ -847,10 +861,12 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
             total_rows += cut_object(start, len[first + k]).rows;
         }
         uint32_t rps = choose_rows_per_seg(total_rows, d->grid);
-        uint64_t t = 0;
+        uint64_t t = 0, tfull = 0;
         for (size_t k = 0; k < cnt; k++) {
             hs.h_seg[k] = (uint32_t)t;
-            t += (cut_object(hs.h_off[k], hs.h_len[k]).rows + rps - 1) / rps;
+            const uint64_t rows = cut_object(hs.h_off[k], hs.h_len[k]).rows;
+            t += (rows + rps - 1) / rps;
+            tfull += rows / rps;
         }
         hs.h_seg[cnt] = (uint32_t)t;
         if ((rc = hs.reserve_tasks(t))) break;
@@ -909,6 +925,8 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
         a.adv_seg = adv_seg;
         a.nobj = (uint32_t)cnt;
         a.ntasks = (uint32_t)t;
+        a.nfull_tasks = (uint32_t)tfull;
+        a.npartial_tasks = (uint32_t)(t - tfull);
         a.rows_per_seg = rps;
         cu(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr));
         cu(cudaMemcpyAsync(hs.h_got, hs.d_got, cnt * 4, cudaMemcpyDeviceToHost, d->stream));
@@ -983,6 +1001,22 @@ int b200_hasher_write(b200_hasher* h, const void* p, size_t n) {
         if (h->fill == h->cap)
             if (int rc = hasher_flush(h)) return rc;
     }
+    return 0;
+}
+
+int b200_hasher_reserve(b200_hasher* h, void** ptr, size_t* avail) {
+    if (!h || !ptr || !avail) return fail(B200_ERR_INVALID, "b200_hasher_reserve");
+    if (h->fill == h->cap)
+        if (int rc = hasher_flush(h)) return rc;
+    *ptr = h->buf + h->fill;
+    *avail = h->cap - h->fill;
+    return 0;
+}
+
+int b200_hasher_commit(b200_hasher* h, size_t n) {
+    if (!h || n > h->cap - h->fill) return fail(B200_ERR_INVALID, "b200_hasher_commit: more than was reserved");
+    h->fill += n;
+    if (h->fill == h->cap) return hasher_flush(h);
     return 0;
 }
 

@@ -1,0 +1,255 @@
+// K2 "fold kernel": CRC-32C of full segments with NO table lookups in the hot loop.
+//
+// Same contract as the row kernel (crc_kernels.cu): for every full segment (rows_per_seg rows of 512 bytes)
+// write the raw CRC register of that segment to seg_raw[task].  Partial segments are left to the row kernel.
+//
+// Idea.  The row kernel pays one shared-memory lookup per byte and is bound by the L1/shared data path
+// (128 B/clk/SM) — and by the power those lookups draw.  Here each lane instead reduces its own contiguous
+// stream modulo a SPARSE multiple of the CRC polynomial,
+//     Q'(x) = y^64 + y^48 + y^5 + x^2 (y^54 + y^37 + y^26),   y = x^32
+// ( = y^5 * (y^59 + y^43 + x^2 (y^49 + y^32 + y^21) + 1), found by tools/find_word_aligned_multiples.c; P | Q').
+// Reducing modulo Q' is a linear feedback shift register over 32-bit WORDS: when a new word enters, the word
+// T that leaves the 64-word window is xor-ed back at five places, two of them word aligned and three of them
+// shifted by the same 2 bits (one funnel shift of (T_prev, T) serves all three).  That is 1 SHF + 5 LOP3 per
+// 32-bit word on the ALU pipe and nothing else — no table, no multiply.  The 64-word state lives in 64
+// registers; the window slides by renaming (the loop is unrolled 64 steps, so every index is static).
+// Only when a lane has consumed its whole stream is the 64-word state reduced modulo P itself (256 byte-table
+// lookups per lane, ~3 % of the work at 16 KB per lane), weighted by x^(8*bytes_after_this_lane) and
+// xor-reduced over the warp.
+//
+// Data movement.  A lane needs a CONTIGUOUS stream, which coalesced register loads cannot give; so the warp
+// stages it through shared memory with cp.async (LDGSTS, 16 B per lane, no registers): one instruction
+// moves four lanes' next 128 bytes fully coalesced (8 lanes x 16 B per row), eight instructions fill a
+// 32-row x 128-byte stage.  Rows are stored with a 128-byte XOR swizzle (chunk j of row l at chunk
+// j ^ (l & 7)) so both the copies and the per-lane 128-bit reads are bank-conflict free.  Three stages per
+// warp are in flight (commit/wait groups), 16 warps x 3 x 4 KB = 192 KB of shared memory.
+// (TMA bulk copies were tried first: UBLKCP takes uniform operands only, so per-lane copies serialise into a
+// 32-iteration loop per warp.)
+#include "crc_kernels.h"
+
+#include <cstdlib>
+
+namespace b200 {
+
+namespace {
+
+constexpr int kFoldSmemTab = 4 * 256 * 4;  // A^4 slicing tables for the final reduction (not replicated)
+
+extern __shared__ __align__(1024) uint8_t fold_smem[];
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+    uint4 v;
+    asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+    return v;
+}
+
+// One LFSR step at body position T (0..63).  Logical word k of the window at step t is r[(k - t) & 63]; the
+// word leaving the window and the word entering it share one register.
+#define FOLD_STEP(T, W)                                           \
+    {                                                             \
+        const uint32_t top = r[(63 - (T)) & 63];                  \
+        r[(63 - (T)) & 63] = (W);                                 \
+        r[(48 - (T)-1) & 63] ^= top;                              \
+        r[(5 - (T)-1) & 63] ^= top;                               \
+        const uint32_t f = __funnelshift_r(tprev, top, 2);        \
+        r[(55 - (T)-1) & 63] ^= f;                                \
+        r[(38 - (T)-1) & 63] ^= f;                                \
+        r[(27 - (T)-1) & 63] ^= f;                                \
+        tprev = top;                                              \
+    }
+#define FOLD_QUAD(T, V) FOLD_STEP((T), (V).x) FOLD_STEP((T) + 1, (V).y) FOLD_STEP((T) + 2, (V).z) FOLD_STEP((T) + 3, (V).w)
+// one stage = 32 words = 8 quads, at body offset B (0 or 32)
+#define FOLD_STAGE(B, ADDR)                                                                       \
+    {                                                                                             \
+        uint4 q0 = lds128((ADDR) + (sw ^ 0)), q1 = lds128((ADDR) + (sw ^ 16)), q2 = lds128((ADDR) + (sw ^ 32)),   \
+              q3 = lds128((ADDR) + (sw ^ 48)), q4 = lds128((ADDR) + (sw ^ 64)), q5 = lds128((ADDR) + (sw ^ 80)),  \
+              q6 = lds128((ADDR) + (sw ^ 96)), q7 = lds128((ADDR) + (sw ^ 112));                              \
+        FOLD_QUAD((B) + 0, q0) FOLD_QUAD((B) + 4, q1) FOLD_QUAD((B) + 8, q2) FOLD_QUAD((B) + 12, q3)   \
+        FOLD_QUAD((B) + 16, q4) FOLD_QUAD((B) + 20, q5) FOLD_QUAD((B) + 24, q6) FOLD_QUAD((B) + 28, q7) \
+    }
+
+__device__ __forceinline__ uint32_t find_object2(const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t task) {
+    uint32_t lo = 0, hi = nobj;
+    while (hi - lo > 1) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (__ldg(seg_start + mid) <= task) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// WARPS warps per CTA (one CTA per SM), STAGES staging buffers per warp, LANE_BYTES (128 or 256) bytes per lane
+// per stage.  Larger LANE_BYTES means longer contiguous bursts per stream in DRAM but fewer warps fit.
+template <int WARPS, int STAGES, int LANE_BYTES>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
+                const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
+                uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv4_tab,
+                const uint32_t* __restrict__ xsq, uint32_t* __restrict__ seg_raw) {
+    constexpr int kThreads = WARPS * 32;
+    constexpr int kWarpStageBytes = 32 * LANE_BYTES;
+    constexpr int kLanesPerRow = LANE_BYTES / 16;      // copy role: this many lanes move one row's stage
+    constexpr int kRowsPerInstr = 32 / kLanesPerRow;
+    constexpr int kCopyInstrs = 32 / kRowsPerInstr;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t* tab = reinterpret_cast<uint32_t*>(fold_smem);  // [4][256]
+    uint8_t* stage_base = fold_smem + kFoldSmemTab;          // [warps][stages][32 rows x LANE_BYTES]
+    for (uint32_t i = threadIdx.x; i < 1024; i += kThreads) tab[i] = __ldg(adv4_tab + i);
+    __syncthreads();
+
+    const uint32_t lane_bytes = rows_per_seg * 16;   // S: bytes of the segment owned by one lane
+    const uint32_t nstage = lane_bytes / LANE_BYTES;  // rows_per_seg is a multiple of 16, so S is one of 256
+    // weight of this lane's register: the (31 - lane) lanes after it still have S bytes each to pass
+    const uint32_t lane_k = gf2_xpow8((uint64_t)lane_bytes * (31 - lane), xsq);
+    const uint32_t warp_stage = smem_u32(stage_base + (size_t)warp * STAGES * kWarpStageBytes);
+    const uint32_t my_row = warp_stage + lane * LANE_BYTES;  // this lane's row inside a stage
+    const uint32_t sw = (lane & 7) << 4;                     // its swizzle (chunk j lives at chunk j ^ (row & 7))
+    const uint32_t crow = lane / kLanesPerRow, cchunk = lane % kLanesPerRow;
+    const uint32_t nwarps = gridDim.x * WARPS;
+
+    for (uint32_t task = warp * gridDim.x + blockIdx.x; task < ntasks; task += nwarps) {
+        uint32_t seg = task;
+        uint64_t o = single_off, n = single_len;
+        if (off) {
+            const uint32_t obj = find_object2(seg_start, nobj, task);
+            seg = task - __ldg(seg_start + obj);
+            o = __ldg(off + obj);
+            n = __ldg(len + obj);
+        }
+        const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
+        const uint64_t row0 = (uint64_t)seg * rows_per_seg;
+        if (cut.rows - row0 < rows_per_seg) continue;  // partial segment: the row kernel's job
+        const uint8_t* src = base + o + cut.head + row0 * kRowBytes;  // lane l's stream starts at src + l*S
+        const uint8_t* csrc = src + (size_t)crow * lane_bytes + cchunk * 16;
+
+        uint32_t r[64];
+#pragma unroll
+        for (int k = 0; k < 64; k++) r[k] = 0;
+        uint32_t tprev = 0;
+
+        uint32_t ibuf = 0;  // staging buffer the next issue() fills
+        auto issue = [&](uint32_t st) {
+            if (st < nstage) {
+                const uint32_t buf = warp_stage + ibuf * kWarpStageBytes;
+                const uint8_t* g = csrc + (size_t)st * LANE_BYTES;
+#pragma unroll
+                for (int k = 0; k < kCopyInstrs; k++) {
+                    const uint32_t row = crow + kRowsPerInstr * k;
+                    cp_async16(buf + row * LANE_BYTES + ((cchunk ^ (row & 7)) << 4),
+                               g + (size_t)(kRowsPerInstr * k) * lane_bytes);
+                }
+            }
+            cp_async_commit();  // always commit so that group counting stays uniform
+            ibuf = ibuf + 1 == STAGES ? 0 : ibuf + 1;
+        };
+        __syncwarp();  // previous task's readers are done with the staging buffers
+#pragma unroll
+        for (int s0 = 0; s0 < STAGES - 1; s0++) issue(s0);
+        uint32_t cbuf = 0;  // staging buffer being consumed
+        if (LANE_BYTES >= 256) {
+            for (uint32_t st = 0; st < nstage; st++) {
+                issue(st + STAGES - 1);
+                cp_async_wait<STAGES - 1>();  // stage st has landed (this lane's part)
+                __syncwarp();                 // ... and everybody else's
+                const uint32_t a = my_row + cbuf * kWarpStageBytes;
+#pragma unroll 1
+                for (uint32_t h = 0; h < LANE_BYTES / 256; h++) {
+                    FOLD_STAGE(0, a + h * 256)
+                    FOLD_STAGE(32, a + h * 256 + 128)
+                }
+                __syncwarp();                 // all lanes done reading before the buffer is refilled
+                cbuf = cbuf + 1 == STAGES ? 0 : cbuf + 1;
+            }
+        } else {
+            for (uint32_t st = 0; st < nstage; st += 2) {
+                issue(st + STAGES - 1);
+                cp_async_wait<STAGES - 1>();
+                __syncwarp();
+                FOLD_STAGE(0, my_row + cbuf * kWarpStageBytes)
+                __syncwarp();
+                cbuf = cbuf + 1 == STAGES ? 0 : cbuf + 1;
+                issue(st + STAGES);
+                cp_async_wait<STAGES - 1>();
+                __syncwarp();
+                FOLD_STAGE(32, my_row + cbuf * kWarpStageBytes)
+                __syncwarp();
+                cbuf = cbuf + 1 == STAGES ? 0 : cbuf + 1;
+            }
+        }
+        // the low part of the last leaving word has not been applied yet (it waits for a partner that never comes)
+        r[54] ^= tprev >> 2;
+        r[37] ^= tprev >> 2;
+        r[26] ^= tprev >> 2;
+        // reduce the 64-word state modulo P: feed words y^63 .. y^0 through the register, 4 bytes at a time
+        uint32_t reg = 0;
+#pragma unroll
+        for (int k = 63; k >= 0; k--) {
+            const uint32_t x = reg ^ r[k];
+            reg = tab[x & 0xFF] ^ tab[256 + ((x >> 8) & 0xFF)] ^ tab[512 + ((x >> 16) & 0xFF)] ^ tab[768 + (x >> 24)];
+        }
+        uint32_t s = gf2_mul(lane_k, reg);
+#pragma unroll
+        for (int d = 16; d; d >>= 1) s ^= __shfl_xor_sync(0xFFFFFFFFu, s, d);
+        if (lane == 0) seg_raw[task] = s;
+    }
+}
+
+struct FoldVariant {
+    int warps, stages, lane_bytes;
+    void (*kernel)(const uint8_t*, const uint64_t*, const uint64_t*, const uint32_t*, uint32_t, uint32_t, uint32_t,
+                   uint64_t, uint64_t, const uint32_t*, const uint32_t*, uint32_t*);
+    size_t smem() const { return kFoldSmemTab + (size_t)warps * stages * 32 * lane_bytes; }
+};
+// Measured on B200 (4096 x 2 MiB, 300 back-to-back steps, GB/s): <8,2,256> 6878 | <7,2,256> 6796 | <4,3,512> 6780 |
+// <6,3,256> 6758 | <9,2,256> 6658 | <8,3,256> 6568 | <12,2,256> 6499 | <4,2,256> 6139 | <16,3,128> 5563.
+// 256-byte bursts per stream matter most (DRAM page locality); beyond ~64 KB in flight per SM more hurts.
+const FoldVariant kVariants[] = {
+    {8, 2, 256, crc_fold_kernel<8, 2, 256>},    // default
+    {8, 3, 256, crc_fold_kernel<8, 3, 256>},
+    {16, 3, 128, crc_fold_kernel<16, 3, 128>},
+    {4, 3, 512, crc_fold_kernel<4, 3, 512>},
+    {7, 2, 256, crc_fold_kernel<7, 2, 256>},
+};
+
+const FoldVariant& fold_variant() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("B200_FOLD_VARIANT");
+        v = e ? atoi(e) : 0;
+        if (v < 0 || v >= (int)(sizeof kVariants / sizeof kVariants[0])) v = 0;
+    }
+    return kVariants[v];
+}
+
+}  // namespace
+
+size_t fold_kernel_smem() { return fold_variant().smem(); }
+
+cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream) {
+    const FoldVariant& fv = fold_variant();
+    static thread_local int attr_dev = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (attr_dev != dev) {
+        cudaError_t e = cudaFuncSetAttribute(fv.kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fv.smem());
+        if (e != cudaSuccess) return e;
+        attr_dev = dev;
+    }
+    if (!a.ntasks) return cudaSuccess;
+    uint32_t need = (a.ntasks + fv.warps - 1) / fv.warps;
+    int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
+    fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, a.off, a.len, a.seg_start, a.nobj, a.ntasks, a.rows_per_seg,
+                                                       a.single_off, a.single_len, t.adv4, t.xpow8_sq, a.seg_raw);
+    return cudaGetLastError();
+}
+
+}  // namespace b200

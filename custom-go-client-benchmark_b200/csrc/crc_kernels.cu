@@ -19,6 +19,8 @@
 //   unaligned head and sub-row tail bytes, init/final inversion, comparison with want[].
 #include "crc_kernels.h"
 
+#include <cstdlib>
+
 namespace b200 {
 
 namespace {
@@ -66,7 +68,7 @@ __device__ __forceinline__ uint32_t find_object(const uint32_t* __restrict__ seg
 __global__ void __launch_bounds__(kRowsThreads, 1)
 crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
                 const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
-                uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv_tab,
+                uint64_t single_off, uint64_t single_len, uint32_t skip_full, const uint32_t* __restrict__ adv_tab,
                 const uint32_t* __restrict__ col_k, uint32_t* __restrict__ seg_raw) {
     // replicate the compact 4x256 table once per bank, at absolute shared address kTabAbs
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
@@ -103,6 +105,7 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
         const uint64_t row0 = (uint64_t)seg * rows_per_seg;
         uint64_t left = cut.rows - row0;
         const uint32_t R = left < rows_per_seg ? (uint32_t)left : rows_per_seg;
+        if (skip_full && R == rows_per_seg) continue;  // full segments belong to the fold kernel
         const uint4* p = reinterpret_cast<const uint4*>(base + o + cut.head + row0 * kRowBytes) + lane;
 
         uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
@@ -241,6 +244,15 @@ __global__ void fill_latency_kernel(int64_t* __restrict__ dst, uint64_t first, s
 
 // dynamic shared memory: everything up to the end of the tables at absolute 0x10000 + 128 KB (the driver's
 // reserved 1 KB sits below the dynamic window; the kernel checks the window start at run time)
+bool fold_enabled(uint32_t rows_per_seg) {
+    static int disabled = -1;
+    if (disabled < 0) {
+        const char* e = getenv("B200_NO_FOLD");
+        disabled = (e && *e && *e != '0') ? 1 : 0;
+    }
+    return !disabled && rows_per_seg >= kFoldMinRows && rows_per_seg % 16 == 0;
+}
+
 size_t rows_kernel_smem() { return kTabAbs + kTabBytes; }
 
 int rows_kernel_grid(int dev) {
@@ -263,12 +275,17 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     cudaError_t e = cudaMemsetAsync(a.nbad, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     if (ev_begin) cudaEventRecord(ev_begin, stream);
-    if (a.ntasks) {
+    const bool fold = fold_enabled(a.rows_per_seg) && a.nfull_tasks > 0;
+    if (fold) {
+        e = launch_fold(a, t, grid, stream);
+        if (e != cudaSuccess) return e;
+    }
+    if (a.ntasks && (!fold || a.npartial_tasks > 0)) {
         uint32_t need = (a.ntasks + kRowsWarps - 1) / kRowsWarps;
         int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
         crc_rows_kernel<<<g, kRowsThreads, rows_kernel_smem(), stream>>>(a.base, a.off, a.len, a.seg_start, a.nobj,
                                                                          a.ntasks, a.rows_per_seg, a.single_off, a.single_len,
-                                                                         t.adv_row, t.col_k, a.seg_raw);
+                                                                         fold ? 1u : 0u, t.adv_row, t.col_k, a.seg_raw);
     }
     if (ev_end) cudaEventRecord(ev_end, stream);
     if (a.nobj)

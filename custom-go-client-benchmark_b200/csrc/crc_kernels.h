@@ -12,6 +12,8 @@ constexpr int kRowWords = 128;
 constexpr int kRowsThreads = 1024;
 constexpr int kRowsWarps = kRowsThreads / 32;
 constexpr int kFinalThreads = 128;
+constexpr int kFoldWarps = 8;  // fold kernel (crc_fold_kernel.cu): default variant runs 8 warps per SM
+constexpr uint32_t kFoldMinRows = 128;  // segments shorter than this stay on the row kernel
 
 // How an object [addr, addr+len) is cut: an unaligned head (< 16 B) so the body starts on a 16-byte
 // boundary, whole 512-byte rows, and a tail (< 512 B).  Rows go to the row kernel, head and tail are
@@ -37,6 +39,7 @@ struct DeviceTables {
     uint32_t* col_k;     // [128] x^(8*4*(128-c)): weight of column c inside a row
     uint32_t* xpow8_sq;  // [64]  x^(8*2^k)
     uint32_t* byte_tab;  // [256] classic one-byte table
+    uint32_t* adv4;      // [4][256] multiply-by-x^32 slicing tables (fold kernel's final reduction)
 };
 
 struct BatchArgs {
@@ -58,13 +61,23 @@ struct BatchArgs {
     // tasks 0..ntasks-1; no plan arrays are read.
     uint64_t single_off;
     uint64_t single_len;
+    // how many of the ntasks segments are full (rows_per_seg rows) / partial; the fold kernel takes the full
+    // ones when it is in use, the row kernel the rest
+    uint32_t nfull_tasks;
+    uint32_t npartial_tasks;
 };
+
+// true when launch_batch will give full segments of this length to the fold kernel
+bool fold_enabled(uint32_t rows_per_seg);
 
 int rows_kernel_grid(int dev);
 size_t rows_kernel_smem();
 // Enqueue row kernel + finalize kernel on `stream`.  ev_* may be null; when given they bracket the row kernel.
 cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream,
                          cudaEvent_t ev_rows_begin, cudaEvent_t ev_rows_end);
+
+size_t fold_kernel_smem();
+cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream);
 
 cudaError_t launch_fill_payload(uint64_t* dst, uint64_t first_word, size_t nwords, uint64_t seed, cudaStream_t s);
 cudaError_t launch_fill_latency(int64_t* dst, uint64_t first, size_t n, uint64_t seed, cudaStream_t s);

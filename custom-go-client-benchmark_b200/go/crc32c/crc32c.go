@@ -21,10 +21,14 @@ package crc32c
 import "C"
 
 import (
+	"encoding/base64"
+	"encoding/binary"
 	"errors"
 	"fmt"
 	"hash"
+	"io"
 	"runtime"
+	"strings"
 	"sync"
 	"unsafe"
 )
@@ -105,6 +109,32 @@ func (d *digest) Write(p []byte) (int, error) {
 		panic(err)
 	}
 	return len(p), nil
+}
+
+// ReadFrom implements io.ReaderFrom, so io.Copy(h, rc) replaces io.CopyBuffer(io.Discard, rc, buf)
+// (main.go:140): the transport reads straight into the hasher's pinned staging buffer.
+func (d *digest) ReadFrom(r io.Reader) (int64, error) {
+	var total int64
+	for {
+		var p unsafe.Pointer
+		var avail C.size_t
+		if err := status(C.b200_hasher_reserve(d.h, &p, &avail)); err != nil {
+			return total, err
+		}
+		n, err := r.Read(unsafe.Slice((*byte)(p), int(avail)))
+		if n > 0 {
+			if e := status(C.b200_hasher_commit(d.h, C.size_t(n))); e != nil {
+				return total, e
+			}
+			total += int64(n)
+		}
+		if err == io.EOF {
+			return total, nil
+		}
+		if err != nil {
+			return total, err
+		}
+	}
 }
 
 func (d *digest) Sum32() uint32 {
@@ -199,4 +229,19 @@ func FreePinned(b []byte) error {
 		return err
 	}
 	return status(C.b200_free_pinned(c, unsafe.Pointer(&b[0])))
+}
+
+// DecodeXGoogHash extracts the CRC-32C from an X-Goog-Hash header value ("crc32c=AAAAAA==,md5=...").
+func DecodeXGoogHash(header string) (uint32, bool) {
+	for _, part := range strings.Split(header, ",") {
+		part = strings.TrimSpace(part)
+		if v, ok := strings.CutPrefix(part, "crc32c="); ok {
+			raw, err := base64.StdEncoding.DecodeString(v)
+			if err != nil || len(raw) != 4 {
+				return 0, false
+			}
+			return binary.BigEndian.Uint32(raw), true
+		}
+	}
+	return 0, false
 }

@@ -52,6 +52,14 @@ class Distribution:
             return 0.0
         return float(Fraction(self.sumsq) - Fraction(self.sum * self.sum, self.count))
 
+    def to_opencensus(self, bounds=None) -> dict:
+        """The fields of OpenCensus view.DistributionData that metrics_exporter.go:22-34 would export
+        (SURVEY 8f.2), from the exact integer partials.  Count == 0 keeps OpenCensus' zero values."""
+        return {"Count": self.count, "Min": float(self.min) if self.count else 0.0,
+                "Max": float(self.max) if self.count else 0.0, "Mean": self.mean,
+                "SumOfSquaredDev": self.sum_of_squared_dev, "CountPerBucket": [int(c) for c in self.counts],
+                "bounds": None if bounds is None else [float(b) for b in bounds]}
+
     @property
     def avg_go_int(self) -> int:
         """sum/int64(size) with Go's truncating integer division (ssd_test/main.go:157)."""

@@ -87,6 +87,13 @@ int b200_crc32c_update_device_noalloc(int dev, uint32_t crc, const void* dptr, s
  * consumes all of p; Sum32 does not disturb the state; Reset returns to the empty message. */
 int b200_hasher_new(b200_ctx* ctx, int dev, b200_hasher** out);
 int b200_hasher_write(b200_hasher* h, const void* p, size_t n);
+/* io.ReaderFrom support: instead of io.CopyBuffer(io.Discard, rc, buf) filling a scratch buffer that is then
+ * hashed (main.go:125,140), the transport reads straight into the hasher's pinned staging.  reserve returns
+ * the free part of that buffer (*avail >= 1; flushes to the GPU first when it is full), commit(n) declares
+ * that n <= *avail bytes were written there.  The pointer is library-owned pinned memory, valid until the
+ * next call on this hasher. */
+int b200_hasher_reserve(b200_hasher* h, void** ptr, size_t* avail);
+int b200_hasher_commit(b200_hasher* h, size_t n);
 int b200_hasher_sum32(b200_hasher* h, uint32_t* out);
 int b200_hasher_reset(b200_hasher* h);
 int b200_hasher_free(b200_hasher* h);

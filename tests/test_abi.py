@@ -104,3 +104,29 @@ def test_missing_library_is_an_error(monkeypatch):
     monkeypatch.setattr(pkg._lib, "SO_PATH", "/nonexistent/libb200crc.so")
     with pytest.raises(FileNotFoundError):
         pkg._lib.load()
+
+
+def test_wire_checksum_codecs():
+    import base64
+    c = pkg.crc32c
+    crc = 0xE3069283  # CRC-32C("123456789")
+    hdr = c.EncodeXGoogHash(crc)
+    assert hdr == "crc32c=" + base64.b64encode(bytes([0xE3, 0x06, 0x92, 0x83])).decode() == "crc32c=4waSgw=="
+    assert c.DecodeXGoogHash(hdr) == crc
+    assert c.DecodeXGoogHash("md5=XrY7u+Ae7tCTyyK7j1rNww==, crc32c=4waSgw==") == crc
+    assert c.DecodeXGoogHash("md5=XrY7u+Ae7tCTyyK7j1rNww==") is None
+    with pytest.raises(ValueError):
+        c.DecodeXGoogHash("crc32c=AAAA")
+    assert c.DecodeFixed32(c.EncodeFixed32(crc)) == crc and c.EncodeFixed32(crc) == bytes([0x83, 0x92, 0x06, 0xE3])
+    assert oracle.crc32c(b"123456789") == crc
+
+
+def test_distribution_export_shape():
+    d = pkg.latency.Distribution(count=4, min=1, max=7, sum=16, sum_wrapped=16, sumsq=84,
+                                 counts=np.array([1, 2, 1], dtype=np.uint64))
+    oc = d.to_opencensus(bounds=[2, 5])
+    assert oc["Count"] == 4 and oc["Mean"] == 4.0 and oc["SumOfSquaredDev"] == 84 - 16 * 16 / 4
+    assert oc["CountPerBucket"] == [1, 2, 1] and oc["Min"] == 1.0 and oc["Max"] == 7.0
+    assert d.avg_go_int == 4
+    neg = pkg.latency.Distribution(3, -5, 1, -7, -7, 27, np.zeros(1, dtype=np.uint64))
+    assert neg.avg_go_int == -2  # Go: -7 / 3 == -2 (truncation toward zero)

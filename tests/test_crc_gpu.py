@@ -95,6 +95,30 @@ def test_hash32_many_small_writes_and_flush_boundary(ctx):
     h.close()
 
 
+def test_hash32_read_from(ctx):
+    import io
+    d = bytes(oracle.payload((20 << 20) + 999))
+    h = crc32c.New(ctx)
+    assert h.ReadFrom(io.BytesIO(d)) == len(d)          # readinto path, crosses the staging buffer twice
+    assert h.Sum32() == oracle.crc32c(d)
+
+    class Dribble:                                       # transport that returns short reads, read() only
+        def __init__(self, data):
+            self.data, self.pos = data, 0
+
+        def read(self, n):
+            n = min(n, 70001)
+            out = self.data[self.pos:self.pos + n]
+            self.pos += len(out)
+            return out
+
+    h.Reset()
+    h.Write(d[:100])
+    assert h.ReadFrom(Dribble(d[100:3_000_000])) == 3_000_000 - 100
+    assert h.Sum32() == oracle.crc32c(d[:3_000_000])
+    h.close()
+
+
 def _batch_check(ctx, host, d, off, ln):
     want, _, _ = oracle.verify_objects(host, off, ln, threads=8)
     got, ok, nbad = crc32c.VerifyObjectsDevice(d, off, ln, want, ctx=ctx)

@@ -10,8 +10,9 @@ no data-path collective — only the timing barrier and the max-over-ranks reduc
 `value`   : whole-job GB/s with inputs resident in HBM, timed with CUDA events on the library's stream.
 `e2e`     : the same batch through the host-buffer entry point b200_crc32c_batch_host (what a Go caller's
             VerifyObjects([]buf, []want) binds): pinned host buffers, H2D copies inside the timed region.
-`roofline`: row kernel algorithmic bytes (1 byte read per byte hashed) / its mean CUDA-event duration over
-            the timed steps, against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
+`roofline`: the dominant kernel (crc_fold_kernel; every segment of this config is a full one, so the row
+            kernel does not run): algorithmic bytes (1 byte read per byte hashed) / its mean CUDA-event
+            duration over the timed steps, against the measured HBM copy bandwidth in MEASURED_PEAKS.json.
 `cpu_baseline`: the oracle's SSE4.2 three-lane CRC-32C (C restatement of Go's amd64 path; Go is not installed
             on the box) on the box's host cores, over the same objects.
 --impl reference times that CPU implementation alone, all host threads, same config/metric.
@@ -253,7 +254,7 @@ def run_b200(args):
         traffic = None
         try:
             with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-                traffic = json.load(f).get("crc_rows_kernel_dram_bytes_per_launch")
+                traffic = json.load(f).get("crc_fold_kernel_dram_bytes_per_launch")
         except Exception:
             pass
         line = {"metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
@@ -267,7 +268,7 @@ def run_b200(args):
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                              "frac": round(achieved / peak, 4), "traffic": traffic,
-                             "frac_of_nominal_8TBps": round(achieved / 8000.0, 4), "kernel": "crc_rows_kernel",
+                             "frac_of_nominal_8TBps": round(achieved / 8000.0, 4), "kernel": "crc_fold_kernel",
                              "kernel_ms": round(rows_ms, 5), "algorithmic_bytes_per_launch": total,
                              "peak_source": peak_src + " — of measured"}}
         if world == 1:

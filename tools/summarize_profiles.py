@@ -2,8 +2,8 @@
 
 usage: python tools/summarize_profiles.py r01
 Reads  gpurun_out/launches.csv (ncu --metrics gpu__time_duration.sum launch list of `bench.py --steps 20 --warmup 3`)
-       gpurun_out/prof_rows.ncu-rep (ncu --set full of crc_rows_kernel, same command)
-Writes profiles/<round>_launches.csv, profiles/<round>_rows_kernel_metrics.csv, profiles/<round>_summary.md,
+       gpurun_out/prof_top.ncu-rep (ncu --set full of the dominant kernel, same command)
+Writes profiles/<round>_launches.csv, profiles/<round>_<kernel>_metrics.csv, profiles/<round>_summary.md,
        profiles/traffic.json (dram bytes per launch of the row kernel, read by bench.py for roofline.traffic)
 """
 import collections
@@ -26,17 +26,17 @@ rows = list(csv.DictReader(io.StringIO("".join(lines))))
 with open(os.path.join(dst, f"{rnd}_launches.csv"), "w") as f:
     f.write("id,kernel,grid,block,duration_ns\n")
     for r in rows:
-        name = r["Kernel Name"].split("(")[0].split("::")[-1]
+        name = r["Kernel Name"].split("(")[0].split("::")[-1].split("<")[0]
         f.write(f'{r["ID"]},{name},"{r["Grid Size"]}","{r["Block Size"]}",{r["Metric Value"]}\n')
 tot = collections.defaultdict(lambda: [0, 0.0])
 for r in rows:
-    name = r["Kernel Name"].split("(")[0].split("::")[-1]
+    name = r["Kernel Name"].split("(")[0].split("::")[-1].split("<")[0]
     tot[name][0] += 1
     tot[name][1] += float(r["Metric Value"])
 all_ns = sum(v[1] for v in tot.values())
 
 # ---- full-set metrics of the row kernel -----------------------------------------------------------------
-raw = subprocess.run(["ncu", "-i", os.path.join(src, "prof_rows.ncu-rep"), "--page", "raw", "--csv"],
+raw = subprocess.run(["ncu", "-i", os.path.join(src, "prof_top.ncu-rep"), "--page", "raw", "--csv"],
                      capture_output=True, text=True).stdout
 rr = list(csv.reader(io.StringIO(raw)))
 hdr, units, vals = rr[0], rr[1], rr[2:]
@@ -48,7 +48,8 @@ keep = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__inst_executed.sum", "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
         "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic",
         "sm__cycles_elapsed.avg", "sm__cycles_elapsed.avg.per_second"]
-with open(os.path.join(dst, f"{rnd}_rows_kernel_metrics.csv"), "w") as f:
+top = max(tot.items(), key=lambda kv: kv[1][1])[0]
+with open(os.path.join(dst, f"{rnd}_{top}_metrics.csv"), "w") as f:
     f.write("metric,unit," + ",".join(f"launch{i}" for i in range(len(vals))) + "\n")
     for k in keep:
         if k in hdr:
@@ -64,8 +65,8 @@ def metric(k, row=0):
 
 
 traffic = sum(metric("dram__bytes_read.sum", r) + metric("dram__bytes_write.sum", r) for r in range(len(vals))) / len(vals)
-json.dump({"crc_rows_kernel_dram_bytes_per_launch": int(traffic), "round": rnd,
-           "source": f"profiles/{rnd}_rows_kernel_metrics.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)"},
+json.dump({f"{top}_dram_bytes_per_launch": int(traffic), "round": rnd,
+           "source": f"profiles/{rnd}_{top}_metrics.csv (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)"},
           open(os.path.join(dst, "traffic.json"), "w"), indent=1)
 
 with open(os.path.join(dst, f"{rnd}_summary.md"), "w") as f:
@@ -75,10 +76,10 @@ with open(os.path.join(dst, f"{rnd}_summary.md"), "w") as f:
     f.write("| kernel | launches | total ms | share |\n|---|---:|---:|---:|\n")
     for k, (n, ns) in sorted(tot.items(), key=lambda kv: -kv[1][1]):
         f.write(f"| {k} | {n} | {ns / 1e6:.3f} | {100 * ns / all_ns:.1f} % |\n")
-    step = tot["crc_rows_kernel"][1] / tot["crc_rows_kernel"][0] + tot["crc_finalize_kernel"][1] / tot["crc_finalize_kernel"][0]
-    f.write(f"\nPer step (one row kernel + one finalize kernel): row kernel share "
-            f"{100 * tot['crc_rows_kernel'][1] / tot['crc_rows_kernel'][0] / step:.1f} % of the step's kernel time.\n\n")
-    f.write("Row kernel, `ncu --set full --clock-control none` (2 launches, mean):\n\n")
+    step = sum(v[1] / v[0] for k, v in tot.items() if k.startswith("crc_"))
+    f.write(f"\nPer step (one {top} + one crc_finalize_kernel): {top} share "
+            f"{100 * tot[top][1] / tot[top][0] / step:.1f} % of the step's kernel time.\n\n")
+    f.write(f"{top}, `ncu --set full --clock-control none` (first of {len(vals)} launches):\n\n")
     f.write("| metric | value |\n|---|---:|\n")
     for k in keep:
         if k in hdr:

@@ -173,17 +173,33 @@ uint32_t env_rows_per_seg() {
     return (uint32_t)v;
 }
 
-// Segment length: a power of two number of rows such that every warp of the persistent grid gets
-// several segments, but segments stay long enough to amortise the per-segment column fold.
-uint32_t choose_rows_per_seg(uint64_t total_rows, int grid) {
+// Segment length (rows, a power of two).  Full segments of >= 256 rows are folded by K2 (8 warps per SM); we
+// want the longest segment that still gives every K2 warp ~6 (at least 2) of them and leaves at most ~10 % of
+// the rows in partial segments.  Inputs too small or too ragged for that use K1's finer grain (32 warps per SM).
+template <typename RowsOf>
+uint32_t plan_rows_per_seg(size_t nobj, RowsOf rows_of, int grid) {
     if (uint32_t e = env_rows_per_seg()) return e;
-    // large inputs: ~6 segments per warp of the fold kernel (16 warps/SM), segments of up to 1024 rows so the
-    // per-segment epilogue stays a few percent; small inputs fall back to the row kernel's finer grain
-    uint64_t target = total_rows / ((uint64_t)grid * kFoldWarps * 6);
-    if (target < kFoldMinRows || !fold_enabled(kFoldMinRows)) target = total_rows / ((uint64_t)grid * kRowsWarps * 6);
+    uint64_t total = 0;
+    for (size_t i = 0; i < nobj; i++) total += rows_of(i);
+    if (fold_enabled(kMaxRowsPerSeg)) {
+        const uint64_t warps = (uint64_t)grid * kFoldWarps;
+        for (int pass = 0; pass < 2; pass++) {
+            const uint64_t want = warps * (pass == 0 ? 6 : 2);
+            for (uint32_t r = kMaxRowsPerSeg; r >= 256; r /= 2) {
+                uint64_t full = 0;
+                for (size_t i = 0; i < nobj; i++) full += rows_of(i) / r;
+                if (full >= want && full * r * 10 >= total * 9) return r;
+            }
+        }
+    }
+    uint64_t target = total / ((uint64_t)grid * kRowsWarps * 6);
     uint32_t r = 16;
-    while ((uint64_t)r * 2 <= target && r < kMaxRowsPerSeg) r *= 2;
+    while ((uint64_t)r * 2 <= target && r < 1024) r *= 2;
     return r;
+}
+
+uint32_t choose_rows_per_seg(uint64_t total_rows, int grid) {  // one object
+    return plan_rows_per_seg(1, [&](size_t) { return total_rows; }, grid);
 }
 
 int ensure_seg_raw(DevState* d, size_t ntasks) {
@@ -640,9 +656,7 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     b->d = d;
     b->nobj = nobj;
     // plan: the arena base is 16-byte aligned, so the cut of object i depends on off[i] only
-    uint64_t total_rows = 0;
-    for (size_t i = 0; i < nobj; i++) total_rows += cut_object(off[i], len[i]).rows;
-    uint32_t rps = choose_rows_per_seg(total_rows, d->grid);
+    uint32_t rps = plan_rows_per_seg(nobj, [&](size_t i) { return cut_object(off[i], len[i]).rows; }, d->grid);
     std::vector<uint32_t> seg_start(nobj + 1);
     for (;;) {
         uint64_t t = 0;
@@ -850,7 +864,6 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
         cudaSetDevice(dev);
         if ((rc = hs.reserve(cnt))) break;
         // plan (the device slab is 256-byte aligned, so cuts depend on the offsets only)
-        uint64_t total_rows = 0;
         used = 0;
         for (size_t k = 0; k < cnt; k++) {
             size_t start = (used + 15) & ~(size_t)15;
@@ -858,9 +871,8 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
             hs.h_len[k] = len[first + k];
             if (want) hs.h_want[k] = want[first + k];
             used = start + len[first + k];
-            total_rows += cut_object(start, len[first + k]).rows;
         }
-        uint32_t rps = choose_rows_per_seg(total_rows, d->grid);
+        uint32_t rps = plan_rows_per_seg(cnt, [&](size_t k) { return cut_object(hs.h_off[k], hs.h_len[k]).rows; }, d->grid);
         uint64_t t = 0, tfull = 0;
         for (size_t k = 0; k < cnt; k++) {
             hs.h_seg[k] = (uint32_t)t;

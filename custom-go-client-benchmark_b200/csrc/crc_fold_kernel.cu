@@ -162,7 +162,7 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
                 __syncwarp();                 // ... and everybody else's
                 const uint32_t a = my_row + cbuf * kWarpStageBytes;
 #pragma unroll 1
-                for (uint32_t h = 0; h < LANE_BYTES / 256; h++) {
+                for (int h = 0; h < LANE_BYTES / 256; h++) {
                     FOLD_STAGE(0, a + h * 256)
                     FOLD_STAGE(32, a + h * 256 + 128)
                 }

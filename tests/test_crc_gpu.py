@@ -209,6 +209,50 @@ def test_rows_per_segment_is_not_a_semantic_knob(rps, arena):
     assert "ok" in out
 
 
+@pytest.mark.parametrize("rps", ["128", "256", "512", "2048"])
+def test_fold_and_row_kernels_mix_on_ragged_objects(rps):
+    """Forces a segment length so that every object is part full segments (fold kernel) and part partial
+    segment (row kernel), with unaligned starts; all must agree with the oracle."""
+    import subprocess, sys
+    code = (
+        "import importlib, numpy as np, oracle\n"
+        "pkg = importlib.import_module('custom-go-client-benchmark_b200')\n"
+        "c = pkg.crc32c.Context([0])\n"
+        "h = oracle.payload((96 << 20) + 64)\n"
+        "d = c.alloc_device(h.size); c.h2d(d, h)\n"
+        "rng = np.random.default_rng(5)\n"
+        "n = 120\n"
+        "ln = rng.integers(50_000, 6_000_000, size=n).astype(np.uint64)\n"
+        "ln[:6] = [65536, 65536 * 2 + 16, 1 << 20, (1 << 20) + 511, (2 << 20) + 513, 4 << 20]\n"
+        "off = rng.integers(0, (96 << 20) - 6_000_000, size=n).astype(np.uint64)\n"
+        "want, _, _ = oracle.verify_objects(h, off, ln, threads=8)\n"
+        "got, ok, nbad = pkg.crc32c.VerifyObjectsDevice(d, off, ln, want, ctx=c)\n"
+        "assert nbad == 0 and (got == want).all(), np.nonzero(got != want)\n"
+        "for s, l in [(0, 96 << 20), (3, (96 << 20) - 7), (17, 5_000_000)]:\n"
+        "    assert pkg.crc32c.UpdateDevice(0x55AA55AA, d + s, l, c) == oracle.crc32c(h[s:s + l], 0x55AA55AA)\n"
+        "print('ok')\n")
+    env = dict(os.environ, B200_ROWS_PER_SEG=rps)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.check_output([sys.executable, "-c", code], env=env, cwd=root, text=True)
+    assert "ok" in out
+
+
+def test_row_kernel_alone_matches(arena):
+    """B200_NO_FOLD=1 keeps everything on the row kernel (the A/B switch used in DESIGN.md)."""
+    import subprocess, sys
+    code = (
+        "import importlib, numpy as np, oracle\n"
+        "pkg = importlib.import_module('custom-go-client-benchmark_b200')\n"
+        "c = pkg.crc32c.Context([0])\n"
+        "h = oracle.payload(40_000_001)\n"
+        "d = c.alloc_device(h.size); c.h2d(d, h)\n"
+        "assert pkg.crc32c.UpdateDevice(0, d + 1, 40_000_000, c) == oracle.crc32c(h[1:])\n"
+        "print('ok')\n")
+    env = dict(os.environ, B200_NO_FOLD="1", B200_ROWS_PER_SEG="1024")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    assert "ok" in subprocess.check_output([sys.executable, "-c", code], env=env, cwd=root, text=True)
+
+
 def test_verify_objects_host_buffers(ctx):
     rng = np.random.default_rng(3)
     sizes = [0, 1, 100, 4096, 2 << 20, 12345, (2 << 20) + 1, 40 << 20, 7]

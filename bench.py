@@ -110,6 +110,30 @@ class ClockSampler:
                 "samples": len(self.samples)}
 
 
+def bind_to_gpu_numa_node(index: int):
+    """Pin this process to the CPUs local to its GPU before any pinned memory is allocated, so that the
+    pinned host buffers of the e2e path land on the GPU's own NUMA node (8 ranks streaming 8 GiB each would
+    otherwise cross sockets).  Best effort: returns a description for the JSON line."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(index)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        path = f"/sys/bus/pci/devices/{bus[-12:].lower()}/local_cpulist"
+        cpus = set()
+        for part in open(path).read().strip().split(","):
+            a, _, b = part.partition("-")
+            cpus.update(range(int(a), int(b or a) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return f"{len(cpus)} cpus local to {bus}"
+    except Exception as e:
+        return f"not bound ({type(e).__name__})"
+    return "not bound"
+
+
 def dist_setup(n_gpus):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -182,6 +206,7 @@ def run_reference(args):
 
 def run_b200(args):
     rank, world, local, dist = dist_setup(args.gpus)
+    affinity = bind_to_gpu_numa_node(local) if world > 1 else "single rank: not bound"
     pkg = importlib.import_module("custom-go-client-benchmark_b200")
     crc32c = pkg.crc32c
     ctx = crc32c.Context([local])
@@ -264,7 +289,7 @@ def run_b200(args):
                 "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": total,
                         "d2h_bytes_per_step": NOBJ * 5 + 8, "steps": e2e_steps, "ms_per_step": round(e2e_ms, 3),
                         "api": "b200_crc32c_batch_host (VerifyObjects on pinned host buffers)",
-                        "pcie_note": "PCIe Gen5 x16 bound (~64 GB/s raw per direction)"},
+                        "pcie_note": "PCIe Gen5 x16 bound (~64 GB/s raw per direction)", "cpu_affinity": affinity},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                              "frac": round(achieved / peak, 4), "traffic": traffic,

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(HERE)
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libb200crc.so")
-SOURCES = ["api.cu", "crc_kernels.cu", "lat_kernels.cu", "tables.cu", "noalloc.cu", "crc_fold_kernel.cu"]
+SOURCES = ["api.cu", "crc_kernels.cu", "lat_kernels.cu", "tables.cu", "noalloc.cu", "crc_fold_kernel.cu", "text_kernels.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-Wall,-Wextra,-Wno-unused-parameter", "-shared", "-cudart", "static"]
 

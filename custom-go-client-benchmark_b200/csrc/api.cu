@@ -1194,3 +1194,88 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
 }
 
 }  // extern "C"
+
+// ---- latency text codec + float64 histogram ----------------------------------------------------------------
+
+extern "C" {
+
+int b200_parse_latency_text(b200_ctx* ctx, int dev, const void* d_text, size_t nbytes, double* d_values,
+                            uint8_t* d_status, size_t max_lines, uint64_t* nlines, uint64_t* first_bad_line,
+                            uint64_t* nbad, uint64_t* ninexact) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || (nbytes && !d_text) || (max_lines && !d_values)) return fail(B200_ERR_INVALID, "b200_parse_latency_text");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    const size_t ntiles = text_tiles(nbytes);
+    unsigned long long *tiles = nullptr, *summary = nullptr;
+    CU(cudaMalloc(&tiles, (ntiles + 1) * sizeof(unsigned long long)));
+    cudaError_t e = cudaMalloc(&summary, 3 * sizeof(unsigned long long));
+    if (e == cudaSuccess)
+        e = launch_text_parse((const unsigned char*)d_text, nbytes, d_values, d_status, max_lines, tiles, summary, d->stream);
+    unsigned long long total = 0, sum3[3] = {~0ull, 0, 0};
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&total, tiles + ntiles, sizeof total, cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sum3, summary, sizeof sum3, cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
+    cudaFree(tiles);
+    cudaFree(summary);
+    if (e != cudaSuccess) return fail_cuda(e, "b200_parse_latency_text");
+    if (nlines) *nlines = total;
+    if (first_bad_line) *first_bad_line = sum3[0];
+    if (nbad) *nbad = sum3[1];
+    if (ninexact) *ninexact = sum3[2];
+    if (total > max_lines) return fail(B200_ERR_TOO_LARGE, "b200_parse_latency_text: more lines than max_lines");
+    return 0;
+}
+
+int b200_hist_fixed_f64(b200_ctx* ctx, int dev, const double* d_values, size_t n, const double* edges, int nedges,
+                        int mode, uint64_t* counts, uint64_t* dropped_below, uint64_t* dropped_above,
+                        uint64_t* nan_count, double* sum_hi, double* sum_lo) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !edges || !counts || (n && !d_values) || (mode != B200_HIST_NUMPY && mode != B200_HIST_OPENCENSUS) ||
+        nedges < (mode == B200_HIST_NUMPY ? 2 : 1) || nedges > B200_HIST_MAX_EDGES)
+        return fail(B200_ERR_INVALID, "b200_hist_fixed_f64");
+    for (int i = 0; i < nedges; i++)
+        if (edges[i] != edges[i] || (i && !(edges[i] > edges[i - 1])))
+            return fail(B200_ERR_INVALID, "b200_hist_fixed_f64: edges must be ascending");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    const size_t nsum = 4 + 2 * (size_t)256 * hist_f64_grid();
+    double* d_sums = nullptr;
+    CU(cudaMalloc(&d_sums, nsum * sizeof(double)));
+    std::vector<double> sums(nsum);
+    unsigned long long c[kMaxThresholds + 1];
+    cudaError_t e = launch_hist_f64(d_values, n, edges, nedges, mode, d->lat.d_counts, d_sums, d->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sums.data(), d_sums, nsum * sizeof(double), cudaMemcpyDeviceToHost, d->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
+    cudaFree(d_sums);
+    if (e != cudaSuccess) return fail_cuda(e, "b200_hist_fixed_f64");
+    uint64_t below = 0, above = 0;
+    if (mode == B200_HIST_NUMPY) {
+        for (int i = 0; i < nedges - 1; i++) counts[i] = c[i + 1];
+        below = c[0];
+        above = c[nedges];
+    } else {
+        for (int i = 0; i <= nedges; i++) counts[i] = c[i];
+    }
+    if (dropped_below) *dropped_below = below;
+    if (dropped_above) *dropped_above = above;
+    if (nan_count) {
+        unsigned long long nn;
+        memcpy(&nn, &sums[2], sizeof nn);
+        *nan_count = nn;
+    }
+    // fold the per-thread double-double partial sums in a fixed order (two-sum), so the result is reproducible
+    double hi = 0, lo = 0;
+    for (size_t i = 4; i + 1 < nsum; i += 2) {
+        double v = sums[i], s = hi + v, bb = s - hi;
+        lo += (hi - (s - bb)) + (v - bb) + sums[i + 1];
+        hi = s;
+    }
+    double s = hi + lo;
+    if (sum_hi) *sum_hi = s;
+    if (sum_lo) *sum_lo = lo - (s - hi);
+    return 0;
+}
+
+}  // extern "C"

@@ -57,6 +57,16 @@ cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned lon
                               int nk, const LatScratch& s, cudaStream_t stream);
 cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch& s, cudaStream_t stream);
 
+// Latency text codec + float64 histogram (text_kernels.cu)
+size_t text_tiles(size_t nbytes);
+cudaError_t launch_text_parse(const unsigned char* d_text, size_t n, double* d_values, unsigned char* d_status,
+                              size_t max_lines, unsigned long long* d_tiles /* text_tiles(n)+1 */,
+                              unsigned long long* d_summary /* [3] */, cudaStream_t stream);
+int hist_f64_grid();
+cudaError_t launch_hist_f64(const double* d_x, size_t n, const double* edges, int nedges, int mode,
+                            unsigned long long* d_counts /* kMaxThresholds+1 */,
+                            double* d_sums /* 4 + 2*256*hist_f64_grid() */, cudaStream_t stream);
+
 // Host helper: fill thresholds / LUT / magic for (edges, mode, divisor).
 int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* out);
 

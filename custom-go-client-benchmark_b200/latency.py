@@ -278,3 +278,90 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
     p20, p50, p90, p99 = select_kth(d_samples_ns, n, divisor, ks, ctx=ctx, dev=dev, group=group,
                                     reduce_device=reduce_device, n_global=size, bounds_ns=(lo, hi))
     return Percentiles(dist_.avg_go_int, p20, p50, p90, p99, dist_.min, dist_.max)
+
+
+# ---- latency text files (execute_pb.sh:4,8 -> README.md:15-35) ------------------------------------------------
+
+@dataclass
+class ParsedLatencyFile:
+    """Result of README.md:25-28's loop over one latency file."""
+    nlines: int
+    first_bad_line: Optional[int]   # where `float(line)` raises ValueError in the reference script
+    nbad: int
+    ninexact: int                   # lines outside the exactly-rounded domain (never produced by the pipeline)
+    d_values: int                   # device float64 array, nlines entries
+    d_status: int                   # device uint8 array
+
+
+def go_duration_line(ns: int) -> str:
+    """What one line of grpc_N.txt looks like: Go's Duration.String() after `tr 'ms' ' '` (execute_pb.sh:4,8)."""
+    def fmt(v: int, unit_digits: int) -> str:
+        whole, frac = divmod(v, 10 ** unit_digits)
+        s = str(whole)
+        if frac:
+            s += "." + str(frac).rjust(unit_digits, "0").rstrip("0")
+        return s
+    neg, u = ns < 0, abs(ns)
+    if u == 0:
+        out = "0s"
+    elif u < 1_000:
+        out = f"{u}ns"
+    elif u < 1_000_000:
+        out = fmt(u, 3) + "µs"
+    elif u < 1_000_000_000:
+        out = fmt(u, 6) + "ms"
+    else:
+        h, rem = divmod(u, 3_600_000_000_000)
+        m, rem = divmod(rem, 60_000_000_000)
+        sec = fmt(rem, 9) + "s"
+        out = (f"{h}h{m}m" if h else (f"{m}m" if m else "")) + sec
+    out = ("-" if neg else "") + out
+    return out.replace("m", " ").replace("s", " ")
+
+
+def parse_latency_text(d_text: int, nbytes: int, max_lines: int, ctx: Optional[Context] = None,
+                       dev: Optional[int] = None) -> ParsedLatencyFile:
+    """README.md:25-28 on the device.  The caller frees d_values / d_status with ctx.free_device."""
+    ctx = ctx or default_context()
+    d_values = ctx.alloc_device(max(max_lines, 1) * 8, dev)
+    d_status = ctx.alloc_device(max(max_lines, 1), dev)
+    nl, fb, nb, ni = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_uint64()
+    try:
+        check(ctx._L.b200_parse_latency_text(ctx._h, ctx._dev(dev), d_text, nbytes, d_values, d_status, max_lines,
+                                             C.byref(nl), C.byref(fb), C.byref(nb), C.byref(ni)))
+    except Exception:
+        ctx.free_device(d_values, dev)
+        ctx.free_device(d_status, dev)
+        raise
+    first = None if fb.value == (1 << 64) - 1 else int(fb.value)
+    return ParsedLatencyFile(int(nl.value), first, int(nb.value), int(ni.value), d_values, d_status)
+
+
+@dataclass
+class FloatHistogram:
+    counts: np.ndarray
+    dropped_below: int
+    dropped_above: int
+    nan_count: int
+    sum: float           # correctly rounded sum of the samples (double-double accumulation)
+    n: int
+
+    @property
+    def mean(self) -> float:
+        """README.md:30 `sum(x) / len(x)`."""
+        return self.sum / self.n
+
+
+def hist_fixed_f64(d_values: int, n: int, edges, mode: int = HIST_NUMPY, ctx: Optional[Context] = None,
+                   dev: Optional[int] = None) -> FloatHistogram:
+    """README.md:32 `plt.hist(x, bins)` (numpy.histogram) or the OpenCensus bucket rule on float64 samples."""
+    ctx = ctx or default_context()
+    edges = np.ascontiguousarray(edges, dtype=np.float64)
+    nb = edges.size - 1 if mode == HIST_NUMPY else edges.size + 1
+    counts = np.zeros(nb, dtype=np.uint64)
+    below, above, nans = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    hi, lo = C.c_double(), C.c_double()
+    check(ctx._L.b200_hist_fixed_f64(ctx._h, ctx._dev(dev), d_values, n, edges.ctypes.data, edges.size, mode,
+                                     counts.ctypes.data, C.byref(below), C.byref(above), C.byref(nans), C.byref(hi),
+                                     C.byref(lo)))
+    return FloatHistogram(counts, int(below.value), int(above.value), int(nans.value), hi.value + lo.value, n)

@@ -185,6 +185,26 @@ int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int6
 int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, uint64_t key_base, int shift,
                      int top, int nk, const uint64_t* prefix, uint64_t* counts);
 
+/* ---- latency text files --------------------------------------------------------------------------------- */
+
+/* README.md:25-28 `for line in f: x.append(float(line))` over the file execute_pb.sh:4,8 writes (one Go
+ * Duration.String() per line with 'm' and 's' replaced by spaces).  d_text: nbytes of text on the device.
+ * d_values[i] = float(line i) for the first max_lines lines (device array); d_status[i] (device, may be NULL):
+ * 0 parsed, 1 ValueError in Python (empty line, status line, "850µ " ...), 2 valid syntax but outside the
+ * exactly-rounded domain (> 15 significant digits or |decimal exponent| > 22; never produced by the reference
+ * pipeline).  *first_bad_line = index of the first line with status != 0 — where the reference script raises —
+ * or UINT64_MAX.  Lines follow Python's universal newlines.  B200_ERR_TOO_LARGE if there are more than
+ * max_lines lines (*nlines is still set). */
+int b200_parse_latency_text(b200_ctx* ctx, int dev, const void* d_text, size_t nbytes, double* d_values,
+                            uint8_t* d_status, size_t max_lines, uint64_t* nlines, uint64_t* first_bad_line,
+                            uint64_t* nbad, uint64_t* ninexact);
+/* README.md:30,32 on the parsed floats: numpy.histogram / OpenCensus buckets on float64 samples (same count
+ * layout as b200_hist_fixed), NaNs counted apart, and the sum of the samples as an unevaluated double-double
+ * (sum_hi + sum_lo) for mean = sum/len.  All outputs are HOST pointers; all but counts may be NULL. */
+int b200_hist_fixed_f64(b200_ctx* ctx, int dev, const double* d_values, size_t n, const double* edges, int nedges,
+                        int mode, uint64_t* counts, uint64_t* dropped_below, uint64_t* dropped_above,
+                        uint64_t* nan_count, double* sum_hi, double* sum_lo);
+
 #ifdef __cplusplus
 }
 #endif

@@ -24,6 +24,7 @@ namespace {
 constexpr int kHistThreads = 256;
 constexpr int kHistWarps = kHistThreads / 32;
 constexpr int kRadixThreads = 512;
+constexpr int kSlowQueue = 128;  // parked samples per warp; overflow falls back to the divergent path
 
 struct U128 {
     unsigned long long lo, hi;
@@ -77,7 +78,13 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom) {
     extern __shared__ __align__(16) unsigned char sm[];
     __shared__ HistParams P;
+    // Samples that need the generic path (>= 2^32 ns, negative, or a cell holding several thresholds) are rare
+    // but would drag their whole warp through ~140 divergent instructions; they are parked in a per-warp queue
+    // and processed 32 at a time instead.
+    __shared__ long long slow_q[kHistWarps][kSlowQueue];
+    __shared__ unsigned slow_n[kHistWarps];
     unsigned* tbl = reinterpret_cast<unsigned*>(sm);  // [warp][bin][lane] private counters
+    if (threadIdx.x < kHistWarps) slow_n[threadIdx.x] = 0;
     {
         const unsigned* src = reinterpret_cast<const unsigned*>(Pg);
         unsigned* dst = reinterpret_cast<unsigned*>(&P);
@@ -106,15 +113,28 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             else add128(m.sum, q, 0);
         }
     };
+    auto park = [&](long long v) {
+        const unsigned at = atomicAdd(&slow_n[warp], 1u);
+        if (at < kSlowQueue) slow_q[warp][at] = v;
+        else slow(v);  // queue full: take the hit now
+    };
+    auto drain = [&]() {
+        __syncwarp();
+        const unsigned cnt = min(slow_n[warp], (unsigned)kSlowQueue);
+        for (unsigned k = lane; k < cnt; k += 32) slow(slow_q[warp][k]);
+        __syncwarp();
+        if (lane == 0) slow_n[warp] = 0;
+        __syncwarp();
+    };
     // fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), everything in 32-bit arithmetic
     auto one = [&](long long v) {
         const unsigned long long uv = (unsigned long long)v;
-        if (uv >> 32) { slow(v); return; }
+        if (uv >> 32) { park(v); return; }
         const unsigned u = (unsigned)uv;
         const int e = 31 - __clz((int)(u | 1));
         const unsigned idx = u < 32 ? u : (unsigned)((e - 4) * 32) + ((u >> (e - 5)) & 31);
         const unsigned cell = P.lut[idx];
-        if ((cell & 0xFF) > 1) { slow(v); return; }  // several thresholds inside this cell: rare
+        if ((cell & 0xFF) > 1) { park(v); return; }  // several thresholds inside this cell: rare
         const unsigned c = (cell >> 8) + (u > P.cell_gt[idx] ? 1u : 0u);
         mine[c * 32]++;
         if (MOMENTS) {
@@ -141,16 +161,21 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
     const size_t npairs = (n - head) / 2;
     size_t i = tid;
-    for (; i + 3 * nthreads < npairs; i += 4 * nthreads) {  // four independent 128-bit loads in flight
+    // The trip count of this loop is the same for all lanes of a warp (it is decided by the warp's LAST lane),
+    // because drain() synchronises the warp.
+    for (; (i - lane) + 31 + 3 * nthreads < npairs; i += 4 * nthreads) {  // four independent 128-bit loads in flight
         longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads), c = __ldg(x2 + i + 2 * nthreads),
                   d = __ldg(x2 + i + 3 * nthreads);
         one(a.x); one(a.y); one(b.x); one(b.y); one(c.x); one(c.y); one(d.x); one(d.y);
+        __syncwarp();
+        if (slow_n[warp] >= kSlowQueue / 2) drain();  // warp-uniform: everyone reads the same counter
     }
     for (; i < npairs; i += nthreads) {
         longlong2 a = __ldg(x2 + i);
         one(a.x); one(a.y);
     }
     if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
+    drain();
 
     __syncthreads();
     for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
@@ -306,7 +331,7 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: 4 by registers, fewer when the private counter tables are large
-    int per_sm = (int)std::min<size_t>(4, (200 * 1024) / (smem + sizeof(HistParams) + 1024));
+    int per_sm = (int)std::min<size_t>(4, (220 * 1024) / (smem + sizeof(HistParams) + kHistWarps * kSlowQueue * 8 + 1024));
     if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);

@@ -228,21 +228,33 @@ def New(ctx: Optional[Context] = None, dev: Optional[int] = None) -> Hash32:
     return Hash32(ctx, dev)
 
 
-def VerifyObjects(bufs: Sequence, want: Optional[Sequence[int]], ctx: Optional[Context] = None,
+def VerifyObjects(bufs, want: Optional[Sequence[int]], ctx: Optional[Context] = None,
                   dev: Optional[int] = None):
-    """VerifyObjects([]buf, []want) -> (bad []int, got []uint32).  Host buffers; flags, never aborts."""
+    """VerifyObjects([]buf, []want) -> (bad []int, got []uint32).  Host buffers; flags, never aborts.
+
+    bufs is a sequence of bytes-like objects, or a 2-D uint8 numpy array whose rows are the objects (the shape
+    of the read loop's per-worker buffers, main.go:125,200) — that form needs no per-object Python work."""
     ctx = ctx or default_context()
-    arrs = [_as_bytes(b) for b in bufs]
-    n = len(arrs)
-    ptrs = (C.c_void_p * max(n, 1))(*[_addr(a) for a in arrs])
-    lens = np.array([a.size for a in arrs], dtype=np.uint64)
+    if isinstance(bufs, np.ndarray) and bufs.ndim == 2 and bufs.dtype == np.uint8 and bufs.strides[1] == 1:
+        n = bufs.shape[0]
+        base = bufs.__array_interface__["data"][0]
+        ptrs = (base + np.arange(n, dtype=np.uint64) * np.uint64(bufs.strides[0])).astype(np.uint64)
+        lens = np.full(n, bufs.shape[1], dtype=np.uint64)
+        ptr_arg, keep = ptrs.ctypes.data, (bufs, ptrs)
+    else:
+        arrs = [_as_bytes(b) for b in bufs]
+        n = len(arrs)
+        ptr_arr = (C.c_void_p * max(n, 1))(*[_addr(a) for a in arrs])
+        lens = np.array([a.size for a in arrs], dtype=np.uint64)
+        ptr_arg, keep = ptr_arr, arrs
     w = None if want is None else np.ascontiguousarray(want, dtype=np.uint32)
     got = np.zeros(n, dtype=np.uint32)
     ok = np.zeros(n, dtype=np.uint8)
     nbad = C.c_uint64()
-    check(ctx._L.b200_crc32c_batch_host(ctx._h, ctx._dev(dev), ptrs, lens.ctypes.data, n,
+    check(ctx._L.b200_crc32c_batch_host(ctx._h, ctx._dev(dev), ptr_arg, lens.ctypes.data, n,
                                         None if w is None else w.ctypes.data, got.ctypes.data, ok.ctypes.data,
                                         C.byref(nbad)))
+    del keep
     bad = [int(i) for i in np.nonzero(ok == 0)[0]]
     assert len(bad) == nbad.value
     return bad, got

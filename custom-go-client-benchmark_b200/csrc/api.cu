@@ -616,7 +616,7 @@ struct b200_batch {
     uint8_t* d_ok = nullptr;
     unsigned long long* d_nbad = nullptr;
     const uint32_t* adv_seg = nullptr;
-    uint32_t ntasks = 0, rows_per_seg = 0, nfull = 0;
+    uint32_t ntasks = 0, rows_per_seg = 0, nfull = 0, small_objects = 0;
     static constexpr int kRing = 256;  // per-run CUDA event triples: begin, row kernel end, all end
     cudaEvent_t ev[kRing][3] = {};
     uint64_t runs = 0, timed_from = 0;
@@ -670,7 +670,13 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     }
     b->rows_per_seg = rps;
     b->ntasks = seg_start[nobj];
-    for (size_t i = 0; i < nobj; i++) b->nfull += (uint32_t)(cut_object(off[i], len[i]).rows / rps);
+    uint64_t max_full = 0;
+    for (size_t i = 0; i < nobj; i++) {
+        const uint64_t f = cut_object(off[i], len[i]).rows / rps;
+        b->nfull += (uint32_t)f;
+        max_full = std::max(max_full, f);
+    }
+    b->small_objects = (nobj >= 1024 && max_full <= 16) ? 1 : 0;
     int rc = get_adv_seg(d, rps, &b->adv_seg);
     auto dev_alloc = [&](void** p, size_t bytes) -> int {
         if (rc) return rc;
@@ -728,6 +734,7 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     a.ntasks = b->ntasks;
     a.nfull_tasks = b->nfull;
     a.npartial_tasks = b->ntasks - b->nfull;
+    a.small_objects = b->small_objects;
     a.rows_per_seg = b->rows_per_seg;
     a.init_crc = 0;
     cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];

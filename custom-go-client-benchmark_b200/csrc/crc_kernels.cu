@@ -31,6 +31,7 @@ namespace {
 constexpr uint32_t kTabAbs = 0x10000;     // absolute shared address of table pair {0,1}; {2,3} follow at +64 KB
 constexpr uint32_t kPairStride = 65536;
 constexpr uint32_t kTabBytes = 4 * 256 * 32 * 4;
+constexpr uint32_t kAdv4Abs = 0x1000;     // absolute shared address of the 4 KB x^32 tables (inside the gap)
 
 extern __shared__ __align__(1024) uint8_t smem_raw[];
 
@@ -45,6 +46,16 @@ __device__ __forceinline__ uint32_t adv_row(uint32_t x, uint32_t lanew) {
     asm volatile("ld.shared.u32 %0, [%1+128];" : "=r"(t1) : "r"(o1));
     asm volatile("ld.shared.u32 %0, [%1+65536];" : "=r"(t2) : "r"(o2));
     asm volatile("ld.shared.u32 %0, [%1+65664];" : "=r"(t3) : "r"(o3));
+    return t0 ^ t1 ^ t2 ^ t3;
+}
+
+// v * x^32 with the 4 KB (un-replicated) tables at kAdv4Abs; used a handful of times per segment only
+__device__ __forceinline__ uint32_t mul_x32(uint32_t v) {
+    uint32_t t0, t1, t2, t3;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t0) : "r"(kAdv4Abs + ((v & 0xFF) << 2)));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t1) : "r"(kAdv4Abs + 1024 + (((v >> 8) & 0xFF) << 2)));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t2) : "r"(kAdv4Abs + 2048 + (((v >> 16) & 0xFF) << 2)));
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t3) : "r"(kAdv4Abs + 3072 + ((v >> 24) << 2)));
     return t0 ^ t1 ^ t2 ^ t3;
 }
 
@@ -69,7 +80,7 @@ __global__ void __launch_bounds__(kRowsThreads, 1)
 crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
                 const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
                 uint64_t single_off, uint64_t single_len, uint32_t skip_full, const uint32_t* __restrict__ adv_tab,
-                const uint32_t* __restrict__ col_k, uint32_t* __restrict__ seg_raw) {
+                const uint32_t* __restrict__ col_k, const uint32_t* __restrict__ adv4_tab, uint32_t* __restrict__ seg_raw) {
     // replicate the compact 4x256 table once per bank, at absolute shared address kTabAbs
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     {
@@ -82,14 +93,15 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
             asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(dst + 16 * k), "r"(val));
     }
     if (smem_base > 1024) asm volatile("trap;");  // the dynamic window must cover [0x10000, 0x30000)
+    // the x^32 slicing tables for the segment epilogue live in the otherwise unused gap below the big tables
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(kAdv4Abs + threadIdx.x * 4), "r"(__ldg(adv4_tab + threadIdx.x)));
     __syncthreads();
 
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t lane4 = lane * 4;
     const uint32_t lanew = 0x00010000u | lane4;
     const uint32_t warp = threadIdx.x >> 5;
-    const uint32_t k0 = __ldg(col_k + lane4), k1 = __ldg(col_k + lane4 + 1), k2 = __ldg(col_k + lane4 + 2),
-                   k3 = __ldg(col_k + lane4 + 3);
+    const uint32_t k3 = __ldg(col_k + lane4 + 3);  // x^(32*(128-c)) of this lane's last column c = 4*lane+3
     const uint32_t nwarps = gridDim.x * kRowsWarps;
 
     for (uint32_t task = warp * gridDim.x + blockIdx.x; task < ntasks; task += nwarps) {
@@ -135,8 +147,12 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
             B200_STEP(x)
         }
 #undef B200_STEP
-        // fold the 128 columns: column c still has to pass over 4*(128-c) bytes of its row
-        uint32_t s = gf2_mul(k0, a0) ^ gf2_mul(k1, a1) ^ gf2_mul(k2, a2) ^ gf2_mul(k3, a3);
+        // fold the 128 columns: column c still has to pass over 4*(128-c) bytes of its row.  In-lane the four
+        // columns are 4 bytes apart (three x^32 table steps), then one multiply by the lane's constant.
+        uint32_t u = mul_x32(a0) ^ a1;
+        u = mul_x32(u) ^ a2;
+        u = mul_x32(u) ^ a3;
+        uint32_t s = gf2_mul(k3, u);
 #pragma unroll
         for (int d = 16; d; d >>= 1) s ^= __shfl_xor_sync(0xFFFFFFFFu, s, d);
         if (lane == 0) seg_raw[task] = s;
@@ -203,6 +219,53 @@ crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict
         s = x;
     }
     for (; i < cut.tail; i++) s = (s >> 8) ^ __ldg(byte_tab + ((s ^ t[i]) & 0xFF));
+    const uint32_t crc = ~s;
+    got[obj] = crc;
+    const bool good = want ? (crc == want[obj]) : true;
+    ok[obj] = good ? 1 : 0;
+    if (!good) atomicAdd(nbad, 1ull);
+}
+
+// Thread-per-object variant for batches whose objects all have few segments (the many-small-objects case:
+// a CTA per object would be a million nearly empty CTAs).
+__global__ void __launch_bounds__(kFinalThreads)
+crc_finalize_small_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off,
+                          const uint64_t* __restrict__ len, const uint32_t* __restrict__ seg_start,
+                          const uint32_t* __restrict__ want, const uint32_t* __restrict__ seg_raw,
+                          const uint32_t* __restrict__ adv_seg, const uint32_t* __restrict__ xsq,
+                          const uint32_t* __restrict__ byte_tab, uint32_t rows_per_seg, uint32_t init_crc, uint32_t nobj,
+                          uint32_t* __restrict__ got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
+    __shared__ uint32_t bt[256];
+    for (int i = threadIdx.x; i < 256; i += kFinalThreads) bt[i] = __ldg(byte_tab + i);
+    __syncthreads();
+    const uint32_t obj = blockIdx.x * kFinalThreads + threadIdx.x;
+    if (obj >= nobj) return;
+    const uint64_t o = off[obj], n = len[obj];
+    const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
+    const uint32_t first = seg_start[obj];
+    const uint64_t nfull = cut.rows / rows_per_seg;
+    const uint32_t last_rows = (uint32_t)(cut.rows % rows_per_seg);
+    const uint8_t* p = base + o;
+    uint32_t F = 0;
+    for (uint64_t j = 0; j < nfull; j++) F = adv_tab4(adv_seg, F) ^ seg_raw[first + j];
+    uint32_t s = ~init_crc;
+    for (uint32_t i = 0; i < cut.head; i++) s = (s >> 8) ^ bt[(s ^ p[i]) & 0xFF];
+    if (nfull) s = gf2_mul(gf2_xpow8(nfull * (uint64_t)rows_per_seg * kRowBytes, xsq), s) ^ F;
+    if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first + nfull];
+    const uint8_t* t = p + cut.head + cut.rows * kRowBytes;  // 16-byte aligned
+    uint32_t i = 0;
+    for (; i + 16 <= cut.tail; i += 16) {
+        const uint4 q = *reinterpret_cast<const uint4*>(t + i);
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            uint32_t x = w[k] ^ s;
+#pragma unroll
+            for (int b = 0; b < 4; b++) x = (x >> 8) ^ bt[x & 0xFF];
+            s = x;
+        }
+    }
+    for (; i < cut.tail; i++) s = (s >> 8) ^ bt[(s ^ t[i]) & 0xFF];
     const uint32_t crc = ~s;
     got[obj] = crc;
     const bool good = want ? (crc == want[obj]) : true;
@@ -285,10 +348,14 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
         int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
         crc_rows_kernel<<<g, kRowsThreads, rows_kernel_smem(), stream>>>(a.base, a.off, a.len, a.seg_start, a.nobj,
                                                                          a.ntasks, a.rows_per_seg, a.single_off, a.single_len,
-                                                                         fold ? 1u : 0u, t.adv_row, t.col_k, a.seg_raw);
+                                                                         fold ? 1u : 0u, t.adv_row, t.col_k, t.adv4, a.seg_raw);
     }
     if (ev_end) cudaEventRecord(ev_end, stream);
-    if (a.nobj)
+    if (a.nobj && a.off && a.small_objects)
+        crc_finalize_small_kernel<<<(a.nobj + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, stream>>>(
+            a.base, a.off, a.len, a.seg_start, a.want, a.seg_raw, a.adv_seg, t.xpow8_sq, t.byte_tab, a.rows_per_seg,
+            a.init_crc, a.nobj, a.got, a.ok, a.nbad);
+    else if (a.nobj)
         crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, a.seg_start, a.want, a.seg_raw,
                                                                   a.adv_seg, t.xpow8_sq, t.byte_tab, a.rows_per_seg,
                                                                   a.init_crc, a.single_off, a.single_len, a.got, a.ok,

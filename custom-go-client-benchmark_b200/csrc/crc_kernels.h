@@ -65,6 +65,8 @@ struct BatchArgs {
     // ones when it is in use, the row kernel the rest
     uint32_t nfull_tasks;
     uint32_t npartial_tasks;
+    // every object has at most a few full segments and there are many objects: finalize one object per THREAD
+    uint32_t small_objects;
 };
 
 // true when launch_batch will give full segments of this length to the fold kernel

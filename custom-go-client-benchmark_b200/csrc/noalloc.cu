@@ -6,7 +6,7 @@
 // cudaFree imply.  The ordinary entry points grow their per-segment scratch with cudaMalloc on demand; this
 // one keeps every byte it needs — the constant tables and the per-segment scratch of the row kernel — in the
 // fixed array below, which is part of the loaded module.  Every GPU that loads libb200crc.so carries the array
-// (about 266 KB) until the process exits, whether or not this entry point is ever called.
+// (about 270 KB) until the process exits, whether or not this entry point is ever called.
 //
 // Consequences the caller has to know:
 //   * Size limit: B200_NOALLOC_MAX_BYTES (32 GiB) per call; larger inputs are rejected with
@@ -40,7 +40,8 @@ constexpr size_t kOffByteTab = 8960;      // [256]  u32
 constexpr size_t kOffGot = 9984;          // u32
 constexpr size_t kOffOk = 10000;          // u8
 constexpr size_t kOffNbad = 10016;        // u64
-constexpr size_t kOffSegRaw = 10240;      // [kMaxTasks] u32
+constexpr size_t kOffAdv4 = 10240;        // [1024] u32  x^32 slicing tables (row kernel's segment epilogue)
+constexpr size_t kOffSegRaw = 14336;      // [kMaxTasks] u32
 constexpr uint32_t kMaxTasks = 65536;
 constexpr size_t kScratchBytes = kOffSegRaw + (size_t)kMaxTasks * sizeof(uint32_t);
 constexpr int kMaxDevices = 64;
@@ -61,8 +62,9 @@ int setup_device(int dev) {  // caller holds g_mu and has made `dev` current
         cudaGetLastError();
         return B200_ERR_CUDA;
     }
-    uint32_t adv_row[1024], col_k[128], xsq[64], byte_tab[256];
+    uint32_t adv_row[1024], col_k[128], xsq[64], byte_tab[256], adv4[1024];
     host_build_adv_table(kRowBytes, adv_row);
+    host_build_adv_table(4, adv4);
     host_build_col_k(col_k);
     host_build_xpow8_sq(xsq);
     host_build_byte_tab(byte_tab);
@@ -70,6 +72,7 @@ int setup_device(int dev) {  // caller holds g_mu and has made `dev` current
     if (e == cudaSuccess) e = cudaMemcpy(p + kOffColK, col_k, sizeof col_k, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(p + kOffXsq, xsq, sizeof xsq, cudaMemcpyHostToDevice);
     if (e == cudaSuccess) e = cudaMemcpy(p + kOffByteTab, byte_tab, sizeof byte_tab, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) e = cudaMemcpy(p + kOffAdv4, adv4, sizeof adv4, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
         cudaGetLastError();
         return B200_ERR_CUDA;
@@ -131,6 +134,7 @@ extern "C" int b200_crc32c_update_device_noalloc(int dev, uint32_t crc, const vo
     t.col_k = (uint32_t*)(p + kOffColK);
     t.xpow8_sq = (uint32_t*)(p + kOffXsq);
     t.byte_tab = (uint32_t*)(p + kOffByteTab);
+    t.adv4 = (uint32_t*)(p + kOffAdv4);
     e = launch_batch(a, t, g_grid[dev], 0, nullptr, nullptr);
     if (e == cudaSuccess) e = cudaMemcpy(out, p + kOffGot, sizeof(uint32_t), cudaMemcpyDeviceToHost);
     if (e != cudaSuccess) {

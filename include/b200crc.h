@@ -71,7 +71,7 @@ int b200_crc32c_update_device(b200_ctx* ctx, int dev, uint32_t crc, const void* 
 /* No counterpart in the reference.  Same result as b200_crc32c_update_device, for callers that cannot
  * allocate device memory: processes that gave all of it to their own pool at start-up, and read loops
  * that cannot take the device-wide synchronisation of cudaMalloc/cudaFree.  Needs no b200_ctx and calls no
- * allocating routine: the row kernel's per-segment scratch and the constant tables live in a fixed ~266 KB
+ * allocating routine: the row kernel's per-segment scratch and the constant tables live in a fixed ~270 KB
  * array inside the library image, which every GPU that loads the library holds until exit.
  *   - n > B200_NOALLOC_MAX_BYTES is rejected with B200_ERR_TOO_LARGE (split and b200_crc32c_combine).
  *   - All calls share that one array per GPU; they are serialised inside the library and each waits for

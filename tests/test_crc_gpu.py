@@ -275,6 +275,16 @@ def test_verify_objects_host_many(ctx):
     want, _, _ = oracle.verify_objects(base, off, np.full(n, 2 << 20, np.uint64), threads=8)
     bad, got = crc32c.VerifyObjects(bufs, want, ctx)
     assert bad == [] and (got == want).all()
+    # the 2-D array form (rows = objects), pinned and pageable
+    bad, got = crc32c.VerifyObjects(base.reshape(n, 2 << 20), want, ctx)
+    assert bad == [] and (got == want).all()
+    pinned = ctx.alloc_pinned(16 * (1 << 20))
+    pinned[:] = base[:16 << 20]
+    w2, _, _ = oracle.verify_objects(base, np.arange(16, dtype=np.uint64) << np.uint64(20), np.full(16, 1 << 20, np.uint64))
+    w2[5] ^= 1
+    bad, got = crc32c.VerifyObjects(pinned.reshape(16, 1 << 20), w2, ctx)
+    assert bad == [5]
+    ctx.free_pinned(pinned)
 
 
 def test_sharded_single_device(ctx, arena):

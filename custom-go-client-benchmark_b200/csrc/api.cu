@@ -77,6 +77,7 @@ struct DevState {
     uint32_t* h_got = nullptr;  // pinned [kSingleSlots]
     cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr};
     cudaEvent_t ev_timer[2] = {nullptr, nullptr};
+    SideStream side{};  // second compute stream: row kernel next to the fold kernel
     LatScratch lat{};
     HostSlab slab[2];
 };
@@ -251,7 +252,7 @@ int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc,
     a.ok = d->d_ok;
     a.nbad = d->d_nbad;
     a.init_crc = init_crc;
-    CU(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr));
+    CU(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr, &d->side));
     return 0;
 }
 
@@ -371,6 +372,9 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
         cudaError_t e = cudaSetDevice(dev);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d->side.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->side.fork, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->side.join, cudaEventDisableTiming);
         for (int b = 0; b < 2 && e == cudaSuccess; b++) {
             e = cudaEventCreateWithFlags(&d->ev_copied[b], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d->ev_done[b], cudaEventDisableTiming);
@@ -428,6 +432,9 @@ int b200_shutdown(b200_ctx* ctx) {
             if (d->ev_done[b]) cudaEventDestroy(d->ev_done[b]);
             if (d->ev_timer[b]) cudaEventDestroy(d->ev_timer[b]);
         }
+        if (d->side.stream) cudaStreamDestroy(d->side.stream);
+        if (d->side.fork) cudaEventDestroy(d->side.fork);
+        if (d->side.join) cudaEventDestroy(d->side.join);
         if (d->stream) cudaStreamDestroy(d->stream);
         if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
         delete d;
@@ -738,7 +745,7 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     a.rows_per_seg = b->rows_per_seg;
     a.init_crc = 0;
     cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];
-    CU(launch_batch(a, d->tabs, d->grid, d->stream, ev[0], ev[1]));
+    CU(launch_batch(a, d->tabs, d->grid, d->stream, ev[0], ev[1], &d->side));
     CU(cudaEventRecord(ev[2], d->stream));
     b->runs++;
     b->ran = true;
@@ -947,7 +954,7 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
         a.nfull_tasks = (uint32_t)tfull;
         a.npartial_tasks = (uint32_t)(t - tfull);
         a.rows_per_seg = rps;
-        cu(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr));
+        cu(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr, &d->side));
         cu(cudaMemcpyAsync(hs.h_got, hs.d_got, cnt * 4, cudaMemcpyDeviceToHost, d->stream));
         cu(cudaMemcpyAsync(hs.h_ok, hs.d_ok, cnt, cudaMemcpyDeviceToHost, d->stream));
         cu(cudaMemcpyAsync(hs.h_nbad, hs.d_nbad, 8, cudaMemcpyDeviceToHost, d->stream));

@@ -325,7 +325,7 @@ int rows_kernel_grid(int dev) {
 }
 
 cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream,
-                         cudaEvent_t ev_begin, cudaEvent_t ev_end) {
+                         cudaEvent_t ev_begin, cudaEvent_t ev_end, const SideStream* side) {
     static thread_local int attr_dev = -1;
     int dev = 0;
     cudaGetDevice(&dev);
@@ -339,16 +339,29 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     if (e != cudaSuccess) return e;
     if (ev_begin) cudaEventRecord(ev_begin, stream);
     const bool fold = fold_enabled(a.rows_per_seg) && a.nfull_tasks > 0;
+    const bool rows = a.ntasks && (!fold || a.npartial_tasks > 0);
+    cudaStream_t rows_stream = stream;
+    if (fold && rows && side) {  // fork: the row kernel overlaps the fold kernel's tail
+        e = cudaEventRecord(side->fork, stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(side->stream, side->fork, 0);
+        if (e != cudaSuccess) return e;
+        rows_stream = side->stream;
+    }
     if (fold) {
         e = launch_fold(a, t, grid, stream);
         if (e != cudaSuccess) return e;
     }
-    if (a.ntasks && (!fold || a.npartial_tasks > 0)) {
+    if (rows) {
         uint32_t need = (a.ntasks + kRowsWarps - 1) / kRowsWarps;
         int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
-        crc_rows_kernel<<<g, kRowsThreads, rows_kernel_smem(), stream>>>(a.base, a.off, a.len, a.seg_start, a.nobj,
-                                                                         a.ntasks, a.rows_per_seg, a.single_off, a.single_len,
-                                                                         fold ? 1u : 0u, t.adv_row, t.col_k, t.adv4, a.seg_raw);
+        crc_rows_kernel<<<g, kRowsThreads, rows_kernel_smem(), rows_stream>>>(
+            a.base, a.off, a.len, a.seg_start, a.nobj, a.ntasks, a.rows_per_seg, a.single_off, a.single_len,
+            fold ? 1u : 0u, t.adv_row, t.col_k, t.adv4, a.seg_raw);
+        if (rows_stream != stream) {  // join
+            e = cudaEventRecord(side->join, rows_stream);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, side->join, 0);
+            if (e != cudaSuccess) return e;
+        }
     }
     if (ev_end) cudaEventRecord(ev_end, stream);
     if (a.nobj && a.off && a.small_objects)

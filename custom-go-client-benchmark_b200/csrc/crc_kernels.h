@@ -75,8 +75,14 @@ bool fold_enabled(uint32_t rows_per_seg);
 int rows_kernel_grid(int dev);
 size_t rows_kernel_smem();
 // Enqueue row kernel + finalize kernel on `stream`.  ev_* may be null; when given they bracket the row kernel.
+// `side` (optional): a second stream plus two events; when both segment kernels are needed the row kernel
+// runs there so that its CTAs fill the SMs the fold kernel's tail leaves idle.
+struct SideStream {
+    cudaStream_t stream;
+    cudaEvent_t fork, join;
+};
 cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream,
-                         cudaEvent_t ev_rows_begin, cudaEvent_t ev_rows_end);
+                         cudaEvent_t ev_rows_begin, cudaEvent_t ev_rows_end, const SideStream* side = nullptr);
 
 size_t fold_kernel_smem();
 cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream);

@@ -10,6 +10,7 @@
 #include <map>
 #include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 
 #include "crc_kernels.h"
@@ -1289,6 +1290,125 @@ int b200_hist_fixed_f64(b200_ctx* ctx, int dev, const double* d_values, size_t n
     double s = hi + lo;
     if (sum_hi) *sum_hi = s;
     if (sum_lo) *sum_lo = lo - (s - hi);
+    return 0;
+}
+
+}  // extern "C"
+
+// ---- several devices driven by one process: per-device kernels, counts summed on the host ----
+
+namespace {
+
+// run f(i) for i in [0, n) on n host threads (device work of different GPUs overlaps); returns the first error
+template <typename F>
+int for_each_device(int n, F f) {
+    std::vector<int> rc(n, 0);
+    std::vector<std::thread> th;
+    for (int i = 1; i < n; i++) th.emplace_back([&, i] { rc[i] = f(i); });
+    rc[0] = f(0);
+    for (auto& t : th) t.join();
+    for (int r : rc)
+        if (r) return r;
+    return 0;
+}
+
+void add128(uint64_t& lo, uint64_t& hi, uint64_t alo, uint64_t ahi) {
+    uint64_t s = lo + alo;
+    hi += ahi + (s < lo);
+    lo = s;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b200_hist_fixed_multi(b200_ctx* ctx, const int* devs, const int64_t* const* d_samples, const size_t* n, int ndev,
+                          int64_t divisor, const double* edges, int nedges, int mode, uint64_t* counts,
+                          b200_lat_stats* stats) {
+    if (!ctx || !devs || !d_samples || !n || ndev < 1 || !counts || nedges < 1 || nedges > B200_HIST_MAX_EDGES)
+        return fail(B200_ERR_INVALID, "b200_hist_fixed_multi");
+    const int nb = mode == B200_HIST_NUMPY ? nedges - 1 : nedges + 1;
+    std::vector<std::vector<uint64_t>> c(ndev, std::vector<uint64_t>(B200_HIST_MAX_EDGES + 2));
+    std::vector<b200_lat_stats> st(ndev);
+    int rc = for_each_device(ndev, [&](int i) {
+        return b200_hist_fixed(ctx, devs[i], d_samples[i], n[i], divisor, edges, nedges, mode, c[i].data(), &st[i]);
+    });
+    if (rc) return rc;
+    for (int b = 0; b < nb; b++) {
+        counts[b] = 0;
+        for (int i = 0; i < ndev; i++) counts[b] += c[i][b];
+    }
+    if (stats) {
+        b200_lat_stats t{};
+        uint64_t sum_hi = 0;
+        bool any = false;
+        for (int i = 0; i < ndev; i++) {
+            if (!st[i].count) continue;
+            t.min = any ? std::min(t.min, st[i].min) : st[i].min;
+            t.max = any ? std::max(t.max, st[i].max) : st[i].max;
+            any = true;
+            t.count += st[i].count;
+            add128(t.sum, sum_hi, st[i].sum, (uint64_t)st[i].sum_hi);
+            add128(t.sumsq_lo, t.sumsq_hi, st[i].sumsq_lo, st[i].sumsq_hi);
+            t.dropped_below += st[i].dropped_below;
+            t.dropped_above += st[i].dropped_above;
+        }
+        t.sum_hi = (int64_t)sum_hi;
+        *stats = t;
+    }
+    return 0;
+}
+
+int b200_select_kth_multi(b200_ctx* ctx, const int* devs, const int64_t* const* d_samples, const size_t* n, int ndev,
+                          int64_t divisor, const uint64_t* k, int nk, int64_t* out) {
+    if (!ctx || !devs || !d_samples || !n || ndev < 1 || !k || !out || nk < 1 || divisor < 1)
+        return fail(B200_ERR_INVALID, "b200_select_kth_multi");
+    uint64_t total = 0;
+    for (int i = 0; i < ndev; i++) total += n[i];
+    if (total == 0) return fail(B200_ERR_EMPTY, "b200_select_kth_multi: no samples (the reference panics, ssd_test/main.go:157)");
+    for (int i = 0; i < nk; i++)
+        if (k[i] >= total) return fail(B200_ERR_INVALID, "b200_select_kth_multi: k >= n");
+    std::vector<int64_t> mn(ndev), mx(ndev);
+    int rc = for_each_device(ndev, [&](int i) { return b200_minmax(ctx, devs[i], d_samples[i], n[i], &mn[i], &mx[i]); });
+    if (rc) return rc;
+    int64_t gmn = INT64_MAX, gmx = INT64_MIN;
+    for (int i = 0; i < ndev; i++)
+        if (n[i]) { gmn = std::min(gmn, mn[i]); gmx = std::max(gmx, mx[i]); }
+    const uint64_t kmin = (uint64_t)gmn ^ 0x8000000000000000ull, range = ((uint64_t)gmx ^ 0x8000000000000000ull) - kmin;
+    int bits = 0;
+    while (bits < 64 && (range >> bits)) bits++;
+    std::vector<std::vector<uint64_t>> cnt(ndev, std::vector<uint64_t>((size_t)kMaxSelect * kRadixBins));
+    for (int g = 0; g < nk; g += kMaxSelect) {
+        const int m = std::min(kMaxSelect, nk - g);
+        uint64_t prefix[kMaxSelect] = {0, 0, 0, 0}, rank[kMaxSelect];
+        for (int i = 0; i < m; i++) rank[i] = k[g + i];
+        int top = bits;
+        bool first = true;
+        while (top > 0) {
+            const int shift = std::max(top - kRadixBits, 0), width = top - shift, nh = first ? 1 : m;
+            rc = for_each_device(ndev, [&](int i) {
+                return b200_radix_count(ctx, devs[i], d_samples[i], n[i], kmin, shift, top, nh, prefix, cnt[i].data());
+            });
+            if (rc) return rc;
+            for (int i = 0; i < m; i++) {
+                const size_t row = first ? 0 : (size_t)i * kRadixBins;
+                uint64_t cum = 0;
+                int dgt = 0;
+                for (; dgt < (1 << width); dgt++) {
+                    uint64_t h = 0;
+                    for (int dv = 0; dv < ndev; dv++) h += cnt[dv][row + dgt];  // the host-side "all-reduce"
+                    if (rank[i] < cum + h) break;
+                    cum += h;
+                }
+                if (dgt == (1 << width)) return fail(B200_ERR_CUDA, "b200_select_kth_multi: inconsistent radix counts");
+                rank[i] -= cum;
+                prefix[i] = (prefix[i] << width) | (uint64_t)dgt;
+            }
+            top = shift;
+            first = false;
+        }
+        for (int i = 0; i < m; i++) out[g + i] = (int64_t)((prefix[i] + kmin) ^ 0x8000000000000000ull) / divisor;
+    }
     return 0;
 }
 

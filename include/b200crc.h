@@ -185,6 +185,15 @@ int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int6
 int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, uint64_t key_base, int shift,
                      int top, int nk, const uint64_t* prefix, uint64_t* counts);
 
+/* One process driving several devices (the other multi-GPU form is one process per GPU with the counts
+ * all-reduced over NCCL by the caller, latency.py): device devs[i] holds n[i] samples at d_samples[i]; the
+ * per-device kernels run concurrently, bin / digit counts are summed on the host.  devs may repeat a device. */
+int b200_hist_fixed_multi(b200_ctx* ctx, const int* devs, const int64_t* const* d_samples, const size_t* n, int ndev,
+                          int64_t divisor, const double* edges, int nedges, int mode, uint64_t* counts,
+                          b200_lat_stats* stats);
+int b200_select_kth_multi(b200_ctx* ctx, const int* devs, const int64_t* const* d_samples, const size_t* n, int ndev,
+                          int64_t divisor, const uint64_t* k, int nk, int64_t* out);
+
 /* ---- latency text files --------------------------------------------------------------------------------- */
 
 /* README.md:25-28 `for line in f: x.append(float(line))` over the file execute_pb.sh:4,8 writes (one Go

@@ -163,6 +163,32 @@ def test_select_all_equal_and_empty(ctx):
     ctx.free_device(d)
 
 
+def test_multi_device_form_with_one_gpu_standing_in_for_three(ctx, samples):
+    """b200_hist_fixed_multi / b200_select_kth_multi: shards on 'several devices' (device 0 three times)."""
+    import ctypes as C
+    ns, d, n = samples
+    cuts = [0, 200_001, 200_001, n]           # one empty shard
+    ptrs = (C.c_void_p * 3)(*[d + 8 * cuts[i] for i in range(3)])
+    sizes = (C.c_size_t * 3)(*[cuts[i + 1] - cuts[i] for i in range(3)])
+    devs = (C.c_int * 3)(0, 0, 0)
+    L = ctx._L
+    edges = lat.README_EDGES
+    counts = np.zeros(15, dtype=np.uint64)
+    st = pkg._lib.LatStats()
+    pkg._lib.check(L.b200_hist_fixed_multi(ctx._h, devs, ptrs, sizes, 3, 1_000_000, edges.ctypes.data, edges.size, 0,
+                                           counts.ctypes.data, C.byref(st)))
+    ms = oracle.ns_to_ms(ns)
+    ref, dropped = oracle.hist_numpy(ms.astype(np.float64))
+    assert list(counts) == list(ref) and st.dropped_below + st.dropped_above == dropped
+    assert (st.count, st.min, st.max, st.sum) == (n, ms.min(), ms.max(), int(ms.sum()))
+    assert (st.sumsq_hi << 64) | st.sumsq_lo == int((ms.astype(object) ** 2).sum())
+    ks = np.array([0, n // 5, n // 2, 9 * n // 10, 99 * n // 100, n - 1], dtype=np.uint64)
+    out = np.zeros(ks.size, dtype=np.int64)
+    pkg._lib.check(L.b200_select_kth_multi(ctx._h, devs, ptrs, sizes, 3, 1000, ks.ctypes.data, ks.size, out.ctypes.data))
+    srt = np.sort(oracle.ns_to_us(ns))
+    assert list(out) == [int(srt[int(k)]) for k in ks]
+
+
 def test_golden_fixture(ctx):
     g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "golden.json")))["latency"]
     n = g["n"]

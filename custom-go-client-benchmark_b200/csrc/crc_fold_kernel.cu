@@ -39,6 +39,7 @@ extern __shared__ __align__(1024) uint8_t fold_smem[];
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// (.L2::128B / .L2::256B prefetch hints on this copy were measured: no difference.)
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
 }

@@ -368,3 +368,30 @@ def test_full_size_config2_properties(ctx):
     assert nbad2 == 1 and list(np.nonzero(~ok2)[0]) == [1234]
     b.close(); b2.close()
     ctx.free_device(d)
+
+
+def test_c_abi_argument_errors(ctx):
+    """Bad arguments come back as B200_ERR_INVALID with a message, never a crash."""
+    import ctypes as C
+    L, h = ctx._L, ctx._h
+    out = C.c_uint32()
+    inv = pkg._lib.ERR_INVALID
+    assert L.b200_crc32c_update_host(h, 0, 0, None, 10, C.byref(out)) == inv          # null data, n > 0
+    assert L.b200_crc32c_update_host(h, 0, 0, None, 0, C.byref(out)) == 0 and out.value == 0
+    assert L.b200_crc32c_update_host(h, 7, 0, None, 0, C.byref(out)) == inv           # device not in the context
+    assert L.b200_crc32c_update_device(h, 0, 0, None, 10, C.byref(out)) == inv
+    assert L.b200_crc32c_update_host(None, 0, 0, None, 0, C.byref(out)) == inv
+    hb = C.c_void_p()
+    assert L.b200_batch_create(h, 0, None, None, 5, None, C.byref(hb)) == inv
+    assert L.b200_batch_results(None, None, None, None) == inv
+    assert L.b200_hasher_write(None, None, 0) == inv
+    assert L.b200_crc32c_sharded(h, None, None, 1, C.byref(out)) == inv
+    assert b"b200_" in L.b200_last_error()
+    n = C.c_int()
+    assert L.b200_device_count(C.byref(n)) == 0 and n.value >= 1
+    assert L.b200_ctx_ndev(h) == 1
+    # a batch that has not run yet has no results
+    off = np.zeros(1, np.uint64); ln = np.full(1, 8, np.uint64)
+    assert L.b200_batch_create(h, 0, off.ctypes.data, ln.ctypes.data, 1, None, C.byref(hb)) == 0
+    assert L.b200_batch_results(hb, None, None, None) == inv
+    assert L.b200_batch_free(hb) == 0

@@ -69,10 +69,14 @@ __device__ __forceinline__ int classify(long long n, const long long* __restrict
 struct Moments {
     unsigned mn32 = 0xFFFFFFFFu, mx32 = 0;                 // of fast-path samples
     long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;  // of slow-path samples
-    U128 sum{0, 0}, sq{0, 0};
+    U128 sum{0, 0}, sq{0, 0};                              // slow path: exact 128-bit
+    unsigned long long fsum = 0, fsq = 0;                  // fast path: q < 2^32, so 64 bits hold ~2^32 samples of q
+    unsigned fsq_carry = 0;                                //   and q*q wraps at most once per add
 };
 
-template <bool MOMENTS>
+// DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic,
+// 2 divisor >= 2^32 (quotient 0).
+template <bool MOMENTS, int DIVMODE>
 __global__ void __launch_bounds__(kHistThreads, 4)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom) {
@@ -97,7 +101,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     unsigned* mine = tbl + (size_t)warp * nbins * 32 + lane;
     Moments m;
     const unsigned magic32 = P.magic32;
-    const int shift32 = P.shift32, mode32 = P.mode32;
+    const int shift32 = P.shift32;
 
     // generic path: any int64 sample
     auto slow = [&](long long v) {
@@ -126,29 +130,31 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         if (lane == 0) slow_n[warp] = 0;
         __syncwarp();
     };
-    // fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), everything in 32-bit arithmetic
+    // fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), everything in 32-bit arithmetic and branch-free up to
+    // the single rare-case test
     auto one = [&](long long v) {
-        const unsigned long long uv = (unsigned long long)v;
-        if (uv >> 32) { park(v); return; }
-        const unsigned u = (unsigned)uv;
+        const unsigned u = (unsigned)v, hi = (unsigned)((unsigned long long)v >> 32);
+        // log-linear cell: row = max(e,4)-4, mantissa = 5 bits below the leading one (u itself for u < 32)
         const int e = 31 - __clz((int)(u | 1));
-        const unsigned idx = u < 32 ? u : (unsigned)((e - 4) * 32) + ((u >> (e - 5)) & 31);
+        const unsigned idx = (unsigned)(max(e, 4) - 4) * 32 + ((u >> (max(e, 5) - 5)) & 31);
         const unsigned cell = P.lut[idx];
-        if ((cell & 0xFF) > 1) { park(v); return; }  // several thresholds inside this cell: rare
+        if (hi | (cell & 0xFE)) { park(v); return; }  // >= 2^32 / negative, or several thresholds in the cell
         const unsigned c = (cell >> 8) + (u > P.cell_gt[idx] ? 1u : 0u);
         mine[c * 32]++;
         if (MOMENTS) {
             m.mn32 = min(m.mn32, u);
             m.mx32 = max(m.mx32, u);
             unsigned q;
-            if (mode32 == 1) {
-                unsigned t = __umulhi(magic32, u);
+            if (DIVMODE == 1) {
+                const unsigned t = __umulhi(magic32, u);
                 q = (t + ((u - t) >> 1)) >> shift32;
             } else {
-                q = mode32 == 0 ? u : 0u;
+                q = DIVMODE == 0 ? u : 0u;
             }
-            add128(m.sum, q, 0);
-            add128(m.sq, (unsigned long long)q * q, 0);
+            m.fsum += q;
+            const unsigned long long sq = (unsigned long long)q * q + m.fsq;
+            m.fsq_carry += sq < m.fsq;
+            m.fsq = sq;
         }
     };
 
@@ -191,6 +197,8 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
         }
         U128 sum = m.sum, sq = m.sq;
+        add128(sum, m.fsum, 0);
+        add128(sq, m.fsq, m.fsq_carry);
 #pragma unroll
         for (int d = 16; d; d >>= 1) {
             long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
@@ -319,7 +327,7 @@ static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
 }
 
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins) {
+                        cudaStream_t stream, int nbins, int mode32) {
     cudaError_t e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     e = reset_moments(s, stream);
@@ -327,16 +335,18 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     if (!n) return cudaSuccess;
     const size_t smem = hist_smem(nbins);
     const int max_smem = (int)hist_smem(kMaxThresholds + 1);
-    e = cudaFuncSetAttribute(hist_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(hist_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*);
+    static const Kernel kernels[2][3] = {{hist_kernel<false, 0>, hist_kernel<false, 1>, hist_kernel<false, 2>},
+                                         {hist_kernel<true, 0>, hist_kernel<true, 1>, hist_kernel<true, 2>}};
+    const Kernel k = kernels[want_moments ? 1 : 0][mode32];
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: 4 by registers, fewer when the private counter tables are large
     int per_sm = (int)std::min<size_t>(4, (220 * 1024) / (smem + sizeof(HistParams) + kHistWarps * kSlowQueue * 8 + 1024));
     if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
-    if (want_moments) hist_kernel<true><<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom);
-    else hist_kernel<false><<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom);
+    k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom);
     return cudaGetLastError();
 }
 

@@ -49,7 +49,7 @@ void lat_scratch_free(LatScratch* s);
 
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins);
+                        cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */);
 // One MSD radix pass over key' = (ns ^ 2^63) - key_base: for each k < nk count the digit
 // (key' >> shift) & (2^(top-shift) - 1) over the samples with key' >> top == d_prefix[k] (all samples when
 // top >= 64).  top - shift <= kRadixBits.

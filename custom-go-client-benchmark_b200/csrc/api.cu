@@ -66,6 +66,7 @@ struct DevState {
     DeviceTables tabs{};
     std::mutex mu;                  // guards the streams and scratch of this device
     std::recursive_mutex stage_mu;  // guards the staging slabs (held across whole host-input calls)
+    std::mutex select_mu;           // one order-statistic query at a time per device (they share lat.d_compact)
     std::map<uint32_t, uint32_t*> adv_seg;  // rows_per_seg -> device [4][256]
     uint32_t* seg_raw = nullptr;            // scratch for single-object runs
     size_t seg_raw_cap = 0;
@@ -1149,12 +1150,55 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
     return 0;
 }
 
+}  // extern "C"
+
+namespace {
+
+// After the first radix pass: copy the samples of the buckets still in play (distinct prefixes pf[0..np)) into
+// the device's compaction buffer so that the remaining passes read `total` samples instead of n.  Returns 0
+// and sets *out when done, 1 when the buckets are too large to be worth it (caller keeps the full data).
+int compact_buckets(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, uint64_t key_base, int top,
+                    const uint64_t* pf, int np, uint64_t total, const int64_t** out) {
+    DevState* d = get_dev(ctx, dev);
+    // worth it only when few samples survive (measured: at 25 % the filtering pass costs more than it saves):
+    // one filtering pass + 2 passes over `total` samples instead of 2 passes over n
+    if (!d || total == 0 || total > n / 8 || n < (1u << 20)) return 1;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    if (d->lat.compact_cap < total) {
+        cudaFree(d->lat.d_compact);
+        d->lat.d_compact = nullptr;
+        d->lat.compact_cap = 0;
+        cudaError_t e = cudaMalloc(&d->lat.d_compact, total * sizeof(long long));
+        if (e != cudaSuccess) {  // no room for the shortcut: not an error
+            cudaGetLastError();
+            return 1;
+        }
+        d->lat.compact_cap = total;
+    }
+    CU(cudaMemcpyAsync(d->lat.d_prefix, pf, np * sizeof(uint64_t), cudaMemcpyHostToDevice, d->stream));
+    CU(launch_compact((const long long*)d_samples, n, key_base, top, np, d->lat, d->stream));
+    unsigned long long got = 0;
+    CU(cudaMemcpyAsync(&got, d->lat.d_compact_n, sizeof got, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    if (got != total) return fail(B200_ERR_CUDA, "select: compaction count differs from the histogram");
+    *out = (const int64_t*)d->lat.d_compact;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
 int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, int64_t lo_ns,
                           int64_t hi_ns, const uint64_t* k, int nk, int64_t* out) {
     if (!k || !out || nk < 1 || divisor < 1 || lo_ns > hi_ns) return fail(B200_ERR_INVALID, "b200_select_kth");
     if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
     for (int i = 0; i < nk; i++)
         if (k[i] >= n) return fail(B200_ERR_INVALID, "b200_select_kth: k >= n");
+    DevState* dsel = get_dev(ctx, dev);
+    if (!dsel) return fail(B200_ERR_INVALID, "b200_select_kth: unknown device");
+    std::lock_guard<std::mutex> sel_lock(dsel->select_mu);
     const uint64_t kmin = (uint64_t)lo_ns ^ 0x8000000000000000ull, kmax = (uint64_t)hi_ns ^ 0x8000000000000000ull;
     const uint64_t range = kmax - kmin;
     int bits = 0;
@@ -1166,6 +1210,8 @@ int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size
         for (int i = 0; i < m; i++) rank[i] = k[g + i];
         int top = bits;
         bool first = true;
+        const int64_t* cur = d_samples;  // what the next pass reads: all samples, or the compacted buckets
+        size_t cur_n = n;
         if (top == 0) {  // all samples equal lo_ns: nothing to resolve
             for (int i = 0; i < m; i++) prefix[i] = 0;
         }
@@ -1173,8 +1219,9 @@ int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size
             int shift = std::max(top - kRadixBits, 0);
             int width = top - shift;
             // first pass: key' < 2^top, so every sample matches prefix 0 and one histogram serves all k
-            int rc = b200_radix_count(ctx, dev, d_samples, n, kmin, shift, top, first ? 1 : m, prefix, counts.data());
+            int rc = b200_radix_count(ctx, dev, cur, cur_n, kmin, shift, top, first ? 1 : m, prefix, counts.data());
             if (rc) return rc;
+            uint64_t bucket[kMaxSelect];
             for (int i = 0; i < m; i++) {
                 const uint64_t* h = counts.data() + (first ? 0 : (size_t)i * kRadixBins);
                 uint64_t cum = 0;
@@ -1187,8 +1234,23 @@ int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size
                     return fail(B200_ERR_INVALID, "b200_select_kth: samples outside the given [lo, hi] range");
                 rank[i] -= cum;
                 prefix[i] = (prefix[i] << width) | (uint64_t)dgt;
+                bucket[i] = h[dgt];
             }
             top = shift;
+            if (first && top > 0) {
+                // the wanted ranks now live in at most m buckets: keep just those samples for the next passes
+                uint64_t pf[kMaxSelect], total = 0;
+                int np = 0;
+                for (int i = 0; i < m; i++) {
+                    bool seen = false;
+                    for (int j = 0; j < np; j++) seen |= pf[j] == prefix[i];
+                    if (!seen) { pf[np++] = prefix[i]; total += bucket[i]; }
+                }
+                const int64_t* small = nullptr;
+                rc = compact_buckets(ctx, dev, d_samples, n, kmin, top, pf, np, total, &small);
+                if (rc < 0) return rc;
+                if (rc == 0) { cur = small; cur_n = (size_t)total; }
+            }
             first = false;
         }
         for (int i = 0; i < m; i++) {

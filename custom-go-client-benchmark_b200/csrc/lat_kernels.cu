@@ -228,12 +228,28 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
 __global__ void __launch_bounds__(kHistThreads)
 minmax_kernel(const long long* __restrict__ x, size_t n, LatMoments* __restrict__ mom) {
     long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
-    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
-    for (size_t i = (size_t)blockIdx.x * kHistThreads + threadIdx.x; i < n; i += nthreads) {
-        long long v = __ldg(x + i);
+    auto one = [&](long long v) {
         mn = v < mn ? v : mn;
         mx = v > mx ? v : mx;
+    };
+    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
+    if (head > n) head = n;
+    const size_t tid = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
+    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
+    if (tid == 0 && head) one(x[0]);
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    size_t i = tid;
+    for (; i + 3 * nthreads < npairs; i += 4 * nthreads) {
+        longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads), c = __ldg(x2 + i + 2 * nthreads),
+                  d = __ldg(x2 + i + 3 * nthreads);
+        one(a.x); one(a.y); one(b.x); one(b.y); one(c.x); one(c.y); one(d.x); one(d.y);
     }
+    for (; i < npairs; i += nthreads) {
+        longlong2 a = __ldg(x2 + i);
+        one(a.x); one(a.y);
+    }
+    if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
 #pragma unroll
     for (int d = 16; d; d >>= 1) {
         long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
@@ -244,6 +260,78 @@ minmax_kernel(const long long* __restrict__ x, size_t n, LatMoments* __restrict_
         atomicMin(&mom->min_ns, mn);
         atomicMax(&mom->max_ns, mx);
     }
+}
+
+// Keep only the samples of the (at most kMaxSelect distinct) buckets the wanted ranks fell into.  Hits are
+// staged per CTA in shared memory and flushed in blocks, so the global counter sees one atomic per ~3000 hits
+// (a warp-level append alone serialises on that counter when 10-20 % of the samples survive).
+constexpr int kCompactStage = 4096;                        // samples staged per CTA
+constexpr int kCompactFlush = kCompactStage - 2 * kRadixThreads;  // a round adds at most 2 per thread
+
+__global__ void __launch_bounds__(kRadixThreads)
+compact_kernel(const long long* __restrict__ x, size_t n, unsigned long long key_base, int top, int nprefix,
+               const unsigned long long* __restrict__ prefix, long long* __restrict__ out,
+               unsigned long long* __restrict__ out_n, size_t cap) {
+    __shared__ long long stage[kCompactStage];
+    __shared__ unsigned stage_n;
+    __shared__ unsigned long long flush_base;
+    unsigned long long pf[kMaxSelect];
+#pragma unroll
+    for (int k = 0; k < kMaxSelect; k++) pf[k] = k < nprefix ? prefix[k] : ~0ull;  // key' >> top < 2^63: never matches
+    if (threadIdx.x == 0) stage_n = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    auto emit = [&](bool hit, long long v) {  // called by all 32 lanes together
+        const unsigned m = __ballot_sync(0xFFFFFFFFu, hit);
+        if (m) {
+            const int leader = __ffs(m) - 1;
+            unsigned base = 0;
+            if (lane == leader) base = atomicAdd(&stage_n, (unsigned)__popc(m));
+            base = __shfl_sync(0xFFFFFFFFu, base, leader);
+            if (hit) stage[base + __popc(m & ((1u << lane) - 1))] = v;
+        }
+    };
+    auto flush = [&]() {  // whole CTA
+        __syncthreads();
+        const unsigned cnt = stage_n;
+        if (threadIdx.x == 0) flush_base = atomicAdd(out_n, (unsigned long long)cnt);
+        __syncthreads();
+        for (unsigned k = threadIdx.x; k < cnt; k += kRadixThreads)
+            if (flush_base + k < cap) out[flush_base + k] = stage[k];
+        __syncthreads();
+        if (threadIdx.x == 0) stage_n = 0;
+        __syncthreads();
+    };
+    auto matches = [&](long long v) {
+        const unsigned long long hi = (((unsigned long long)v ^ 0x8000000000000000ull) - key_base) >> top;
+        return hi == pf[0] || hi == pf[1] || hi == pf[2] || hi == pf[3];
+    };
+    // every thread makes the same number of trips (ballots and CTA barriers); 16-byte loads in the body
+    const size_t head = (reinterpret_cast<uintptr_t>(x) & 15) && n ? 1 : 0;
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    const size_t nthreads = (size_t)gridDim.x * kRadixThreads;
+    const size_t tid = (size_t)blockIdx.x * kRadixThreads + threadIdx.x;
+    const size_t rounds = (npairs + nthreads - 1) / nthreads;
+    size_t i = tid;
+    for (size_t r = 0; r < rounds; r++, i += nthreads) {
+        longlong2 a = make_longlong2(0, 0);
+        const bool in = i < npairs;
+        if (in) a = __ldg(x2 + i);
+        emit(in && matches(a.x), a.x);
+        emit(in && matches(a.y), a.y);
+        __syncthreads();
+        if (stage_n > kCompactFlush) flush();  // CTA-uniform: everyone reads the same counter after the barrier
+    }
+    // the unaligned first sample and an odd last one: warp 0 of block 0, lanes 0 and 1
+    if (blockIdx.x == 0 && threadIdx.x < 32) {
+        long long v = 0;
+        bool hit = false;
+        if (lane == 0 && head) { v = x[0]; hit = matches(v); }
+        if (lane == 1 && head + 2 * npairs < n) { v = x[n - 1]; hit = matches(v); }
+        emit(hit, v);
+    }
+    flush();
 }
 
 __global__ void __launch_bounds__(kRadixThreads)
@@ -307,6 +395,7 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     if (e == cudaSuccess) e = cudaMalloc(&s->d_mom, sizeof(LatMoments));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_compact_n, sizeof(unsigned long long));
     return e;
 }
 
@@ -316,6 +405,8 @@ void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_mom);
     cudaFree(s->d_radix);
     cudaFree(s->d_prefix);
+    cudaFree(s->d_compact);
+    cudaFree(s->d_compact_n);
     memset(s, 0, sizeof *s);
 }
 
@@ -355,6 +446,16 @@ cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch
     if (e != cudaSuccess || !n) return e;
     int grid = (int)std::min<size_t>((size_t)sm_count() * 8, (n + kHistThreads - 1) / kHistThreads);
     minmax_kernel<<<grid, kHistThreads, 0, stream>>>(d_samples, n, s.d_mom);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_compact(const long long* d_samples, size_t n, unsigned long long key_base, int top, int nprefix,
+                           const LatScratch& s, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(s.d_compact_n, 0, sizeof(unsigned long long), stream);
+    if (e != cudaSuccess || !n) return e;
+    int grid = (int)std::min<size_t>((size_t)sm_count() * 4, (n + kRadixThreads - 1) / kRadixThreads);
+    compact_kernel<<<grid, kRadixThreads, 0, stream>>>(d_samples, n, key_base, top, nprefix, s.d_prefix, s.d_compact,
+                                                      s.d_compact_n, s.compact_cap);
     return cudaGetLastError();
 }
 

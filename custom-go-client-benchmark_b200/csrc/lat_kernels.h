@@ -42,6 +42,9 @@ struct LatScratch {
     LatMoments* d_mom;
     unsigned long long* d_radix;        // [kMaxSelect][kRadixBins]
     unsigned long long* d_prefix;       // [kMaxSelect]
+    long long* d_compact;               // samples of the buckets still in play after the first radix pass (lazy)
+    size_t compact_cap;                 // in samples
+    unsigned long long* d_compact_n;    // device counter
 };
 
 cudaError_t lat_scratch_init(LatScratch* s);
@@ -56,6 +59,10 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
 cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned long long key_base, int shift, int top,
                               int nk, const LatScratch& s, cudaStream_t stream);
 cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch& s, cudaStream_t stream);
+// Append to s.d_compact every sample whose key' >> top equals one of the nprefix (distinct) values in
+// s.d_prefix; the count lands in *s.d_compact_n.  At most s.compact_cap samples are written.
+cudaError_t launch_compact(const long long* d_samples, size_t n, unsigned long long key_base, int top, int nprefix,
+                           const LatScratch& s, cudaStream_t stream);
 
 // Latency text codec + float64 histogram (text_kernels.cu)
 size_t text_tiles(size_t nbytes);

@@ -149,6 +149,28 @@ def test_select_every_rank_with_duplicates_and_negatives(ctx):
     ctx.free_device(d)
 
 
+def test_select_with_bucket_compaction_unaligned(ctx):
+    """n >= 2^20 makes the select copy the surviving buckets after its first pass; unaligned start, odd count."""
+    n = 3_000_002
+    d = ctx.alloc_device(n * 8)
+    ctx.fill_latency_ns(d, n, oracle.SEED, first=77)
+    ns = oracle.latency_ns(n, first=77)
+    for start, cnt in [(1, n - 1), (0, n), (3, 2_500_000)]:
+        srt = np.sort(oracle.ns_to_us(ns[start:start + cnt]))
+        ks = [0, 1, cnt // 5, cnt // 2, 9 * cnt // 10, 99 * cnt // 100, cnt - 2, cnt - 1]
+        got = lat.select_kth(d + 8 * start, cnt, 1000, ks, ctx=ctx)
+        assert got == [int(srt[k]) for k in ks], (start, cnt)
+    # a spike: most samples in one bucket (compaction is skipped, the full-data path must agree)
+    spike = np.full(2_000_000, 57_000_123, dtype=np.int64)
+    spike[::1000] = np.arange(2000) * 5_000_000
+    ds = upload(ctx, spike)
+    srt = np.sort(spike)
+    assert lat.select_kth(ds, spike.size, 1, [0, 999, 1_000_000, spike.size - 1], ctx=ctx) == [
+        int(srt[0]), int(srt[999]), int(srt[1_000_000]), int(srt[-1])]
+    ctx.free_device(ds)
+    ctx.free_device(d)
+
+
 def test_select_all_equal_and_empty(ctx):
     ns = np.full(1000, 123456789, dtype=np.int64)
     d = upload(ctx, ns)

@@ -36,3 +36,13 @@ ks = np.array([n // 5, n // 2, 9 * n // 10, 99 * n // 100], dtype=np.uint64)
 out = np.zeros(4, dtype=np.int64)
 ms = timeit(lambda: L.b200_select_kth(h, 0, d, n, 1000, ks.ctypes.data, 4, out.ctypes.data))
 print(f"select 4 ranks         : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s   {out}")
+# radix building blocks
+kmin = (mn.value + (1 << 63)) & ((1 << 64) - 1)
+bits = (mx.value - mn.value).bit_length()
+cnt = np.zeros(4 * 4096, dtype=np.uint64)
+pf = np.zeros(4, dtype=np.uint64)
+ms = timeit(lambda: L.b200_radix_count(h, 0, d, n, kmin, bits - 12, bits, 1, pf.ctypes.data, cnt.ctypes.data))
+print(f"radix pass 1 (1 histogram, all samples) : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s   bits={bits}")
+pf[:] = [19, 23, 29, 38]
+ms = timeit(lambda: L.b200_radix_count(h, 0, d, n, kmin, bits - 24, bits - 12, 4, pf.ctypes.data, cnt.ctypes.data))
+print(f"radix pass 2 (4 prefixes, full data)    : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s")

@@ -160,6 +160,15 @@ def test_select_with_bucket_compaction_unaligned(ctx):
         ks = [0, 1, cnt // 5, cnt // 2, 9 * cnt // 10, 99 * cnt // 100, cnt - 2, cnt - 1]
         got = lat.select_kth(d + 8 * start, cnt, 1000, ks, ctx=ctx)
         assert got == [int(srt[k]) for k in ks], (start, cnt)
+    # spread-out values: each wanted rank's bucket holds ~1/4096 of the samples, so the compaction path runs
+    rng = np.random.default_rng(9)
+    wide = rng.integers(-2**39, 2**39, size=(1 << 21) + 3).astype(np.int64)
+    dw = upload(ctx, wide)
+    for start, cnt in [(0, wide.size), (1, wide.size - 2)]:
+        srt = np.sort(wide[start:start + cnt])
+        ks = [0, 7, cnt // 5, cnt // 2, cnt // 2 + 1, 9 * cnt // 10, 99 * cnt // 100, cnt - 1]
+        assert lat.select_kth(dw + 8 * start, cnt, 1, ks, ctx=ctx) == [int(srt[k]) for k in ks]
+    ctx.free_device(dw)
     # a spike: most samples in one bucket (compaction is skipped, the full-data path must agree)
     spike = np.full(2_000_000, 57_000_123, dtype=np.int64)
     spike[::1000] = np.arange(2000) * 5_000_000

@@ -228,8 +228,9 @@ int ensure_stage(DevState* d, size_t bytes) {
     return 0;
 }
 
-// Enqueue CRC of one device buffer on d->stream; result lands in d->d_got[slot].  Caller holds d->mu.
-int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc, int slot) {
+// Enqueue CRC of one device buffer on d->stream; result lands in d->d_got[slot], or — when `running` is given —
+// the CRC at *running (device) is continued over the buffer and written back there.  Caller holds d->mu.
+int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc, int slot, uint32_t* running = nullptr) {
     uintptr_t addr = (uintptr_t)dptr;
     uintptr_t base = addr & ~(uintptr_t)15;
     BatchArgs a{};
@@ -250,7 +251,8 @@ int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc,
     a.nfull_tasks = (uint32_t)(cut.rows / a.rows_per_seg);
     a.npartial_tasks = a.ntasks - a.nfull_tasks;
     a.seg_raw = d->seg_raw;
-    a.got = d->d_got + slot;
+    a.got = running ? running : d->d_got + slot;
+    a.init_ptr = running;
     a.ok = d->d_ok;
     a.nbad = d->d_nbad;
     a.init_crc = init_crc;
@@ -981,13 +983,39 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
 
 struct b200_hasher {
     b200_ctx* ctx = nullptr;
+    DevState* d = nullptr;
     int dev = 0;
-    uint32_t crc = 0;      // CRC of everything flushed so far
-    uint8_t* buf = nullptr;  // pinned
+    // Two pinned staging buffers and their device twins.  A full buffer is handed to the GPU (H2D on the copy
+    // stream, kernels on the compute stream, running CRC kept on the device) while the caller fills the other;
+    // only Sum32 waits for the GPU.
+    uint8_t* h_buf[2] = {nullptr, nullptr};
+    uint8_t* d_buf[2] = {nullptr, nullptr};
+    cudaEvent_t copied[2] = {nullptr, nullptr}, done[2] = {nullptr, nullptr};
+    bool pending[2] = {false, false};
+    uint32_t* d_state = nullptr;  // CRC of everything handed over so far
+    uint32_t* h_state = nullptr;  // pinned
+    int cur = 0;
     size_t fill = 0, cap = 0;
 };
 
 extern "C" {
+
+int b200_hasher_free(b200_hasher* h) {
+    if (!h) return 0;
+    cudaSetDevice(h->dev);
+    for (int b = 0; b < 2; b++) {
+        if (h->pending[b]) cudaEventSynchronize(h->done[b]);
+        cudaFreeHost(h->h_buf[b]);
+        cudaFree(h->d_buf[b]);
+        if (h->copied[b]) cudaEventDestroy(h->copied[b]);
+        if (h->done[b]) cudaEventDestroy(h->done[b]);
+    }
+    cudaFree(h->d_state);
+    cudaFreeHost(h->h_state);
+    cudaGetLastError();
+    delete h;
+    return 0;
+}
 
 int b200_hasher_new(b200_ctx* ctx, int dev, b200_hasher** out) {
     DevState* d = get_dev(ctx, dev);
@@ -995,25 +1023,48 @@ int b200_hasher_new(b200_ctx* ctx, int dev, b200_hasher** out) {
     b200_hasher* h = new (std::nothrow) b200_hasher;
     if (!h) return fail(B200_ERR_NOMEM, "b200_hasher_new");
     h->ctx = ctx;
+    h->d = d;
     h->dev = dev;
     h->cap = 8u << 20;  // four of the read loop's 2 MiB buffers (main.go:125)
-    CU(cudaSetDevice(dev));
-    cudaError_t e = cudaHostAlloc(&h->buf, h->cap, cudaHostAllocDefault);
+    cudaError_t e = cudaSetDevice(dev);
+    for (int b = 0; b < 2 && e == cudaSuccess; b++) {
+        e = cudaHostAlloc(&h->h_buf[b], h->cap, cudaHostAllocDefault);
+        if (e == cudaSuccess) e = cudaMalloc(&h->d_buf[b], h->cap);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->copied[b], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&h->done[b], cudaEventDisableTiming);
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_state, sizeof(uint32_t));
+    if (e == cudaSuccess) e = cudaHostAlloc(&h->h_state, sizeof(uint32_t), cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaMemset(h->d_state, 0, sizeof(uint32_t));
     if (e != cudaSuccess) {
-        delete h;
-        return fail_cuda(e, "cudaHostAlloc");
+        b200_hasher_free(h);
+        return fail_cuda(e, "b200_hasher_new");
     }
     *out = h;
     return 0;
 }
 
+// Hand the current staging buffer to the GPU (asynchronously) and switch to the other one.
 static int hasher_flush(b200_hasher* h) {
     if (!h->fill) return 0;
-    uint32_t c = 0;
-    int rc = b200_crc32c_stream_host(h->ctx, h->dev, h->crc, h->buf, h->fill, h->cap, &c);
-    if (rc) return rc;
-    h->crc = c;
+    DevState* d = h->d;
+    const int b = h->cur;
+    {
+        std::lock_guard<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(h->dev));
+        CU(cudaMemcpyAsync(h->d_buf[b], h->h_buf[b], h->fill, cudaMemcpyHostToDevice, d->copy_stream));
+        CU(cudaEventRecord(h->copied[b], d->copy_stream));
+        CU(cudaStreamWaitEvent(d->stream, h->copied[b], 0));
+        if (int rc = enqueue_single(d, h->d_buf[b], h->fill, 0, 0, h->d_state)) return rc;
+        CU(cudaEventRecord(h->done[b], d->stream));
+    }
+    h->pending[b] = true;
+    h->cur = b ^ 1;
     h->fill = 0;
+    if (h->pending[h->cur]) {  // the buffer we are about to fill must have been consumed
+        CU(cudaEventSynchronize(h->done[h->cur]));
+        h->pending[h->cur] = false;
+    }
     return 0;
 }
 
@@ -1022,7 +1073,7 @@ int b200_hasher_write(b200_hasher* h, const void* p, size_t n) {
     const uint8_t* s = (const uint8_t*)p;
     while (n) {
         size_t take = std::min(n, h->cap - h->fill);
-        memcpy(h->buf + h->fill, s, take);
+        memcpy(h->h_buf[h->cur] + h->fill, s, take);
         h->fill += take;
         s += take;
         n -= take;
@@ -1036,7 +1087,7 @@ int b200_hasher_reserve(b200_hasher* h, void** ptr, size_t* avail) {
     if (!h || !ptr || !avail) return fail(B200_ERR_INVALID, "b200_hasher_reserve");
     if (h->fill == h->cap)
         if (int rc = hasher_flush(h)) return rc;
-    *ptr = h->buf + h->fill;
+    *ptr = h->h_buf[h->cur] + h->fill;
     *avail = h->cap - h->fill;
     return 0;
 }
@@ -1051,22 +1102,29 @@ int b200_hasher_commit(b200_hasher* h, size_t n) {
 int b200_hasher_sum32(b200_hasher* h, uint32_t* out) {
     if (!h || !out) return fail(B200_ERR_INVALID, "b200_hasher_sum32");
     if (int rc = hasher_flush(h)) return rc;
-    *out = h->crc;
+    DevState* d = h->d;
+    cudaEvent_t last = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(h->dev));
+        CU(cudaMemcpyAsync(h->h_state, h->d_state, sizeof(uint32_t), cudaMemcpyDeviceToHost, d->stream));
+        // wait for this hasher's own work only: other hashers keep the stream busy
+        last = h->done[h->cur ^ 1];
+        CU(cudaEventRecord(last, d->stream));
+    }
+    CU(cudaEventSynchronize(last));
+    h->pending[0] = h->pending[1] = false;  // everything before `last` on the stream has finished
+    *out = *h->h_state;
     return 0;
 }
 
 int b200_hasher_reset(b200_hasher* h) {
     if (!h) return fail(B200_ERR_INVALID, "b200_hasher_reset");
-    h->crc = 0;
+    DevState* d = h->d;
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(h->dev));
+    CU(cudaMemsetAsync(h->d_state, 0, sizeof(uint32_t), d->stream));  // ordered after the chunks already queued
     h->fill = 0;
-    return 0;
-}
-
-int b200_hasher_free(b200_hasher* h) {
-    if (!h) return 0;
-    cudaSetDevice(h->dev);
-    cudaFreeHost(h->buf);
-    delete h;
     return 0;
 }
 

@@ -170,8 +170,8 @@ crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict
                     const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ want,
                     const uint32_t* __restrict__ seg_raw, const uint32_t* __restrict__ adv_seg,
                     const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab, uint32_t rows_per_seg,
-                    uint32_t init_crc, uint64_t single_off, uint64_t single_len, uint32_t* __restrict__ got,
-                    uint8_t* __restrict__ ok, unsigned long long* nbad) {
+                    uint32_t init_crc, const uint32_t* init_ptr, uint64_t single_off, uint64_t single_len,
+                    uint32_t* got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
     __shared__ uint32_t red[kFinalThreads / 32];
     const uint32_t obj = blockIdx.x;
     const uint64_t o = off ? off[obj] : single_off;
@@ -206,7 +206,7 @@ crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict
     }
     if (threadIdx.x != 0) return;
 
-    uint32_t s = ~init_crc;
+    uint32_t s = ~(init_ptr ? *init_ptr : init_crc);
     for (uint32_t i = 0; i < cut.head; i++) s = (s >> 8) ^ __ldg(byte_tab + ((s ^ p[i]) & 0xFF));
     if (nfull) s = gf2_mul(gf2_xpow8(nfull * seg_bytes, xsq), s) ^ F;
     if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first + nfull];
@@ -371,7 +371,7 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     else if (a.nobj)
         crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, a.seg_start, a.want, a.seg_raw,
                                                                   a.adv_seg, t.xpow8_sq, t.byte_tab, a.rows_per_seg,
-                                                                  a.init_crc, a.single_off, a.single_len, a.got, a.ok,
+                                                                  a.init_crc, a.init_ptr, a.single_off, a.single_len, a.got, a.ok,
                                                                   a.nbad);
     return cudaGetLastError();
 }

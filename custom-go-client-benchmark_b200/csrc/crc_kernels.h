@@ -57,6 +57,8 @@ struct BatchArgs {
     uint32_t ntasks;
     uint32_t rows_per_seg;
     uint32_t init_crc;          // crc32.Update's first argument, same for every object (0 = fresh checksum)
+    const uint32_t* init_ptr;   // single-object mode: when set, the first argument is read from the device
+                                // (may alias `got`: a running CRC that stays on the device between chunks)
     // single-object mode (off == nullptr): the object is base[single_off .. single_off+single_len) and owns
     // tasks 0..ntasks-1; no plan arrays are read.
     uint64_t single_off;

@@ -57,6 +57,24 @@ def measured_peaks():
         return 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md); MEASURED_PEAKS.json absent"
 
 
+def cuda_pci_bus_id(index: int):
+    """PCI bus id of CUDA device `index` (NVML numbers GPUs differently under CUDA_VISIBLE_DEVICES)."""
+    import ctypes
+    lib = importlib.import_module("custom-go-client-benchmark_b200")._lib.load()
+    buf = ctypes.create_string_buffer(32)
+    return buf.value.decode() if lib.b200_device_pci_bus_id(index, buf, 32) == 0 else None
+
+
+def nvml_handle(pynvml, index: int):
+    bus = cuda_pci_bus_id(index)
+    if bus:
+        try:
+            return pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+        except Exception:
+            pass
+    return pynvml.nvmlDeviceGetHandleByIndex(index)
+
+
 class ClockSampler:
     """Samples SM clock and throttle reasons through NVML while the timed region runs."""
 
@@ -68,7 +86,7 @@ class ClockSampler:
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
-            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.h = nvml_handle(pynvml, index)
             self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
         except Exception as e:  # NVML missing: report that rather than invent numbers
             self.nv, self.err = None, repr(e)
@@ -115,11 +133,9 @@ def bind_to_gpu_numa_node(index: int):
     pinned host buffers of the e2e path land on the GPU's own NUMA node (8 ranks streaming 8 GiB each would
     otherwise cross sockets).  Best effort: returns a description for the JSON line."""
     try:
-        import pynvml
-        pynvml.nvmlInit()
-        h = pynvml.nvmlDeviceGetHandleByIndex(index)
-        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
-        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bus = cuda_pci_bus_id(index)
+        if not bus:
+            return "not bound (no PCI bus id)"
         path = f"/sys/bus/pci/devices/{bus[-12:].lower()}/local_cpulist"
         cpus = set()
         for part in open(path).read().strip().split(","):

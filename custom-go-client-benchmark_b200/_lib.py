@@ -36,6 +36,7 @@ SIGNATURES = {
     "b200_strerror": (C.c_char_p, [_int]),
     "b200_last_error": (C.c_char_p, []),
     "b200_device_count": (_int, [C.POINTER(_int)]),
+    "b200_device_pci_bus_id": (_int, [_int, C.c_char_p, _int]),
     "b200_init": (_int, [_int, C.POINTER(_int), _pp]),
     "b200_shutdown": (_int, [_vp]),
     "b200_ctx_ndev": (_int, [_vp]),

@@ -348,6 +348,12 @@ int b200_device_count(int* n) {
     return 0;
 }
 
+int b200_device_pci_bus_id(int dev, char* buf, int len) {
+    if (!buf || len < 16) return fail(B200_ERR_INVALID, "b200_device_pci_bus_id: buffer of at least 16 bytes");
+    CU(cudaDeviceGetPCIBusId(buf, len, dev));
+    return 0;
+}
+
 int b200_init(int ndev, const int* devs, b200_ctx** out) {
     if (!out || ndev < 1) return fail(B200_ERR_INVALID, "b200_init: ndev < 1 or out is null");
     int have = 0;

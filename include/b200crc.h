@@ -41,6 +41,8 @@ typedef struct b200_batch b200_batch;   /* a prepared VerifyObjects plan for dev
 const char* b200_strerror(int status);
 const char* b200_last_error(void);
 int b200_device_count(int* n);
+/* PCI bus id ("0000:1b:00.0") of CUDA device `dev`, e.g. to find the same GPU in NVML or its NUMA node in sysfs. */
+int b200_device_pci_bus_id(int dev, char* buf, int len);
 
 /* devs == NULL means devices 0..ndev-1.  Replaces nothing in the reference (it has no device). */
 int b200_init(int ndev, const int* devs, b200_ctx** out);

@@ -264,9 +264,14 @@ class Percentiles:
 
 
 def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Optional[Context] = None,
-                dev: Optional[int] = None, group=None, reduce_device=None) -> Percentiles:
-    dist_ = hist_fixed(d_samples_ns, n, divisor, OC_DEFAULT_LATENCY_BOUNDS, HIST_OPENCENSUS, ctx=ctx, dev=dev,
-                       group=group, reduce_device=reduce_device)
+                dev: Optional[int] = None, group=None, reduce_device=None,
+                dist: Optional[Distribution] = None) -> Percentiles:
+    """avg / P20 / P50 / P90 / p99 / min / max of trunc(sample/divisor) exactly as ssd_test/main.go:147-163 prints
+    them.  `dist` may be a Distribution already computed over the same samples WITH THE SAME divisor (any
+    edges): its count, sum and min/max are reused instead of a second pass over the data."""
+    dist_ = dist if dist is not None else hist_fixed(d_samples_ns, n, divisor, OC_DEFAULT_LATENCY_BOUNDS,
+                                                     HIST_OPENCENSUS, ctx=ctx, dev=dev, group=group,
+                                                     reduce_device=reduce_device)
     size = dist_.count
     if size == 0:
         raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")

@@ -27,15 +27,51 @@ constexpr int kTileBytes = kTextThreads * 16;
 __constant__ double c_pow10[23] = {1e0,  1e1,  1e2,  1e3,  1e4,  1e5,  1e6,  1e7,  1e8,  1e9,  1e10, 1e11,
                                    1e12, 1e13, 1e14, 1e15, 1e16, 1e17, 1e18, 1e19, 1e20, 1e21, 1e22};
 
+constexpr int kHalo = 256;  // bytes staged beyond the tile: lines are short, longer ones fall back to global reads
+
+// The bytes of one tile (plus one byte before and kHalo after) staged in shared memory; anything else is read
+// from global memory.
+struct TextView {
+    const unsigned char* g;
+    const unsigned char* sm;
+    size_t sbase, send;  // [sbase, send) is staged
+    __device__ __forceinline__ unsigned char operator[](size_t i) const {
+        return (i >= sbase && i < send) ? sm[i - sbase] : __ldg(g + i);
+    }
+};
+
+// cooperative load of tile `tile` into sm (kTileBytes + kHalo + 16 bytes)
+__device__ __forceinline__ TextView stage_tile(const unsigned char* __restrict__ t, size_t n, size_t tile,
+                                               unsigned char* sm) {
+    const size_t tbase = tile * (size_t)kTileBytes;
+    const size_t sbase = tbase ? tbase - 16 : 0;                       // keeps 16-byte alignment of the copies
+    size_t send = tbase + kTileBytes + kHalo;
+    if (send > n) send = n;
+    const size_t len = send > sbase ? send - sbase : 0;
+    if ((reinterpret_cast<uintptr_t>(t) & 15) == 0) {
+        const size_t nvec = len / 16;
+        const uint4* src = reinterpret_cast<const uint4*>(t + sbase);
+        uint4* dst = reinterpret_cast<uint4*>(sm);
+        for (size_t i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = __ldg(src + i);
+        for (size_t i = nvec * 16 + threadIdx.x; i < len; i += blockDim.x) sm[i] = __ldg(t + sbase + i);
+    } else {
+        for (size_t i = threadIdx.x; i < len; i += blockDim.x) sm[i] = __ldg(t + sbase + i);
+    }
+    __syncthreads();
+    return TextView{t, sm, sbase, send};
+}
+
 __device__ __forceinline__ bool is_space(unsigned char c) {
     return c == ' ' || (c >= 9 && c <= 13) || (c >= 0x1c && c <= 0x1f);
 }
-__device__ __forceinline__ bool line_ends_at(const unsigned char* t, size_t n, size_t i) {
+template <typename Text>
+__device__ __forceinline__ bool line_ends_at(const Text& t, size_t n, size_t i) {
     return t[i] == '\n' || (t[i] == '\r' && (i + 1 >= n || t[i + 1] != '\n'));
 }
 
 // bit k of the result: a line starts at byte base + k (k < 16)
-__device__ __forceinline__ unsigned start_mask(const unsigned char* __restrict__ t, size_t n, size_t base) {
+template <typename Text>
+__device__ __forceinline__ unsigned start_mask(const Text& t, size_t n, size_t base) {
     unsigned m = 0;
     if (base >= n) return 0;
 #pragma unroll
@@ -47,8 +83,10 @@ __device__ __forceinline__ unsigned start_mask(const unsigned char* __restrict__
 }
 
 __global__ void __launch_bounds__(kTextThreads)
-text_count_kernel(const unsigned char* __restrict__ t, size_t n, unsigned long long* __restrict__ tile_counts) {
+text_count_kernel(const unsigned char* __restrict__ tg, size_t n, unsigned long long* __restrict__ tile_counts) {
     __shared__ unsigned wsum[kTextThreads / 32];
+    __shared__ __align__(16) unsigned char stage[kTileBytes + kHalo + 16];
+    const TextView t = stage_tile(tg, n, blockIdx.x, stage);
     const size_t base = ((size_t)blockIdx.x * kTextThreads + threadIdx.x) * 16;
     unsigned c = __popc(start_mask(t, n, base));
 #pragma unroll
@@ -96,14 +134,16 @@ struct Parsed {
 
 __device__ __forceinline__ unsigned char lower(unsigned char c) { return (c >= 'A' && c <= 'Z') ? c + 32 : c; }
 
-__device__ bool match_word(const unsigned char* t, size_t s, size_t e, const char* w) {
+template <typename Text>
+__device__ bool match_word(const Text& t, size_t s, size_t e, const char* w) {
     size_t i = s;
     for (; *w; w++, i++)
         if (i >= e || lower(t[i]) != (unsigned char)*w) return false;
     return i == e;
 }
 
-__device__ Parsed parse_float(const unsigned char* __restrict__ t, size_t n, size_t s) {
+template <typename Text>
+__device__ Parsed parse_float(const Text& t, size_t n, size_t s) {
     Parsed r{0.0, 1};
     size_t e = s;
     while (e < n && !line_ends_at(t, n, e)) e++;  // e = terminator (or n)
@@ -209,10 +249,12 @@ __device__ Parsed parse_float(const unsigned char* __restrict__ t, size_t n, siz
 }
 
 __global__ void __launch_bounds__(kTextThreads)
-text_parse_kernel(const unsigned char* __restrict__ t, size_t n, const unsigned long long* __restrict__ tile_base,
+text_parse_kernel(const unsigned char* __restrict__ tg, size_t n, const unsigned long long* __restrict__ tile_base,
                   double* __restrict__ values, unsigned char* __restrict__ status, size_t max_lines,
                   unsigned long long* __restrict__ summary /* [0] first bad line, [1] bad count, [2] inexact count */) {
     __shared__ unsigned wsum[kTextThreads / 32];
+    __shared__ __align__(16) unsigned char stage[kTileBytes + kHalo + 16];
+    const TextView t = stage_tile(tg, n, blockIdx.x, stage);
     const size_t base = ((size_t)blockIdx.x * kTextThreads + threadIdx.x) * 16;
     const unsigned m = start_mask(t, n, base);
     const unsigned c = __popc(m);

@@ -108,6 +108,25 @@ def test_float_grammar_cases(ctx):
 
 
 @pytest.mark.gpu
+def test_unaligned_text_pointer_and_long_lines(ctx):
+    # lines longer than the staged halo, tile-boundary straddling, and a text buffer that is not 16-byte aligned
+    lines = ["1.5"] * 700 + [" " * 300 + "42.25" + " " * 300, "x" * 5000, "7e0"] + ["0.125  "] * 900
+    data = ("\n".join(lines) + "\n").encode()
+    ref, bad = reference_script(data)
+    d = ctx.alloc_device(len(data) + 16)
+    for shift in (0, 1, 7):
+        ctx.h2d(d + shift, np.frombuffer(data, dtype=np.uint8))
+        p = lat.parse_latency_text(d + shift, len(data), len(lines) + 1, ctx=ctx)
+        vals = np.zeros(p.nlines); stat = np.zeros(p.nlines, dtype=np.uint8)
+        ctx.d2h(vals, p.d_values); ctx.d2h(stat, p.d_status)
+        ctx.free_device(p.d_values); ctx.free_device(p.d_status)
+        assert p.nlines == len(ref) and p.first_bad_line == bad[0] and p.nbad == len(bad) == 1
+        good = stat == 0
+        assert [v for v, g in zip(vals, good) if g] == [r for r in ref if r is not None]
+    ctx.free_device(d)
+
+
+@pytest.mark.gpu
 def test_documented_deviation_non_ascii(ctx):
     # Python's float() also accepts Unicode decimal digits and strips U+00A0 / U+0085; the codec is ASCII only
     # and reports such lines as unparsable (the reference pipeline — Go's Duration.String() — never emits them).

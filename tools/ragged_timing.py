@@ -45,11 +45,13 @@ reps = nl // 200_000
 data = np.frombuffer(chunk * reps, dtype=np.uint8)
 dt = ctx.alloc_device(data.size)
 ctx.h2d(dt, data)
-p = lat.parse_latency_text(dt, data.size, nl, ctx=ctx)
-ctx.free_device(p.d_values); ctx.free_device(p.d_status)
+import ctypes as C
+dv = ctx.alloc_device(nl * 8); dst = ctx.alloc_device(nl)
+out = [C.c_uint64() for _ in range(4)]
+call = lambda: pkg._lib.check(ctx._L.b200_parse_latency_text(ctx._h, 0, dt, data.size, dv, dst, nl, *[C.byref(o) for o in out]))
+call()
 t0 = time.perf_counter()
-for _ in range(3):
-    p = lat.parse_latency_text(dt, data.size, nl, ctx=ctx)
-    ctx.free_device(p.d_values); ctx.free_device(p.d_status)
-ms = (time.perf_counter() - t0) / 3 * 1e3
-print(f"text parse: {p.nlines} lines, {data.size/1e6:.1f} MB in {ms:.2f} ms -> {data.size/ms/1e6:.1f} GB/s, {p.nlines/ms/1e3:.1f} Mlines/s (bad={p.nbad})")
+for _ in range(5):
+    call()
+ms = (time.perf_counter() - t0) / 5 * 1e3
+print(f"text parse: {out[0].value} lines, {data.size/1e6:.1f} MB in {ms:.2f} ms -> {data.size/ms/1e6:.1f} GB/s, {out[0].value/ms/1e3:.1f} Mlines/s (bad={out[2].value})")

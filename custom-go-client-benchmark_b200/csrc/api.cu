@@ -167,13 +167,13 @@ int get_adv_seg(DevState* d, uint32_t rows_per_seg, const uint32_t** out) {
 
 constexpr uint32_t kMaxRowsPerSeg = 2048;  // 1 MiB segments: 32 KB per lane in the fold kernel
 
-uint32_t env_rows_per_seg() {
-    static int v = -1;
-    if (v < 0) {
+uint32_t env_rows_per_seg() {  // test / tuning override, read once
+    static const uint32_t v = [] {
         const char* e = getenv("B200_ROWS_PER_SEG");
-        v = e ? atoi(e) : 0;
-    }
-    return (uint32_t)v;
+        const int x = e ? atoi(e) : 0;
+        return (uint32_t)(x > 0 ? x : 0);
+    }();
+    return v;
 }
 
 // Segment length (rows, a power of two).  Full segments of >= 256 rows are folded by K2 (8 warps per SM); we

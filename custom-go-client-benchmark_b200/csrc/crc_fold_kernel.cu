@@ -222,12 +222,11 @@ const FoldVariant kVariants[] = {
 };
 
 const FoldVariant& fold_variant() {
-    static int v = -1;
-    if (v < 0) {
+    static const int v = [] {  // tuning override, read once
         const char* e = getenv("B200_FOLD_VARIANT");
-        v = e ? atoi(e) : 0;
-        if (v < 0 || v >= (int)(sizeof kVariants / sizeof kVariants[0])) v = 0;
-    }
+        const int x = e ? atoi(e) : 0;
+        return (x < 0 || x >= (int)(sizeof kVariants / sizeof kVariants[0])) ? 0 : x;
+    }();
     return kVariants[v];
 }
 

@@ -308,11 +308,10 @@ __global__ void fill_latency_kernel(int64_t* __restrict__ dst, uint64_t first, s
 // dynamic shared memory: everything up to the end of the tables at absolute 0x10000 + 128 KB (the driver's
 // reserved 1 KB sits below the dynamic window; the kernel checks the window start at run time)
 bool fold_enabled(uint32_t rows_per_seg) {
-    static int disabled = -1;
-    if (disabled < 0) {
+    static const bool disabled = [] {  // A/B switch, read once
         const char* e = getenv("B200_NO_FOLD");
-        disabled = (e && *e && *e != '0') ? 1 : 0;
-    }
+        return e && *e && *e != '0';
+    }();
     return !disabled && rows_per_seg >= kFoldMinRows && rows_per_seg % 16 == 0;
 }
 

@@ -13,13 +13,12 @@ void host_build_xpow8_sq(uint32_t out[64]) {
 }
 
 uint32_t host_xpow8(uint64_t nbytes) {
-    static uint32_t sq[64];
-    static bool ready = false;
-    if (!ready) {  // benign race: every thread writes identical values
-        host_build_xpow8_sq(sq);
-        ready = true;
-    }
-    return gf2_xpow8(nbytes, sq);
+    struct Squares {
+        uint32_t sq[64];
+        Squares() { host_build_xpow8_sq(sq); }
+    };
+    static const Squares s;  // thread-safe one-time initialisation
+    return gf2_xpow8(nbytes, s.sq);
 }
 
 // out[t*256 + v] = x^(8*nbytes) * (v << 8t): slicing tables for "advance a register over nbytes zero bytes"

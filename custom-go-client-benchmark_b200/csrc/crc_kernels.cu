@@ -103,13 +103,29 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t k3 = __ldg(col_k + lane4 + 3);  // x^(32*(128-c)) of this lane's last column c = 4*lane+3
     const uint32_t nwarps = gridDim.x * kRowsWarps;
+    // Every warp takes a CONTIGUOUS run of tasks, so the object a task belongs to is found by one binary search
+    // at the start and a forward walk afterwards (a search per task is a ~20-deep chain of dependent loads,
+    // which is what bounds batches of small objects).  Warps are numbered CTA-major across the grid.
+    const uint32_t gw = warp * gridDim.x + blockIdx.x;
+    const uint32_t task_lo = (uint32_t)((uint64_t)ntasks * gw / nwarps);
+    const uint32_t task_hi = (uint32_t)((uint64_t)ntasks * (gw + 1) / nwarps);
+    uint32_t obj = 0, obj_first = 0, obj_next = ntasks;  // tasks [obj_first, obj_next) belong to obj
+    if (off && task_lo < task_hi) {
+        obj = find_object(seg_start, nobj, task_lo);
+        obj_first = __ldg(seg_start + obj);
+        obj_next = __ldg(seg_start + obj + 1);
+    }
 
-    for (uint32_t task = warp * gridDim.x + blockIdx.x; task < ntasks; task += nwarps) {
+    for (uint32_t task = task_lo; task < task_hi; task++) {
         uint32_t seg = task;
         uint64_t o = single_off, n = single_len;
         if (off) {
-            const uint32_t obj = find_object(seg_start, nobj, task);
-            seg = task - __ldg(seg_start + obj);
+            while (task >= obj_next) {  // objects without segments are stepped over
+                obj++;
+                obj_first = obj_next;
+                obj_next = __ldg(seg_start + obj + 1);
+            }
+            seg = task - obj_first;
             o = __ldg(off + obj);
             n = __ldg(len + obj);
         }

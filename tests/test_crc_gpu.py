@@ -450,3 +450,15 @@ def test_sharded_object_over_two_devices_in_one_process():
         c.free_device(ptrs[dev], dev)
         c.free_device(dptr[dev], dev)
     c.close()
+
+
+def test_verify_objects_host_with_an_object_larger_than_a_slab(ctx):
+    """An object bigger than the 256 MiB device slab is streamed on its own, between ordinary slabs."""
+    big = oracle.payload((300 << 20) + 5)
+    bufs = [b"abc", big[:1000], big, big[7:4096 + 7], b""]
+    want = [oracle.crc32c(b) for b in bufs]
+    bad, got = crc32c.VerifyObjects(bufs, want, ctx)
+    assert bad == [] and list(got) == want
+    want[2] ^= 0x100
+    bad, got = crc32c.VerifyObjects(bufs, want, ctx)
+    assert bad == [2]

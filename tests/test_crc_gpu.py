@@ -462,3 +462,47 @@ def test_verify_objects_host_with_an_object_larger_than_a_slab(ctx):
     want[2] ^= 0x100
     bad, got = crc32c.VerifyObjects(bufs, want, ctx)
     assert bad == [2]
+
+
+def test_concurrent_callers_share_one_context(ctx, arena):
+    """48 goroutines call into the reference's storage client at once (main.go:36,200-212); the C ABI promises
+    the same: any entry point from any thread, calls on one device serialise.  ctypes drops the GIL, so these
+    threads really are inside the library together."""
+    from concurrent.futures import ThreadPoolExecutor
+    host, d = arena
+    lat = pkg.latency
+    ns = oracle.latency_ns(300_000)
+    dns = ctx.alloc_device(ns.nbytes)
+    ctx.h2d(dns, ns)
+    ref_hist, _ = oracle.hist_numpy(oracle.ns_to_ms(ns).astype(np.float64))
+    srt = np.sort(oracle.ns_to_us(ns))
+
+    def worker(w):
+        rng = np.random.default_rng(w)
+        for it in range(12):
+            kind = (w + it) % 5
+            start, n = int(rng.integers(0, 4096)), int(rng.integers(1, 6 << 20))
+            want = oracle.crc32c(host[start:start + n])
+            if kind == 0:
+                assert crc32c.UpdateDevice(0, d + start, n, ctx) == want
+            elif kind == 1:
+                assert crc32c.Checksum(host[start:start + n], ctx) == want
+            elif kind == 2:
+                h = crc32c.New(ctx)
+                h.Write(host[start:start + n // 2]); h.Write(host[start + n // 2:start + n])
+                assert h.Sum32() == want
+                h.close()
+            elif kind == 3:
+                bufs = [host[start:start + n], host[start + 5:start + 5 + n // 3]]
+                bad, got = crc32c.VerifyObjects(bufs, [want, oracle.crc32c(bufs[1]) ^ 1], ctx)
+                assert bad == [1] and got[0] == want
+            else:
+                assert list(lat.hist_readme(dns, ns.size, ctx=ctx).counts) == list(ref_hist)
+                k = int(rng.integers(0, ns.size))
+                assert lat.select_kth(dns, ns.size, 1000, [k], ctx=ctx) == [int(srt[k])]
+                assert crc32c.UpdateDeviceNoAlloc(0, d + start, n) == want
+        return True
+
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        assert all(ex.map(worker, range(8)))
+    ctx.free_device(dns)

@@ -506,3 +506,64 @@ def test_concurrent_callers_share_one_context(ctx, arena):
     with ThreadPoolExecutor(max_workers=8) as ex:
         assert all(ex.map(worker, range(8)))
     ctx.free_device(dns)
+
+
+def test_single_bit_walk_across_every_structural_boundary(ctx):
+    """CRC is linear, so a buffer with ONE bit set exercises exactly one weight of the whole scheme: heads,
+    rows, lanes, segments (row kernel and fold kernel), tails.  Random payloads can mask a wrong weight that
+    only a lone bit exposes."""
+    n = (12 << 20) + 531
+    d = ctx.alloc_device(n + 64)
+    zeros = np.zeros(n + 64, dtype=np.uint8)
+    ctx.h2d(d, zeros)
+    base_crc = {s: oracle.crc32c(zeros[s:n]) for s in (0, 5)}
+    seg = 2048 * 512
+    positions = sorted({0, 1, 4, 5, 15, 16, 17, 511, 512, 513, 1023, 8191, 8192, 16383, 16384, 32767, 32768,
+                        65535, 65536, 65537, (1 << 20) - 1, 1 << 20, (1 << 20) + 1, seg - 1, seg, seg + 1,
+                        2 * seg + 300, 5 * seg - 1, 5 * seg, 11 * seg + 7, n - 532, n - 531, n - 530, n - 17, n - 16,
+                        n - 2, n - 1} | {k * 32768 + 5 for k in range(1, 40, 7)} | {k * 16384 for k in range(1, 64, 9)})
+    one = np.zeros(1, dtype=np.uint8)
+    for pos in positions:
+        for bit in (0, 7):
+            one[0] = 1 << bit
+            ctx.h2d(d + pos, one)
+            for start in (0, 5):
+                if pos < start:
+                    continue
+                host = zeros[start:n].copy()
+                host[pos - start] = one[0]
+                got = crc32c.UpdateDevice(0, d + start, n - start, ctx)
+                assert got == oracle.crc32c(host), (pos, bit, start)
+                assert got != base_crc[start]
+            one[0] = 0
+            ctx.h2d(d + pos, one)
+    ctx.free_device(d)
+
+
+@pytest.mark.parametrize("rps", ["256", "1024"])
+def test_single_bit_walk_through_the_fold_kernel(rps):
+    """Same walk with the segment length forced so the fold kernel takes the full segments: lone bits at stage
+    (256 B), lane (rps*16 B) and segment (rps*512 B) boundaries, in the first/last word of the 64-word window."""
+    import subprocess, sys
+    code = (
+        "import importlib, os, numpy as np, oracle\n"
+        "pkg = importlib.import_module('custom-go-client-benchmark_b200')\n"
+        "c = pkg.crc32c.Context([0])\n"
+        "rps = int(os.environ['B200_ROWS_PER_SEG']); S = rps * 16; seg = rps * 512\n"
+        "n = 5 * seg + 777\n"
+        "z = np.zeros(n + 32, dtype=np.uint8)\n"
+        "d = c.alloc_device(z.size); c.h2d(d, z)\n"
+        "pos = sorted({0, 3, 4, 252, 255, 256, 259, 260, 511, 512, S - 1, S, S + 4, 2 * S - 1, 31 * S, 31 * S + 255, seg - 4,\n"
+        "              seg - 1, seg, seg + 1, seg + S, 3 * seg + 17 * S + 300, 4 * seg - 1, 5 * seg - 1, 5 * seg, n - 1})\n"
+        "one = np.zeros(1, dtype=np.uint8)\n"
+        "for p in pos:\n"
+        "    for start in (0, 3):\n"
+        "        if p < start: continue\n"
+        "        one[0] = 0x80; c.h2d(d + p, one)\n"
+        "        h = z[start:n].copy(); h[p - start] = 0x80\n"
+        "        assert pkg.crc32c.UpdateDevice(0xABCD1234, d + start, n - start, c) == oracle.crc32c(h, 0xABCD1234), (p, start)\n"
+        "        one[0] = 0; c.h2d(d + p, one)\n"
+        "print('ok')\n")
+    env = dict(os.environ, B200_ROWS_PER_SEG=rps)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    assert "ok" in subprocess.check_output([sys.executable, "-c", code], env=env, cwd=root, text=True)

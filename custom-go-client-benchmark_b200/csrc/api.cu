@@ -107,13 +107,13 @@ int HostSlab::reserve(size_t nobj) {
     cap = 0;
     CU(cudaMalloc(&d_off, c * 8));
     CU(cudaMalloc(&d_len, c * 8));
-    CU(cudaMalloc(&d_seg, (c + 1) * 4));
+    CU(cudaMalloc(&d_seg, 3 * (c + 1) * 4));
     CU(cudaMalloc(&d_want, c * 4));
     CU(cudaMalloc(&d_got, c * 4));
     CU(cudaMalloc(&d_ok, c));
     CU(cudaHostAlloc(&h_off, c * 8, cudaHostAllocDefault));
     CU(cudaHostAlloc(&h_len, c * 8, cudaHostAllocDefault));
-    CU(cudaHostAlloc(&h_seg, (c + 1) * 4, cudaHostAllocDefault));
+    CU(cudaHostAlloc(&h_seg, 3 * (c + 1) * 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&h_want, c * 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&h_got, c * 4, cudaHostAllocDefault));
     CU(cudaHostAlloc(&h_ok, c, cudaHostAllocDefault));
@@ -176,33 +176,95 @@ uint32_t env_rows_per_seg() {  // test / tuning override, read once
     return v;
 }
 
-// Segment length (rows, a power of two).  Full segments of >= 256 rows are folded by K2 (8 warps per SM); we
-// want the longest segment that still gives every K2 warp ~6 (at least 2) of them and leaves at most ~10 % of
-// the rows in partial segments.  Inputs too small or too ragged for that use K1's finer grain (32 warps per SM).
+constexpr uint32_t kShortRows = 256;  // short segments: 128 KB, 4 KB per lane in the fold kernel
+
+// The segmentation of a batch (see SegPlan in crc_kernels.h) and its task counts.
+struct HostPlan {
+    SegPlan p{16, 0};
+    uint64_t ntasks = 0, nlong = 0, nshort = 0, npartial = 0, max_long = 0;
+};
+
+// Long segments: the longest power of two (<= 2048 rows) that still gives every warp of the fold kernel
+// (8 per SM) ~6, or at least 2, of them; what the long segments leave over in each object is cut into short
+// 256-row segments, which the fold kernel also takes, so only < 256 rows per object reach the row kernel.
+// Inputs too small for that use the row kernel's finer grain alone (32 warps per SM).
 template <typename RowsOf>
-uint32_t plan_rows_per_seg(size_t nobj, RowsOf rows_of, int grid) {
-    if (uint32_t e = env_rows_per_seg()) return e;
+HostPlan make_plan(size_t nobj, RowsOf rows_of, int grid) {
+    HostPlan h;
     uint64_t total = 0;
     for (size_t i = 0; i < nobj; i++) total += rows_of(i);
-    if (fold_enabled(kMaxRowsPerSeg)) {
+    bool chosen = false;
+    if (uint32_t e = env_rows_per_seg()) {
+        h.p.a = e;
+        h.p.b = (fold_enabled(e) && e > kShortRows && e % kShortRows == 0) ? kShortRows : 0;
+        chosen = true;
+    } else if (fold_enabled(kMaxRowsPerSeg)) {
         const uint64_t warps = (uint64_t)grid * kFoldWarps;
-        for (int pass = 0; pass < 2; pass++) {
+        for (int pass = 0; pass < 2 && !chosen; pass++) {
             const uint64_t want = warps * (pass == 0 ? 6 : 2);
-            for (uint32_t r = kMaxRowsPerSeg; r >= 256; r /= 2) {
+            for (uint32_t r = kMaxRowsPerSeg; r >= kShortRows && !chosen; r /= 2) {
                 uint64_t full = 0;
                 for (size_t i = 0; i < nobj; i++) full += rows_of(i) / r;
-                if (full >= want && full * r * 10 >= total * 9) return r;
+                if (full >= want) {
+                    h.p.a = r;
+                    h.p.b = r > kShortRows ? kShortRows : 0;
+                    chosen = true;
+                }
             }
         }
     }
-    uint64_t target = total / ((uint64_t)grid * kRowsWarps * 6);
-    uint32_t r = 16;
-    while ((uint64_t)r * 2 <= target && r < 1024) r *= 2;
-    return r;
+    if (!chosen) {
+        uint64_t target = total / ((uint64_t)grid * kRowsWarps * 6);
+        uint32_t r = 16;
+        while ((uint64_t)r * 2 <= target && r < 1024) r *= 2;
+        h.p.a = r;
+        h.p.b = 0;
+    }
+    for (;;) {  // task ids are 32-bit
+        h.ntasks = h.nlong = h.nshort = h.npartial = h.max_long = 0;
+        for (size_t i = 0; i < nobj; i++) {
+            const uint64_t rows = rows_of(i), na = rows / h.p.a, rem = rows - na * h.p.a;
+            const uint64_t nb = h.p.b ? rem / h.p.b : 0;
+            h.nlong += na;
+            h.nshort += nb;
+            h.npartial += (rem - nb * h.p.b) ? 1 : 0;
+            h.max_long = std::max(h.max_long, na);
+        }
+        h.ntasks = h.nlong + h.nshort + h.npartial;
+        if (h.ntasks <= (1u << 30)) break;
+        h.p.a *= 2;
+    }
+    return h;
 }
 
-uint32_t choose_rows_per_seg(uint64_t total_rows, int grid) {  // one object
-    return plan_rows_per_seg(1, [&](size_t) { return total_rows; }, grid);
+// per-kind prefix sums of segment counts: out[k * (nobj + 1) + i] (TaskTable in crc_kernels.h)
+template <typename RowsOf>
+void fill_task_prefix(size_t nobj, RowsOf rows_of, SegPlan p, uint32_t* out) {
+    uint64_t run[3] = {0, 0, 0};
+    for (size_t i = 0; i <= nobj; i++) {
+        for (int k = 0; k < 3; k++) out[(size_t)k * (nobj + 1) + i] = (uint32_t)run[k];
+        if (i == nobj) break;
+        uint64_t n[3];
+        seg_counts(rows_of(i), p, n);
+        for (int k = 0; k < 3; k++) run[k] += n[k];
+    }
+}
+
+// fill the launch arguments that describe the plan; looks up (or builds) the shift tables of both lengths
+int apply_plan(DevState* d, const HostPlan& h, BatchArgs* a);
+
+int apply_plan(DevState* d, const HostPlan& h, BatchArgs* a) {
+    a->rows_per_seg = h.p.a;
+    a->rows_per_seg2 = h.p.b;
+    a->ntasks = (uint32_t)h.ntasks;
+    a->nfull_tasks = (uint32_t)h.nlong;
+    a->nshort_tasks = (uint32_t)h.nshort;
+    a->npartial_tasks = (uint32_t)h.npartial;
+    if (int rc = get_adv_seg(d, h.p.a, &a->adv_seg)) return rc;
+    a->adv_seg2 = a->adv_seg;
+    if (h.p.b)
+        if (int rc = get_adv_seg(d, h.p.b, &a->adv_seg2)) return rc;
+    return 0;
 }
 
 int ensure_seg_raw(DevState* d, size_t ntasks) {
@@ -238,18 +300,10 @@ int enqueue_single(DevState* d, const void* dptr, uint64_t n, uint32_t init_crc,
     a.single_off = addr - base;
     a.single_len = n;
     ObjectCut cut = cut_object(addr, n);
-    a.rows_per_seg = choose_rows_per_seg(cut.rows, d->grid);
-    uint64_t ntasks = (cut.rows + a.rows_per_seg - 1) / a.rows_per_seg;
-    while (ntasks > (1u << 30)) {
-        a.rows_per_seg *= 2;
-        ntasks = (cut.rows + a.rows_per_seg - 1) / a.rows_per_seg;
-    }
-    if (int rc = ensure_seg_raw(d, ntasks)) return rc;
-    if (int rc = get_adv_seg(d, a.rows_per_seg, &a.adv_seg)) return rc;
+    const HostPlan h = make_plan(1, [&](size_t) { return cut.rows; }, d->grid);
+    if (int rc = ensure_seg_raw(d, h.ntasks)) return rc;
+    if (int rc = apply_plan(d, h, &a)) return rc;
     a.nobj = 1;
-    a.ntasks = (uint32_t)ntasks;
-    a.nfull_tasks = (uint32_t)(cut.rows / a.rows_per_seg);
-    a.npartial_tasks = a.ntasks - a.nfull_tasks;
     a.seg_raw = d->seg_raw;
     a.got = running ? running : d->d_got + slot;
     a.init_ptr = running;
@@ -632,8 +686,8 @@ struct b200_batch {
     uint32_t* d_got = nullptr;
     uint8_t* d_ok = nullptr;
     unsigned long long* d_nbad = nullptr;
-    const uint32_t* adv_seg = nullptr;
-    uint32_t ntasks = 0, rows_per_seg = 0, nfull = 0, small_objects = 0;
+    HostPlan plan;
+    uint32_t small_objects = 0;
     static constexpr int kRing = 256;  // per-run CUDA event triples: begin, row kernel end, all end
     cudaEvent_t ev[kRing][3] = {};
     uint64_t runs = 0, timed_from = 0;
@@ -673,28 +727,12 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     b->d = d;
     b->nobj = nobj;
     // plan: the arena base is 16-byte aligned, so the cut of object i depends on off[i] only
-    uint32_t rps = plan_rows_per_seg(nobj, [&](size_t i) { return cut_object(off[i], len[i]).rows; }, d->grid);
-    std::vector<uint32_t> seg_start(nobj + 1);
-    for (;;) {
-        uint64_t t = 0;
-        for (size_t i = 0; i < nobj; i++) {
-            seg_start[i] = (uint32_t)t;
-            t += (cut_object(off[i], len[i]).rows + rps - 1) / rps;
-        }
-        seg_start[nobj] = (uint32_t)t;
-        if (t <= (1u << 30)) break;
-        rps *= 2;
-    }
-    b->rows_per_seg = rps;
-    b->ntasks = seg_start[nobj];
-    uint64_t max_full = 0;
-    for (size_t i = 0; i < nobj; i++) {
-        const uint64_t f = cut_object(off[i], len[i]).rows / rps;
-        b->nfull += (uint32_t)f;
-        max_full = std::max(max_full, f);
-    }
-    b->small_objects = (nobj >= 1024 && max_full <= 16) ? 1 : 0;
-    int rc = get_adv_seg(d, rps, &b->adv_seg);
+    auto rows_of = [&](size_t i) { return cut_object(off[i], len[i]).rows; };
+    b->plan = make_plan(nobj, rows_of, d->grid);
+    std::vector<uint32_t> seg_start(3 * (nobj + 1));
+    fill_task_prefix(nobj, rows_of, b->plan.p, seg_start.data());
+    b->small_objects = (nobj >= 1024 && b->plan.max_long <= 16) ? 1 : 0;
+    int rc = 0;
     auto dev_alloc = [&](void** p, size_t bytes) -> int {
         if (rc) return rc;
         cudaError_t e = cudaMalloc(p, bytes ? bytes : 16);
@@ -704,9 +742,9 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     };
     dev_alloc((void**)&b->d_off, nobj * 8);
     dev_alloc((void**)&b->d_len, nobj * 8);
-    dev_alloc((void**)&b->d_seg_start, (nobj + 1) * 4);
+    dev_alloc((void**)&b->d_seg_start, 3 * (nobj + 1) * 4);
     if (want) dev_alloc((void**)&b->d_want, nobj * 4);
-    dev_alloc((void**)&b->d_seg_raw, (size_t)b->ntasks * 4);
+    dev_alloc((void**)&b->d_seg_raw, (size_t)b->plan.ntasks * 4);
     dev_alloc((void**)&b->d_got, nobj * 4);
     dev_alloc((void**)&b->d_ok, nobj);
     dev_alloc((void**)&b->d_nbad, 8);
@@ -718,7 +756,7 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
         cu(cudaMemcpy(b->d_len, len, nobj * 8, cudaMemcpyHostToDevice), "upload len");
         if (want) cu(cudaMemcpy(b->d_want, want, nobj * 4, cudaMemcpyHostToDevice), "upload want");
     }
-    if (!rc) cu(cudaMemcpy(b->d_seg_start, seg_start.data(), (nobj + 1) * 4, cudaMemcpyHostToDevice), "upload plan");
+    if (!rc) cu(cudaMemcpy(b->d_seg_start, seg_start.data(), 3 * (nobj + 1) * 4, cudaMemcpyHostToDevice), "upload plan");
     for (auto& t : b->ev)
         for (cudaEvent_t& e : t)
             if (!rc) cu(cudaEventCreate(&e), "event");
@@ -746,13 +784,9 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     a.got = b->d_got;
     a.ok = b->d_ok;
     a.nbad = b->d_nbad;
-    a.adv_seg = b->adv_seg;
+    if (int rc = apply_plan(d, b->plan, &a)) return rc;
     a.nobj = (uint32_t)b->nobj;
-    a.ntasks = b->ntasks;
-    a.nfull_tasks = b->nfull;
-    a.npartial_tasks = b->ntasks - b->nfull;
     a.small_objects = b->small_objects;
-    a.rows_per_seg = b->rows_per_seg;
     a.init_crc = 0;
     cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];
     CU(launch_batch(a, d->tabs, d->grid, d->stream, ev[0], ev[1], &d->side));
@@ -812,8 +846,11 @@ int b200_batch_kernel_ms(b200_batch* b, float* total_ms, float* rows_kernel_ms) 
 
 int b200_batch_launches(const b200_batch* b, int* launches_per_run) {
     if (!b || !launches_per_run) return fail(B200_ERR_INVALID, "b200_batch_launches");
-    const bool fold = fold_enabled(b->rows_per_seg) && b->nfull > 0;
-    *launches_per_run = (fold ? 1 : 0) + ((b->ntasks && (!fold || b->ntasks > b->nfull)) ? 1 : 0) + (b->nobj ? 1 : 0);
+    const HostPlan& h = b->plan;  // mirrors launch_batch
+    const bool fold_long = fold_enabled(h.p.a) && h.nlong > 0;
+    const bool fold_short = h.p.b && fold_enabled(h.p.b) && h.nshort > 0;
+    const bool rows = h.ntasks && (h.npartial > 0 || (!fold_long && h.nlong > 0) || (!fold_short && h.nshort > 0));
+    *launches_per_run = (fold_long ? 1 : 0) + (fold_short ? 1 : 0) + (rows ? 1 : 0) + (b->nobj ? 1 : 0);
     return 0;
 }
 
@@ -896,23 +933,17 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
             if (want) hs.h_want[k] = want[first + k];
             used = start + len[first + k];
         }
-        uint32_t rps = plan_rows_per_seg(cnt, [&](size_t k) { return cut_object(hs.h_off[k], hs.h_len[k]).rows; }, d->grid);
-        uint64_t t = 0, tfull = 0;
-        for (size_t k = 0; k < cnt; k++) {
-            hs.h_seg[k] = (uint32_t)t;
-            const uint64_t rows = cut_object(hs.h_off[k], hs.h_len[k]).rows;
-            t += (rows + rps - 1) / rps;
-            tfull += rows / rps;
-        }
-        hs.h_seg[cnt] = (uint32_t)t;
-        if ((rc = hs.reserve_tasks(t))) break;
-        const uint32_t* adv_seg = nullptr;
-        if ((rc = get_adv_seg(d, rps, &adv_seg))) break;
+        auto rows_of = [&](size_t k) { return cut_object(hs.h_off[k], hs.h_len[k]).rows; };
+        const HostPlan hp = make_plan(cnt, rows_of, d->grid);
+        fill_task_prefix(cnt, rows_of, hp.p, hs.h_seg);
+        if ((rc = hs.reserve_tasks(hp.ntasks))) break;
+        BatchArgs a{};
+        if ((rc = apply_plan(d, hp, &a))) break;
         cudaError_t e = cudaSuccess;
         auto cu = [&](cudaError_t x) { if (e == cudaSuccess) e = x; };
         cu(cudaMemcpyAsync(hs.d_off, hs.h_off, cnt * 8, cudaMemcpyHostToDevice, d->copy_stream));
         cu(cudaMemcpyAsync(hs.d_len, hs.h_len, cnt * 8, cudaMemcpyHostToDevice, d->copy_stream));
-        cu(cudaMemcpyAsync(hs.d_seg, hs.h_seg, (cnt + 1) * 4, cudaMemcpyHostToDevice, d->copy_stream));
+        cu(cudaMemcpyAsync(hs.d_seg, hs.h_seg, 3 * (cnt + 1) * 4, cudaMemcpyHostToDevice, d->copy_stream));
         if (want) cu(cudaMemcpyAsync(hs.d_want, hs.h_want, cnt * 4, cudaMemcpyHostToDevice, d->copy_stream));
         // data: merge host-contiguous pinned neighbours into single copies
         size_t k = 0;
@@ -948,7 +979,6 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
         cu(cudaEventRecord(d->ev_copied[slot], d->copy_stream));
         cu(cudaStreamWaitEvent(d->stream, d->ev_copied[slot], 0));
         if (e != cudaSuccess) { rc = fail_cuda(e, "slab upload"); break; }
-        BatchArgs a{};
         a.base = d->d_stage[slot];
         a.off = hs.d_off;
         a.len = hs.d_len;
@@ -958,12 +988,7 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
         a.got = hs.d_got;
         a.ok = hs.d_ok;
         a.nbad = hs.d_nbad;
-        a.adv_seg = adv_seg;
         a.nobj = (uint32_t)cnt;
-        a.ntasks = (uint32_t)t;
-        a.nfull_tasks = (uint32_t)tfull;
-        a.npartial_tasks = (uint32_t)(t - tfull);
-        a.rows_per_seg = rps;
         cu(launch_batch(a, d->tabs, d->grid, d->stream, nullptr, nullptr, &d->side));
         cu(cudaMemcpyAsync(hs.h_got, hs.d_got, cnt * 4, cudaMemcpyDeviceToHost, d->stream));
         cu(cudaMemcpyAsync(hs.h_ok, hs.d_ok, cnt, cudaMemcpyDeviceToHost, d->stream));

@@ -93,7 +93,7 @@ __device__ __forceinline__ uint32_t find_object2(const uint32_t* __restrict__ se
 template <int WARPS, int STAGES, int LANE_BYTES>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
-                const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
+                TaskTable tt, SegPlan plan, uint32_t kind,
                 uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv4_tab,
                 const uint32_t* __restrict__ xsq, uint32_t* __restrict__ seg_raw) {
     constexpr int kThreads = WARPS * 32;
@@ -107,6 +107,7 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     for (uint32_t i = threadIdx.x; i < 1024; i += kThreads) tab[i] = __ldg(adv4_tab + i);
     __syncthreads();
 
+    const uint32_t rows_per_seg = kind == kSegLong ? plan.a : plan.b;  // this launch folds segments of this length
     const uint32_t lane_bytes = rows_per_seg * 16;   // S: bytes of the segment owned by one lane
     const uint32_t nstage = lane_bytes / LANE_BYTES;  // rows_per_seg is a multiple of 16, so S is one of 256
     // weight of this lane's register: the (31 - lane) lanes after it still have S bytes each to pass
@@ -116,20 +117,23 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     const uint32_t sw = (lane & 7) << 4;                     // its swizzle (chunk j lives at chunk j ^ (row & 7))
     const uint32_t crow = lane / kLanesPerRow, cchunk = lane % kLanesPerRow;
     const uint32_t nwarps = gridDim.x * WARPS;
+    // this launch's tasks: the segments of kind `kind`, numbered 0..ntasks-1 over the whole batch, dealt round
+    // robin so every warp gets the same number (+-1)
+    const uint32_t ntasks = tt.count[kind], raw_base = tt.base(kind);
+    const uint32_t* __restrict__ seg_start = off ? tt.prefix(kind) : nullptr;
 
     for (uint32_t task = warp * gridDim.x + blockIdx.x; task < ntasks; task += nwarps) {
         uint32_t seg = task;
         uint64_t o = single_off, n = single_len;
         if (off) {
-            const uint32_t obj = find_object2(seg_start, nobj, task);
+            const uint32_t obj = find_object2(seg_start, tt.nobj, task);
             seg = task - __ldg(seg_start + obj);
             o = __ldg(off + obj);
             n = __ldg(len + obj);
         }
         const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
-        const uint64_t row0 = (uint64_t)seg * rows_per_seg;
-        if (cut.rows - row0 < rows_per_seg) continue;  // partial segment: the row kernel's job
-        const uint8_t* src = base + o + cut.head + row0 * kRowBytes;  // lane l's stream starts at src + l*S
+        const Seg sg = seg_of(cut.rows, plan, kind, seg);
+        const uint8_t* src = base + o + cut.head + sg.row0 * kRowBytes;  // lane l's stream starts at src + l*S
         const uint8_t* csrc = src + (size_t)crow * lane_bytes + cchunk * 16;
 
         uint32_t r[64];
@@ -200,14 +204,14 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
         uint32_t s = gf2_mul(lane_k, reg);
 #pragma unroll
         for (int d = 16; d; d >>= 1) s ^= __shfl_xor_sync(0xFFFFFFFFu, s, d);
-        if (lane == 0) seg_raw[task] = s;
+        if (lane == 0) seg_raw[raw_base + task] = s;
     }
 }
 
 struct FoldVariant {
     int warps, stages, lane_bytes;
-    void (*kernel)(const uint8_t*, const uint64_t*, const uint64_t*, const uint32_t*, uint32_t, uint32_t, uint32_t,
-                   uint64_t, uint64_t, const uint32_t*, const uint32_t*, uint32_t*);
+    void (*kernel)(const uint8_t*, const uint64_t*, const uint64_t*, TaskTable, SegPlan, uint32_t, uint64_t, uint64_t,
+                   const uint32_t*, const uint32_t*, uint32_t*);
     size_t smem() const { return kFoldSmemTab + (size_t)warps * stages * 32 * lane_bytes; }
 };
 // Measured on B200 (4096 x 2 MiB, 300 back-to-back steps, GB/s): <8,2,256> 6878 | <7,2,256> 6796 | <4,3,512> 6780 |
@@ -234,7 +238,7 @@ const FoldVariant& fold_variant() {
 
 size_t fold_kernel_smem() { return fold_variant().smem(); }
 
-cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream) {
+cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind) {
     const FoldVariant& fv = fold_variant();
     static thread_local int attr_dev = -1;
     int dev = 0;
@@ -244,11 +248,12 @@ cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cud
         if (e != cudaSuccess) return e;
         attr_dev = dev;
     }
-    if (!a.ntasks) return cudaSuccess;
-    uint32_t need = (a.ntasks + fv.warps - 1) / fv.warps;
+    const TaskTable tt{a.seg_start, a.nobj, {a.nfull_tasks, a.nshort_tasks, a.npartial_tasks}};
+    if (!tt.count[kind]) return cudaSuccess;
+    uint32_t need = (tt.count[kind] + fv.warps - 1) / fv.warps;
     int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
-    fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, a.off, a.len, a.seg_start, a.nobj, a.ntasks, a.rows_per_seg,
-                                                       a.single_off, a.single_len, t.adv4, t.xpow8_sq, a.seg_raw);
+    fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, a.off, a.len, tt, SegPlan{a.rows_per_seg, a.rows_per_seg2},
+                                                       kind, a.single_off, a.single_len, t.adv4, t.xpow8_sq, a.seg_raw);
     return cudaGetLastError();
 }
 

@@ -78,9 +78,10 @@ __device__ __forceinline__ uint32_t find_object(const uint32_t* __restrict__ seg
 
 __global__ void __launch_bounds__(kRowsThreads, 1)
 crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
-                const uint32_t* __restrict__ seg_start, uint32_t nobj, uint32_t ntasks, uint32_t rows_per_seg,
-                uint64_t single_off, uint64_t single_len, uint32_t skip_full, const uint32_t* __restrict__ adv_tab,
+                TaskTable tt, SegPlan plan,
+                uint64_t single_off, uint64_t single_len, uint32_t skip_kinds, const uint32_t* __restrict__ adv_tab,
                 const uint32_t* __restrict__ col_k, const uint32_t* __restrict__ adv4_tab, uint32_t* __restrict__ seg_raw) {
+    // skip_kinds: bit k set = segments of SegKind k are the fold kernel's, not ours
     // replicate the compact 4x256 table once per bank, at absolute shared address kTabAbs
     const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     {
@@ -103,15 +104,20 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     const uint32_t warp = threadIdx.x >> 5;
     const uint32_t k3 = __ldg(col_k + lane4 + 3);  // x^(32*(128-c)) of this lane's last column c = 4*lane+3
     const uint32_t nwarps = gridDim.x * kRowsWarps;
-    // Every warp takes a CONTIGUOUS run of tasks, so the object a task belongs to is found by one binary search
-    // at the start and a forward walk afterwards (a search per task is a ~20-deep chain of dependent loads,
-    // which is what bounds batches of small objects).  Warps are numbered CTA-major across the grid.
+    // Kind by kind, every warp takes a CONTIGUOUS run of that kind's tasks, so the object a task belongs to is
+    // found by one binary search at the start and a forward walk afterwards (a search per task is a ~20-deep
+    // chain of dependent loads, which is what bounds batches of small objects).  Warps are numbered CTA-major.
     const uint32_t gw = warp * gridDim.x + blockIdx.x;
+    for (uint32_t kind = 0; kind < 3; kind++) {
+    if ((skip_kinds >> kind) & 1) continue;  // these segments belong to the fold kernel
+    const uint32_t ntasks = tt.count[kind];
+    const uint32_t* __restrict__ seg_start = off ? tt.prefix(kind) : nullptr;
+    const uint32_t raw_base = tt.base(kind);
     const uint32_t task_lo = (uint32_t)((uint64_t)ntasks * gw / nwarps);
     const uint32_t task_hi = (uint32_t)((uint64_t)ntasks * (gw + 1) / nwarps);
     uint32_t obj = 0, obj_first = 0, obj_next = ntasks;  // tasks [obj_first, obj_next) belong to obj
     if (off && task_lo < task_hi) {
-        obj = find_object(seg_start, nobj, task_lo);
+        obj = find_object(seg_start, tt.nobj, task_lo);
         obj_first = __ldg(seg_start + obj);
         obj_next = __ldg(seg_start + obj + 1);
     }
@@ -120,7 +126,7 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
         uint32_t seg = task;
         uint64_t o = single_off, n = single_len;
         if (off) {
-            while (task >= obj_next) {  // objects without segments are stepped over
+            while (task >= obj_next) {  // objects without segments of this kind are stepped over
                 obj++;
                 obj_first = obj_next;
                 obj_next = __ldg(seg_start + obj + 1);
@@ -130,10 +136,9 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
             n = __ldg(len + obj);
         }
         const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
-        const uint64_t row0 = (uint64_t)seg * rows_per_seg;
-        uint64_t left = cut.rows - row0;
-        const uint32_t R = left < rows_per_seg ? (uint32_t)left : rows_per_seg;
-        if (skip_full && R == rows_per_seg) continue;  // full segments belong to the fold kernel
+        const Seg sg = seg_of(cut.rows, plan, kind, seg);
+        const uint64_t row0 = sg.row0;
+        const uint32_t R = sg.rows;
         const uint4* p = reinterpret_cast<const uint4*>(base + o + cut.head + row0 * kRowBytes) + lane;
 
         uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
@@ -171,8 +176,9 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
         uint32_t s = gf2_mul(k3, u);
 #pragma unroll
         for (int d = 16; d; d >>= 1) s ^= __shfl_xor_sync(0xFFFFFFFFu, s, d);
-        if (lane == 0) seg_raw[task] = s;
+        if (lane == 0) seg_raw[raw_base + task] = s;
     }
+    }  // kind
 }
 
 __device__ __forceinline__ uint32_t adv_tab4(const uint32_t* __restrict__ t, uint32_t s) {
@@ -183,23 +189,29 @@ __device__ __forceinline__ uint32_t adv_tab4(const uint32_t* __restrict__ t, uin
 // One CTA per object.
 __global__ void __launch_bounds__(kFinalThreads)
 crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
-                    const uint32_t* __restrict__ seg_start, const uint32_t* __restrict__ want,
+                    TaskTable tt, const uint32_t* __restrict__ want,
                     const uint32_t* __restrict__ seg_raw, const uint32_t* __restrict__ adv_seg,
-                    const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab, uint32_t rows_per_seg,
-                    uint32_t init_crc, const uint32_t* init_ptr, uint64_t single_off, uint64_t single_len,
-                    uint32_t* got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
+                    const uint32_t* __restrict__ adv_seg2, const uint32_t* __restrict__ xsq,
+                    const uint32_t* __restrict__ byte_tab, SegPlan plan, uint32_t init_crc, const uint32_t* init_ptr,
+                    uint64_t single_off, uint64_t single_len, uint32_t* got, uint8_t* __restrict__ ok,
+                    unsigned long long* nbad) {
     __shared__ uint32_t red[kFinalThreads / 32];
     const uint32_t obj = blockIdx.x;
     const uint64_t o = off ? off[obj] : single_off;
     const uint64_t n = off ? len[obj] : single_len;
     const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
-    const uint32_t first = off ? seg_start[obj] : 0;
-    const uint64_t nfull = cut.rows / rows_per_seg;
-    const uint32_t last_rows = (uint32_t)(cut.rows % rows_per_seg);
-    const uint64_t seg_bytes = (uint64_t)rows_per_seg * kRowBytes;
+    // where this object's raw segment registers sit: one run per kind
+    const uint32_t first = off ? tt.prefix(kSegLong)[obj] : 0;
+    const uint32_t first_short = tt.base(kSegShort) + (off ? tt.prefix(kSegShort)[obj] : 0);
+    const uint32_t first_part = tt.base(kSegPartial) + (off ? tt.prefix(kSegPartial)[obj] : 0);
+    const uint64_t nfull = cut.rows / plan.a;                       // long segments
+    const uint64_t rem = cut.rows - nfull * plan.a;
+    const uint32_t nshort = plan.b ? (uint32_t)(rem / plan.b) : 0;  // short segments (< a/b of them)
+    const uint32_t last_rows = (uint32_t)(rem - (uint64_t)nshort * plan.b);
+    const uint64_t seg_bytes = (uint64_t)plan.a * kRowBytes;
     const uint8_t* p = base + o;
 
-    // F = sum over full segments j of x^(8*seg_bytes*(nfull-1-j)) * raw_j
+    // F = sum over long segments j of x^(8*seg_bytes*(nfull-1-j)) * raw_j
     uint32_t F = 0;
     if (nfull > 64) {
         const uint64_t per = (nfull + kFinalThreads - 1) / kFinalThreads;
@@ -225,7 +237,8 @@ crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict
     uint32_t s = ~(init_ptr ? *init_ptr : init_crc);
     for (uint32_t i = 0; i < cut.head; i++) s = (s >> 8) ^ __ldg(byte_tab + ((s ^ p[i]) & 0xFF));
     if (nfull) s = gf2_mul(gf2_xpow8(nfull * seg_bytes, xsq), s) ^ F;
-    if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first + nfull];
+    for (uint32_t j = 0; j < nshort; j++) s = adv_tab4(adv_seg2, s) ^ seg_raw[first_short + j];
+    if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first_part];
     const uint8_t* t = p + cut.head + cut.rows * kRowBytes;  // 16-byte aligned
     uint32_t i = 0;
     for (; i + 4 <= cut.tail; i += 4) {  // sub-row tail, a word at a time
@@ -246,10 +259,11 @@ crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict
 // a CTA per object would be a million nearly empty CTAs).
 __global__ void __launch_bounds__(kFinalThreads)
 crc_finalize_small_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off,
-                          const uint64_t* __restrict__ len, const uint32_t* __restrict__ seg_start,
+                          const uint64_t* __restrict__ len, TaskTable tt,
                           const uint32_t* __restrict__ want, const uint32_t* __restrict__ seg_raw,
-                          const uint32_t* __restrict__ adv_seg, const uint32_t* __restrict__ xsq,
-                          const uint32_t* __restrict__ byte_tab, uint32_t rows_per_seg, uint32_t init_crc, uint32_t nobj,
+                          const uint32_t* __restrict__ adv_seg, const uint32_t* __restrict__ adv_seg2,
+                          const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab, SegPlan plan,
+                          uint32_t init_crc, uint32_t nobj,
                           uint32_t* __restrict__ got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
     __shared__ uint32_t bt[256];
     for (int i = threadIdx.x; i < 256; i += kFinalThreads) bt[i] = __ldg(byte_tab + i);
@@ -258,16 +272,20 @@ crc_finalize_small_kernel(const uint8_t* __restrict__ base, const uint64_t* __re
     if (obj >= nobj) return;
     const uint64_t o = off[obj], n = len[obj];
     const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
-    const uint32_t first = seg_start[obj];
-    const uint64_t nfull = cut.rows / rows_per_seg;
-    const uint32_t last_rows = (uint32_t)(cut.rows % rows_per_seg);
+    const uint32_t first = tt.prefix(kSegLong)[obj];
+    const uint32_t first_short = tt.base(kSegShort) + tt.prefix(kSegShort)[obj];
+    const uint32_t first_part = tt.base(kSegPartial) + tt.prefix(kSegPartial)[obj];
+    const uint64_t nfull = cut.rows / plan.a;
+    const uint64_t rem = cut.rows - nfull * plan.a;
+    const uint32_t nshort = plan.b ? (uint32_t)(rem / plan.b) : 0;
+    const uint32_t last_rows = (uint32_t)(rem - (uint64_t)nshort * plan.b);
     const uint8_t* p = base + o;
-    uint32_t F = 0;
-    for (uint64_t j = 0; j < nfull; j++) F = adv_tab4(adv_seg, F) ^ seg_raw[first + j];
     uint32_t s = ~init_crc;
     for (uint32_t i = 0; i < cut.head; i++) s = (s >> 8) ^ bt[(s ^ p[i]) & 0xFF];
-    if (nfull) s = gf2_mul(gf2_xpow8(nfull * (uint64_t)rows_per_seg * kRowBytes, xsq), s) ^ F;
-    if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first + nfull];
+    // the state walks over the segments in order: s <- x^(8*segment bytes) * s ^ raw(segment)
+    for (uint64_t j = 0; j < nfull; j++) s = adv_tab4(adv_seg, s) ^ seg_raw[first + j];
+    for (uint32_t j = 0; j < nshort; j++) s = adv_tab4(adv_seg2, s) ^ seg_raw[first_short + j];
+    if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first_part];
     const uint8_t* t = p + cut.head + cut.rows * kRowBytes;  // 16-byte aligned
     uint32_t i = 0;
     for (; i + 16 <= cut.tail; i += 16) {
@@ -353,41 +371,55 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     cudaError_t e = cudaMemsetAsync(a.nbad, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     if (ev_begin) cudaEventRecord(ev_begin, stream);
-    const bool fold = fold_enabled(a.rows_per_seg) && a.nfull_tasks > 0;
-    const bool rows = a.ntasks && (!fold || a.npartial_tasks > 0);
-    cudaStream_t rows_stream = stream;
-    if (fold && rows && side) {  // fork: the row kernel overlaps the fold kernel's tail
+    const SegPlan plan{a.rows_per_seg, a.rows_per_seg2};
+    const TaskTable tt{a.seg_start, a.nobj, {a.nfull_tasks, a.nshort_tasks, a.npartial_tasks}};
+    const bool fold_long = !a.no_fold && fold_enabled(plan.a) && a.nfull_tasks > 0;
+    const bool fold_short = !a.no_fold && plan.b && fold_enabled(plan.b) && a.nshort_tasks > 0;
+    const uint32_t skip_kinds = (fold_long ? 1u << kSegLong : 0u) | (fold_short ? 1u << kSegShort : 0u);
+    const bool rows = a.ntasks && (a.npartial_tasks > 0 || (!fold_long && a.nfull_tasks > 0) ||
+                                   (!fold_short && a.nshort_tasks > 0));
+    // The long segments run on `stream`; the short ones and the row kernel run next to them on the side stream
+    // (when there is one), so that their CTAs fill the SMs the long fold kernel's tail leaves idle.
+    cudaStream_t second = stream;
+    const bool forked = fold_long && (fold_short || rows) && side;
+    if (forked) {
         e = cudaEventRecord(side->fork, stream);
         if (e == cudaSuccess) e = cudaStreamWaitEvent(side->stream, side->fork, 0);
         if (e != cudaSuccess) return e;
-        rows_stream = side->stream;
+        second = side->stream;
     }
-    if (fold) {
-        e = launch_fold(a, t, grid, stream);
+    if (fold_long) {
+        e = launch_fold(a, t, grid, stream, kSegLong);
+        if (e != cudaSuccess) return e;
+    }
+    if (fold_short) {
+        e = launch_fold(a, t, grid, second, kSegShort);
         if (e != cudaSuccess) return e;
     }
     if (rows) {
-        uint32_t need = (a.ntasks + kRowsWarps - 1) / kRowsWarps;
+        uint32_t mine = 0;  // tasks of the kinds the row kernel takes
+        for (uint32_t k = 0; k < 3; k++)
+            if (!((skip_kinds >> k) & 1)) mine = mine > tt.count[k] ? mine : tt.count[k];
+        uint32_t need = (mine + kRowsWarps - 1) / kRowsWarps;
         int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
-        crc_rows_kernel<<<g, kRowsThreads, rows_kernel_smem(), rows_stream>>>(
-            a.base, a.off, a.len, a.seg_start, a.nobj, a.ntasks, a.rows_per_seg, a.single_off, a.single_len,
-            fold ? 1u : 0u, t.adv_row, t.col_k, t.adv4, a.seg_raw);
-        if (rows_stream != stream) {  // join
-            e = cudaEventRecord(side->join, rows_stream);
-            if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, side->join, 0);
-            if (e != cudaSuccess) return e;
-        }
+        crc_rows_kernel<<<g ? g : 1, kRowsThreads, rows_kernel_smem(), second>>>(
+            a.base, a.off, a.len, tt, plan, a.single_off, a.single_len, skip_kinds, t.adv_row, t.col_k, t.adv4, a.seg_raw);
+    }
+    if (forked) {  // join
+        e = cudaEventRecord(side->join, second);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(stream, side->join, 0);
+        if (e != cudaSuccess) return e;
     }
     if (ev_end) cudaEventRecord(ev_end, stream);
     if (a.nobj && a.off && a.small_objects)
         crc_finalize_small_kernel<<<(a.nobj + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, stream>>>(
-            a.base, a.off, a.len, a.seg_start, a.want, a.seg_raw, a.adv_seg, t.xpow8_sq, t.byte_tab, a.rows_per_seg,
+            a.base, a.off, a.len, tt, a.want, a.seg_raw, a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, plan,
             a.init_crc, a.nobj, a.got, a.ok, a.nbad);
     else if (a.nobj)
-        crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, a.seg_start, a.want, a.seg_raw,
-                                                                  a.adv_seg, t.xpow8_sq, t.byte_tab, a.rows_per_seg,
-                                                                  a.init_crc, a.init_ptr, a.single_off, a.single_len, a.got, a.ok,
-                                                                  a.nbad);
+        crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, tt, a.want, a.seg_raw,
+                                                                  a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, plan,
+                                                                  a.init_crc, a.init_ptr, a.single_off, a.single_len, a.got,
+                                                                  a.ok, a.nbad);
     return cudaGetLastError();
 }
 

@@ -33,6 +33,50 @@ B200_HD ObjectCut cut_object(uint64_t addr, uint64_t len) {
     return c;
 }
 
+// How the rows of an object body are cut into segments (= tasks).  Two lengths: as many LONG segments of
+// `a` rows as fit, then as many SHORT segments of `b` rows as fit in what is left (b == 0: none), then one
+// partial segment with the rest.  Long and short segments are "full" (the fold kernel can take them); the
+// partial one always goes to the row kernel.  With b == 0 this is the plain one-length scheme.
+enum SegKind : uint32_t { kSegLong = 0, kSegShort = 1, kSegPartial = 2 };
+struct SegPlan {
+    uint32_t a, b;
+};
+struct Seg {
+    uint64_t row0;  // first row of the segment inside the body
+    uint32_t rows;  // its length
+    uint32_t kind;
+};
+// number of segments of each kind in a body of `rows` rows
+B200_HD void seg_counts(uint64_t rows, SegPlan p, uint64_t n[3]) {
+    n[kSegLong] = rows / p.a;
+    const uint64_t rem = rows - n[kSegLong] * p.a;
+    n[kSegShort] = p.b ? rem / p.b : 0;
+    n[kSegPartial] = (rem - n[kSegShort] * p.b) ? 1 : 0;
+}
+// the j-th segment of kind `kind`
+B200_HD Seg seg_of(uint64_t rows, SegPlan p, uint32_t kind, uint64_t j) {
+    if (kind == kSegLong) return Seg{j * p.a, p.a, kSegLong};
+    const uint64_t na = rows / p.a, rem = rows - na * p.a;
+    if (kind == kSegShort) return Seg{na * p.a + j * p.b, p.b, kSegShort};
+    const uint64_t nb = p.b ? rem / p.b : 0;
+    return Seg{na * p.a + nb * p.b, (uint32_t)(rem - nb * p.b), kSegPartial};
+}
+
+// Tasks are numbered kind by kind: all long segments of the batch first, then the short ones, then the
+// partial ones, so that a kernel that takes one kind can hand every warp the same number of them.  For kind
+// k, start[k * (nobj + 1) + i] is the number of kind-k segments of objects 0..i-1 (a prefix sum with a final
+// total); seg_raw[] is indexed by the global id base(k) + local id.  In single-object mode start is null and
+// object 0 owns all count[k] segments of each kind.
+struct TaskTable {
+    const uint32_t* start;
+    uint32_t nobj;
+    uint32_t count[3];
+    B200_HD uint32_t base(uint32_t kind) const {
+        return kind == kSegLong ? 0 : kind == kSegShort ? count[0] : count[0] + count[1];
+    }
+    B200_HD const uint32_t* prefix(uint32_t kind) const { return start + (size_t)kind * (nobj + 1); }
+};
+
 // Constant tables a device needs (built once per context on the host, see tables.cu).
 struct DeviceTables {
     uint32_t* adv_row;   // [4][256] multiply-by-x^(8*512) slicing tables (compact; kernels replicate per bank)
@@ -46,7 +90,7 @@ struct BatchArgs {
     const uint8_t* base;        // device arena, 16-byte aligned
     const uint64_t* off;        // [nobj] device
     const uint64_t* len;        // [nobj] device
-    const uint32_t* seg_start;  // [nobj+1] device: first task of each object
+    const uint32_t* seg_start;  // [3][nobj+1] device: per-kind prefix sums of segment counts (see TaskTable)
     const uint32_t* want;       // [nobj] device or nullptr
     uint32_t* seg_raw;          // [ntasks] device scratch: raw CRC register of each segment
     uint32_t* got;              // [nobj] device
@@ -55,7 +99,9 @@ struct BatchArgs {
     const uint32_t* adv_seg;    // [4][256] multiply-by-x^(8*512*rows_per_seg) tables (device)
     uint32_t nobj;
     uint32_t ntasks;
-    uint32_t rows_per_seg;
+    uint32_t rows_per_seg;      // long segments
+    uint32_t rows_per_seg2;     // short segments (0 = none)
+    const uint32_t* adv_seg2;   // [4][256] multiply-by-x^(8*512*rows_per_seg2) tables (device), when rows_per_seg2
     uint32_t init_crc;          // crc32.Update's first argument, same for every object (0 = fresh checksum)
     const uint32_t* init_ptr;   // single-object mode: when set, the first argument is read from the device
                                 // (may alias `got`: a running CRC that stays on the device between chunks)
@@ -63,12 +109,14 @@ struct BatchArgs {
     // tasks 0..ntasks-1; no plan arrays are read.
     uint64_t single_off;
     uint64_t single_len;
-    // how many of the ntasks segments are full (rows_per_seg rows) / partial; the fold kernel takes the full
-    // ones when it is in use, the row kernel the rest
-    uint32_t nfull_tasks;
+    // how many of the ntasks segments are long / short / partial; the fold kernel takes the long and short
+    // ones when it is in use for that length, the row kernel the rest
+    uint32_t nfull_tasks;       // long
+    uint32_t nshort_tasks;
     uint32_t npartial_tasks;
     // every object has at most a few full segments and there are many objects: finalize one object per THREAD
     uint32_t small_objects;
+    uint32_t no_fold;           // keep every segment on the row kernel (the caller has no tables for the fold kernel)
 };
 
 // true when launch_batch will give full segments of this length to the fold kernel
@@ -87,7 +135,8 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
                          cudaEvent_t ev_rows_begin, cudaEvent_t ev_rows_end, const SideStream* side = nullptr);
 
 size_t fold_kernel_smem();
-cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream);
+// kind: kSegLong or kSegShort — which of the two full-segment lengths this launch folds
+cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind);
 
 cudaError_t launch_fill_payload(uint64_t* dst, uint64_t first_word, size_t nwords, uint64_t seed, cudaStream_t s);
 cudaError_t launch_fill_latency(int64_t* dst, uint64_t first, size_t n, uint64_t seed, cudaStream_t s);

@@ -120,8 +120,12 @@ extern "C" int b200_crc32c_update_device_noalloc(int dev, uint32_t crc, const vo
     }
     a.rows_per_seg = rps;
     a.ntasks = (uint32_t)ntasks;
-    a.nfull_tasks = 0;  // everything on the row kernel: this path carries no tables for the fold kernel
-    a.npartial_tasks = (uint32_t)ntasks;
+    a.rows_per_seg2 = 0;  // one segment length
+    a.adv_seg2 = nullptr;
+    a.nfull_tasks = (uint32_t)(cut.rows / rps);
+    a.nshort_tasks = 0;
+    a.npartial_tasks = (uint32_t)(ntasks - cut.rows / rps);
+    a.no_fold = 1;        // everything on the row kernel
     a.nobj = 1;
     a.seg_raw = (uint32_t*)(p + kOffSegRaw);
     a.got = (uint32_t*)(p + kOffGot);

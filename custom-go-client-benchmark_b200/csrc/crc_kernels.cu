@@ -262,11 +262,13 @@ crc_finalize_small_kernel(const uint8_t* __restrict__ base, const uint64_t* __re
                           const uint64_t* __restrict__ len, TaskTable tt,
                           const uint32_t* __restrict__ want, const uint32_t* __restrict__ seg_raw,
                           const uint32_t* __restrict__ adv_seg, const uint32_t* __restrict__ adv_seg2,
-                          const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab, SegPlan plan,
-                          uint32_t init_crc, uint32_t nobj,
+                          const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab,
+                          const uint32_t* __restrict__ adv4_tab, SegPlan plan, uint32_t init_crc, uint32_t nobj,
                           uint32_t* __restrict__ got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
     __shared__ uint32_t bt[256];
+    __shared__ uint32_t w4[1024];  // x^32 slicing tables: a whole tail word per step instead of four byte steps
     for (int i = threadIdx.x; i < 256; i += kFinalThreads) bt[i] = __ldg(byte_tab + i);
+    for (int i = threadIdx.x; i < 1024; i += kFinalThreads) w4[i] = __ldg(adv4_tab + i);
     __syncthreads();
     const uint32_t obj = blockIdx.x * kFinalThreads + threadIdx.x;
     if (obj >= nobj) return;
@@ -280,26 +282,42 @@ crc_finalize_small_kernel(const uint8_t* __restrict__ base, const uint64_t* __re
     const uint32_t nshort = plan.b ? (uint32_t)(rem / plan.b) : 0;
     const uint32_t last_rows = (uint32_t)(rem - (uint64_t)nshort * plan.b);
     const uint8_t* p = base + o;
+    // One thread walks the whole object, so every dependent global load is ~a microsecond of latency chain:
+    // the head comes from the ONE aligned 16-byte word that contains it, the tail is read in 16-byte words one
+    // ahead of use.  (Reading the rest of an aligned 16-byte word past either end of the object is safe: such a
+    // word holds at least one byte of the object and cannot cross a page, so it is mapped.)
+    auto bytes_of = [&](const uint4& q, uint32_t from, uint32_t count, uint32_t st) {
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (uint32_t k = 0; k < 16; k++)
+            if (k >= from && k < from + count) st = (st >> 8) ^ bt[(st ^ (w[k >> 2] >> (8 * (k & 3)))) & 0xFF];
+        return st;
+    };
+    auto word_step = [&](uint32_t st, uint32_t w) {
+        const uint32_t x = w ^ st;
+        return w4[x & 0xFF] ^ w4[256 + ((x >> 8) & 0xFF)] ^ w4[512 + ((x >> 16) & 0xFF)] ^ w4[768 + (x >> 24)];
+    };
+    const uint8_t* t = p + cut.head + cut.rows * kRowBytes;  // 16-byte aligned start of the tail
+    const uint32_t nvec = (cut.tail + 15) / 16;
+    uint4 q = make_uint4(0, 0, 0, 0), hq = q;
+    if (cut.head) hq = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)15));
+    if (nvec) q = __ldg(reinterpret_cast<const uint4*>(t));
     uint32_t s = ~init_crc;
-    for (uint32_t i = 0; i < cut.head; i++) s = (s >> 8) ^ bt[(s ^ p[i]) & 0xFF];
+    if (cut.head) s = bytes_of(hq, (uint32_t)(reinterpret_cast<uintptr_t>(p) & 15), cut.head, s);
     // the state walks over the segments in order: s <- x^(8*segment bytes) * s ^ raw(segment)
     for (uint64_t j = 0; j < nfull; j++) s = adv_tab4(adv_seg, s) ^ seg_raw[first + j];
     for (uint32_t j = 0; j < nshort; j++) s = adv_tab4(adv_seg2, s) ^ seg_raw[first_short + j];
     if (last_rows) s = gf2_mul(gf2_xpow8((uint64_t)last_rows * kRowBytes, xsq), s) ^ seg_raw[first_part];
-    const uint8_t* t = p + cut.head + cut.rows * kRowBytes;  // 16-byte aligned
-    uint32_t i = 0;
-    for (; i + 16 <= cut.tail; i += 16) {
-        const uint4 q = *reinterpret_cast<const uint4*>(t + i);
-        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            uint32_t x = w[k] ^ s;
-#pragma unroll
-            for (int b = 0; b < 4; b++) x = (x >> 8) ^ bt[x & 0xFF];
-            s = x;
+    for (uint32_t v = 0; v < nvec; v++) {
+        const uint4 cur = q;
+        if (v + 1 < nvec) q = __ldg(reinterpret_cast<const uint4*>(t) + v + 1);
+        const uint32_t left = cut.tail - v * 16;
+        if (left >= 16) {
+            s = word_step(word_step(word_step(word_step(s, cur.x), cur.y), cur.z), cur.w);
+        } else {
+            s = bytes_of(cur, 0, left, s);
         }
     }
-    for (; i < cut.tail; i++) s = (s >> 8) ^ bt[(s ^ t[i]) & 0xFF];
     const uint32_t crc = ~s;
     got[obj] = crc;
     const bool good = want ? (crc == want[obj]) : true;
@@ -413,7 +431,7 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     if (ev_end) cudaEventRecord(ev_end, stream);
     if (a.nobj && a.off && a.small_objects)
         crc_finalize_small_kernel<<<(a.nobj + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, stream>>>(
-            a.base, a.off, a.len, tt, a.want, a.seg_raw, a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, plan,
+            a.base, a.off, a.len, tt, a.want, a.seg_raw, a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, t.adv4, plan,
             a.init_crc, a.nobj, a.got, a.ok, a.nbad);
     else if (a.nobj)
         crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, tt, a.want, a.seg_raw,

@@ -24,6 +24,7 @@ namespace {
 constexpr int kHistThreads = 256;
 constexpr int kHistWarps = kHistThreads / 32;
 constexpr int kRadixThreads = 512;
+constexpr int kTrashRows = 3;   // counter rows past the real bins: where parked samples' no-op updates land
 constexpr int kSlowQueue = 128;  // parked samples per warp; overflow falls back to the divergent path
 
 struct U128 {
@@ -66,22 +67,42 @@ __device__ __forceinline__ int classify(long long n, const long long* __restrict
 }
 
 // Per-thread running moments.  Fast path values fit 32 bits, so their squares fit 64.
+struct SlowMoments {                                       // of generic-path samples: exact 128-bit
+    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
+    U128 sum{0, 0}, sq{0, 0};
+};
 struct Moments {
     unsigned mn32 = 0xFFFFFFFFu, mx32 = 0;                 // of fast-path samples
-    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;  // of slow-path samples
-    U128 sum{0, 0}, sq{0, 0};                              // slow path: exact 128-bit
     unsigned long long fsum = 0, fsq = 0;                  // fast path: q < 2^32, so 64 bits hold ~2^32 samples of q
     unsigned fsq_carry = 0;                                //   and q*q wraps at most once per add
 };
 
-// DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic,
-// 2 divisor >= 2^32 (quotient 0).
+// Generic path: any int64 sample.  Thresholds, LUT and the 64-bit magic are read from global memory and the
+// moments live in local memory: this runs for a handful of samples per million, and keeping it out of line
+// keeps the fast loop's registers and instruction cache to itself.
+__device__ __noinline__ void slow_sample(long long v, const HistParams* __restrict__ Pg, unsigned* mine,
+                                         SlowMoments* s) {
+    const int c = classify(v, Pg->thr, Pg->nthr, Pg->lut);
+    mine[c * 32]++;
+    if (s) {
+        s->mn = v < s->mn ? v : s->mn;
+        s->mx = v > s->mx ? v : s->mx;
+        const unsigned long long a = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
+        const unsigned long long q = udiv_magic(a, *Pg);
+        add128(s->sq, q * q, __umul64hi(q, q));
+        if (v < 0) add128(s->sum, 0ull - q, q ? ~0ull : 0ull);
+        else add128(s->sum, q, 0);
+    }
+}
+
+// DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic with
+// the add fix-up, 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28.
 template <bool MOMENTS, int DIVMODE>
 __global__ void __launch_bounds__(kHistThreads, 4)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom) {
     extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ HistParams P;
+    __shared__ uint2 fast[kFastCells];
     // Samples that need the generic path (>= 2^32 ns, negative, or a cell holding several thresholds) are rare
     // but would drag their whole warp through ~140 divergent instructions; they are parked in a per-warp queue
     // and processed 32 at a time instead.
@@ -89,34 +110,18 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     __shared__ unsigned slow_n[kHistWarps];
     unsigned* tbl = reinterpret_cast<unsigned*>(sm);  // [warp][bin][lane] private counters
     if (threadIdx.x < kHistWarps) slow_n[threadIdx.x] = 0;
-    {
-        const unsigned* src = reinterpret_cast<const unsigned*>(Pg);
-        unsigned* dst = reinterpret_cast<unsigned*>(&P);
-        for (int i = threadIdx.x; i < (int)(sizeof(HistParams) / 4); i += kHistThreads) dst[i] = src[i];
-    }
-    const int nbins = Pg->nthr + 1;
-    for (int i = threadIdx.x; i < kHistWarps * nbins * 32; i += kHistThreads) tbl[i] = 0;
+    for (int i = threadIdx.x; i < kFastCells; i += kHistThreads) fast[i] = Pg->fast[i];
+    const int nbins = Pg->nthr + 1, rows = nbins + kTrashRows;
+    for (int i = threadIdx.x; i < kHistWarps * rows * 32; i += kHistThreads) tbl[i] = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned* mine = tbl + (size_t)warp * nbins * 32 + lane;
+    unsigned* mine = tbl + (size_t)warp * rows * 32 + lane;
     Moments m;
-    const unsigned magic32 = P.magic32;
-    const int shift32 = P.shift32;
+    const unsigned magic32 = Pg->magic32;
+    const int shift32 = Pg->shift32, pre32 = Pg->pre32;
 
-    // generic path: any int64 sample
-    auto slow = [&](long long v) {
-        int c = classify(v, P.thr, P.nthr, P.lut);
-        mine[c * 32]++;
-        if (MOMENTS) {
-            m.mn = v < m.mn ? v : m.mn;
-            m.mx = v > m.mx ? v : m.mx;
-            unsigned long long a = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
-            unsigned long long q = udiv_magic(a, P);
-            add128(m.sq, q * q, __umul64hi(q, q));
-            if (v < 0) add128(m.sum, 0ull - q, q ? ~0ull : 0ull);
-            else add128(m.sum, q, 0);
-        }
-    };
+    SlowMoments sm_slow;
+    auto slow = [&](long long v) { slow_sample(v, Pg, mine, MOMENTS ? &sm_slow : nullptr); };
     auto park = [&](long long v) {
         const unsigned at = atomicAdd(&slow_n[warp], 1u);
         if (at < kSlowQueue) slow_q[warp][at] = v;
@@ -130,31 +135,86 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         if (lane == 0) slow_n[warp] = 0;
         __syncwarp();
     };
-    // fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), everything in 32-bit arithmetic and branch-free up to
-    // the single rare-case test
-    auto one = [&](long long v) {
+    // Fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), 32-bit arithmetic only.  lookup() fetches the sample's
+    // cell and says whether the sample has to be parked; count() bumps the lane's private counter.
+    auto lookup = [&](long long v, uint2& w) -> unsigned {
         const unsigned u = (unsigned)v, hi = (unsigned)((unsigned long long)v >> 32);
-        // log-linear cell: row = max(e,4)-4, mantissa = 5 bits below the leading one (u itself for u < 32)
-        const int e = 31 - __clz((int)(u | 1));
-        const unsigned idx = (unsigned)(max(e, 4) - 4) * 32 + ((u >> (max(e, 5) - 5)) & 31);
-        const unsigned cell = P.lut[idx];
-        if (hi | (cell & 0xFE)) { park(v); return; }  // >= 2^32 / negative, or several thresholds in the cell
-        const unsigned c = (cell >> 8) + (u > P.cell_gt[idx] ? 1u : 0u);
-        mine[c * 32]++;
+        const unsigned t = max(__float_as_uint(__uint2float_rz(u)) >> 18, 4063u) - 4063u;
+        w = fast[t];
+        return hi | (w.y & 4u);  // >= 2^32 / negative, or several thresholds in the cell
+    };
+    auto quotient = [&](unsigned u) -> unsigned {
+        if (DIVMODE == 1) {
+            const unsigned t = __umulhi(magic32, u);
+            return (t + ((u - t) >> 1)) >> shift32;
+        }
+        if (DIVMODE == 3) return __umulhi(u >> pre32, magic32) >> shift32;
+        return DIVMODE == 0 ? u : 0u;
+    };
+    auto count = [&](unsigned u, const uint2 w) {
+        const unsigned off = w.y + (u > w.x ? 128u : 0u);
+        ++*reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(mine) + off);
         if (MOMENTS) {
             m.mn32 = min(m.mn32, u);
             m.mx32 = max(m.mx32, u);
-            unsigned q;
-            if (DIVMODE == 1) {
-                const unsigned t = __umulhi(magic32, u);
-                q = (t + ((u - t) >> 1)) >> shift32;
-            } else {
-                q = DIVMODE == 0 ? u : 0u;
+        }
+    };
+    auto accumulate = [&](unsigned q) {  // running 64-bit sums; q*q wraps at most once per add
+        m.fsum += q;
+        const unsigned long long sq = (unsigned long long)q * q + m.fsq;
+        m.fsq_carry += sq < m.fsq;
+        m.fsq = sq;
+    };
+    auto one = [&](long long v) {
+        uint2 w;
+        if (lookup(v, w)) { park(v); return; }
+        count((unsigned)v, w);
+        if (MOMENTS) accumulate(quotient((unsigned)v));
+    };
+    // Eight samples at a time, without a branch in the common work: a sample that has to be parked still walks
+    // through the counting code, but adds 0 to its counter and contributes the neutral element to every moment
+    // (its mask `keep` is 0).  Roughly one sample in 200 of a realistic run is such a sample (a multi-second
+    // stall), i.e. three warp iterations in four hold at least one, so a branch around the common work would
+    // be divergent most of the time.  Only the parking itself is conditional.
+    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
+        const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+        uint2 w[8];
+        unsigned keep[8], any = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const unsigned rare = lookup(v[k], w[k]);
+            any |= rare;
+            keep[k] = rare ? 0u : 0xFFFFFFFFu;
+        }
+        unsigned s = 0;
+        unsigned long long sq = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            const unsigned u = (unsigned)v[k];
+            const unsigned off = w[k].y + (u > w[k].x ? 128u : 0u);
+            *reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(mine) + off) += keep[k] & 1u;
+            if (MOMENTS) {
+                m.mn32 = min(m.mn32, u | ~keep[k]);
+                m.mx32 = max(m.mx32, u & keep[k]);
+                const unsigned q = quotient(u) & keep[k];
+                if (DIVMODE == 3) {  // quotients < 2^28: eight of them fit 32 bits, eight squares fit 64
+                    s += q;
+                    sq += (unsigned long long)q * q;
+                } else {
+                    accumulate(q);
+                }
             }
-            m.fsum += q;
-            const unsigned long long sq = (unsigned long long)q * q + m.fsq;
+        }
+        if (MOMENTS && DIVMODE == 3) {
+            m.fsum += s;
+            sq += m.fsq;
             m.fsq_carry += sq < m.fsq;
             m.fsq = sq;
+        }
+        if (any) {
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                if (!keep[k]) park(v[k]);
         }
     };
 
@@ -172,7 +232,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     for (; (i - lane) + 31 + 3 * nthreads < npairs; i += 4 * nthreads) {  // four independent 128-bit loads in flight
         longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads), c = __ldg(x2 + i + 2 * nthreads),
                   d = __ldg(x2 + i + 3 * nthreads);
-        one(a.x); one(a.y); one(b.x); one(b.y); one(c.x); one(c.y); one(d.x); one(d.y);
+        eight(a, b, c, d);
         __syncwarp();
         if (slow_n[warp] >= kSlowQueue / 2) drain();  // warp-uniform: everyone reads the same counter
     }
@@ -187,16 +247,16 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
         unsigned long long t = 0;
         for (int w = 0; w < kHistWarps; w++)
-            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * nbins + b) * 32 + ((l + b) & 31)];
+            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * rows + b) * 32 + ((l + b) & 31)];
         if (t) atomicAdd(counts + b, t);
     }
     if (MOMENTS) {
-        long long mn = m.mn, mx = m.mx;
+        long long mn = sm_slow.mn, mx = sm_slow.mx;
         if (m.mn32 <= m.mx32) {  // this thread saw fast-path samples
             mn = (long long)m.mn32 < mn ? (long long)m.mn32 : mn;
             mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
         }
-        U128 sum = m.sum, sq = m.sq;
+        U128 sum = sm_slow.sum, sq = sm_slow.sq;
         add128(sum, m.fsum, 0);
         add128(sq, m.fsq, m.fsq_carry);
 #pragma unroll
@@ -377,7 +437,7 @@ radix_kernel(const long long* __restrict__ x, size_t n, unsigned long long key_b
     }
 }
 
-size_t hist_smem(int nbins) { return (size_t)kHistWarps * nbins * 32 * sizeof(unsigned); }
+size_t hist_smem(int nbins) { return (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned); }
 
 int sm_count() {
     int dev = 0, sms = 148;
@@ -427,13 +487,15 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     const size_t smem = hist_smem(nbins);
     const int max_smem = (int)hist_smem(kMaxThresholds + 1);
     using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*);
-    static const Kernel kernels[2][3] = {{hist_kernel<false, 0>, hist_kernel<false, 1>, hist_kernel<false, 2>},
-                                         {hist_kernel<true, 0>, hist_kernel<true, 1>, hist_kernel<true, 2>}};
+    // without moments the quotient is never formed, so one instantiation serves all modes
+    static const Kernel kernels[2][4] = {
+        {hist_kernel<false, 0>, hist_kernel<false, 0>, hist_kernel<false, 0>, hist_kernel<false, 0>},
+        {hist_kernel<true, 0>, hist_kernel<true, 1>, hist_kernel<true, 2>, hist_kernel<true, 3>}};
     const Kernel k = kernels[want_moments ? 1 : 0][mode32];
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: 4 by registers, fewer when the private counter tables are large
-    int per_sm = (int)std::min<size_t>(4, (220 * 1024) / (smem + sizeof(HistParams) + kHistWarps * kSlowQueue * 8 + 1024));
+    int per_sm = (int)std::min<size_t>(4, (220 * 1024) / (smem + sizeof(uint2) * kFastCells + kHistWarps * kSlowQueue * 8 + 1024));
     if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
@@ -525,13 +587,31 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
             else if (P->thr[j] <= (long long)hi) extra++;
         }
         P->lut[idx] = (unsigned short)((base << 8) | (extra > 255 ? 255 : extra));
-        // thresholds inside a cell are > lo >= 0, so thr - 1 >= 0; beyond 32 bits no fast-path sample exceeds it
-        unsigned int gt = 0xFFFFFFFFu;
-        if (extra >= 1 && base < m) {
-            long long t1 = P->thr[base] - 1;
-            gt = t1 >= 0xFFFFFFFFll ? 0xFFFFFFFFu : (unsigned int)t1;
+    }
+    // fast-path cells (see HistParams::fast)
+    for (int t = 0; t < kFastCells; t++) {
+        unsigned long long lo = 0, hi = 0;
+        bool empty = false;
+        if (t >= 1) {
+            const int e = (t - 1) / 32, mant = (t - 1) % 32;
+            if (e >= 5) {
+                lo = (1ull << e) + ((unsigned long long)mant << (e - 5));
+                hi = lo + (1ull << (e - 5)) - 1;
+            } else {  // fewer than five bits below the leading one: only every 2^(5-e)-th cell is populated
+                empty = (mant & ((1 << (5 - e)) - 1)) != 0;
+                lo = hi = (1ull << e) + (unsigned long long)(mant >> (5 - e));
+            }
         }
-        P->cell_gt[idx] = gt;
+        int base = 0, extra = 0;
+        for (int j = 0; j < m && !empty; j++) {
+            if (P->thr[j] <= (long long)lo) base++;
+            else if (P->thr[j] <= (long long)hi) extra++;
+        }
+        // thresholds inside a cell are > lo >= 0 and <= hi < 2^32, so thr - 1 fits 32 bits
+        P->fast[t].x = extra >= 1 ? (unsigned int)(P->thr[base] - 1) : 0xFFFFFFFFu;
+        // A cell with two or more thresholds sends the sample to the generic path; its (no-op) counter update is
+        // pointed at the trash rows past the last bin, and bit 2 keeps the address word-aligned.
+        P->fast[t].y = extra >= 2 ? (unsigned int)(m + 1) * 128u | 4u : (unsigned int)base * 128u;
     }
     // 32-bit dividends (Granlund-Montgomery, N = 32): l = ceil(log2 d), m' = floor(2^32 (2^l - d) / d) + 1,
     // q = (t + ((n - t) >> 1)) >> (l - 1) with t = umulhi(m', n)
@@ -546,6 +626,28 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
         P->magic32 = (unsigned int)((((unsigned __int128)1 << 32) * ((1ull << l) - d32)) / d32 + 1);
         P->shift32 = l - 1;
         P->mode32 = 1;
+        // Cheaper when it exists: strip the divisor's trailing zero bits first (d = 2^pre * d'), then the dividend
+        // has only 32 - pre bits and a 32-bit magic M = ceil(2^k / d') without fix-up is exact as soon as
+        // (M d' - 2^k) (2^(32-pre) - 1) < 2^k.  Divisors >= 16 also bound the quotient below 2^28, which lets the
+        // kernel sum eight quotients in 32 bits and eight squares in 64.
+        int pre = 0;
+        while (!((d32 >> pre) & 1)) pre++;
+        const unsigned long long dp = d32 >> pre;
+        if (d32 >= 16 && dp > 1) {
+            const unsigned __int128 nmax = ((unsigned __int128)1 << (32 - pre)) - 1;
+            for (int post = 0; post < 32; post++) {
+                const unsigned __int128 two_k = (unsigned __int128)1 << (32 + post);
+                const unsigned __int128 M = (two_k + dp - 1) / dp;
+                if (M >> 32) break;
+                if ((M * dp - two_k) * nmax < two_k) {
+                    P->magic32 = (unsigned int)M;
+                    P->shift32 = post;
+                    P->pre32 = pre;
+                    P->mode32 = 3;
+                    break;
+                }
+            }
+        }
     }
     // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)
     P->divisor = divisor;

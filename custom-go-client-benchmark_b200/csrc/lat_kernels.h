@@ -7,6 +7,7 @@ namespace b200 {
 
 constexpr int kMaxThresholds = 66;      // B200_HIST_MAX_EDGES + slack
 constexpr int kLutCells = 2048;         // log-linear cells: 32 per power of two
+constexpr int kFastCells = 1025;        // fast path (0 <= n < 2^32): {0} plus 32 cells per power of two
 constexpr int kRadixBits = 12;
 constexpr int kRadixBins = 1 << kRadixBits;
 constexpr int kMaxSelect = 4;           // order statistics resolved per pass
@@ -24,14 +25,20 @@ struct LatMoments {
 struct HistParams {
     long long thr[kMaxThresholds];      // thresholds in raw ns, ascending: count(n) = #{j : thr[j] <= n}
     int nthr;
-    unsigned short lut[kLutCells];      // (base << 8) | extra for each log-linear cell of n >= 0
-    unsigned int cell_gt[kLutCells];    // fast path (0 <= n < 2^32): count = base + (n > cell_gt[cell]);
-                                        // = (first threshold inside the cell) - 1, or 0xFFFFFFFF if none
+    unsigned short lut[kLutCells];      // (base << 8) | extra for each log-linear cell of n >= 0 (generic path)
+    // Fast path (0 <= n < 2^32).  Cell t = max(bits(float_rz(n)) >> 18, 4063) - 4063: the float's exponent and
+    // top five mantissa bits, i.e. 0 -> cell 0, 1 -> cell 1, 32 cells per power of two after that.
+    //   fast[t].x = (first threshold inside the cell) - 1, or 0xFFFFFFFF if none
+    //   fast[t].y = 128 * #{thresholds <= low end of the cell}; a cell holding two or more thresholds (generic
+    //               path) has 128 * (nthr + 1) | 4 instead: bit 2 is the flag, the offset a scratch row
+    // so the sample's counter sits at byte offset fast[t].y + 128 * (n > fast[t].x) of the lane's column.
+    uint2 fast[kFastCells];
     unsigned long long magic;           // division by `divisor` as multiply-high (see lat_kernels.cu)
     int magic_shift;
     int magic_add;
-    unsigned int magic32;               // the same for 32-bit dividends: q = (t + ((n - t) >> 1)) >> shift32,
-    int shift32;                        //   t = umulhi(magic32, n); mode32: 0 = divisor 1, 1 = magic, 2 = q is 0
+    unsigned int magic32;               // the same for 32-bit dividends.  mode32: 0 = divisor 1, 2 = q is 0,
+    int shift32;                        //   1: q = (t + ((n - t) >> 1)) >> shift32, t = umulhi(magic32, n)
+    int pre32;                          //   3: q = umulhi(n >> pre32, magic32) >> shift32, and q < 2^28
     int mode32;
     long long divisor;
 };

@@ -23,6 +23,10 @@ namespace {
 
 constexpr int kHistThreads = 256;
 constexpr int kHistWarps = kHistThreads / 32;
+#ifndef B200_HIST_CTAS
+#define B200_HIST_CTAS 3
+#endif
+constexpr int kHistCtasPerSm = B200_HIST_CTAS;  // 3 x 256 threads: 85 registers each, room for the prefetched tile
 constexpr int kRadixThreads = 512;
 constexpr int kTrashRows = 3;   // counter rows past the real bins: where parked samples' no-op updates land
 constexpr int kSlowQueue = 128;  // parked samples per warp; overflow falls back to the divergent path
@@ -95,27 +99,42 @@ __device__ __noinline__ void slow_sample(long long v, const HistParams* __restri
     }
 }
 
+// Shared memory map of the histogram kernel, in ABSOLUTE shared addresses so that the hot loop addresses the
+// cell table and the counters as register + immediate (the compiler's own shared pointers carry a window base
+// it keeps recomputing under register pressure).  The driver's reserved 1 KB sits below the dynamic window;
+// the kernel checks the window start at run time.
+constexpr unsigned kSlowNAbs = 0x400;                                   // unsigned[kHistWarps]
+constexpr unsigned kSlowQAbs = 0x440;                                   // long long[kHistWarps][kSlowQueue]
+constexpr unsigned kFastAbs = kSlowQAbs + kHistWarps * kSlowQueue * 8;  // uint2[kFastCells]
+constexpr unsigned kCntAbs = kFastAbs + kFastCells * 8;                 // unsigned[kHistWarps][rows][32]
+constexpr int kFastBias = (int)kFastAbs - kFastFirst * 8;               // cell address = bias + 8 * (bits >> 18)
+
+extern __shared__ __align__(1024) unsigned char hist_smem_raw[];
+
 // DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic with
 // the add fix-up, 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28.
 template <bool MOMENTS, int DIVMODE>
-__global__ void __launch_bounds__(kHistThreads, 4)
+__global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom) {
-    extern __shared__ __align__(16) unsigned char sm[];
-    __shared__ uint2 fast[kFastCells];
+    const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
+    if (smem_base > kSlowNAbs) asm volatile("trap;");
+    unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
     // Samples that need the generic path (>= 2^32 ns, negative, or a cell holding several thresholds) are rare
     // but would drag their whole warp through ~140 divergent instructions; they are parked in a per-warp queue
     // and processed 32 at a time instead.
-    __shared__ long long slow_q[kHistWarps][kSlowQueue];
-    __shared__ unsigned slow_n[kHistWarps];
-    unsigned* tbl = reinterpret_cast<unsigned*>(sm);  // [warp][bin][lane] private counters
+    unsigned* const slow_n = reinterpret_cast<unsigned*>(sm0 + kSlowNAbs);
+    long long* const slow_q = reinterpret_cast<long long*>(sm0 + kSlowQAbs);
+    uint2* const fast = reinterpret_cast<uint2*>(sm0 + kFastAbs);
+    unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kCntAbs);  // [warp][row][lane] private counters
     if (threadIdx.x < kHistWarps) slow_n[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < kFastCells; i += kHistThreads) fast[i] = Pg->fast[i];
     const int nbins = Pg->nthr + 1, rows = nbins + kTrashRows;
     for (int i = threadIdx.x; i < kHistWarps * rows * 32; i += kHistThreads) tbl[i] = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned* mine = tbl + (size_t)warp * rows * 32 + lane;
+    unsigned* const mine = tbl + (size_t)warp * rows * 32 + lane;
+    const unsigned mine_abs = kCntAbs + (unsigned)(warp * rows * 32 + lane) * 4u;
     Moments m;
     const unsigned magic32 = Pg->magic32;
     const int shift32 = Pg->shift32, pre32 = Pg->pre32;
@@ -124,24 +143,31 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     auto slow = [&](long long v) { slow_sample(v, Pg, mine, MOMENTS ? &sm_slow : nullptr); };
     auto park = [&](long long v) {
         const unsigned at = atomicAdd(&slow_n[warp], 1u);
-        if (at < kSlowQueue) slow_q[warp][at] = v;
+        if (at < kSlowQueue) slow_q[warp * kSlowQueue + at] = v;
         else slow(v);  // queue full: take the hit now
     };
     auto drain = [&]() {
         __syncwarp();
         const unsigned cnt = min(slow_n[warp], (unsigned)kSlowQueue);
-        for (unsigned k = lane; k < cnt; k += 32) slow(slow_q[warp][k]);
+        for (unsigned k = lane; k < cnt; k += 32) slow(slow_q[warp * kSlowQueue + k]);
         __syncwarp();
         if (lane == 0) slow_n[warp] = 0;
         __syncwarp();
     };
     // Fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), 32-bit arithmetic only.  lookup() fetches the sample's
-    // cell and says whether the sample has to be parked; count() bumps the lane's private counter.
+    // cell and says whether the sample has to be parked; bump() adds to one of the lane's private counters.
     auto lookup = [&](long long v, uint2& w) -> unsigned {
         const unsigned u = (unsigned)v, hi = (unsigned)((unsigned long long)v >> 32);
-        const unsigned t = max(__float_as_uint(__uint2float_rz(u)) >> 18, 4063u) - 4063u;
-        w = fast[t];
+        const unsigned idx8 = (__float_as_uint(__uint2float_rz(u | 1u)) >> 15) & 0x3FFF8u;
+        asm("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(w.x), "=r"(w.y) : "r"(idx8), "n"(kFastBias));
         return hi | (w.y & 4u);  // >= 2^32 / negative, or several thresholds in the cell
+    };
+    auto bump = [&](unsigned u, const uint2 w, unsigned inc) {
+        const unsigned addr = mine_abs + w.y + (u > w.x ? 128u : 0u);
+        unsigned c;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
+        c += inc;
+        asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
     };
     auto quotient = [&](unsigned u) -> unsigned {
         if (DIVMODE == 1) {
@@ -150,14 +176,6 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         }
         if (DIVMODE == 3) return __umulhi(u >> pre32, magic32) >> shift32;
         return DIVMODE == 0 ? u : 0u;
-    };
-    auto count = [&](unsigned u, const uint2 w) {
-        const unsigned off = w.y + (u > w.x ? 128u : 0u);
-        ++*reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(mine) + off);
-        if (MOMENTS) {
-            m.mn32 = min(m.mn32, u);
-            m.mx32 = max(m.mx32, u);
-        }
     };
     auto accumulate = [&](unsigned q) {  // running 64-bit sums; q*q wraps at most once per add
         m.fsum += q;
@@ -168,8 +186,13 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     auto one = [&](long long v) {
         uint2 w;
         if (lookup(v, w)) { park(v); return; }
-        count((unsigned)v, w);
-        if (MOMENTS) accumulate(quotient((unsigned)v));
+        const unsigned u = (unsigned)v;
+        bump(u, w, 1u);
+        if (MOMENTS) {
+            m.mn32 = min(m.mn32, u);
+            m.mx32 = max(m.mx32, u);
+            accumulate(quotient(u));
+        }
     };
     // Eight samples at a time, without a branch in the common work: a sample that has to be parked still walks
     // through the counting code, but adds 0 to its counter and contributes the neutral element to every moment
@@ -191,8 +214,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const unsigned u = (unsigned)v[k];
-            const unsigned off = w[k].y + (u > w[k].x ? 128u : 0u);
-            *reinterpret_cast<unsigned*>(reinterpret_cast<unsigned char*>(mine) + off) += keep[k] & 1u;
+            bump(u, w[k], keep[k] & 1u);
             if (MOMENTS) {
                 m.mn32 = min(m.mn32, u | ~keep[k]);
                 m.mx32 = max(m.mx32, u & keep[k]);
@@ -218,7 +240,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         }
     };
 
-    // head (to 16-byte alignment), vector body, tail
+    // head (to 16-byte alignment), tiles of 16 KB per CTA, remainder, tail
     size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
     if (head > n) head = n;
     const size_t tid = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
@@ -226,16 +248,28 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     if (tid == 0 && head) one(x[0]);
     const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
     const size_t npairs = (n - head) / 2;
-    size_t i = tid;
-    // The trip count of this loop is the same for all lanes of a warp (it is decided by the warp's LAST lane),
-    // because drain() synchronises the warp.
-    for (; (i - lane) + 31 + 3 * nthreads < npairs; i += 4 * nthreads) {  // four independent 128-bit loads in flight
-        longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads), c = __ldg(x2 + i + 2 * nthreads),
-                  d = __ldg(x2 + i + 3 * nthreads);
-        eight(a, b, c, d);
-        __syncwarp();
-        if (slow_n[warp] >= kSlowQueue / 2) drain();  // warp-uniform: everyone reads the same counter
+    // A CTA takes whole tiles of 4 x kHistThreads pairs, so a thread's four 128-bit loads are a fixed 4 KB apart
+    // and the trip count is the same for every thread of the CTA (drain() synchronises warps).
+    constexpr size_t kTilePairs = 4 * kHistThreads;
+    const size_t ntiles = npairs / kTilePairs;
+    // The next tile's loads are issued before the current tile is counted (the kernel is otherwise bound by
+    // the latency of its own loads: 8 warps per scheduler do not cover ~1 us of HBM latency under load).
+    if ((size_t)blockIdx.x < ntiles) {
+        const longlong2* p = x2 + (size_t)blockIdx.x * kTilePairs + threadIdx.x;
+        longlong2 a = __ldg(p), b = __ldg(p + kHistThreads), c = __ldg(p + 2 * kHistThreads),
+                  d = __ldg(p + 3 * kHistThreads);
+        for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
+            const size_t tn = t + gridDim.x < ntiles ? t + gridDim.x : t;  // last round: reload (and ignore) the same tile
+            p = x2 + tn * kTilePairs + threadIdx.x;
+            const longlong2 na = __ldg(p), nb = __ldg(p + kHistThreads), nc = __ldg(p + 2 * kHistThreads),
+                            nd = __ldg(p + 3 * kHistThreads);
+            eight(a, b, c, d);
+            a = na; b = nb; c = nc; d = nd;
+            __syncwarp();
+            if (slow_n[warp] >= kSlowQueue / 2) drain();  // warp-uniform: everyone reads the same counter
+        }
     }
+    size_t i = ntiles * kTilePairs + tid;
     for (; i < npairs; i += nthreads) {
         longlong2 a = __ldg(x2 + i);
         one(a.x); one(a.y);
@@ -437,7 +471,8 @@ radix_kernel(const long long* __restrict__ x, size_t n, unsigned long long key_b
     }
 }
 
-size_t hist_smem(int nbins) { return (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned); }
+// dynamic window: everything up to the end of the counters (absolute address, see the map above)
+size_t hist_smem(int nbins) { return kCntAbs + (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned); }
 
 int sm_count() {
     int dev = 0, sms = 148;
@@ -494,8 +529,8 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     const Kernel k = kernels[want_moments ? 1 : 0][mode32];
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
-    // resident CTAs per SM: 4 by registers, fewer when the private counter tables are large
-    int per_sm = (int)std::min<size_t>(4, (220 * 1024) / (smem + sizeof(uint2) * kFastCells + kHistWarps * kSlowQueue * 8 + 1024));
+    // resident CTAs per SM: kHistCtasPerSm by registers, fewer when the private counter tables are large
+    int per_sm = (int)std::min<size_t>(kHistCtasPerSm, (224 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
@@ -588,19 +623,19 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
         }
         P->lut[idx] = (unsigned short)((base << 8) | (extra > 255 ? 255 : extra));
     }
-    // fast-path cells (see HistParams::fast)
+    // fast-path cells (see HistParams::fast): the cell of n is read off float_rz(n | 1)
     for (int t = 0; t < kFastCells; t++) {
-        unsigned long long lo = 0, hi = 0;
+        unsigned long long lo, hi;
         bool empty = false;
-        if (t >= 1) {
-            const int e = (t - 1) / 32, mant = (t - 1) % 32;
-            if (e >= 5) {
-                lo = (1ull << e) + ((unsigned long long)mant << (e - 5));
-                hi = lo + (1ull << (e - 5)) - 1;
-            } else {  // fewer than five bits below the leading one: only every 2^(5-e)-th cell is populated
-                empty = (mant & ((1 << (5 - e)) - 1)) != 0;
-                lo = hi = (1ull << e) + (unsigned long long)(mant >> (5 - e));
-            }
+        const int e = t / 32, mant = t % 32;
+        if (e >= 6) {  // bit 0 lies below the five mantissa bits: the | 1 does not move the cell
+            lo = (1ull << e) + ((unsigned long long)mant << (e - 5));
+            hi = lo + (1ull << (e - 5)) - 1;
+        } else {  // n | 1 is the odd number 2^e + (mant >> (5 - e)); the cell is that number and the even one below
+            const unsigned long long odd = (1ull << e) + (unsigned long long)(mant >> (5 - e));
+            empty = (mant & ((1 << (5 - e)) - 1)) != 0 || !(odd & 1);
+            lo = odd - 1;
+            hi = odd;
         }
         int base = 0, extra = 0;
         for (int j = 0; j < m && !empty; j++) {

@@ -7,7 +7,8 @@ namespace b200 {
 
 constexpr int kMaxThresholds = 66;      // B200_HIST_MAX_EDGES + slack
 constexpr int kLutCells = 2048;         // log-linear cells: 32 per power of two
-constexpr int kFastCells = 1025;        // fast path (0 <= n < 2^32): {0} plus 32 cells per power of two
+constexpr int kFastCells = 1024;        // fast path (0 <= n < 2^32): 32 cells per power of two
+constexpr int kFastFirst = 127 * 32;    // float bits >> 18 of 1.0f: the first cell's index
 constexpr int kRadixBits = 12;
 constexpr int kRadixBins = 1 << kRadixBits;
 constexpr int kMaxSelect = 4;           // order statistics resolved per pass
@@ -26,8 +27,8 @@ struct HistParams {
     long long thr[kMaxThresholds];      // thresholds in raw ns, ascending: count(n) = #{j : thr[j] <= n}
     int nthr;
     unsigned short lut[kLutCells];      // (base << 8) | extra for each log-linear cell of n >= 0 (generic path)
-    // Fast path (0 <= n < 2^32).  Cell t = max(bits(float_rz(n)) >> 18, 4063) - 4063: the float's exponent and
-    // top five mantissa bits, i.e. 0 -> cell 0, 1 -> cell 1, 32 cells per power of two after that.
+    // Fast path (0 <= n < 2^32).  Cell t = (bits(float_rz(n | 1)) >> 18) - kFastFirst: the float's exponent and
+    // top five mantissa bits, i.e. 32 cells per power of two; below 64 a cell is the pair {2k, 2k+1}.
     //   fast[t].x = (first threshold inside the cell) - 1, or 0xFFFFFFFF if none
     //   fast[t].y = 128 * #{thresholds <= low end of the cell}; a cell holding two or more thresholds (generic
     //               path) has 128 * (nthr + 1) | 4 instead: bit 2 is the flag, the offset a scratch row

@@ -106,6 +106,40 @@ def test_fractional_and_negative_edges(ctx):
     ctx.free_device(d)
 
 
+def test_fast_path_cells_and_divisors(ctx):
+    """The 32-bit fast path: every log-linear cell boundary below 2^32 (and the pair cells below 64), thresholds
+    that split a cell, cells that hold two thresholds (generic path), and each way the kernel divides."""
+    rng = np.random.default_rng(11)
+    vals = list(range(0, 200))
+    for e in range(6, 33):
+        for mant in (0, 1, 13, 31):
+            b = (1 << e) + (mant << (e - 5))
+            vals += [b - 1, b, b + 1]
+    vals += [(1 << 32) - 1, 1 << 32, (1 << 32) + 1, 1 << 40, -1, -(1 << 33)]
+    ns = np.concatenate([np.array(vals, dtype=np.int64),
+                         rng.integers(0, 1 << 32, size=200_000, dtype=np.int64),
+                         rng.integers(0, 4096, size=100_000, dtype=np.int64),
+                         rng.integers(-(1 << 34), 1 << 36, size=5_000, dtype=np.int64)])
+    rng.shuffle(ns)
+    d = upload(ctx, ns)
+    absn = np.abs(ns).astype(object)
+    for div in (1, 2, 16, 17, 24, 1000, 1_000_000, 999_983, (1 << 31) + 1, (1 << 32) + 5):
+        v = np.array([int(a) // div * (1 if x >= 0 else -1) for a, x in zip(absn, ns)], dtype=object)  # Go truncation
+        vf = v.astype(np.float64)
+        top = float((1 << 36) // div + 2)
+        for edges in (np.array([0, 1, 2, 3, 4, 5, 6.5, 7, 33, 34, 63, 64, 65, 100, 1000, 4000, top]) ,
+                      np.array([0.5, 2, 1e3, 1e6, 2.0 ** 31, 2.0 ** 32 - 1, 2.0 ** 32, 2.0 ** 33, 2.0 ** 37])):
+            edges = np.unique(edges.astype(np.float64))
+            oc = lat.hist_fixed(d, ns.size, div, edges, pkg._lib.HIST_OPENCENSUS, ctx=ctx)
+            assert list(oc.counts) == list(oracle.hist_opencensus(vf, edges)), (div, edges)
+            assert oc.sum == int(v.sum()) and oc.sumsq == int((v * v).sum()), div
+            assert (oc.min, oc.max) == (int(v.min()), int(v.max())), div
+            h = lat.hist_fixed(d, ns.size, div, edges, pkg._lib.HIST_NUMPY, ctx=ctx)
+            ref, dropped = oracle.hist_numpy(vf, edges)
+            assert list(h.counts) == list(ref) and h.dropped_below + h.dropped_above == dropped, (div, edges)
+    ctx.free_device(d)
+
+
 def test_histogram_unaligned_and_tiny(ctx, samples):
     ns, d, n = samples
     for start, cnt in [(1, 1001), (3, 2), (5, 1), (0, 0), (7, 100000)]:

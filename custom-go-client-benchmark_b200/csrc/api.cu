@@ -4,6 +4,10 @@
 #include "b200crc.h"
 
 #include <algorithm>
+#include <chrono>
+#include <climits>
+#include <cmath>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -66,7 +70,8 @@ struct DevState {
     DeviceTables tabs{};
     std::mutex mu;                  // guards the streams and scratch of this device
     std::recursive_mutex stage_mu;  // guards the staging slabs (held across whole host-input calls)
-    std::mutex select_mu;           // one order-statistic query at a time per device (they share lat.d_compact)
+    std::recursive_mutex select_mu; // one order-statistic query at a time per device (they share lat.d_compact);
+                                    // recursive: the sampled select runs ordinary selects on its sample
     std::map<uint32_t, uint32_t*> adv_seg;  // rows_per_seg -> device [4][256]
     uint32_t* seg_raw = nullptr;            // scratch for single-object runs
     size_t seg_raw_cap = 0;
@@ -1243,6 +1248,40 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
 
 namespace {
 
+int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
+                int64_t* out);  // below, after the radix select it builds on
+
+// Inputs up to this many samples are selected with all passes queued on the device (one host round trip);
+// longer ones that the sampled select did not settle take the host-driven passes with bucket compaction.
+size_t resident_select_max() {  // tuning / test override: B200_SELECT_RESIDENT_MAX=0 forces the host-driven passes
+    static const size_t v = [] {
+        const char* e = getenv("B200_SELECT_RESIDENT_MAX");
+        return e && *e ? (size_t)strtoull(e, nullptr, 10) : (size_t)1 << 26;
+    }();
+    return v;
+}
+
+int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, bool have_bounds,
+                    int64_t lo, int64_t hi, const uint64_t* k, int nk, int64_t* out) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d) return fail(B200_ERR_INVALID, "b200_select_kth: unknown device");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    for (int g = 0; g < nk; g += kSelMax) {
+        SelRanks r{};
+        r.nk = std::min(kSelMax, nk - g);
+        for (int i = 0; i < r.nk; i++) r.rank[i] = k[g + i];
+        CU(launch_select_resident((const long long*)d_samples, n, r, have_bounds, lo, hi, d->lat, d->stream));
+        SelState st;
+        CU(cudaMemcpyAsync(&st, d->lat.d_sel, sizeof st, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+        if (st.bad || st.top != 0)
+            return fail(B200_ERR_INVALID, "b200_select_kth: samples outside the given [lo, hi] range");
+        for (int i = 0; i < r.nk; i++) out[g + i] = st.result[i] / divisor;  // truncating division is monotone
+    }
+    return 0;
+}
+
 // After the first radix pass: copy the samples of the buckets still in play (distinct prefixes pf[0..np)) into
 // the device's compaction buffer so that the remaining passes read `total` samples instead of n.  Returns 0
 // and sets *out when done, 1 when the buckets are too large to be worth it (caller keeps the full data).
@@ -1287,7 +1326,12 @@ int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size
         if (k[i] >= n) return fail(B200_ERR_INVALID, "b200_select_kth: k >= n");
     DevState* dsel = get_dev(ctx, dev);
     if (!dsel) return fail(B200_ERR_INVALID, "b200_select_kth: unknown device");
-    std::lock_guard<std::mutex> sel_lock(dsel->select_mu);
+    {   // the one-pass sampled select needs no bounds; when it misses, the radix passes below use them
+        const int rc = try_sampled(ctx, dev, d_samples, n, divisor, k, nk, out);
+        if (rc <= 0) return rc;
+    }
+    if (n <= resident_select_max()) return select_resident(ctx, dev, d_samples, n, divisor, true, lo_ns, hi_ns, k, nk, out);
+    std::lock_guard<std::recursive_mutex> sel_lock(dsel->select_mu);
     const uint64_t kmin = (uint64_t)lo_ns ^ 0x8000000000000000ull, kmax = (uint64_t)hi_ns ^ 0x8000000000000000ull;
     const uint64_t range = kmax - kmin;
     int bits = 0;
@@ -1350,10 +1394,186 @@ int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size
     return 0;
 }
 
+}  // extern "C"
+
+namespace {
+
+thread_local int g_sampled_depth = 0;  // the selects a sampled select runs on its own buffers must not nest
+
+size_t sampled_select_min() {  // inputs at least this long try the sampled shortcut first (tuning / test override)
+    static const size_t v = [] {
+        const char* e = getenv("B200_SELECT_SAMPLED_MIN");
+        return e && *e ? (size_t)strtoull(e, nullptr, 10) : (size_t)1 << 24;
+    }();
+    return v;
+}
+
+int sampled_trace(const char* what, int rc) {  // B200_SELECT_TRACE=1: say on stderr how a sampled select ended
+    static const bool on = [] {
+        const char* e = getenv("B200_SELECT_TRACE");
+        return e && *e && *e != '0';
+    }();
+    if (on) fprintf(stderr, "b200 select: sampled %s\n", what);
+    return rc;
+}
+
+bool grow(long long** buf, size_t* cap, size_t want) {
+    if (*cap >= want) return true;
+    cudaFree(*buf);
+    *buf = nullptr;
+    *cap = 0;
+    if (cudaMalloc(buf, want * sizeof(long long)) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    *cap = want;
+    return true;
+}
+
+// Exact order statistics in ONE pass over the samples instead of min/max + three radix passes:
+//   1. a stratified sample (one input per stratum of `stride`) gives, for every wanted rank, a bracket
+//      [lo, hi] of sample order statistics a few standard deviations either side of the rank's expected position;
+//   2. one histogram pass over all samples with the bracket ends as thresholds counts the samples below each
+//      bracket and keeps the samples inside the brackets (about 1 % of the input);
+//   3. if every rank did fall into its bracket (checked with the exact counts), it is resolved among the kept
+//      samples, by the ordinary radix select.
+// The result is exact whenever it is given; a miss (returns 1) makes the caller take the radix passes.
+int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
+                   int nk, int64_t* out) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || nk > kMaxSelect) return 1;
+    std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
+    struct Depth {
+        Depth() { g_sampled_depth++; }
+        ~Depth() { g_sampled_depth--; }
+    } depth;
+    const auto t0 = std::chrono::steady_clock::now();
+    auto ms_since = [&](std::chrono::steady_clock::time_point t) {
+        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count();
+    };
+    const size_t stride = std::max<size_t>(16, (n + ((size_t)1 << 22) - 1) >> 22);
+    const size_t s = n / stride;
+    if (s < 4096) return sampled_trace("skip: input too short", 1);
+    // sample rank of an input rank r is about r / stride, with a standard deviation below sqrt(s) / 2
+    const uint64_t margin = (uint64_t)(2.5 * std::sqrt((double)s)) + 2;
+    uint64_t want[2 * kMaxSelect];
+    bool open_lo[kMaxSelect], open_hi[kMaxSelect];
+    int nwant = 0, lo_at[kMaxSelect], hi_at[kMaxSelect];
+    for (int i = 0; i < nk; i++) {
+        const uint64_t c = k[i] / stride;
+        open_lo[i] = c < margin;
+        open_hi[i] = c + margin + 1 >= s;
+        lo_at[i] = hi_at[i] = -1;
+        if (!open_lo[i]) { lo_at[i] = nwant; want[nwant++] = c - margin; }
+        if (!open_hi[i]) { hi_at[i] = nwant; want[nwant++] = c + margin + 1; }
+    }
+    int64_t got[2 * kMaxSelect];
+    {
+        std::unique_lock<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(dev));
+        if (!grow(&d->lat.d_sample, &d->lat.sample_cap, s)) return sampled_trace("skip: no memory for the sample", 1);
+        CU(launch_sample((const long long*)d_samples, stride, d->lat.d_sample, s, d->stream));
+    }
+    if (nwant) {
+        int rc = b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_sample, s, 1, want, nwant, got);
+        if (rc) return rc < 0 ? rc : 1;
+    }
+    const double ms_sample = ms_since(t0);
+    // brackets, ascending and disjoint (overlapping or touching ones are merged)
+    struct Bracket { int64_t lo, hi; };
+    const int64_t kMin = INT64_MIN, kMax = INT64_MAX - 1;  // hi + 1 must not overflow
+    Bracket br[kMaxSelect];
+    for (int i = 0; i < nk; i++) {
+        br[i].lo = open_lo[i] ? kMin : got[lo_at[i]];
+        br[i].hi = open_hi[i] ? kMax : std::min(got[hi_at[i]], kMax);
+    }
+    for (int i = 1; i < nk; i++)  // at most kMaxSelect entries: insertion sort by lo
+        for (int j = i; j > 0 && br[j].lo < br[j - 1].lo; j--) std::swap(br[j], br[j - 1]);
+    int nb = 0;
+    for (int i = 0; i < nk; i++) {
+        if (nb && br[i].lo <= br[nb - 1].hi + 1) br[nb - 1].hi = std::max(br[nb - 1].hi, br[i].hi);
+        else br[nb++] = br[i];
+    }
+    long long thr[2 * kMaxSelect];
+    for (int j = 0; j < nb; j++) {
+        thr[2 * j] = br[j].lo;      // bins 2j+1 are the brackets, even bins the gaps
+        thr[2 * j + 1] = br[j].hi + 1;
+    }
+    HistParams P;
+    // a bracket that starts at INT64_MIN leaves bin 0 empty, which the builder allows (thresholds stay ascending)
+    if (host_build_hist_params_thr(thr, 2 * nb, &P)) return sampled_trace("skip: thresholds", 1);
+    // room for twice the expected number of samples inside the brackets, at least n/64; more than n/8 is not worth it
+    const size_t expect = (size_t)nk * (2 * margin + 2) * stride;
+    const size_t cap = std::min<size_t>(std::max<size_t>(2 * expect, n / 64), n / 8);
+    unsigned long long c[kMaxThresholds + 1], kept = 0;
+    {
+        std::unique_lock<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(dev));
+        if (!grow(&d->lat.d_collect, &d->lat.collect_cap, cap)) return sampled_trace("skip: no memory for the brackets", 1);
+        CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
+        HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
+        CU(launch_hist((const long long*)d_samples, n, d->lat, false, d->stream, P.nthr + 1, P.mode32, &col));
+        CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaMemcpyAsync(&kept, d->lat.d_compact_n, sizeof kept, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+    }
+    const double ms_pass = ms_since(t0) - ms_sample;
+    uint64_t inside = 0, total = 0;
+    for (int j = 0; j <= 2 * nb; j++) total += c[j];
+    for (int j = 0; j < nb; j++) inside += c[2 * j + 1];
+    if (total != n || kept != inside) return fail(B200_ERR_CUDA, "select: bracket pass lost samples");
+    if (inside > cap || inside == 0) return sampled_trace("miss: brackets too heavy", 1);
+    // rank among the kept samples = (kept samples in earlier brackets) + (rank - samples below this bracket)
+    uint64_t rank_kept[kMaxSelect];
+    for (int i = 0; i < nk; i++) {
+        uint64_t below = 0, kept_before = 0;
+        int j = 0;
+        for (;; j++) {
+            if (j == nb) return sampled_trace("miss: rank beyond the brackets", 1);
+            below += c[2 * j];
+            if (k[i] < below) return sampled_trace("miss: rank between brackets", 1);
+            if (k[i] < below + c[2 * j + 1]) break;
+            below += c[2 * j + 1];
+            kept_before += c[2 * j + 1];
+        }
+        rank_kept[i] = kept_before + (k[i] - below);
+    }
+    int rc = b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, rank_kept, nk, out);
+    if (rc) return rc < 0 ? rc : 1;
+    char msg[160];
+    snprintf(msg, sizeof msg, "ok (sample of %zu + brackets %.3f ms, pass %.3f ms, %llu kept + select %.3f ms)", s, ms_sample,
+             ms_pass, (unsigned long long)inside, ms_since(t0) - ms_sample - ms_pass);
+    return sampled_trace(msg, 0);
+}
+
+// 0 = out[] is filled, 1 = not attempted or missed (take the radix passes), < 0 = error
+int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
+                int64_t* out) {
+    if (g_sampled_depth != 0 || n < sampled_select_min() || nk > kMaxSelect || !d_samples || ((uintptr_t)d_samples & 7))
+        return 1;
+    for (int i = 0; i < nk; i++)
+        if (k[i] >= n) return 1;  // the caller reports it
+    return select_sampled(ctx, dev, d_samples, n, divisor, k, nk, out);
+}
+
+}  // namespace
+
+extern "C" {
+
 int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
                     int nk, int64_t* out) {
     if (!k || !out || nk < 1 || divisor < 1) return fail(B200_ERR_INVALID, "b200_select_kth");
     if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
+    {
+        const int rc = try_sampled(ctx, dev, d_samples, n, divisor, k, nk, out);
+        if (rc <= 0) return rc;  // done, or a real error; 1 = take the radix passes
+    }
+    if (n <= resident_select_max()) {
+        for (int i = 0; i < nk; i++)
+            if (k[i] >= n) return fail(B200_ERR_INVALID, "b200_select_kth: k >= n");
+        if (!get_dev(ctx, dev) || !d_samples) return fail(B200_ERR_INVALID, "b200_select_kth");
+        return select_resident(ctx, dev, d_samples, n, divisor, false, 0, 0, k, nk, out);
+    }
     int64_t mn, mx;
     if (int rc = b200_minmax(ctx, dev, d_samples, n, &mn, &mx)) return rc;
     return b200_select_kth_range(ctx, dev, d_samples, n, divisor, mn, mx, k, nk, out);

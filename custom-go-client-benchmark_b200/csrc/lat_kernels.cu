@@ -85,9 +85,13 @@ struct Moments {
 // moments live in local memory: this runs for a handful of samples per million, and keeping it out of line
 // keeps the fast loop's registers and instruction cache to itself.
 __device__ __noinline__ void slow_sample(long long v, const HistParams* __restrict__ Pg, unsigned* mine,
-                                         SlowMoments* s) {
+                                         SlowMoments* s, const HistCollect* col) {
     const int c = classify(v, Pg->thr, Pg->nthr, Pg->lut);
     mine[c * 32]++;
+    if (col && (c & 1)) {
+        const unsigned long long at = atomicAdd(col->count, 1ull);
+        if (at < col->cap) col->buf[at] = v;
+    }
     if (s) {
         s->mn = v < s->mn ? v : s->mn;
         s->mx = v > s->mx ? v : s->mx;
@@ -105,18 +109,27 @@ __device__ __noinline__ void slow_sample(long long v, const HistParams* __restri
 // the kernel checks the window start at run time.
 constexpr unsigned kSlowNAbs = 0x400;                                   // unsigned[kHistWarps]
 constexpr unsigned kSlowQAbs = 0x440;                                   // long long[kHistWarps][kSlowQueue]
-constexpr unsigned kFastAbs = kSlowQAbs + kHistWarps * kSlowQueue * 8;  // uint2[kFastCells]
-constexpr unsigned kCntAbs = kFastAbs + kFastCells * 8;                 // unsigned[kHistWarps][rows][32]
-constexpr int kFastBias = (int)kFastAbs - kFastFirst * 8;               // cell address = bias + 8 * (bits >> 18)
+constexpr unsigned kFastAbs = kSlowQAbs + kHistWarps * kSlowQueue * 8;  // uint2 / uint4 [kFastCells]
+// then unsigned[kHistWarps][rows][32] counters, then (collecting kernels) long long[kLaneQueue][kHistThreads]
+constexpr int kLaneQueue = 16;                                          // collected samples a lane can hold
+constexpr unsigned kLaneQueueStride = kHistThreads * 8;                 // bytes between a lane's slots
 
 extern __shared__ __align__(1024) unsigned char hist_smem_raw[];
 
 // DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic with
 // the add fix-up, 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28.
-template <bool MOMENTS, int DIVMODE>
+// COLLECT: cells may hold two thresholds and the samples of odd bins are appended to col.buf.
+template <bool MOMENTS, int DIVMODE, bool COLLECT>
 __global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
-            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom) {
+            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, const HistCollect col) {
+    // cell entries are 8 bytes; collecting kernels keep the cells' second compare values in a table of their own,
+    // read (under a predicate) only by the lanes whose cell has one: 16-byte entries cost twice the shared-memory
+    // wavefronts on every look-up and made the pass LSU-bound
+    constexpr unsigned kFast2Abs = kFastAbs + kFastCells * 8;
+    constexpr unsigned kCntAbs = kFast2Abs + (COLLECT ? kFastCells * 4 : 0);
+    constexpr int kFastBias = (int)kFastAbs - kFastFirst * 8;   // cell address = bias + 8 * (bits >> 18)
+    constexpr int kFast2Bias = (int)kFast2Abs - kFastFirst * 4;
     const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
     if (smem_base > kSlowNAbs) asm volatile("trap;");
     unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
@@ -125,10 +138,15 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     // and processed 32 at a time instead.
     unsigned* const slow_n = reinterpret_cast<unsigned*>(sm0 + kSlowNAbs);
     long long* const slow_q = reinterpret_cast<long long*>(sm0 + kSlowQAbs);
-    uint2* const fast = reinterpret_cast<uint2*>(sm0 + kFastAbs);
     unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kCntAbs);  // [warp][row][lane] private counters
     if (threadIdx.x < kHistWarps) slow_n[threadIdx.x] = 0;
-    for (int i = threadIdx.x; i < kFastCells; i += kHistThreads) fast[i] = Pg->fast[i];
+    for (int i = threadIdx.x; i < kFastCells; i += kHistThreads) {
+        const uint4 c = Pg->fast[i];
+        // bit 3 of a collecting kernel's entry: the cell has a second compare value
+        reinterpret_cast<uint2*>(sm0 + kFastAbs)[i] =
+            COLLECT ? make_uint2(c.x, c.y | (c.z != 0xFFFFFFFFu && !(c.y & 4u) ? 8u : 0u)) : make_uint2(c.x, c.w);
+        if (COLLECT) reinterpret_cast<unsigned*>(sm0 + kFast2Abs)[i] = c.z;
+    }
     const int nbins = Pg->nthr + 1, rows = nbins + kTrashRows;
     for (int i = threadIdx.x; i < kHistWarps * rows * 32; i += kHistThreads) tbl[i] = 0;
     __syncthreads();
@@ -139,8 +157,12 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     const unsigned magic32 = Pg->magic32;
     const int shift32 = Pg->shift32, pre32 = Pg->pre32;
 
+    // collecting kernels: a lane's pending samples sit in its own slots until some lane of the warp runs short
+    const unsigned q_base = kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + threadIdx.x * 8u;
+    unsigned q_addr = q_base;
+
     SlowMoments sm_slow;
-    auto slow = [&](long long v) { slow_sample(v, Pg, mine, MOMENTS ? &sm_slow : nullptr); };
+    auto slow = [&](long long v) { slow_sample(v, Pg, mine, MOMENTS ? &sm_slow : nullptr, COLLECT ? &col : nullptr); };
     auto park = [&](long long v) {
         const unsigned at = atomicAdd(&slow_n[warp], 1u);
         if (at < kSlowQueue) slow_q[warp * kSlowQueue + at] = v;
@@ -156,18 +178,56 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     };
     // Fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), 32-bit arithmetic only.  lookup() fetches the sample's
     // cell and says whether the sample has to be parked; bump() adds to one of the lane's private counters.
-    auto lookup = [&](long long v, uint2& w) -> unsigned {
+    // (w.z is the cell's second compare value, used by collecting kernels only)
+    auto lookup = [&](long long v, uint4& w) -> unsigned {
         const unsigned u = (unsigned)v, hi = (unsigned)((unsigned long long)v >> 32);
-        const unsigned idx8 = (__float_as_uint(__uint2float_rz(u | 1u)) >> 15) & 0x3FFF8u;
-        asm("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(w.x), "=r"(w.y) : "r"(idx8), "n"(kFastBias));
-        return hi | (w.y & 4u);  // >= 2^32 / negative, or several thresholds in the cell
+        const unsigned bits = __float_as_uint(__uint2float_rz(u | 1u));
+        const unsigned idx = (bits >> 15) & 0x3FFF8u;
+        asm("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(w.x), "=r"(w.y) : "r"(idx), "n"(kFastBias));
+        if (COLLECT) {
+            asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\tmov.u32 %0, 0xFFFFFFFF;\n\t"
+                "@p ld.shared.u32 %0, [%1+%3];\n\t}"
+                : "=r"(w.z) : "r"(idx >> 1), "r"(w.y & 8u), "n"(kFast2Bias));
+            w.y &= ~8u;
+        }
+        return hi | (w.y & 4u);  // >= 2^32 / negative, or more thresholds in the cell than we compare with
     };
-    auto bump = [&](unsigned u, const uint2 w, unsigned inc) {
-        const unsigned addr = mine_abs + w.y + (u > w.x ? 128u : 0u);
+    // returns the byte offset of the counter row: bit 7 = the sample's bin is odd
+    auto bump = [&](unsigned u, const uint4 w, unsigned inc) -> unsigned {
+        unsigned off = w.y + (u > w.x ? 128u : 0u);
+        if (COLLECT) off += u > w.z ? 128u : 0u;
+        const unsigned addr = mine_abs + off;
         unsigned c;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
         c += inc;
         asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+        return off;
+    };
+    // keep the sample if `in` (0 or 128) is set: the slot is written under a predicate, the cursor moves by in * 16
+    auto collect = [&](long long v, unsigned in) {
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.shared.v2.u32 [%0], {%1, %2};\n\t}"
+                     ::"r"(q_addr), "r"((unsigned)v), "r"((unsigned)((unsigned long long)v >> 32)), "r"(in) : "memory");
+        static_assert(kLaneQueueStride == 128u << 4, "cursor step");
+        q_addr += in << 4;
+    };
+    auto flush = [&]() {  // whole warp: one global atomic for everything the 32 lanes hold
+        const unsigned cnt = (q_addr - q_base) / kLaneQueueStride;
+        unsigned incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        const unsigned total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        unsigned long long at = 0;
+        if (lane == 31 && total) at = atomicAdd(col.count, (unsigned long long)total);
+        at = __shfl_sync(0xFFFFFFFFu, at, 31) + (incl - cnt);
+        for (unsigned e = 0; e < cnt; e++) {
+            unsigned lo, hi;
+            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(q_base + e * kLaneQueueStride) : "memory");
+            if (at + e < col.cap) col.buf[at + e] = (long long)(((unsigned long long)hi << 32) | lo);
+        }
+        q_addr = q_base;
     };
     auto quotient = [&](unsigned u) -> unsigned {
         if (DIVMODE == 1) {
@@ -184,10 +244,11 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         m.fsq = sq;
     };
     auto one = [&](long long v) {
-        uint2 w;
+        uint4 w;
         if (lookup(v, w)) { park(v); return; }
         const unsigned u = (unsigned)v;
-        bump(u, w, 1u);
+        const unsigned off = bump(u, w, 1u);
+        if (COLLECT) collect(v, off & 128u);
         if (MOMENTS) {
             m.mn32 = min(m.mn32, u);
             m.mx32 = max(m.mx32, u);
@@ -201,7 +262,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     // be divergent most of the time.  Only the parking itself is conditional.
     auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
         const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
-        uint2 w[8];
+        uint4 w[8];
         unsigned keep[8], any = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
@@ -214,7 +275,8 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
 #pragma unroll
         for (int k = 0; k < 8; k++) {
             const unsigned u = (unsigned)v[k];
-            bump(u, w[k], keep[k] & 1u);
+            const unsigned off = bump(u, w[k], keep[k] & 1u);
+            if (COLLECT) collect(v[k], off & keep[k] & 128u);
             if (MOMENTS) {
                 m.mn32 = min(m.mn32, u | ~keep[k]);
                 m.mx32 = max(m.mx32, u & keep[k]);
@@ -267,6 +329,8 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             a = na; b = nb; c = nc; d = nd;
             __syncwarp();
             if (slow_n[warp] >= kSlowQueue / 2) drain();  // warp-uniform: everyone reads the same counter
+            // a round adds at most 8 samples to a lane's slots (7 + 8 < kLaneQueue), the tails after the loop at most 4
+            if (COLLECT && __any_sync(0xFFFFFFFFu, q_addr >= q_base + (kLaneQueue - 8) * kLaneQueueStride)) flush();
         }
     }
     size_t i = ntiles * kTilePairs + tid;
@@ -276,6 +340,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     }
     if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
     drain();
+    if (COLLECT) flush();
 
     __syncthreads();
     for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
@@ -471,8 +536,143 @@ radix_kernel(const long long* __restrict__ x, size_t n, unsigned long long key_b
     }
 }
 
-// dynamic window: everything up to the end of the counters (absolute address, see the map above)
-size_t hist_smem(int nbins) { return kCntAbs + (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned); }
+// ---- device-resident radix select (see SelState) ------------------------------------------------------------
+
+__global__ void sel_init_kernel(SelState* st, const LatMoments* __restrict__ mom, SelRanks ranks, int have_bounds,
+                                long long lo, long long hi, unsigned long long n) {
+    if (threadIdx.x || blockIdx.x) return;
+    if (!have_bounds) {
+        lo = mom->min_ns;
+        hi = mom->max_ns;
+    }
+    const unsigned long long kmin = (unsigned long long)lo ^ 0x8000000000000000ull,
+                             kmax = (unsigned long long)hi ^ 0x8000000000000000ull;
+    const unsigned long long range = kmax - kmin;
+    st->key_base = kmin;
+    st->top = lo > hi ? 0 : 64 - __clzll((long long)range);
+    st->nk = ranks.nk;
+    st->nhist = 1;
+    st->bad = lo > hi;
+    for (int k = 0; k < kSelMax; k++) {
+        st->prefix[k] = 0;
+        st->rank[k] = k < ranks.nk ? ranks.rank[k] : 0;
+        st->result[k] = lo;  // all samples equal: nothing to resolve
+        if (k < ranks.nk && ranks.rank[k] >= n) st->bad = 1;
+    }
+}
+
+__global__ void __launch_bounds__(kRadixThreads)
+sel_pass_kernel(const long long* __restrict__ x, size_t n, const SelState* __restrict__ st,
+                unsigned long long* __restrict__ out) {
+    const int top = st->top;
+    if (top == 0 || st->bad) return;
+    extern __shared__ __align__(16) unsigned char sm[];
+    unsigned* hist = reinterpret_cast<unsigned*>(sm);  // [nhist][kRadixBins]
+    const int nhist = st->nhist, nk = st->nk;
+    for (int i = threadIdx.x; i < nhist * kRadixBins; i += kRadixThreads) hist[i] = 0;
+    __shared__ unsigned long long pf[kSelMax];
+    if (threadIdx.x < kSelMax) pf[threadIdx.x] = threadIdx.x < nk ? st->prefix[threadIdx.x] : ~0ull;
+    __syncthreads();
+    const int shift = top > kRadixBits ? top - kRadixBits : 0;
+    const unsigned mask = (1u << (top - shift)) - 1;
+    const unsigned long long key_base = st->key_base;
+    auto one = [&](long long v) {
+        const unsigned long long key = ((unsigned long long)v ^ 0x8000000000000000ull) - key_base;
+        const unsigned dgt = (unsigned)(key >> shift) & mask;
+        const unsigned long long hi = top >= 64 ? 0 : key >> top;
+        if (nhist == 1) {  // first pass: every sample has hi == 0 == every prefix, one histogram serves all ranks
+            if (hi == 0) atomicAdd(hist + dgt, 1u);
+        } else {
+#pragma unroll
+            for (int k = 0; k < kSelMax; k++)
+                if (hi == pf[k]) atomicAdd(hist + k * kRadixBins + dgt, 1u);
+        }
+    };
+    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
+    if (head > n) head = n;
+    const size_t tid = (size_t)blockIdx.x * kRadixThreads + threadIdx.x;
+    const size_t nthreads = (size_t)gridDim.x * kRadixThreads;
+    if (tid == 0 && head) one(x[0]);
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    size_t i = tid;
+    for (; i + nthreads < npairs; i += 2 * nthreads) {
+        const longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads);
+        one(a.x); one(a.y); one(b.x); one(b.y);
+    }
+    for (; i < npairs; i += nthreads) {
+        const longlong2 a = __ldg(x2 + i);
+        one(a.x); one(a.y);
+    }
+    if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
+    __syncthreads();
+    for (int i2 = threadIdx.x; i2 < nhist * kRadixBins; i2 += kRadixThreads) {
+        const unsigned c = hist[i2];
+        if (c) atomicAdd(out + i2, (unsigned long long)c);
+    }
+}
+
+// One CTA: for every rank find the digit whose bucket holds it, descend, and clear the histograms.
+__global__ void __launch_bounds__(1024)
+sel_scan_kernel(SelState* st, unsigned long long* __restrict__ hist) {
+    const int top = st->top;
+    if (top == 0 || st->bad) return;
+    const int nk = st->nk, nhist = st->nhist;
+    const int shift = top > kRadixBits ? top - kRadixBits : 0, width = top - shift;
+    __shared__ unsigned long long warp_tot[32];
+    __shared__ unsigned long long new_prefix[kSelMax], new_rank[kSelMax];
+    __shared__ int found[kSelMax];
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    if (t < kSelMax) found[t] = 0;
+    __syncthreads();
+    for (int k = 0; k < nk; k++) {
+        const unsigned long long* h = hist + (size_t)(nhist == 1 ? 0 : k) * kRadixBins;
+        unsigned long long c[4], sum = 0;
+#pragma unroll
+        for (int j = 0; j < 4; j++) { c[j] = h[4 * t + j]; sum += c[j]; }  // bins [4t, 4t+4)
+        unsigned long long incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        unsigned long long before = incl - sum;
+        for (int w = 0; w < warp; w++) before += warp_tot[w];
+        const unsigned long long r = st->rank[k];
+        if (r >= before && r < before + sum) {  // exactly one thread
+            unsigned long long cum = before;
+            int j = 0;
+            while (r >= cum + c[j]) cum += c[j++];
+            new_prefix[k] = (st->prefix[k] << width) | (unsigned long long)(4 * t + j);
+            new_rank[k] = r - cum;
+            found[k] = 1;
+        }
+        __syncthreads();
+    }
+    for (int i = t; i < nhist * kRadixBins; i += 1024) hist[i] = 0;
+    if (t == 0) {
+        int bad = 0;
+        for (int k = 0; k < nk; k++) {
+            if (!found[k]) { bad = 1; continue; }
+            st->prefix[k] = new_prefix[k];
+            st->rank[k] = new_rank[k];
+            if (shift == 0) st->result[k] = (long long)((new_prefix[k] + st->key_base) ^ 0x8000000000000000ull);
+        }
+        st->top = shift;
+        st->nhist = nk;
+        st->bad = bad;
+    }
+}
+
+// dynamic window: everything up to the end of the counters / lane slots (absolute address, see the map above)
+size_t hist_smem(int nbins, bool collect) {
+    size_t end = kFastAbs + (size_t)kFastCells * (collect ? 12 : 8) +
+                 (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned);
+    if (collect) end += (size_t)kLaneQueue * kLaneQueueStride;
+    return end;
+}
 
 int sm_count() {
     int dev = 0, sms = 148;
@@ -481,7 +681,26 @@ int sm_count() {
     return sms;
 }
 
+// One sample per stratum of `stride` consecutive inputs, at a hashed position inside the stratum (a fixed
+// position would alias with anything periodic in the data, e.g. 48 workers writing round-robin).
+__global__ void __launch_bounds__(256)
+sample_kernel(const long long* __restrict__ x, size_t stride, long long* __restrict__ out, size_t s) {
+    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    if (i >= s) return;
+    unsigned long long z = (i + 1) * 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    out[i] = __ldg(x + i * stride + z % stride);
+}
+
 }  // namespace
+
+cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream) {
+    if (!s) return cudaSuccess;
+    sample_kernel<<<(unsigned)((s + 255) / 256), 256, 0, stream>>>(d_samples, stride, d_out, s);
+    return cudaGetLastError();
+}
 
 cudaError_t lat_scratch_init(LatScratch* s) {
     memset(s, 0, sizeof *s);
@@ -491,6 +710,8 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_compact_n, sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_sel, sizeof(SelState));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
     return e;
 }
 
@@ -502,6 +723,10 @@ void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_prefix);
     cudaFree(s->d_compact);
     cudaFree(s->d_compact_n);
+    cudaFree(s->d_sel);
+    cudaFree(s->d_sel_hist);
+    cudaFree(s->d_sample);
+    cudaFree(s->d_collect);
     memset(s, 0, sizeof *s);
 }
 
@@ -513,20 +738,27 @@ static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
 }
 
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins, int mode32) {
+                        cudaStream_t stream, int nbins, int mode32, const HistCollect* collect) {
+    if (collect && want_moments) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     e = reset_moments(s, stream);
     if (e != cudaSuccess) return e;
+    if (collect) {
+        e = cudaMemsetAsync(collect->count, 0, sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
     if (!n) return cudaSuccess;
-    const size_t smem = hist_smem(nbins);
-    const int max_smem = (int)hist_smem(kMaxThresholds + 1);
-    using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*);
+    const size_t smem = hist_smem(nbins, collect != nullptr);
+    const int max_smem = (int)hist_smem(kMaxThresholds + 1, collect != nullptr);
+    using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*, HistCollect);
     // without moments the quotient is never formed, so one instantiation serves all modes
     static const Kernel kernels[2][4] = {
-        {hist_kernel<false, 0>, hist_kernel<false, 0>, hist_kernel<false, 0>, hist_kernel<false, 0>},
-        {hist_kernel<true, 0>, hist_kernel<true, 1>, hist_kernel<true, 2>, hist_kernel<true, 3>}};
-    const Kernel k = kernels[want_moments ? 1 : 0][mode32];
+        {hist_kernel<false, 0, false>, hist_kernel<false, 0, false>, hist_kernel<false, 0, false>,
+         hist_kernel<false, 0, false>},
+        {hist_kernel<true, 0, false>, hist_kernel<true, 1, false>, hist_kernel<true, 2, false>,
+         hist_kernel<true, 3, false>}};
+    const Kernel k = collect ? hist_kernel<false, 0, true> : kernels[want_moments ? 1 : 0][mode32];
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: kHistCtasPerSm by registers, fewer when the private counter tables are large
@@ -534,7 +766,8 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
-    k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom);
+    k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom,
+                                            collect ? *collect : HistCollect{nullptr, nullptr, 0});
     return cudaGetLastError();
 }
 
@@ -543,6 +776,35 @@ cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch
     if (e != cudaSuccess || !n) return e;
     int grid = (int)std::min<size_t>((size_t)sm_count() * 8, (n + kHistThreads - 1) / kHistThreads);
     minmax_kernel<<<grid, kHistThreads, 0, stream>>>(d_samples, n, s.d_mom);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_select_resident(const long long* d_samples, size_t n, const SelRanks& ranks, bool have_bounds,
+                                   long long lo, long long hi, const LatScratch& s, cudaStream_t stream) {
+    cudaError_t e = cudaMemsetAsync(s.d_sel_hist, 0, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    if (!have_bounds) {
+        e = launch_minmax(d_samples, n, s, stream);
+        if (e != cudaSuccess) return e;
+    }
+    sel_init_kernel<<<1, 32, 0, stream>>>(s.d_sel, s.d_mom, ranks, have_bounds ? 1 : 0, lo, hi, (unsigned long long)n);
+    const size_t smem = (size_t)kSelMax * kRadixBins * sizeof(unsigned);
+    e = cudaFuncSetAttribute(sel_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const size_t want_ctas = (n / 4 + kRadixThreads - 1) / kRadixThreads;
+    const int grid = (int)std::min<size_t>((size_t)sm_count(), want_ctas ? want_ctas : 1);
+    // with bounds the number of passes is known; without, the kernels past the last needed pass return at once
+    int rounds = kSelRounds;
+    if (have_bounds && lo <= hi) {
+        const unsigned long long range = ((unsigned long long)hi ^ 0x8000000000000000ull) - ((unsigned long long)lo ^ 0x8000000000000000ull);
+        int bits = 0;
+        while (bits < 64 && (range >> bits)) bits++;
+        rounds = (bits + kRadixBits - 1) / kRadixBits;
+    }
+    for (int r = 0; r < rounds; r++) {
+        sel_pass_kernel<<<grid, kRadixThreads, smem, stream>>>(d_samples, n, s.d_sel, s.d_sel_hist);
+        sel_scan_kernel<<<1, 1024, 0, stream>>>(s.d_sel, s.d_sel_hist);
+    }
     return cudaGetLastError();
 }
 
@@ -587,6 +849,8 @@ long long first_n_with_quotient_at_least(double E, long long d) {
     return ((long long)E - 1) * d + 1;
 }
 
+void finish_hist_params(HistParams* P, long long divisor);
+
 }  // namespace
 
 int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* P) {
@@ -606,6 +870,27 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
         for (int j = 0; j < nedges; j++) P->thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
     }
     P->nthr = m;
+    finish_hist_params(P, divisor);
+    return 0;
+}
+
+int host_build_hist_params_thr(const long long* thr, int nthr, HistParams* P) {
+    memset(P, 0, sizeof *P);
+    if (nthr < 1 || nthr > kMaxThresholds) return -1;
+    for (int j = 0; j < nthr; j++) {
+        if (j && !(thr[j] > thr[j - 1])) return -1;
+        P->thr[j] = thr[j];
+    }
+    P->nthr = nthr;
+    finish_hist_params(P, 1);
+    return 0;
+}
+
+namespace {
+
+// thresholds (P->thr, P->nthr) -> cell tables and division magics
+void finish_hist_params(HistParams* P, long long divisor) {
+    const int m = P->nthr;
     // log-linear LUT over n >= 0
     for (int idx = 0; idx < kLutCells; idx++) {
         unsigned long long lo, hi;
@@ -644,9 +929,13 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
         }
         // thresholds inside a cell are > lo >= 0 and <= hi < 2^32, so thr - 1 fits 32 bits
         P->fast[t].x = extra >= 1 ? (unsigned int)(P->thr[base] - 1) : 0xFFFFFFFFu;
-        // A cell with two or more thresholds sends the sample to the generic path; its (no-op) counter update is
-        // pointed at the trash rows past the last bin, and bit 2 keeps the address word-aligned.
-        P->fast[t].y = extra >= 2 ? (unsigned int)(m + 1) * 128u | 4u : (unsigned int)base * 128u;
+        P->fast[t].z = extra >= 2 ? (unsigned int)(P->thr[base + 1] - 1) : 0xFFFFFFFFu;
+        // A cell with more thresholds than the kernel compares with sends the sample to the generic path; its
+        // (no-op) counter update is pointed at the trash rows past the last bin, and bit 2 keeps the address
+        // word-aligned.
+        const unsigned int row = (unsigned int)base * 128u, generic = (unsigned int)(m + 1) * 128u | 4u;
+        P->fast[t].w = extra >= 2 ? generic : row;
+        P->fast[t].y = extra >= 3 ? generic : row;
     }
     // 32-bit dividends (Granlund-Montgomery, N = 32): l = ceil(log2 d), m' = floor(2^32 (2^l - d) / d) + 1,
     // q = (t + ((n - t) >> 1)) >> (l - 1) with t = umulhi(m', n)
@@ -711,7 +1000,8 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
             P->magic_shift = l;
         }
     }
-    return 0;
 }
+
+}  // namespace
 
 }  // namespace b200

@@ -30,10 +30,14 @@ struct HistParams {
     // Fast path (0 <= n < 2^32).  Cell t = (bits(float_rz(n | 1)) >> 18) - kFastFirst: the float's exponent and
     // top five mantissa bits, i.e. 32 cells per power of two; below 64 a cell is the pair {2k, 2k+1}.
     //   fast[t].x = (first threshold inside the cell) - 1, or 0xFFFFFFFF if none
-    //   fast[t].y = 128 * #{thresholds <= low end of the cell}; a cell holding two or more thresholds (generic
-    //               path) has 128 * (nthr + 1) | 4 instead: bit 2 is the flag, the offset a scratch row
-    // so the sample's counter sits at byte offset fast[t].y + 128 * (n > fast[t].x) of the lane's column.
-    uint2 fast[kFastCells];
+    //   fast[t].z = (second threshold inside the cell) - 1, or 0xFFFFFFFF
+    //   fast[t].w = 128 * #{thresholds <= low end of the cell}: byte offset of the counter row, for kernels that
+    //               compare with .x only; a cell holding two or more thresholds (generic path) has
+    //               128 * (nthr + 1) | 4 instead: bit 2 is the flag, the offset a scratch row
+    //   fast[t].y = the same for kernels that compare with .x and .z (flag from three thresholds up)
+    // so the sample's counter sits at byte offset .w + 128 * (n > .x)  [or .y + 128 * (n > .x) + 128 * (n > .z)]
+    // of the lane's column.
+    uint4 fast[kFastCells];
     unsigned long long magic;           // division by `divisor` as multiply-high (see lat_kernels.cu)
     int magic_shift;
     int magic_add;
@@ -42,6 +46,32 @@ struct HistParams {
     int pre32;                          //   3: q = umulhi(n >> pre32, magic32) >> shift32, and q < 2^28
     int mode32;
     long long divisor;
+};
+
+// Optional output of the histogram pass: the samples that fall into an ODD bin (bins are numbered from 0; the
+// sampled select puts its brackets there) are appended to buf in no particular order.  *count ends up as the
+// number of such samples even when it exceeds cap (the excess is not stored).
+struct HistCollect {
+    long long* buf;
+    unsigned long long* count;          // device counter, zeroed by the launch
+    unsigned long long cap;
+};
+
+// Device-resident radix select: all passes are queued without a host round trip (the host-driven select pays
+// one launch + copy + synchronise per pass, which dominates on inputs of a few million samples).
+constexpr int kSelMax = 8;              // order statistics resolved together
+constexpr int kSelRounds = 6;           // ceil(64 / kRadixBits) passes cover any int64 range
+struct SelState {
+    unsigned long long key_base;        // min key; key = ns ^ 2^63
+    unsigned long long prefix[kSelMax], rank[kSelMax];
+    long long result[kSelMax];
+    int top;                            // bits of key - key_base still unresolved
+    int nk, nhist;                      // ranks; histograms the next pass fills (1 on the first pass)
+    int bad;                            // a rank fell outside the counted samples
+};
+struct SelRanks {
+    unsigned long long rank[kSelMax];
+    int nk;
 };
 
 struct LatScratch {
@@ -53,6 +83,12 @@ struct LatScratch {
     long long* d_compact;               // samples of the buckets still in play after the first radix pass (lazy)
     size_t compact_cap;                 // in samples
     unsigned long long* d_compact_n;    // device counter
+    SelState* d_sel;                    // device-resident select
+    unsigned long long* d_sel_hist;     // [kSelMax][kRadixBins]
+    long long* d_sample;                // stratified sample of the input (sampled select, lazy)
+    size_t sample_cap;
+    long long* d_collect;               // samples inside the brackets (sampled select, lazy)
+    size_t collect_cap;
 };
 
 cudaError_t lat_scratch_init(LatScratch* s);
@@ -60,7 +96,14 @@ void lat_scratch_free(LatScratch* s);
 
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */);
+                        cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */,
+                        const HistCollect* collect = nullptr /* without moments only */);
+// out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
+cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream);
+// All the passes of a radix select of up to kSelMax ranks over [lo, hi] (pass have_bounds = false to take the
+// bounds from a min/max pass first), queued on the stream; the answer lands in s.d_sel (result[], bad).
+cudaError_t launch_select_resident(const long long* d_samples, size_t n, const SelRanks& ranks, bool have_bounds,
+                                   long long lo, long long hi, const LatScratch& s, cudaStream_t stream);
 // One MSD radix pass over key' = (ns ^ 2^63) - key_base: for each k < nk count the digit
 // (key' >> shift) & (2^(top-shift) - 1) over the samples with key' >> top == d_prefix[k] (all samples when
 // top >= 64).  top - shift <= kRadixBits.
@@ -84,5 +127,7 @@ cudaError_t launch_hist_f64(const double* d_x, size_t n, const double* edges, in
 
 // Host helper: fill thresholds / LUT / magic for (edges, mode, divisor).
 int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* out);
+// The same from raw thresholds (strictly ascending int64 ns, divisor 1): bin(n) = #{j : thr[j] <= n}.
+int host_build_hist_params_thr(const long long* thr, int nthr, HistParams* out);
 
 }  // namespace b200

@@ -214,6 +214,77 @@ def test_select_with_bucket_compaction_unaligned(ctx):
     ctx.free_device(d)
 
 
+SAMPLED_SELECT_CODE = r"""
+import importlib, sys
+import numpy as np
+import oracle
+pkg = importlib.import_module('custom-go-client-benchmark_b200')
+crc32c, lat = pkg.crc32c, pkg.latency
+ctx = crc32c.Context([0])
+
+def check(ns, ranks, div, start=0):
+    ns = np.ascontiguousarray(ns, dtype=np.int64)
+    d = ctx.alloc_device(ns.nbytes)
+    ctx.h2d(d, ns)
+    part = np.sort(ns[start:])
+    got = lat.select_kth(d + 8 * start, part.size, div, ranks, ctx=ctx)
+    want = [int(abs(int(part[k])) // div * (1 if part[k] >= 0 else -1)) for k in ranks]
+    assert list(got) == want, (list(got), want)
+    ctx.free_device(d)
+    print('case done', flush=True)
+    sys.stderr.write('--\n'); sys.stderr.flush()
+
+n = 3_000_001
+base = oracle.latency_ns(n)
+q = lambda m, ps: [int(m * p) for p in ps]
+check(base, q(n, [0.2, 0.5, 0.9, 0.99]), 1_000_000)            # the README / ssd_test ranks
+check(base, q(n - 1, [0.2, 0.5, 0.9, 0.99]), 1, start=1)        # 16-byte misaligned start
+check(base, [0, n // 2, n - 1], 1000)                           # brackets open at both ends
+check(base, [n // 2, n // 2 + 1, n // 2 + 2, n // 2 + 700], 1)  # overlapping brackets merge
+rng = np.random.default_rng(3)
+wide = rng.integers(-(1 << 40), 1 << 40, size=n)                # negative, and beyond the 32-bit fast path
+check(wide, q(n, [0.001, 0.25, 0.75, 0.999]), 7)
+check(np.sort(base), q(n, [0.1, 0.5, 0.95]), 1)                 # sorted input
+period = (np.arange(n) % 48) * 1_000_000 + rng.integers(0, 1000, size=n)   # 48 workers, round robin
+check(period, q(n, [0.2, 0.5, 0.9, 0.99]), 1)
+coarse = (base // 1_000_000) * 1_000_000                        # ~100 distinct values: brackets get too heavy
+check(coarse, q(n, [0.2, 0.5, 0.9, 0.99]), 1_000_000)
+check(np.full(n, 12345, dtype=np.int64), [0, n // 2, n - 1], 1)  # all equal
+print('ok')
+"""
+
+
+def test_sampled_select_matches_sort():
+    """The one-pass sampled select (taken for >= 2^24 samples by default) forced onto 3 * 10^6 samples: exact on every
+    kind of input, whether its brackets catch the ranks (trace says ok) or it hands over to the radix passes."""
+    import subprocess, sys
+    env = dict(os.environ, B200_SELECT_SAMPLED_MIN="100000", B200_SELECT_TRACE="1")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", SAMPLED_SELECT_CODE], env=env, cwd=root, text=True,
+                       capture_output=True, timeout=600)
+    assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
+    cases = r.stderr.split("--\n")[:-1]
+    assert len(cases) == 9, r.stderr
+    for i in (0, 1, 2, 3, 4, 5, 6):  # the brackets must catch the ranks on all the spread-out inputs
+        assert "sampled ok" in cases[i], (i, cases[i])
+    for i in (7, 8):                 # heavy duplicates: a miss, then the radix passes
+        assert "sampled miss" in cases[i], (i, cases[i])
+
+
+def test_host_driven_select_still_matches():
+    """Inputs up to 2^26 samples take the device-resident select and longer ones the sampled select, so the
+    host-driven passes with bucket compaction only run after a sampled miss on a very long input.  Force them
+    (and switch the other two off) and run the select tests of this file again."""
+    import subprocess, sys
+    env = dict(os.environ, B200_SELECT_RESIDENT_MAX="0", B200_SELECT_SAMPLED_MIN=str(1 << 62))
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "pytest", "-q", "-x", "-m", "gpu", "-k",
+                        "(select or percentile or golden or multi_device) and not host_driven and not sampled",
+                        os.path.join(root, "tests", "test_latency_gpu.py")],
+                       env=env, cwd=root, text=True, capture_output=True, timeout=900)
+    assert r.returncode == 0 and " passed" in r.stdout, r.stdout + r.stderr
+
+
 def test_select_all_equal_and_empty(ctx):
     ns = np.full(1000, 123456789, dtype=np.int64)
     d = upload(ctx, ns)

@@ -168,12 +168,15 @@ typedef struct {
 int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                     const double* edges, int nedges, int mode, uint64_t* counts, b200_lat_stats* stats);
 /* Exact order statistics: out[i] = k[i]-th smallest (0-based) of trunc(sample/divisor), i.e. sorted[k[i]]
- * of ssd_test/main.go:158-163.  Samples are not modified (MSD radix select, no sort).  k and out are HOST
- * arrays.  B200_ERR_EMPTY when n == 0 (the reference panics there). */
+ * of ssd_test/main.go:158-163.  Samples are not modified (no sort: one sampled histogram pass for long
+ * inputs, MSD radix select otherwise).  k and out are HOST arrays.  B200_ERR_EMPTY when n == 0
+ * (the reference panics there). */
 int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                     const uint64_t* k, int nk, int64_t* out);
 /* The same when the caller already knows bounds lo_ns <= every sample <= hi_ns (for instance from the min/max
- * of a previous b200_hist_fixed): saves the min/max pass.  Samples outside the bounds are an error. */
+ * of a previous b200_hist_fixed): saves the min/max pass of the radix select.  The bounds must be true: a
+ * sample outside them is either reported as B200_ERR_INVALID (radix select) or ranked like any other
+ * sample (the sampled pass for long inputs does not look at the bounds). */
 int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, int64_t lo_ns,
                           int64_t hi_ns, const uint64_t* k, int nk, int64_t* out);
 /* Building blocks of b200_select_kth for the one-process-per-GPU form, where the caller all-reduces the

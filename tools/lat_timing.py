@@ -11,7 +11,7 @@ ctx.fill_latency_ns(d, n, 0xC0FFEE)
 L, h = ctx._L, ctx._h
 
 
-def timeit(f, reps=5):
+def timeit(f, reps=int(os.environ.get("LAT_REPS", "5"))):  # LAT_REPS=1 under ncu
     f()
     t0 = time.perf_counter()
     for _ in range(reps):

@@ -1168,6 +1168,23 @@ int b200_hasher_reset(b200_hasher* h) {
 
 // ---- latency reduction ----------------------------------------------------------------------------------
 
+namespace {
+
+void fill_stats(const LatMoments& m, int64_t divisor, b200_lat_stats* stats) {
+    memset(stats, 0, sizeof *stats);
+    stats->count = m.count;
+    if (m.count) {
+        stats->min = m.min_ns / divisor;  // C division truncates toward zero, as Go's does
+        stats->max = m.max_ns / divisor;
+    }
+    stats->sum = m.sum_lo;
+    stats->sum_hi = m.sum_hi;
+    stats->sumsq_lo = m.sumsq_lo;
+    stats->sumsq_hi = m.sumsq_hi;
+}
+
+}  // namespace
+
 extern "C" {
 
 int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
@@ -1197,16 +1214,7 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         for (int i = 0; i <= nedges; i++) counts[i] = c[i];
     }
     if (stats) {
-        memset(stats, 0, sizeof *stats);
-        stats->count = m.count;
-        if (m.count) {
-            stats->min = m.min_ns / divisor;  // C division truncates toward zero, as Go's does
-            stats->max = m.max_ns / divisor;
-        }
-        stats->sum = m.sum_lo;
-        stats->sum_hi = m.sum_hi;
-        stats->sumsq_lo = m.sumsq_lo;
-        stats->sumsq_hi = m.sumsq_hi;
+        fill_stats(m, divisor, stats);
         stats->dropped_below = below;
         stats->dropped_above = above;
     }
@@ -1249,7 +1257,7 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
 namespace {
 
 int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
-                int64_t* out);  // below, after the radix select it builds on
+                int64_t* out, b200_lat_stats* stats = nullptr);  // below, after the radix select it builds on
 
 // Inputs up to this many samples are selected with all passes queued on the device (one host round trip);
 // longer ones that the sampled select did not settle take the host-driven passes with bucket compaction.
@@ -1439,7 +1447,7 @@ bool grow(long long** buf, size_t* cap, size_t want) {
 //      samples, by the ordinary radix select.
 // The result is exact whenever it is given; a miss (returns 1) makes the caller take the radix passes.
 int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
-                   int nk, int64_t* out) {
+                   int nk, int64_t* out, b200_lat_stats* stats) {
     DevState* d = get_dev(ctx, dev);
     if (!d || nk > kMaxSelect) return 1;
     std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
@@ -1501,19 +1509,22 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     }
     HistParams P;
     // a bracket that starts at INT64_MIN leaves bin 0 empty, which the builder allows (thresholds stay ascending)
-    if (host_build_hist_params_thr(thr, 2 * nb, &P)) return sampled_trace("skip: thresholds", 1);
+    // the divisor only matters to the moments (stats); the thresholds are raw nanoseconds
+    if (host_build_hist_params_thr(thr, 2 * nb, stats ? divisor : 1, &P)) return sampled_trace("skip: thresholds", 1);
     // room for twice the expected number of samples inside the brackets, at least n/64; more than n/8 is not worth it
     const size_t expect = (size_t)nk * (2 * margin + 2) * stride;
     const size_t cap = std::min<size_t>(std::max<size_t>(2 * expect, n / 64), n / 8);
     unsigned long long c[kMaxThresholds + 1], kept = 0;
+    LatMoments mom{};
     {
         std::unique_lock<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         if (!grow(&d->lat.d_collect, &d->lat.collect_cap, cap)) return sampled_trace("skip: no memory for the brackets", 1);
         CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
         HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
-        CU(launch_hist((const long long*)d_samples, n, d->lat, false, d->stream, P.nthr + 1, P.mode32, &col));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, &col));
         CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
+        if (stats) CU(cudaMemcpyAsync(&mom, d->lat.d_mom, sizeof mom, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaMemcpyAsync(&kept, d->lat.d_compact_n, sizeof kept, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
     }
@@ -1540,6 +1551,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     }
     int rc = b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, rank_kept, nk, out);
     if (rc) return rc < 0 ? rc : 1;
+    if (stats) fill_stats(mom, divisor, stats);  // moments of the whole input, from the bracket pass
     char msg[160];
     snprintf(msg, sizeof msg, "ok (sample of %zu + brackets %.3f ms, pass %.3f ms, %llu kept + select %.3f ms)", s, ms_sample,
              ms_pass, (unsigned long long)inside, ms_since(t0) - ms_sample - ms_pass);
@@ -1548,12 +1560,12 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
 
 // 0 = out[] is filled, 1 = not attempted or missed (take the radix passes), < 0 = error
 int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
-                int64_t* out) {
+                int64_t* out, b200_lat_stats* stats) {
     if (g_sampled_depth != 0 || n < sampled_select_min() || nk > kMaxSelect || !d_samples || ((uintptr_t)d_samples & 7))
         return 1;
     for (int i = 0; i < nk; i++)
         if (k[i] >= n) return 1;  // the caller reports it
-    return select_sampled(ctx, dev, d_samples, n, divisor, k, nk, out);
+    return select_sampled(ctx, dev, d_samples, n, divisor, k, nk, out, stats);
 }
 
 }  // namespace
@@ -1577,6 +1589,40 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     int64_t mn, mx;
     if (int rc = b200_minmax(ctx, dev, d_samples, n, &mn, &mx)) return rc;
     return b200_select_kth_range(ctx, dev, d_samples, n, divisor, mn, mx, k, nk, out);
+}
+
+int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                          const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats) {
+    if (!k || !out || !stats || nk < 1 || divisor < 1 || !d_samples || ((uintptr_t)d_samples & 7))
+        return fail(B200_ERR_INVALID, "b200_select_kth_stats");
+    if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
+    for (int i = 0; i < nk; i++)
+        if (k[i] >= n) return fail(B200_ERR_INVALID, "b200_select_kth: k >= n");
+    DevState* d = get_dev(ctx, dev);
+    if (!d) return fail(B200_ERR_INVALID, "b200_select_kth: unknown device");
+    {   // long inputs: moments and brackets in the same pass
+        const int rc = try_sampled(ctx, dev, d_samples, n, divisor, k, nk, out, stats);
+        if (rc <= 0) return rc;
+    }
+    // otherwise one pass for the moments (a histogram with a single threshold), then the radix select between
+    // the minimum and maximum that pass found
+    LatMoments m;
+    {
+        HistParams P;
+        const long long zero = 0;
+        if (host_build_hist_params_thr(&zero, 1, divisor, &P)) return fail(B200_ERR_INVALID, "b200_select_kth_stats");
+        std::lock_guard<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(dev));
+        CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, true, d->stream, P.nthr + 1, P.mode32));
+        CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+    }
+    fill_stats(m, divisor, stats);
+    g_sampled_depth++;  // the sampled route had its chance above
+    const int rc = b200_select_kth_range(ctx, dev, d_samples, n, divisor, m.min_ns, m.max_ns, k, nk, out);
+    g_sampled_depth--;
+    return rc;
 }
 
 }  // extern "C"

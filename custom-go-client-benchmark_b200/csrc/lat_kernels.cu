@@ -120,7 +120,7 @@ extern __shared__ __align__(1024) unsigned char hist_smem_raw[];
 // the add fix-up, 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28.
 // COLLECT: cells may hold two thresholds and the samples of odd bins are appended to col.buf.
 template <bool MOMENTS, int DIVMODE, bool COLLECT>
-__global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
+__global__ void __launch_bounds__(kHistThreads, (MOMENTS && COLLECT) ? kHistCtasPerSm - 1 : kHistCtasPerSm)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, const HistCollect col) {
     // cell entries are 8 bytes; collecting kernels keep the cells' second compare values in a table of their own,
@@ -580,8 +580,8 @@ sel_pass_kernel(const long long* __restrict__ x, size_t n, const SelState* __res
         const unsigned long long key = ((unsigned long long)v ^ 0x8000000000000000ull) - key_base;
         const unsigned dgt = (unsigned)(key >> shift) & mask;
         const unsigned long long hi = top >= 64 ? 0 : key >> top;
-        if (nhist == 1) {  // first pass: every sample has hi == 0 == every prefix, one histogram serves all ranks
-            if (hi == 0) atomicAdd(hist + dgt, 1u);
+        if (nhist == 1) {  // first pass (every sample has hi == 0 == every prefix: one histogram serves all), or nk == 1
+            if (hi == pf[0]) atomicAdd(hist + dgt, 1u);
         } else {
 #pragma unroll
             for (int k = 0; k < kSelMax; k++)
@@ -757,7 +757,6 @@ static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
 
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
                         cudaStream_t stream, int nbins, int mode32, const HistCollect* collect) {
-    if (collect && want_moments) return cudaErrorInvalidValue;
     cudaError_t e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     e = reset_moments(s, stream);
@@ -776,11 +775,18 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
          hist_kernel<false, 0, false>},
         {hist_kernel<true, 0, false>, hist_kernel<true, 1, false>, hist_kernel<true, 2, false>,
          hist_kernel<true, 3, false>}};
-    const Kernel k = collect ? hist_kernel<false, 0, true> : kernels[want_moments ? 1 : 0][mode32];
+    static const Kernel collecting[2][4] = {
+        {hist_kernel<false, 0, true>, hist_kernel<false, 0, true>, hist_kernel<false, 0, true>,
+         hist_kernel<false, 0, true>},
+        {hist_kernel<true, 0, true>, hist_kernel<true, 1, true>, hist_kernel<true, 2, true>,
+         hist_kernel<true, 3, true>}};
+    const Kernel k = (collect ? collecting : kernels)[want_moments ? 1 : 0][mode32];
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: kHistCtasPerSm by registers, fewer when the private counter tables are large
-    int per_sm = (int)std::min<size_t>(kHistCtasPerSm, (224 * 1024) / (smem + 1024));
+    // (the kernel that keeps moments AND collects needs more registers than a third of the file)
+    const int by_regs = collect && want_moments ? kHistCtasPerSm - 1 : kHistCtasPerSm;
+    int per_sm = (int)std::min<size_t>(by_regs, (224 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
@@ -892,15 +898,15 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
     return 0;
 }
 
-int host_build_hist_params_thr(const long long* thr, int nthr, HistParams* P) {
+int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, HistParams* P) {
     memset(P, 0, sizeof *P);
-    if (nthr < 1 || nthr > kMaxThresholds) return -1;
+    if (nthr < 1 || nthr > kMaxThresholds || divisor < 1) return -1;
     for (int j = 0; j < nthr; j++) {
         if (j && !(thr[j] > thr[j - 1])) return -1;
         P->thr[j] = thr[j];
     }
     P->nthr = nthr;
-    finish_hist_params(P, 1);
+    finish_hist_params(P, divisor);
     return 0;
 }
 

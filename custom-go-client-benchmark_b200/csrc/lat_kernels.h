@@ -97,7 +97,7 @@ void lat_scratch_free(LatScratch* s);
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
                         cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */,
-                        const HistCollect* collect = nullptr /* without moments only */);
+                        const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream);
 // All the passes of a radix select of up to kSelMax ranks over [lo, hi] (pass have_bounds = false to take the
@@ -127,7 +127,8 @@ cudaError_t launch_hist_f64(const double* d_x, size_t n, const double* edges, in
 
 // Host helper: fill thresholds / LUT / magic for (edges, mode, divisor).
 int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* out);
-// The same from raw thresholds (strictly ascending int64 ns, divisor 1): bin(n) = #{j : thr[j] <= n}.
-int host_build_hist_params_thr(const long long* thr, int nthr, HistParams* out);
+// The same from raw thresholds (strictly ascending int64 ns): bin(n) = #{j : thr[j] <= n}; the divisor only
+// scales the moments.
+int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, HistParams* out);
 
 }  // namespace b200

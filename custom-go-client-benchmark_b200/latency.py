@@ -269,6 +269,19 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
     """avg / P20 / P50 / P90 / p99 / min / max of trunc(sample/divisor) exactly as ssd_test/main.go:147-163 prints
     them.  `dist` may be a Distribution already computed over the same samples WITH THE SAME divisor (any
     edges): its count, sum and min/max are reused instead of a second pass over the data."""
+    if dist is None and not _Reducer(group, reduce_device).active:
+        # one process: ranks and moments from one call (one pass over long inputs), ssd_test/main.go:147-163
+        if n == 0:
+            raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
+        ctx_ = ctx or default_context()
+        karr = np.array([n // 5, n // 2, (9 * n) // 10, (99 * n) // 100], dtype=np.uint64)
+        out = np.zeros(4, dtype=np.int64)
+        st = LatStats()
+        check(ctx_._L.b200_select_kth_stats(ctx_._h, ctx_._dev(dev), d_samples_ns, n, divisor, karr.ctypes.data, 4,
+                                            out.ctypes.data, C.byref(st)))
+        whole = merge_distribution(_Reducer(), np.zeros(0, dtype=np.uint64), st.count, st.min, st.max,
+                                   _signed(st.sum, st.sum_hi), (st.sumsq_hi << 64) | st.sumsq_lo, 0, 0)
+        return Percentiles(whole.avg_go_int, int(out[0]), int(out[1]), int(out[2]), int(out[3]), whole.min, whole.max)
     dist_ = dist if dist is not None else hist_fixed(d_samples_ns, n, divisor, OC_DEFAULT_LATENCY_BOUNDS,
                                                      HIST_OPENCENSUS, ctx=ctx, dev=dev, group=group,
                                                      reduce_device=reduce_device)

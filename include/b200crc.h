@@ -173,6 +173,12 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
  * (the reference panics there). */
 int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                     const uint64_t* k, int nk, int64_t* out);
+/* b200_select_kth plus count / min / max / exact sums of trunc(sample/divisor) over ALL samples: everything
+ * ssd_test/main.go:147-163 prints (the avg from the sum, sorted[k], min, max) from one call.  Long inputs get
+ * the moments from the same pass over the samples that settles the ranks; short ones take one extra pass.
+ * stats->dropped_* are 0. */
+int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                          const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats);
 /* The same when the caller already knows bounds lo_ns <= every sample <= hi_ns (for instance from the min/max
  * of a previous b200_hist_fixed): saves the min/max pass of the radix select.  The bounds must be true: a
  * sample outside them is either reported as B200_ERR_INVALID (radix select) or ranked like any other

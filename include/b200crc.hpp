@@ -216,13 +216,13 @@ struct Percentiles {  // the seven lines ssd_test prints (ssd_test/main.go:157-1
 inline Percentiles ComputePercentiles(const Context& c, const int64_t* d_samples_ns, size_t n, int64_t divisor = kNsPerUs,
                                       int dev = -1) {
     if (n == 0) throw Error(B200_ERR_EMPTY, "percentiles of an empty sample set (Go panics at ssd_test/main.go:157)");
-    Distribution d = HistFixed(c, d_samples_ns, n, divisor, OcDefaultLatencyBounds(), B200_HIST_OPENCENSUS, dev);
     const uint64_t size = n;
     uint64_t ks[4] = {size / 5, size / 2, (9 * size) / 10, (99 * size) / 100};
     int64_t out[4];
-    check(b200_select_kth(c.get(), dev < 0 ? c.device() : dev, d_samples_ns, n, divisor, ks, 4, out));
-    const int64_t sum = (int64_t)d.stats.sum;  // Go's wrapping int64 sum
-    return {sum / (int64_t)size, out[0], out[1], out[2], out[3], d.stats.min, d.stats.max};
+    b200_lat_stats st;
+    check(b200_select_kth_stats(c.get(), dev < 0 ? c.device() : dev, d_samples_ns, n, divisor, ks, 4, out, &st));
+    const int64_t sum = (int64_t)st.sum;  // Go's wrapping int64 sum
+    return {sum / (int64_t)size, out[0], out[1], out[2], out[3], st.min, st.max};
 }
 
 }  // namespace latency

@@ -140,6 +140,17 @@ def test_fast_path_cells_and_divisors(ctx):
     ctx.free_device(d)
 
 
+def test_histogram_with_the_maximum_number_of_edges(ctx, samples):
+    ns, d, n = samples
+    ms = oracle.ns_to_ms(ns)
+    edges = np.linspace(1.0, 190.0, pkg._lib.HIST_MAX_EDGES if hasattr(pkg._lib, "HIST_MAX_EDGES") else 64)
+    for mode, ref in ((pkg._lib.HIST_OPENCENSUS, oracle.hist_opencensus(ms.astype(np.float64), edges)),
+                      (pkg._lib.HIST_NUMPY, oracle.hist_numpy(ms.astype(np.float64), edges)[0])):
+        h = lat.hist_fixed(d, n, lat.NS_PER_MS, edges, mode, ctx=ctx)
+        assert list(h.counts) == list(ref)
+        assert h.sum == int(ms.sum())
+
+
 def test_histogram_unaligned_and_tiny(ctx, samples):
     ns, d, n = samples
     for start, cnt in [(1, 1001), (3, 2), (5, 1), (0, 0), (7, 100000)]:
@@ -250,6 +261,19 @@ check(period, q(n, [0.2, 0.5, 0.9, 0.99]), 1)
 coarse = (base // 1_000_000) * 1_000_000                        # ~100 distinct values: brackets get too heavy
 check(coarse, q(n, [0.2, 0.5, 0.9, 0.99]), 1_000_000)
 check(np.full(n, 12345, dtype=np.int64), [0, n // 2, n - 1], 1)  # all equal
+
+def seven(ns):  # what ssd_test prints: ranks and moments from ONE call (b200_select_kth_stats)
+    d = ctx.alloc_device(ns.nbytes)
+    ctx.h2d(d, ns)
+    o = oracle.percentiles_i64(oracle.ns_to_us(ns))
+    p = lat.percentiles(d, ns.size, lat.NS_PER_US, ctx=ctx)
+    assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (o.avg, o.p20, o.p50, o.p90, o.p99, o.min, o.max)
+    ctx.free_device(d)
+    sys.stderr.write('--\n'); sys.stderr.flush()
+
+seven(base)                                                     # moments from the bracket pass
+seven(np.ascontiguousarray(wide))                               # negative samples: truncation toward zero
+seven(np.ascontiguousarray(coarse))                             # a miss: moments from an extra pass
 print('ok')
 """
 
@@ -264,10 +288,10 @@ def test_sampled_select_matches_sort():
                        capture_output=True, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
     cases = r.stderr.split("--\n")[:-1]
-    assert len(cases) == 9, r.stderr
-    for i in (0, 1, 2, 3, 4, 5, 6):  # the brackets must catch the ranks on all the spread-out inputs
+    assert len(cases) == 12, r.stderr
+    for i in (0, 1, 2, 3, 4, 5, 6, 9, 10):  # the brackets must catch the ranks on all the spread-out inputs
         assert "sampled ok" in cases[i], (i, cases[i])
-    for i in (7, 8):                 # heavy duplicates: a miss, then the radix passes
+    for i in (7, 8, 11):                    # heavy duplicates: a miss, then the radix passes
         assert "sampled miss" in cases[i], (i, cases[i])
 
 
@@ -283,6 +307,19 @@ def test_host_driven_select_still_matches():
                         os.path.join(root, "tests", "test_latency_gpu.py")],
                        env=env, cwd=root, text=True, capture_output=True, timeout=900)
     assert r.returncode == 0 and " passed" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.parametrize("nk", [1, 2, 3, 5, 8, 9, 17])
+def test_select_any_number_of_ranks(ctx, samples, nk):
+    """The device-resident select resolves up to 8 ranks together (one histogram while they share a prefix, one
+    each afterwards) and groups beyond that; a single rank keeps a single histogram throughout."""
+    ns, d, n = samples
+    m = 300_000
+    srt = np.sort(oracle.ns_to_us(ns[:m]))
+    rng = np.random.default_rng(nk)
+    for _ in range(3):
+        ks = [int(x) for x in rng.integers(0, m, size=nk)]
+        assert lat.select_kth(d, m, 1000, ks, ctx=ctx) == [int(srt[k]) for k in ks]
 
 
 def test_select_all_equal_and_empty(ctx):

@@ -1260,11 +1260,12 @@ int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int6
                 int64_t* out, b200_lat_stats* stats = nullptr);  // below, after the radix select it builds on
 
 // Inputs up to this many samples are selected with all passes queued on the device (one host round trip);
-// longer ones that the sampled select did not settle take the host-driven passes with bucket compaction.
+// longer ones that the sampled select did not settle take the host-driven passes with bucket compaction
+// (2^26 samples: 1.1 ms resident, 0.64 ms host-driven with compaction, 0.57 ms sampled).
 size_t resident_select_max() {  // tuning / test override: B200_SELECT_RESIDENT_MAX=0 forces the host-driven passes
     static const size_t v = [] {
         const char* e = getenv("B200_SELECT_RESIDENT_MAX");
-        return e && *e ? (size_t)strtoull(e, nullptr, 10) : (size_t)1 << 26;
+        return e && *e ? (size_t)strtoull(e, nullptr, 10) : (size_t)1 << 25;  // measured: tools/select_routes.py
     }();
     return v;
 }

@@ -296,7 +296,7 @@ def test_sampled_select_matches_sort():
 
 
 def test_host_driven_select_still_matches():
-    """Inputs up to 2^26 samples take the device-resident select and longer ones the sampled select, so the
+    """Inputs up to 2^25 samples take the device-resident select and longer ones the sampled select, so the
     host-driven passes with bucket compaction only run after a sampled miss on a very long input.  Force them
     (and switch the other two off) and run the select tests of this file again."""
     import subprocess, sys

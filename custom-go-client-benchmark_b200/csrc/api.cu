@@ -464,7 +464,13 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
         if (!rc) rc = upload(&d->tabs.xpow8_sq, xsq, 64);
         if (!rc) rc = upload(&d->tabs.byte_tab, byte_tab, 256);
         if (!rc) rc = upload(&d->tabs.adv4, adv4, 1024);
-        if (!rc) rc = lat_scratch_init(&d->lat) == cudaSuccess ? 0 : fail(B200_ERR_CUDA, "latency scratch");
+        if (!rc) {
+            const cudaError_t e = lat_scratch_init(&d->lat);
+            if (e == cudaErrorInvalidConfiguration)
+                rc = fail(B200_ERR_CUDA, "this driver reserves more than 1 KB of shared memory per CTA: the kernels' "
+                                         "absolute shared-memory maps do not fit");
+            else if (e != cudaSuccess) rc = fail_cuda(e, "latency scratch");
+        }
         if (rc) {
             b200_shutdown(ctx);
             return rc;

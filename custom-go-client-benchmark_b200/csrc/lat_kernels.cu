@@ -720,14 +720,29 @@ cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* 
     return cudaGetLastError();
 }
 
+// Where a kernel's dynamic shared memory starts when it has no static shared memory: the histogram and CRC row
+// kernels lay their tables out at absolute shared addresses and need it to be at most 1 KB (the driver's
+// reserved block).  Asked once per device at set-up, so that a driver that reserves more fails b200_init
+// with a message instead of trapping inside a kernel later.
+__global__ void smem_base_probe_kernel(unsigned long long* out) {
+    extern __shared__ __align__(1024) unsigned char probe_smem[];
+    *out = (unsigned long long)__cvta_generic_to_shared(probe_smem);
+}
+
 cudaError_t lat_scratch_init(LatScratch* s) {
     memset(s, 0, sizeof *s);
-    cudaError_t e = cudaMalloc(&s->d_params, sizeof(HistParams));
+    cudaError_t e = cudaMalloc(&s->d_compact_n, sizeof(unsigned long long));
+    if (e != cudaSuccess) return e;
+    unsigned long long base = ~0ull;
+    smem_base_probe_kernel<<<1, 1, 1024>>>(s->d_compact_n);
+    e = cudaMemcpy(&base, s->d_compact_n, sizeof base, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return e;
+    if (base > 1024) return cudaErrorInvalidConfiguration;  // see smem_base_probe_kernel
+    e = cudaMalloc(&s->d_params, sizeof(HistParams));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_counts, (kMaxThresholds + 1) * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_mom, sizeof(LatMoments));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_compact_n, sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel, sizeof(SelState));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
     return e;

@@ -333,6 +333,22 @@ def test_select_all_equal_and_empty(ctx):
         lat.select_kth(d, 1000, 1, [1000], ctx=ctx)
     with pytest.raises(ZeroDivisionError):
         lat.percentiles(d, 0, ctx=ctx)
+    # the one-call form (ranks + moments) reports the same conditions
+    import ctypes as C
+    L, h = ctx._L, ctx._h
+    st = pkg._lib.LatStats()
+    out = np.zeros(1, dtype=np.int64)
+
+    def stats_call(n, k, ptr=None, divisor=1000):
+        karr = np.array([k], dtype=np.uint64)
+        return L.b200_select_kth_stats(h, 0, d if ptr is None else ptr, n, divisor, karr.ctypes.data, 1,
+                                       out.ctypes.data, C.byref(st))
+    assert stats_call(1000, 999) == 0 and out[0] == 123456
+    assert (st.count, st.min, st.max, st.sum) == (1000, 123456, 123456, 123456 * 1000)
+    assert stats_call(0, 0) == pkg._lib.ERR_EMPTY
+    assert stats_call(1000, 1000) == pkg._lib.ERR_INVALID      # k >= n
+    assert stats_call(999, 0, ptr=d + 4) == pkg._lib.ERR_INVALID  # samples must be 8-byte aligned
+    assert stats_call(1000, 0, divisor=0) == pkg._lib.ERR_INVALID
     ctx.free_device(d)
 
 

@@ -36,6 +36,8 @@ ks = np.array([n // 5, n // 2, 9 * n // 10, 99 * n // 100], dtype=np.uint64)
 out = np.zeros(4, dtype=np.int64)
 ms = timeit(lambda: L.b200_select_kth(h, 0, d, n, 1000, ks.ctypes.data, 4, out.ctypes.data))
 print(f"select 4 ranks         : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s   {out}")
+ms = timeit(lambda: lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx))
+print(f"percentiles (7 lines)  : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s   {lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)}")
 # radix building blocks
 kmin = (mn.value + (1 << 63)) & ((1 << 64) - 1)
 bits = (mx.value - mn.value).bit_length()

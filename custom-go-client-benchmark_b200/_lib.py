@@ -76,6 +76,8 @@ SIGNATURES = {
     "b200_hist_fixed": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _int, _vp, C.POINTER(LatStats)]),
     "b200_select_kth": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp]),
     "b200_select_kth_stats": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp, _vp]),
+    "b200_select_sample": (_int, [_vp, _int, _vp, _sz, _sz, _pp, C.POINTER(_sz)]),
+    "b200_bracket_pass": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _u64, _vp, _pp, C.POINTER(_u64), _vp]),
     "b200_select_kth_range": (_int, [_vp, _int, _vp, _sz, _i64, _i64, _i64, _vp, _int, _vp]),
     "b200_hist_fixed_multi": (_int, [_vp, _vp, _vp, _vp, _int, _i64, _vp, _int, _int, _vp, C.POINTER(LatStats)]),
     "b200_select_kth_multi": (_int, [_vp, _vp, _vp, _vp, _int, _i64, _vp, _int, _vp]),

@@ -1598,6 +1598,54 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     return b200_select_kth_range(ctx, dev, d_samples, n, divisor, mn, mx, k, nk, out);
 }
 
+int b200_select_sample(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, size_t stride,
+                       const int64_t** d_sample, size_t* nsample) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !d_sample || !nsample || stride < 1 || (n && !d_samples) || ((uintptr_t)d_samples & 7))
+        return fail(B200_ERR_INVALID, "b200_select_sample");
+    std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    const size_t s = n / stride;
+    if (s && !grow(&d->lat.d_sample, &d->lat.sample_cap, s)) return fail(B200_ERR_NOMEM, "b200_select_sample");
+    CU(launch_sample((const long long*)d_samples, stride, d->lat.d_sample, s, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    *d_sample = (const int64_t*)d->lat.d_sample;
+    *nsample = s;
+    return 0;
+}
+
+int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                      const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
+                      uint64_t* nkept, b200_lat_stats* stats) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !thresholds || !counts || !d_kept || !nkept || nthr < 1 || nthr > B200_HIST_MAX_EDGES || divisor < 1 ||
+        (n && !d_samples) || ((uintptr_t)d_samples & 7))
+        return fail(B200_ERR_INVALID, "b200_bracket_pass");
+    HistParams P;
+    static_assert(sizeof(long long) == sizeof(int64_t), "threshold type");
+    if (host_build_hist_params_thr((const long long*)thresholds, nthr, divisor, &P))
+        return fail(B200_ERR_INVALID, "b200_bracket_pass: thresholds must be strictly ascending");
+    std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    if (cap && !grow(&d->lat.d_collect, &d->lat.collect_cap, (size_t)cap)) return fail(B200_ERR_NOMEM, "b200_bracket_pass");
+    CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
+    HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
+    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, &col));
+    unsigned long long c[kMaxThresholds + 1], kept = 0;
+    LatMoments m{};
+    CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaMemcpyAsync(&kept, d->lat.d_compact_n, sizeof kept, cudaMemcpyDeviceToHost, d->stream));
+    if (stats) CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    for (int i = 0; i <= nthr; i++) counts[i] = c[i];
+    *nkept = kept;
+    *d_kept = (const int64_t*)d->lat.d_collect;
+    if (stats) fill_stats(m, divisor, stats);
+    return 0;
+}
+
 int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                           const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats) {
     if (!k || !out || !stats || nk < 1 || divisor < 1 || !d_samples || ((uintptr_t)d_samples & 7))

@@ -165,7 +165,7 @@ def hist_opencensus(d_samples_ns: int, n: int, **kw) -> Distribution:
 
 
 def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int, ks: Sequence[int],
-                 n_global: Optional[int] = None):
+                 n_global: Optional[int] = None, global_bounds: Optional[tuple] = None):
     """MSD radix select over the union of all ranks' samples.
 
     minmax_fn() -> (min, max) of this rank's raw samples; count_fn(key_base, shift, top, prefixes) -> uint64
@@ -179,8 +179,11 @@ def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int,
         raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
     if any(k >= ntot or k < 0 for k in ks):
         raise ValueError("k >= n")
-    mn, mx = minmax_fn()
-    gmn, gmx = red.min_i64(mn), red.max_i64(mx)
+    if global_bounds is not None:  # bounds every rank already agrees on: no collective needed
+        gmn, gmx = int(global_bounds[0]), int(global_bounds[1])
+    else:
+        mn, mx = minmax_fn()
+        gmn, gmx = red.min_i64(mn), red.max_i64(mx)
     kmin, kmax = (gmn + _SIGN) & _M64, (gmx + _SIGN) & _M64
     bits = (kmax - kmin).bit_length()
     res = []
@@ -215,6 +218,141 @@ def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int,
     return res
 
 
+SAMPLED_SELECT_MIN = 1 << 24      # total samples from which the multi-rank select tries one sampled pass first
+_I64_MIN, _I64_MAX = -(1 << 63), (1 << 63) - 1
+
+
+def merge_brackets(brackets):
+    """[(lo, hi)] closed intervals -> ascending, disjoint, non-touching intervals (b200_select_kth does the same)."""
+    out = []
+    for lo, hi in sorted((int(a), int(b)) for a, b in brackets):
+        if out and lo <= out[-1][1] + 1:
+            out[-1][1] = max(out[-1][1], hi)
+        else:
+            out.append([lo, hi])
+    return [(a, b) for a, b in out]
+
+
+def locate_in_brackets(counts, k: int):
+    """counts[c] = samples with exactly c thresholds (lo0, hi0+1, lo1, hi1+1, ...) below or at them, so odd c are
+    the brackets.  Returns the 0-based rank of global rank k among the kept (odd-bin) samples, or None when k fell
+    between brackets (a miss)."""
+    below = kept_before = 0
+    for j in range((len(counts) - 1) // 2):
+        below += int(counts[2 * j])
+        if k < below:
+            return None
+        inside = int(counts[2 * j + 1])
+        if k < below + inside:
+            return kept_before + (k - below)
+        below += inside
+        kept_before += inside
+    return None
+
+
+def sampled_select(red: _Reducer, n_local: int, n_global: int, divisor: int, ks: Sequence[int], sample_fn,
+                   sample_select_fn, bracket_fn, kept_count_fn, kept_minmax_fn):
+    """One pass over every rank's samples instead of min/max + three radix passes (the multi-rank form of what
+    b200_select_kth does on one device).  Collectives carry a few dozen integers only.
+
+      sample_fn(stride) -> s                 this rank's stratified sample (one input per `stride`), its size
+      sample_select_fn(ranks) -> values      order statistics of that sample (local, exact)
+      bracket_fn(thresholds, cap) -> (counts, nkept, stats)   the histogram pass that keeps the odd bins
+      kept_count_fn / kept_minmax_fn         radix-select building blocks over the kept samples
+
+    Every rank brackets each wanted quantile with ITS sample, a few standard deviations either side; the union of
+    the ranks' brackets (min of the lower ends, max of the upper ends) holds the global order statistic whenever
+    every local bracket holds the local quantile, whatever the ranks' distributions are - it is just wide when
+    they differ, and then (or on a ~1e-6 tail event) the exact counts of the pass say so and None is returned:
+    the caller takes the radix passes.  Returns (values, stats) otherwise."""
+    ks = [int(k) for k in ks]
+    nk = len(ks)
+    stride = max(16, -(-n_global // (1 << 22)))
+    s = sample_fn(stride)
+    ok = s >= 1024
+    margin = int(2.5 * np.sqrt(max(s, 1))) + 2
+    want, where = [], []
+    for k in ks:
+        c = k * s // n_global
+        lo_at = hi_at = None
+        if ok and c >= margin:
+            lo_at = len(want); want.append(c - margin)
+        if ok and c + margin + 1 < s:
+            hi_at = len(want); want.append(c + margin + 1)
+        where.append((lo_at, hi_at))
+    got = sample_select_fn(want) if want else []
+    vec = [1 if ok else 0]
+    vec += [_I64_MIN if a is None else int(got[a]) for a, _ in where]
+    vec += [-(_I64_MAX - 1) if b is None else -min(int(got[b]), _I64_MAX - 1) for _, b in where]
+    g = [int(x) for x in red._run(np.array(vec, dtype=np.int64), "MIN")]
+    if g[0] == 0:
+        return None  # some rank holds too few samples to bracket anything
+    br = merge_brackets([(g[1 + i], -g[1 + nk + i]) for i in range(nk)])
+    thr = []
+    for lo, hi in br:
+        thr += [lo, hi + 1]
+    # room for several times the expected number of samples inside this rank's share of the brackets (the union
+    # over ranks is wider than one rank's own), at least n/64; more than n/8 is not worth keeping
+    expect = nk * (2 * margin + 2) * stride
+    cap = max(min(max(8 * expect, n_local // 64), n_local // 8), 1024)
+    counts, nkept, stats = bracket_fn(thr, cap)
+    tot = red.sum_u64(np.array([int(c) for c in counts] + [int(nkept), 1 if nkept > cap else 0], dtype=np.uint64))
+    gc = [int(x) for x in tot[:len(thr) + 1]]
+    inside = sum(gc[1::2])
+    if int(tot[-1]) or sum(gc) != n_global or int(tot[-2]) != inside or inside == 0:
+        return None  # brackets too heavy for the buffers (heavy duplicates, ranks with very different data)
+    rank_kept = [locate_in_brackets(gc, k) for k in ks]
+    if any(r is None for r in rank_kept):
+        return None
+    open_ended = br[0][0] == _I64_MIN or br[-1][1] == _I64_MAX - 1
+    vals = radix_select(red, int(nkept), kept_minmax_fn, kept_count_fn, divisor, rank_kept, n_global=inside,
+                        global_bounds=None if open_ended else (br[0][0], br[-1][1]))
+    return vals, stats
+
+
+def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, want_stats):
+    """sampled_select over this rank's device samples through the C ABI building blocks."""
+    state = {}
+
+    def sample_fn(stride):
+        p, cnt = C.c_void_p(), C.c_size_t()
+        check(L.b200_select_sample(h, d, d_samples, n, stride, C.byref(p), C.byref(cnt)))
+        state["sample"] = (p.value, cnt.value)
+        return cnt.value
+
+    def sample_select_fn(ranks):
+        p, cnt = state["sample"]
+        karr = np.array(ranks, dtype=np.uint64)
+        out = np.zeros(karr.size, dtype=np.int64)
+        check(L.b200_select_kth(h, d, p, cnt, 1, karr.ctypes.data, karr.size, out.ctypes.data))
+        return [int(x) for x in out]
+
+    def bracket_fn(thr, cap):
+        tarr = np.array(thr, dtype=np.int64)
+        counts = np.zeros(tarr.size + 1, dtype=np.uint64)
+        p, nkept, st = C.c_void_p(), C.c_uint64(), LatStats()
+        check(L.b200_bracket_pass(h, d, d_samples, n, divisor, tarr.ctypes.data, tarr.size, cap, counts.ctypes.data,
+                                  C.byref(p), C.byref(nkept), C.byref(st) if want_stats else None))
+        state["kept"] = (p.value, min(nkept.value, cap))
+        return counts, nkept.value, (st if want_stats else None)
+
+    def kept_count_fn(key_base, shift, top, prefixes):
+        p, cnt = state["kept"]
+        counts = np.zeros(len(prefixes) * RADIX_BINS, dtype=np.uint64)
+        parr = np.array(prefixes, dtype=np.uint64)
+        check(L.b200_radix_count(h, d, p, cnt, key_base, shift, top, len(prefixes), parr.ctypes.data, counts.ctypes.data))
+        return counts
+
+    def kept_minmax_fn():
+        p, cnt = state["kept"]
+        mn, mx = C.c_int64(), C.c_int64()
+        check(L.b200_minmax(h, d, p, cnt, C.byref(mn), C.byref(mx)))
+        return mn.value, mx.value
+
+    return sampled_select(red, n, n_global, divisor, ks, sample_fn, sample_select_fn, bracket_fn, kept_count_fn,
+                          kept_minmax_fn)
+
+
 def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Optional[Context] = None,
                dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None,
                bounds_ns: Optional[tuple] = None):
@@ -233,6 +371,13 @@ def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Opt
             check(L.b200_select_kth_range(h, d, d_samples, n, divisor, int(bounds_ns[0]), int(bounds_ns[1]),
                                           karr.ctypes.data, karr.size, out.ctypes.data))
         return [int(x) for x in out]
+
+    ntot = n_global if n_global is not None else int(red.sum_u64(np.array([n], dtype=np.uint64))[0])
+    if ntot >= SAMPLED_SELECT_MIN and all(0 <= int(k) < ntot for k in ks) and 0 < len(ks) <= SELECT_MAX_K:
+        r = _sampled_select_on_gpu(red, L, h, d, d_samples, n, ntot, divisor, ks, False)
+        if r is not None:
+            return r[0]
+    n_global = ntot
 
     def minmax_fn():
         if bounds_ns is not None:
@@ -282,6 +427,19 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
         whole = merge_distribution(_Reducer(), np.zeros(0, dtype=np.uint64), st.count, st.min, st.max,
                                    _signed(st.sum, st.sum_hi), (st.sumsq_hi << 64) | st.sumsq_lo, 0, 0)
         return Percentiles(whole.avg_go_int, int(out[0]), int(out[1]), int(out[2]), int(out[3]), whole.min, whole.max)
+    if dist is None:
+        # several ranks: one sampled pass gives the ranks and the moments; the radix passes if it misses
+        red = _Reducer(group, reduce_device)
+        ctx_ = ctx or default_context()
+        size = int(red.sum_u64(np.array([n], dtype=np.uint64))[0])
+        if size >= SAMPLED_SELECT_MIN:
+            ks = [size // 5, size // 2, (9 * size) // 10, (99 * size) // 100]
+            r = _sampled_select_on_gpu(red, ctx_._L, ctx_._h, ctx_._dev(dev), d_samples_ns, n, size, divisor, ks, True)
+            if r is not None:
+                (p20, p50, p90, p99), st = r
+                whole = merge_distribution(red, np.zeros(0, dtype=np.uint64), st.count, st.min, st.max,
+                                           _signed(st.sum, st.sum_hi), (st.sumsq_hi << 64) | st.sumsq_lo, 0, 0)
+                return Percentiles(whole.avg_go_int, p20, p50, p90, p99, whole.min, whole.max)
     dist_ = dist if dist is not None else hist_fixed(d_samples_ns, n, divisor, OC_DEFAULT_LATENCY_BOUNDS,
                                                      HIST_OPENCENSUS, ctx=ctx, dev=dev, group=group,
                                                      reduce_device=reduce_device)

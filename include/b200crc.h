@@ -179,6 +179,20 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
  * stats->dropped_* are 0. */
 int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                           const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats);
+/* Building blocks of the sampled select for the one-process-per-GPU form (custom-go-client-benchmark_b200/latency.py;
+ * b200_select_kth runs the same steps itself on one device).
+ * b200_select_sample: one sample per stratum of `stride` consecutive inputs, at a hashed position inside the
+ *   stratum; *nsample = n / stride of them land in a library-owned device buffer, *d_sample.
+ * b200_bracket_pass: counts[c] (HOST, nthr + 1 entries) = samples with exactly c of the strictly ascending raw
+ *   thresholds <= sample; the samples of ODD c (the brackets, when the thresholds are lo0, hi0+1, lo1, hi1+1, ...)
+ *   are kept, in no particular order, in a library-owned device buffer *d_kept; *nkept is their number, of which
+ *   only the first `cap` are stored.  stats (may be NULL): moments of trunc(sample/divisor) over all n samples.
+ * Both buffers stay valid until the next b200_select_* / b200_bracket_pass call on the same device. */
+int b200_select_sample(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, size_t stride,
+                       const int64_t** d_sample, size_t* nsample);
+int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                      const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
+                      uint64_t* nkept, b200_lat_stats* stats);
 /* The same when the caller already knows bounds lo_ns <= every sample <= hi_ns (for instance from the min/max
  * of a previous b200_hist_fixed): saves the min/max pass of the radix select.  The bounds must be true: a
  * sample outside them is either reported as B200_ERR_INVALID (radix select) or ranked like any other

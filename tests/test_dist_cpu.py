@@ -41,6 +41,31 @@ def _np_count_fn(samples):
     return count_fn
 
 
+def _np_sampled_fns(samples, divisor, seed):
+    """numpy stand-ins with the contracts of b200_select_sample / b200_select_kth on the sample / b200_bracket_pass
+    and the radix building blocks over the kept samples."""
+    st = {}
+
+    def sample_fn(stride):
+        rng = np.random.default_rng(seed)
+        s = samples.size // stride
+        st["sample"] = np.sort(samples[np.arange(s) * stride + rng.integers(0, stride, size=s)]) if s else samples[:0]
+        return s
+
+    def sample_select_fn(ranks):
+        return [int(st["sample"][r]) for r in ranks]
+
+    def bracket_fn(thr, cap):
+        c = np.searchsorted(np.array(thr, dtype=np.int64), samples, side="right")  # thresholds <= sample
+        counts = np.bincount(c, minlength=len(thr) + 1).astype(np.uint64)
+        kept = samples[c % 2 == 1]
+        st["kept"] = kept[:cap]
+        return counts, kept.size, None
+
+    return (sample_fn, sample_select_fn, bracket_fn, lambda *a: _np_count_fn(st["kept"])(*a),
+            lambda: (int(st["kept"].min()), int(st["kept"].max())) if st["kept"].size else ((1 << 63) - 1, -(1 << 63)))
+
+
 def _worker(rank, world, port, q):
     import torch.distributed as dist
     sys.path.insert(0, ROOT)
@@ -96,6 +121,31 @@ def _worker(rank, world, port, q):
         got = lat.radix_select(red, part.size, mm, _np_count_fn(part), 1, [0, 600, all_v.size - 1])
         srt = np.sort(all_v)
         assert got == [int(srt[0]), int(srt[600]), int(srt[-1])]
+        # --- 4. sampled select: one bracket pass per rank, a handful of integers per collective --------------
+        n = 4_000_000                                 # (below ~10^6 the brackets of four ranks are wider than the buffers)
+        ns_all = oracle.latency_ns(n)
+        for split in (n // 2, n // 3):                # equal and unequal shares
+            ns = ns_all[:split] if rank == 0 else ns_all[split:]
+            ks = [n // 5, n // 2, 9 * n // 10, 99 * n // 100]
+            r = lat.sampled_select(red, ns.size, n, 1000, ks, *_np_sampled_fns(ns, 1000, rank))
+            assert r is not None, "the brackets should catch the ranks on spread-out data"
+            srt = np.sort(ns_all // 1000)
+            assert r[0] == [int(srt[k]) for k in ks], r[0]
+        # extreme ranks open the brackets at the ends; ranks whose data differ widen them: exact or a clean miss
+        shifted = ns_all[:n // 2] if rank == 0 else ns_all[n // 2:] + 3_000_000
+        both = np.concatenate([ns_all[:n // 2], ns_all[n // 2:] + 3_000_000])
+        for ks in ([0, n // 2, n - 1], [n // 3]):
+            r = lat.sampled_select(red, shifted.size, n, 1, ks, *_np_sampled_fns(shifted, 1, rank))
+            if r is not None:
+                srt = np.sort(both)
+                assert r[0] == [int(srt[k]) for k in ks]
+        # heavy duplicates: brackets too heavy for the buffers -> None on every rank (the caller falls back)
+        coarse = (ns_all // 5_000_000) * 5_000_000
+        part = coarse[:n // 2] if rank == 0 else coarse[n // 2:]
+        assert lat.sampled_select(red, part.size, n, 1, [n // 2], *_np_sampled_fns(part, 1, rank)) is None
+        # a rank with almost nothing cannot bracket: None everywhere
+        part = ns_all[:100] if rank == 0 else ns_all[100:]
+        assert lat.sampled_select(red, part.size, n, 1, [n // 2], *_np_sampled_fns(part, 1, rank)) is None
         q.put((rank, "ok"))
     except Exception as e:  # surface the failure in the parent
         import traceback

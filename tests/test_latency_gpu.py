@@ -322,6 +322,45 @@ def test_select_any_number_of_ranks(ctx, samples, nk):
         assert lat.select_kth(d, m, 1000, ks, ctx=ctx) == [int(srt[k]) for k in ks]
 
 
+def test_multi_rank_sampled_select_building_blocks(ctx):
+    """b200_select_sample + b200_bracket_pass under the multi-rank protocol (latency.sampled_select), here with one
+    rank: exact ranks and exact moments from one pass; tests/test_dist_cpu.py runs the protocol across two ranks."""
+    n = 5_000_001
+    ns = oracle.latency_ns(n)
+    d = upload(ctx, ns)
+    red = lat._Reducer()
+    for start, div in ((0, 1000), (1, 1)):
+        part = ns[start:]
+        m = part.size
+        ks = [m // 5, m // 2, 9 * m // 10, 99 * m // 100]
+        r = lat._sampled_select_on_gpu(red, ctx._L, ctx._h, 0, d + 8 * start, m, m, div, ks, True)
+        assert r is not None
+        vals, st = r
+        v = part // div
+        srt = np.sort(v)
+        assert vals == [int(srt[k]) for k in ks]
+        assert (st.count, st.min, st.max, st.sum) == (m, int(v.min()), int(v.max()), int(v.sum()))
+    # the building blocks directly: strata and odd-bin bookkeeping
+    import ctypes as C
+    p, cnt = C.c_void_p(), C.c_size_t()
+    assert ctx._L.b200_select_sample(ctx._h, 0, d, n, 1000, C.byref(p), C.byref(cnt)) == 0 and cnt.value == n // 1000
+    sample = np.empty(cnt.value, dtype=np.int64)
+    ctx.d2h(sample, p.value)
+    strata = ns[:cnt.value * 1000].reshape(-1, 1000)
+    assert all(sample[i] in strata[i] for i in range(0, cnt.value, 97))
+    thr = np.array([30_000_000, 30_100_000, 60_000_000, 60_000_001], dtype=np.int64)
+    counts = np.zeros(5, dtype=np.uint64)
+    kp, nkept = C.c_void_p(), C.c_uint64()
+    assert ctx._L.b200_bracket_pass(ctx._h, 0, d, n, 1, thr.ctypes.data, 4, 1 << 20, counts.ctypes.data, C.byref(kp),
+                                    C.byref(nkept), None) == 0
+    c = np.searchsorted(thr, ns, side="right")
+    assert list(counts) == list(np.bincount(c, minlength=5))
+    kept = np.empty(nkept.value, dtype=np.int64)
+    ctx.d2h(kept, kp.value)
+    assert nkept.value == int((c % 2 == 1).sum()) and (np.sort(kept) == np.sort(ns[c % 2 == 1])).all()
+    ctx.free_device(d)
+
+
 def test_select_all_equal_and_empty(ctx):
     ns = np.full(1000, 123456789, dtype=np.int64)
     d = upload(ctx, ns)

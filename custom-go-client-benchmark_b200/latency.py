@@ -103,15 +103,26 @@ class _Reducer:
     def sum_u64(self, arr: np.ndarray) -> np.ndarray:
         # split into 32-bit halves so the int64 all-reduce cannot overflow for < 2^31 ranks
         a = arr.astype(np.uint64)
-        lo = self._run((a & np.uint64(0xFFFFFFFF)).astype(np.int64), "SUM").astype(object)
-        hi = self._run((a >> np.uint64(32)).astype(np.int64), "SUM").astype(object)
-        return lo + hi * (1 << 32)  # python ints
+        halves = np.concatenate([(a & np.uint64(0xFFFFFFFF)).astype(np.int64), (a >> np.uint64(32)).astype(np.int64)])
+        r = self._run(halves, "SUM").astype(object)  # one collective for both halves
+        return r[:a.size] + r[a.size:] * (1 << 32)  # python ints
+
+    def sum_counts(self, arr: np.ndarray) -> np.ndarray:
+        """Sum of sample counts over ranks as int64: one collective and no Python-int arithmetic.  For counts
+        only (their total is the number of samples, far below 2^63); 64-bit limbs go through sum_u64."""
+        return self._run(np.ascontiguousarray(arr).astype(np.int64), "SUM")
 
     def min_i64(self, v: int) -> int:
         return int(self._run(np.array([v], dtype=np.int64), "MIN")[0])
 
     def max_i64(self, v: int) -> int:
         return int(self._run(np.array([v], dtype=np.int64), "MAX")[0])
+
+    def minmax_i64(self, mn: int, mx: int):
+        """(min over ranks of mn, max over ranks of mx) in one collective: MIN of [mn, ~mx] (~ reverses the order
+        of int64 without overflowing at INT64_MIN)."""
+        r = self._run(np.array([mn, ~mx], dtype=np.int64), "MIN")
+        return int(r[0]), ~int(r[1])
 
 
 def merge_distribution(red: _Reducer, counts: np.ndarray, cnt: int, mn: int, mx: int, total: int, sumsq: int,
@@ -132,8 +143,7 @@ def merge_distribution(red: _Reducer, counts: np.ndarray, cnt: int, mn: int, mx:
         total = sum(int(r[nb + 3 + i]) << (32 * i) for i in range(4)) - world * off
         sumsq = sum(int(r[nb + 7 + i]) << (32 * i) for i in range(4))
         big = (1 << 63) - 1
-        mn = red.min_i64(mn if had else big)
-        mx = red.max_i64(mx if had else -big - 1)
+        mn, mx = red.minmax_i64(mn if had else big, mx if had else -big - 1)
     wrapped = total & _M64
     wrapped = wrapped - (1 << 64) if wrapped >= _SIGN else wrapped
     return Distribution(cnt, mn, mx, total, wrapped, sumsq, counts, below, above)
@@ -183,7 +193,7 @@ def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int,
         gmn, gmx = int(global_bounds[0]), int(global_bounds[1])
     else:
         mn, mx = minmax_fn()
-        gmn, gmx = red.min_i64(mn), red.max_i64(mx)
+        gmn, gmx = red.minmax_i64(mn, mx)
     kmin, kmax = (gmn + _SIGN) & _M64, (gmx + _SIGN) & _M64
     bits = (kmax - kmin).bit_length()
     res = []
@@ -197,18 +207,14 @@ def radix_select(red: _Reducer, n_local: int, minmax_fn, count_fn, divisor: int,
             width = top - shift
             # first pass: key' < 2^top, so every sample matches prefix 0 and one histogram serves all k
             pfx = [0] if first else prefix
-            tot = red.sum_u64(np.asarray(count_fn(kmin, shift, top, pfx), dtype=np.uint64).reshape(-1))
+            tot = red.sum_counts(np.asarray(count_fn(kmin, shift, top, pfx), dtype=np.uint64).reshape(-1))
             for i in range(m):
                 row = tot[0:RADIX_BINS] if first else tot[i * RADIX_BINS:(i + 1) * RADIX_BINS]
-                cum = 0
-                for dgt in range(1 << width):
-                    c = int(row[dgt])
-                    if rank[i] < cum + c:
-                        break
-                    cum += c
-                else:
+                cs = np.cumsum(row[:1 << width])
+                dgt = int(np.searchsorted(cs, rank[i], side="right"))  # first digit whose running count exceeds the rank
+                if dgt == 1 << width:
                     raise RuntimeError("inconsistent radix counts")
-                rank[i] -= cum
+                rank[i] -= int(cs[dgt - 1]) if dgt else 0
                 prefix[i] = (prefix[i] << width) | dgt
             top, first = shift, False
         for i in range(m):
@@ -296,7 +302,7 @@ def sampled_select(red: _Reducer, n_local: int, n_global: int, divisor: int, ks:
     expect = nk * (2 * margin + 2) * stride
     cap = max(min(max(8 * expect, n_local // 64), n_local // 8), 1024)
     counts, nkept, stats = bracket_fn(thr, cap)
-    tot = red.sum_u64(np.array([int(c) for c in counts] + [int(nkept), 1 if nkept > cap else 0], dtype=np.uint64))
+    tot = red.sum_counts(np.array([int(c) for c in counts] + [int(nkept), 1 if nkept > cap else 0], dtype=np.uint64))
     gc = [int(x) for x in tot[:len(thr) + 1]]
     inside = sum(gc[1::2])
     if int(tot[-1]) or sum(gc) != n_global or int(tot[-2]) != inside or inside == 0:

@@ -74,6 +74,7 @@ SIGNATURES = {
     "b200_fill_payload_device": (_int, [_vp, _int, _vp, _u64, _sz, _u64]),
     "b200_fill_latency_ns_device": (_int, [_vp, _int, _vp, _u64, _sz, _u64]),
     "b200_hist_fixed": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _int, _vp, C.POINTER(LatStats)]),
+    "b200_hist_fixed_pair": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _int, _vp, _vp, _int, _int, _vp, _vp, _vp]),
     "b200_select_kth": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp]),
     "b200_select_kth_stats": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp, _vp]),
     "b200_select_sample": (_int, [_vp, _int, _vp, _sz, _sz, _pp, C.POINTER(_sz)]),

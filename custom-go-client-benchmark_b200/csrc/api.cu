@@ -1227,6 +1227,68 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     return 0;
 }
 
+int b200_hist_fixed_pair(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                         const double* edges_a, int nedges_a, int mode_a, uint64_t* counts_a,
+                         const double* edges_b, int nedges_b, int mode_b, uint64_t* counts_b,
+                         uint64_t* dropped_b, b200_lat_stats* stats) {
+    DevState* d = get_dev(ctx, dev);
+    auto mode_ok = [](int m) { return m == B200_HIST_NUMPY || m == B200_HIST_OPENCENSUS; };
+    if (!d || !edges_a || !edges_b || !counts_a || !counts_b || (n && !d_samples) || ((uintptr_t)d_samples & 7) ||
+        !mode_ok(mode_a) || !mode_ok(mode_b) || nedges_a > B200_HIST_MAX_EDGES || nedges_b > B200_HIST_MAX_EDGES)
+        return fail(B200_ERR_INVALID, "b200_hist_fixed_pair");
+    // One pass with the union of the two threshold sets; each histogram's bin is then a sum of union bins.
+    long long ta[kMaxThresholds], tb[kMaxThresholds], u[2 * kMaxThresholds];
+    const int ma = host_edges_to_thresholds(edges_a, nedges_a, mode_a, divisor, ta);
+    const int mb = host_edges_to_thresholds(edges_b, nedges_b, mode_b, divisor, tb);
+    if (ma < 0 || mb < 0) return fail(B200_ERR_INVALID, "b200_hist_fixed_pair: edges must be ascending, divisor >= 1");
+    const int mu = (int)(std::unique(u, std::merge(ta, ta + ma, tb, tb + mb, u)) - u);
+    if (mu > kMaxThresholds)
+        return fail(B200_ERR_TOO_LARGE, "b200_hist_fixed_pair: more than 66 distinct thresholds between the two edge sets");
+    HistParams P;
+    if (host_build_hist_params_thr(u, mu, divisor, &P)) return fail(B200_ERR_INVALID, "b200_hist_fixed_pair");
+    unsigned long long c[kMaxThresholds + 1];
+    LatMoments m;
+    {
+        std::lock_guard<std::mutex> lk(d->mu);
+        CU(cudaSetDevice(dev));
+        CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32));
+        CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+    }
+    // union bin g holds the samples with exactly g union thresholds <= them, i.e. those in [u[g-1], u[g]); the
+    // number of a histogram's own thresholds <= such a sample is the number of them <= u[g-1]
+    auto split = [&](const long long* t, int mt, int mode, int nedges, uint64_t* counts, uint64_t* below, uint64_t* above) {
+        uint64_t own[kMaxThresholds + 1] = {0};
+        for (int g = 0; g <= mu; g++) {
+            const int k = g == 0 ? 0 : (int)(std::upper_bound(t, t + mt, u[g - 1]) - t);
+            own[k] += c[g];
+        }
+        *below = *above = 0;
+        if (mode == B200_HIST_NUMPY) {
+            for (int i = 0; i < nedges - 1; i++) counts[i] = own[i + 1];
+            *below = own[0];
+            *above = own[nedges];
+        } else {
+            for (int i = 0; i <= nedges; i++) counts[i] = own[i];
+        }
+    };
+    uint64_t below_a, above_a, below_b, above_b;
+    split(ta, ma, mode_a, nedges_a, counts_a, &below_a, &above_a);
+    split(tb, mb, mode_b, nedges_b, counts_b, &below_b, &above_b);
+    if (dropped_b) {
+        dropped_b[0] = below_b;
+        dropped_b[1] = above_b;
+    }
+    if (stats) {
+        fill_stats(m, divisor, stats);
+        stats->dropped_below = below_a;
+        stats->dropped_above = above_a;
+    }
+    return 0;
+}
+
 int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t* mn, int64_t* mx) {
     DevState* d = get_dev(ctx, dev);
     if (!d || !mn || !mx || (n && !d_samples)) return fail(B200_ERR_INVALID, "b200_minmax");

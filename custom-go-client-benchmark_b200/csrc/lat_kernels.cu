@@ -892,8 +892,7 @@ void finish_hist_params(HistParams* P, long long divisor);
 
 }  // namespace
 
-int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* P) {
-    memset(P, 0, sizeof *P);
+int host_edges_to_thresholds(const double* edges, int nedges, int mode, long long divisor, long long* thr) {
     if (divisor < 1 || nedges < 1 || nedges > kMaxThresholds - 2) return -1;
     for (int i = 0; i < nedges; i++) {
         if (std::isnan(edges[i])) return -1;
@@ -903,11 +902,18 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
     int m = 0;
     if (mode == 0) {  // numpy: below edges[0] -> count 0 (dropped); last edge inclusive; above -> count nedges
         if (nedges < 2) return -1;
-        for (int j = 0; j < nedges - 1; j++) P->thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
-        P->thr[m++] = first_n_with_quotient_at_least(std::floor(edges[nedges - 1]) + 1, divisor);
+        for (int j = 0; j < nedges - 1; j++) thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
+        thr[m++] = first_n_with_quotient_at_least(std::floor(edges[nedges - 1]) + 1, divisor);
     } else {  // opencensus: bucket = #{bounds <= v}
-        for (int j = 0; j < nedges; j++) P->thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
+        for (int j = 0; j < nedges; j++) thr[m++] = first_n_with_quotient_at_least(std::ceil(edges[j]), divisor);
     }
+    return m;
+}
+
+int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* P) {
+    memset(P, 0, sizeof *P);
+    const int m = host_edges_to_thresholds(edges, nedges, mode, divisor, P->thr);
+    if (m < 0) return -1;
     P->nthr = m;
     finish_hist_params(P, divisor);
     return 0;

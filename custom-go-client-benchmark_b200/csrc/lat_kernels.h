@@ -127,6 +127,9 @@ cudaError_t launch_hist_f64(const double* d_x, size_t n, const double* edges, in
 
 // Host helper: fill thresholds / LUT / magic for (edges, mode, divisor).
 int host_build_hist_params(const double* edges, int nedges, int mode, long long divisor, HistParams* out);
+// Just the thresholds of (edges, mode, divisor): ascending (not necessarily strictly) raw-ns values such that the
+// bin of a sample is the number of thresholds <= it.  Returns their number (<= kMaxThresholds) or -1.
+int host_edges_to_thresholds(const double* edges, int nedges, int mode, long long divisor, long long* thr);
 // The same from raw thresholds (strictly ascending int64 ns): bin(n) = #{j : thr[j] <= n}; the divisor only
 // scales the moments.
 int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, HistParams* out);

@@ -101,8 +101,7 @@ def reduce_latencies(latencies_ns: np.ndarray, ctx: Optional[crc32c.Context] = N
     try:
         if a.size:
             ctx.h2d(d, a)
-        readme = latency.hist_readme(d, a.size, ctx=ctx)
-        oc = latency.hist_opencensus(d, a.size, ctx=ctx)
+        readme, oc = latency.hist_readme_and_opencensus(d, a.size, ctx=ctx)  # one pass for both
         pct = latency.percentiles(d, a.size, latency.NS_PER_US, ctx=ctx) if a.size else None
     finally:
         ctx.free_device(d)

@@ -167,6 +167,15 @@ typedef struct {
  * Exact for |v| < 2^53 (float64(v) is then exact). */
 int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                     const double* edges, int nedges, int mode, uint64_t* counts, b200_lat_stats* stats);
+/* Two histograms of the same samples with the same divisor from ONE pass (for instance the README bins and the
+ * OpenCensus distribution of a run, README.md:21-32 and metrics_exporter.go:22-34, which the reference computes
+ * separately): counts_a / counts_b as b200_hist_fixed would fill them for (edges_a, mode_a) and (edges_b, mode_b).
+ * stats (may be NULL) holds the moments and histogram a's dropped counts; dropped_b (may be NULL) receives
+ * histogram b's {below, above}.  B200_ERR_TOO_LARGE if the two edge sets have more than 66 distinct thresholds. */
+int b200_hist_fixed_pair(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                         const double* edges_a, int nedges_a, int mode_a, uint64_t* counts_a,
+                         const double* edges_b, int nedges_b, int mode_b, uint64_t* counts_b,
+                         uint64_t* dropped_b, b200_lat_stats* stats);
 /* Exact order statistics: out[i] = k[i]-th smallest (0-based) of trunc(sample/divisor), i.e. sorted[k[i]]
  * of ssd_test/main.go:158-163.  Samples are not modified (no sort: one sampled histogram pass for long
  * inputs, MSD radix select otherwise).  k and out are HOST arrays.  B200_ERR_EMPTY when n == 0

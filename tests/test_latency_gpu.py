@@ -73,6 +73,45 @@ def test_opencensus_distribution(ctx, samples):
     assert abs(h.sum_of_squared_dev - s.sum_sq_dev) <= 1e-9 * s.sum_sq_dev
 
 
+def test_two_histograms_from_one_pass(ctx, samples):
+    ns, d, n = samples
+    ms = oracle.ns_to_ms(ns).astype(np.float64)
+    readme, oc = lat.hist_readme_and_opencensus(d, n, ctx=ctx)
+    ref, dropped = oracle.hist_numpy(ms)
+    assert list(readme.counts) == list(ref) and readme.dropped_below + readme.dropped_above == dropped
+    assert list(oc.counts) == list(oracle.hist_opencensus(ms)) and oc.dropped_below == oc.dropped_above == 0
+    one = lat.hist_opencensus(d, n, ctx=ctx)
+    assert (oc.count, oc.min, oc.max, oc.sum, oc.sumsq) == (one.count, one.min, one.max, one.sum, one.sumsq)
+    assert (readme.sum, readme.sumsq) == (one.sum, one.sumsq)
+    # any two edge sets: fractional edges that collapse onto one threshold, shared edges, both modes, negatives
+    rng = np.random.default_rng(9)
+    v = rng.integers(-40_000_000, 150_000_000, size=70_001).astype(np.int64)
+    dv = upload(ctx, v)
+    for div in (1_000_000, 1000, 7):
+        q = ((np.abs(v) // div) * np.sign(v)).astype(np.float64)
+        ea = np.array([-3.5, -3.25, 0, 0.25, 0.5, 19.9, 20, 95, 1e4], dtype=np.float64)
+        eb = np.array([-10, 0, 20, 20.5, 77, 1e4, 1e5], dtype=np.float64)
+        for ma, mb in ((pkg._lib.HIST_NUMPY, pkg._lib.HIST_OPENCENSUS), (pkg._lib.HIST_OPENCENSUS, pkg._lib.HIST_NUMPY),
+                       (pkg._lib.HIST_NUMPY, pkg._lib.HIST_NUMPY)):
+            a, b = lat.hist_fixed_pair(dv, v.size, div, ea, ma, eb, mb, ctx=ctx)
+            for h, e, m in ((a, ea, ma), (b, eb, mb)):
+                want = lat.hist_fixed(dv, v.size, div, e, m, ctx=ctx)
+                assert list(h.counts) == list(want.counts), (div, m)
+                assert (h.dropped_below, h.dropped_above, h.sum, h.min, h.max) == (
+                    want.dropped_below, want.dropped_above, want.sum, want.min, want.max)
+                if m == pkg._lib.HIST_NUMPY:
+                    ref, dropped = oracle.hist_numpy(q, e)
+                    assert list(h.counts) == list(ref) and h.dropped_below + h.dropped_above == dropped
+                else:
+                    assert list(h.counts) == list(oracle.hist_opencensus(q, e))
+    # too many distinct thresholds between the two sets
+    big_a, big_b = np.arange(0, 64, dtype=np.float64), np.arange(0.0, 64.0) + 100
+    with pytest.raises(pkg.B200Error) as e:
+        lat.hist_fixed_pair(dv, v.size, 1, big_a, pkg._lib.HIST_OPENCENSUS, big_b, pkg._lib.HIST_OPENCENSUS, ctx=ctx)
+    assert e.value.status == pkg._lib.ERR_TOO_LARGE
+    ctx.free_device(dv)
+
+
 def test_histogram_edge_values(ctx):
     ms_vals = [19, 20, 24, 25, 90, 94, 95, 96, 100, 0, -5]
     ns = np.array([v * 1_000_000 for v in ms_vals] + [19_999_999, 20_000_000, 24_999_999, 25_000_000,

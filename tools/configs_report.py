@@ -141,6 +141,9 @@ def main():
         t1 = time.perf_counter()
         oc = lat.hist_opencensus(d, n, ctx=ctx, reduce_device=rd)
         t2 = time.perf_counter()
+        both = lat.hist_readme_and_opencensus(d, n, ctx=ctx, reduce_device=rd)
+        t2c = time.perf_counter()
+        assert list(both[0].counts) == list(h.counts) and list(both[1].counts) == list(oc.counts)
         p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx, reduce_device=rd)  # first call sizes the scratch buffers
         barrier()
         t2b = time.perf_counter()
@@ -163,7 +166,9 @@ def main():
                               "oc35_counts": [int(x) for x in oc.counts], "mean_ms": oc.mean,
                               "us": {"avg": p.avg, "p20": p.p20, "p50": p.p50, "p90": p.p90, "p99": p.p99,
                                      "min": p.min, "max": p.max},
-                              "hist_ms": round(hist_ms, 3), "oc_ms": round(oc_ms, 3), "percentiles_ms": round(pct_ms, 3),
+                              "hist_ms": round(hist_ms, 3), "oc_ms": round(oc_ms, 3),
+                              "hist_and_oc_one_pass_ms": round(max_over_ranks((t2c - t2) * 1e3), 3),
+                              "percentiles_ms": round(pct_ms, 3),
                               "hist_GBps_at_8B_per_sample": round(N * 8 / hist_ms / 1e6, 1),
                               "percentiles_GBps_at_8B_per_sample": round(N * 8 / pct_ms / 1e6, 1)}))
         ctx.free_device(d)

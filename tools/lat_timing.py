@@ -29,6 +29,8 @@ print(f"hist numpy15 only      : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s")
 oc = lat.OC_DEFAULT_LATENCY_BOUNDS
 ms = timeit(lambda: L.b200_hist_fixed(h, 0, d, n, 1000000, oc.ctypes.data, oc.size, 1, counts.ctypes.data, C.byref(st)))
 print(f"hist oc35 + moments    : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s")
+ms = timeit(lambda: lat.hist_readme_and_opencensus(d, n, ctx=ctx))
+print(f"numpy15 + oc35 + moments, one pass: {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s")
 mn, mx = C.c_int64(), C.c_int64()
 ms = timeit(lambda: L.b200_minmax(h, 0, d, n, C.byref(mn), C.byref(mx)))
 print(f"minmax                 : {ms:8.3f} ms  {n*8/ms/1e6:8.1f} GB/s")

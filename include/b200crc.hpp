@@ -23,6 +23,7 @@
 #include <memory>
 #include <stdexcept>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "b200crc.h"
@@ -207,6 +208,23 @@ inline Distribution HistFixed(const Context& c, const int64_t* d_samples_ns, siz
     check(b200_hist_fixed(c.get(), dev < 0 ? c.device() : dev, d_samples_ns, n, divisor, edges.data(), (int)edges.size(),
                           mode, d.counts.data(), &d.stats));
     return d;
+}
+
+// Two histograms of the same samples from one pass (README bins + OpenCensus buckets of one run).
+inline std::pair<Distribution, Distribution> HistFixedPair(const Context& c, const int64_t* d_samples_ns, size_t n,
+                                                           int64_t divisor, const std::vector<double>& edges_a, int mode_a,
+                                                           const std::vector<double>& edges_b, int mode_b, int dev = -1) {
+    Distribution a, b;
+    a.counts.resize(mode_a == B200_HIST_NUMPY ? edges_a.size() - 1 : edges_a.size() + 1);
+    b.counts.resize(mode_b == B200_HIST_NUMPY ? edges_b.size() - 1 : edges_b.size() + 1);
+    uint64_t dropped_b[2] = {0, 0};
+    check(b200_hist_fixed_pair(c.get(), dev < 0 ? c.device() : dev, d_samples_ns, n, divisor, edges_a.data(),
+                               (int)edges_a.size(), mode_a, a.counts.data(), edges_b.data(), (int)edges_b.size(), mode_b,
+                               b.counts.data(), dropped_b, &a.stats));
+    b.stats = a.stats;
+    b.stats.dropped_below = dropped_b[0];
+    b.stats.dropped_above = dropped_b[1];
+    return {a, b};
 }
 
 struct Percentiles {  // the seven lines ssd_test prints (ssd_test/main.go:157-163), in sample units

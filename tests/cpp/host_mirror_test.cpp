@@ -92,6 +92,11 @@ int main() {
     std::vector<uint64_t> ocref(bounds.size() + 1);
     oracle_hist_opencensus(msf.data(), n, bounds.data(), (int)bounds.size(), ocref.data());
     REQUIRE(latency::HistFixed(ctx, dns, n, latency::kNsPerMs, bounds, B200_HIST_OPENCENSUS).counts == ocref);
+    auto both = latency::HistFixedPair(ctx, dns, n, latency::kNsPerMs, edges, B200_HIST_NUMPY, bounds, B200_HIST_OPENCENSUS);
+    REQUIRE(both.first.counts == hist.counts);
+    REQUIRE(both.second.counts == ocref);
+    REQUIRE(both.first.stats.dropped_below == hist.stats.dropped_below);
+    REQUIRE(both.second.stats.sum == hist.stats.sum);
     oracle_percentiles op;
     REQUIRE(oracle_percentiles_i64(us.data(), n, &op) == 0);
     auto p = latency::ComputePercentiles(ctx, dns, n);

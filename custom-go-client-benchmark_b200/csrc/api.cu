@@ -1499,11 +1499,18 @@ bool grow(long long** buf, size_t* cap, size_t want) {
     cudaFree(*buf);
     *buf = nullptr;
     *cap = 0;
-    if (cudaMalloc(buf, want * sizeof(long long)) != cudaSuccess) {
+    // a little headroom, so that a caller whose inputs creep up in length does not pay cudaFree + cudaMalloc
+    // (about a millisecond each) on every call
+    size_t room = want + want / 4;
+    if (cudaMalloc(buf, room * sizeof(long long)) != cudaSuccess) {
         cudaGetLastError();
-        return false;
+        room = want;
+        if (cudaMalloc(buf, room * sizeof(long long)) != cudaSuccess) {
+            cudaGetLastError();
+            return false;
+        }
     }
-    *cap = want;
+    *cap = room;
     return true;
 }
 
@@ -1549,7 +1556,13 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         std::unique_lock<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         if (!grow(&d->lat.d_sample, &d->lat.sample_cap, s)) return sampled_trace("skip: no memory for the sample", 1);
-        CU(launch_sample((const long long*)d_samples, stride, d->lat.d_sample, s, d->stream));
+        CU(launch_sample((const long long*)d_samples, stride, d->lat.d_sample, s, d->stream, d->lat.d_compact_n));
+        unsigned long long outside = 0;
+        CU(cudaMemcpyAsync(&outside, d->lat.d_compact_n, sizeof outside, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaStreamSynchronize(d->stream));
+        // the histogram pass takes negative samples and samples >= 2^32 ns one by one on its generic path: a
+        // multi-second tail is fine, a data set that mostly lives there (not latencies) is faster by radix passes
+        if (outside > s / 16) return sampled_trace("skip: too much of the input is outside the 32-bit fast path", 1);
     }
     if (nwant) {
         int rc = b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_sample, s, 1, want, nwant, got);

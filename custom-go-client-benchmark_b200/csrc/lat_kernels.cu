@@ -702,21 +702,34 @@ int sm_count() {
 // One sample per stratum of `stride` consecutive inputs, at a hashed position inside the stratum (a fixed
 // position would alias with anything periodic in the data, e.g. 48 workers writing round-robin).
 __global__ void __launch_bounds__(256)
-sample_kernel(const long long* __restrict__ x, size_t stride, long long* __restrict__ out, size_t s) {
+sample_kernel(const long long* __restrict__ x, size_t stride, long long* __restrict__ out, size_t s,
+              unsigned long long* __restrict__ outside) {
     const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-    if (i >= s) return;
-    unsigned long long z = (i + 1) * 0x9E3779B97F4A7C15ull;
-    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
-    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
-    z ^= z >> 31;
-    out[i] = __ldg(x + i * stride + z % stride);
+    bool wide = false;
+    if (i < s) {
+        unsigned long long z = (i + 1) * 0x9E3779B97F4A7C15ull;
+        z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+        z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+        z ^= z >> 31;
+        const long long v = __ldg(x + i * stride + z % stride);
+        out[i] = v;
+        wide = ((unsigned long long)v >> 32) != 0;  // negative or >= 2^32: not on the histogram kernel's fast path
+    }
+    // how much of the sample the 32-bit fast path cannot take: the caller decides whether a histogram pass pays
+    const unsigned m = __ballot_sync(0xFFFFFFFFu, wide);
+    if (outside && m && (threadIdx.x & 31) == 0) atomicAdd(outside, (unsigned long long)__popc(m));
 }
 
 }  // namespace
 
-cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream) {
+cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
+                          unsigned long long* d_outside) {
+    if (d_outside) {
+        cudaError_t e = cudaMemsetAsync(d_outside, 0, sizeof *d_outside, stream);
+        if (e != cudaSuccess) return e;
+    }
     if (!s) return cudaSuccess;
-    sample_kernel<<<(unsigned)((s + 255) / 256), 256, 0, stream>>>(d_samples, stride, d_out, s);
+    sample_kernel<<<(unsigned)((s + 255) / 256), 256, 0, stream>>>(d_samples, stride, d_out, s, d_outside);
     return cudaGetLastError();
 }
 

@@ -99,7 +99,9 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
                         cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */,
                         const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
-cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream);
+// *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32
+cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
+                          unsigned long long* d_outside = nullptr);
 // All the passes of a radix select of up to kSelMax ranks over [lo, hi] (pass have_bounds = false to take the
 // bounds from a min/max pass first), queued on the stream; the answer lands in s.d_sel (result[], bad).
 cudaError_t launch_select_resident(const long long* d_samples, size_t n, const SelRanks& ranks, bool have_bounds,

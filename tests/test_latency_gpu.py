@@ -328,10 +328,12 @@ def test_sampled_select_matches_sort():
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
     cases = r.stderr.split("--\n")[:-1]
     assert len(cases) == 12, r.stderr
-    for i in (0, 1, 2, 3, 4, 5, 6, 9, 10):  # the brackets must catch the ranks on all the spread-out inputs
+    for i in (0, 1, 2, 3, 5, 6, 9):  # the brackets must catch the ranks on all the spread-out inputs
         assert "sampled ok" in cases[i], (i, cases[i])
-    for i in (7, 8, 11):                    # heavy duplicates: a miss, then the radix passes
+    for i in (7, 8, 11):             # heavy duplicates: a miss, then the radix passes
         assert "sampled miss" in cases[i], (i, cases[i])
+    for i in (4, 10):                # mostly negative / beyond 2^32: not latency-shaped, left to the radix passes
+        assert "sampled skip" in cases[i], (i, cases[i])
 
 
 def test_host_driven_select_still_matches():

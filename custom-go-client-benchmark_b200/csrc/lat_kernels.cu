@@ -88,9 +88,16 @@ __device__ __noinline__ void slow_sample(long long v, const HistParams* __restri
                                          SlowMoments* s, const HistCollect* col) {
     const int c = classify(v, Pg->thr, Pg->nthr, Pg->lut);
     mine[c * 32]++;
-    if (col && (c & 1)) {
-        const unsigned long long at = atomicAdd(col->count, 1ull);
-        if (at < col->cap) col->buf[at] = v;
+    if (col) {  // odd bins are kept; one global atomic for all the lanes that are here together
+        const bool hit = c & 1;
+        const unsigned peers = __ballot_sync(__activemask(), hit);
+        if (hit) {
+            const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+            unsigned long long at = 0;
+            if (lane == leader) at = atomicAdd(col->count, (unsigned long long)__popc(peers));
+            at = __shfl_sync(peers, at, leader) + __popc(peers & ((1u << lane) - 1));
+            if (at < col->cap) col->buf[at] = v;
+        }
     }
     if (s) {
         s->mn = v < s->mn ? v : s->mn;

@@ -1525,7 +1525,7 @@ bool grow(long long** buf, size_t* cap, size_t want) {
 int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
                    int nk, int64_t* out, b200_lat_stats* stats) {
     DevState* d = get_dev(ctx, dev);
-    if (!d || nk > kMaxSelect) return 1;
+    if (!d || nk > kSelMax) return 1;
     std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
     struct Depth {
         Depth() { g_sampled_depth++; }
@@ -1540,9 +1540,9 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     if (s < 4096) return sampled_trace("skip: input too short", 1);
     // sample rank of an input rank r is about r / stride, with a standard deviation below sqrt(s) / 2
     const uint64_t margin = (uint64_t)(2.5 * std::sqrt((double)s)) + 2;
-    uint64_t want[2 * kMaxSelect];
-    bool open_lo[kMaxSelect], open_hi[kMaxSelect];
-    int nwant = 0, lo_at[kMaxSelect], hi_at[kMaxSelect];
+    uint64_t want[2 * kSelMax];
+    bool open_lo[kSelMax], open_hi[kSelMax];
+    int nwant = 0, lo_at[kSelMax], hi_at[kSelMax];
     for (int i = 0; i < nk; i++) {
         const uint64_t c = k[i] / stride;
         open_lo[i] = c < margin;
@@ -1551,7 +1551,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         if (!open_lo[i]) { lo_at[i] = nwant; want[nwant++] = c - margin; }
         if (!open_hi[i]) { hi_at[i] = nwant; want[nwant++] = c + margin + 1; }
     }
-    int64_t got[2 * kMaxSelect];
+    int64_t got[2 * kSelMax];
     {
         std::unique_lock<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
@@ -1572,19 +1572,19 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     // brackets, ascending and disjoint (overlapping or touching ones are merged)
     struct Bracket { int64_t lo, hi; };
     const int64_t kMin = INT64_MIN, kMax = INT64_MAX - 1;  // hi + 1 must not overflow
-    Bracket br[kMaxSelect];
+    Bracket br[kSelMax];
     for (int i = 0; i < nk; i++) {
         br[i].lo = open_lo[i] ? kMin : got[lo_at[i]];
         br[i].hi = open_hi[i] ? kMax : std::min(got[hi_at[i]], kMax);
     }
-    for (int i = 1; i < nk; i++)  // at most kMaxSelect entries: insertion sort by lo
+    for (int i = 1; i < nk; i++)  // at most kSelMax entries: insertion sort by lo
         for (int j = i; j > 0 && br[j].lo < br[j - 1].lo; j--) std::swap(br[j], br[j - 1]);
     int nb = 0;
     for (int i = 0; i < nk; i++) {
         if (nb && br[i].lo <= br[nb - 1].hi + 1) br[nb - 1].hi = std::max(br[nb - 1].hi, br[i].hi);
         else br[nb++] = br[i];
     }
-    long long thr[2 * kMaxSelect];
+    long long thr[2 * kSelMax];
     for (int j = 0; j < nb; j++) {
         thr[2 * j] = br[j].lo;      // bins 2j+1 are the brackets, even bins the gaps
         thr[2 * j + 1] = br[j].hi + 1;
@@ -1617,7 +1617,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     if (total != n || kept != inside) return fail(B200_ERR_CUDA, "select: bracket pass lost samples");
     if (inside > cap || inside == 0) return sampled_trace("miss: brackets too heavy", 1);
     // rank among the kept samples = (kept samples in earlier brackets) + (rank - samples below this bracket)
-    uint64_t rank_kept[kMaxSelect];
+    uint64_t rank_kept[kSelMax];
     for (int i = 0; i < nk; i++) {
         uint64_t below = 0, kept_before = 0;
         int j = 0;
@@ -1643,11 +1643,16 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
 // 0 = out[] is filled, 1 = not attempted or missed (take the radix passes), < 0 = error
 int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
                 int64_t* out, b200_lat_stats* stats) {
-    if (g_sampled_depth != 0 || n < sampled_select_min() || nk > kMaxSelect || !d_samples || ((uintptr_t)d_samples & 7))
-        return 1;
+    if (g_sampled_depth != 0 || n < sampled_select_min() || !d_samples || ((uintptr_t)d_samples & 7)) return 1;
     for (int i = 0; i < nk; i++)
         if (k[i] >= n) return 1;  // the caller reports it
-    return select_sampled(ctx, dev, d_samples, n, divisor, k, nk, out, stats);
+    // up to kSelMax ranks share a pass; more take one pass per group (the moments come from the first)
+    for (int g = 0; g < nk; g += kSelMax) {
+        const int rc = select_sampled(ctx, dev, d_samples, n, divisor, k + g, std::min(kSelMax, nk - g), out + g,
+                                      g == 0 ? stats : nullptr);
+        if (rc) return rc;  // a miss in any group: the caller redoes all of them by radix passes
+    }
+    return 0;
 }
 
 }  // namespace

@@ -315,6 +315,7 @@ seven(np.ascontiguousarray(wide))                               # negative sampl
 seven(np.ascontiguousarray(coarse))                             # a miss: moments from an extra pass
 stalls = np.where(rng.random(n) < 0.03, rng.integers(5 * 10**9, 10**11, size=n), base)   # p99 among 5-100 s reads:
 check(stalls, q(n, [0.5, 0.9, 0.99, 0.999]), 1000)              # brackets beyond the 32-bit fast path
+check(base, q(n, [0.01, 0.05, 0.1, 0.25, 0.5, 0.75, 0.9, 0.99, 0.999]), 1000)   # nine ranks: a pass of 8 and a pass of 1
 print('ok')
 """
 
@@ -329,8 +330,9 @@ def test_sampled_select_matches_sort():
                        capture_output=True, timeout=600)
     assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
     cases = r.stderr.split("--\n")[:-1]
-    assert len(cases) == 13, r.stderr
-    for i in (0, 1, 2, 3, 5, 6, 9, 12):  # the brackets must catch the ranks on all the spread-out inputs
+    assert len(cases) == 14, r.stderr
+    assert cases[13].count("sampled ok") == 2, cases[13]
+    for i in (0, 1, 2, 3, 5, 6, 9, 12, 13):  # the brackets must catch the ranks on all the spread-out inputs
         assert "sampled ok" in cases[i], (i, cases[i])
     for i in (7, 8, 11):             # heavy duplicates: a miss, then the radix passes
         assert "sampled miss" in cases[i], (i, cases[i])

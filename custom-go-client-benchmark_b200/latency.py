@@ -404,7 +404,7 @@ def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Opt
         return [int(x) for x in out]
 
     ntot = n_global if n_global is not None else int(red.sum_u64(np.array([n], dtype=np.uint64))[0])
-    if ntot >= SAMPLED_SELECT_MIN and all(0 <= int(k) < ntot for k in ks) and 0 < len(ks) <= SELECT_MAX_K:
+    if ntot >= SAMPLED_SELECT_MIN and all(0 <= int(k) < ntot for k in ks) and 0 < len(ks) <= 2 * SELECT_MAX_K:
         r = _sampled_select_on_gpu(red, L, h, d, d_samples, n, ntot, divisor, ks, False)
         if r is not None:
             return r[0]

@@ -13,10 +13,18 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rnd = sys.argv[1] if len(sys.argv) > 1 else "r01"
-rep = os.path.join(ROOT, "gpurun_out", "lat_prof.ncu-rep")
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-rr = list(csv.reader(io.StringIO(raw)))
-hdr, units, vals = rr[0], rr[1], rr[2:]
+hdr = units = None
+vals = []
+for name in ("lat_prof.ncu-rep", "lat_prof2.ncu-rep"):  # the second, optional: hist_kernel launches only (all variants)
+    rep = os.path.join(ROOT, "gpurun_out", name)
+    if not os.path.exists(rep):
+        continue
+    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rr = list(csv.reader(io.StringIO(raw)))
+    if hdr is None:
+        hdr, units = rr[0], rr[1]
+    assert rr[0] == hdr
+    vals += rr[2:]
 name_i = hdr.index("Kernel Name")
 
 

@@ -16,6 +16,14 @@ no data-path collective — only the timing barrier and the max-over-ranks reduc
 `cpu_baseline`: the oracle's SSE4.2 three-lane CRC-32C (C restatement of Go's amd64 path; Go is not installed
             on the box) on the box's host cores, over the same objects.
 --impl reference times that CPU implementation alone, all host threads, same config/metric.
+Beside the headline line's keys, at EVERY N:
+`config3` : BASELINE config 3 — ONE 64 GiB object (the splitmix stream) sharded over the N ranks, rank r hashes bytes
+            [r*L/N, (r+1)*L/N), the (crc, len) pairs are all-gathered and folded with the GF(2) combine on the host;
+            strong scaling; the CRC is compared with tests/golden/config3.json (made on the CPU).
+`config5` : BASELINE config 5 — 10^9 latency samples split over the N ranks: README histogram, OpenCensus buckets and
+            the seven ssd_test lines with the counts all-reduced over NCCL; compared with tests/golden/config5.json.
+`e2e.h2d_only` : a bare cudaMemcpy of the same pinned arena on every rank at once — the ceiling of the host-buffer path.
+`multi_device_parity` : the one-process multi-GPU entry points checked on distinct devices (tests/multidev_checks.py).
 """
 from __future__ import annotations
 
@@ -160,7 +168,9 @@ def dist_setup(n_gpus):
         import torch.distributed as d
         torch.cuda.set_device(local)
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        d.init_process_group("nccl", device_id=torch.device("cuda", local))
+        import datetime
+        # a rank that dies must fail the others within minutes, not hold the box until the job limit
+        d.init_process_group("nccl", device_id=torch.device("cuda", local), timeout=datetime.timedelta(minutes=5))
         dist = d
     return rank, world, local, dist
 
@@ -254,12 +264,187 @@ def latency_side_measurement(pkg, ctx, n=500_000_000, reps=5):
         return {"error": f"{type(e).__name__}: {e}"[:300]}
 
 
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def golden(name):
+    with open(os.path.join(GOLDEN, name)) as f:
+        return json.load(f)
+
+
+class Ranks:
+    """The few collectives the bench itself needs (timing reductions, gathers), over NCCL."""
+
+    def __init__(self, dist, rank, world, local):
+        self.dist, self.rank, self.world, self.local = dist, rank, world, local
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+
+    def reduce(self, values, op="MAX"):
+        if self.dist is None:
+            return [float(v) for v in values]
+        import torch
+        t = torch.tensor([float(v) for v in values], dtype=torch.float64, device=f"cuda:{self.local}")
+        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op))
+        return [float(x) for x in t]
+
+    def gather_i64(self, values):
+        """every rank's int64 vector, on every rank: [world][len(values)]"""
+        if self.dist is None:
+            return [[int(v) for v in values]]
+        import torch
+        t = torch.tensor([int(v) for v in values], dtype=torch.int64, device=f"cuda:{self.local}")
+        out = [torch.empty_like(t) for _ in range(self.world)]
+        self.dist.all_gather(out, t)
+        return [[int(x) for x in o.cpu()] for o in out]
+
+
+def multi_device_parity(rk):
+    """Rank 0, before anything is timed: b200_crc32c_sharded / b200_hist_fixed_multi / b200_select_kth_multi on
+    distinct GPUs against the oracle, whenever the box shows more than one (the test box has one GPU)."""
+    out = None
+    if rk.rank == 0:
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tests"))
+            import multidev_checks
+            nd = min(multidev_checks.ngpu(), 4)
+            out = "skipped: one GPU visible" if nd < 2 else dict(multidev_checks.multi_device_parity(nd), result="ok")
+        except AssertionError as e:
+            out = f"FAILED: {e}"
+    rk.barrier()
+    return out
+
+
+def config3_block(rk, crc32c, ctx, oracle_mod):
+    """ONE 64 GiB object sharded over the ranks (strong scaling), host-side GF(2) fold; checked against the golden."""
+    g = golden("config3.json")
+    L, W, r = int(g["bytes"]), rk.world, rk.rank
+    lo, hi = L * r // W // 8 * 8, L * (r + 1) // W // 8 * 8
+    n = hi - lo
+    d = ctx.alloc_device(n)
+    ctx.fill_payload(d, n // 8, SEED, first_word=lo // 8)
+    crc = crc32c.UpdateDevice(0, d, n, ctx)  # warm-up, and this shard's value
+    reps = 5
+    rk.barrier()
+    ctx.timer_start()
+    for _ in range(reps):
+        assert crc32c.UpdateDevice(0, d, n, ctx) == crc
+    ms = ctx.timer_stop() / reps
+    # the whole operation as a caller sees it: shard CRC, all-gather of (crc, len), fold
+    rk.barrier()
+    t0 = time.perf_counter()
+    c = crc32c.UpdateDevice(0, d, n, ctx)
+    parts = rk.gather_i64([c, n])
+    total = 0
+    for pc, pn in parts:
+        total = crc32c.Combine(total, pc, pn)
+    op_ms = (time.perf_counter() - t0) * 1e3
+    # this rank's shard against the golden's 1 GiB pieces (CPU-made), and one piece regenerated by the oracle here
+    piece = int(g["piece_bytes"])
+    shard_ok = 1
+    if lo % piece == 0 and hi % piece == 0:
+        acc = 0
+        for pc in g["piece_crc32c"][lo // piece:hi // piece]:
+            acc = crc32c.Combine(acc, pc, piece)
+        shard_ok = int(acc == crc)
+    chk = 64 << 20
+    spot_ok = int(crc32c.UpdateDevice(0, d + n - chk, chk, ctx) ==
+                  oracle_mod.crc32c(oracle_mod.payload(chk, seed=SEED, first_word=(hi - chk) // 8)))
+    ctx.free_device(d)
+    ms, op_ms = rk.reduce([ms, op_ms], "MAX")
+    shard_ok, spot_ok = rk.reduce([shard_ok, spot_ok], "MIN")
+    out = {"workload": "config 3: one 64 GiB object (splitmix64 stream) sharded over the ranks, per-GPU CRCs folded "
+                       "with the GF(2) combine on the host; no GPU<->GPU exchange", "scaling": "strong",
+           "bytes": L, "n_gpus": W, "crc32c": f"{total:#010x}", "golden": g["crc32c_hex"],
+           "golden_ok": bool(total == int(g["crc32c"]) and shard_ok and spot_ok),
+           "shards_match_golden_pieces": bool(shard_ok), "oracle_spot_check_per_rank": bool(spot_ok),
+           "ms": round(ms, 4), "GB/s": round(L / ms / 1e6, 1),
+           "timing": f"CUDA events around {reps} b200_crc32c_update_device calls on the shard, max over ranks",
+           "operation_ms": round(op_ms, 3),
+           "operation": "wall clock: shard CRC + all_gather of (crc, len) + host fold, max over ranks"}
+    # the same object on ONE GPU in the same run (rank 0; the others wait), for the strong-scaling efficiency
+    if W > 1:
+        n1 = None
+        if r == 0:
+            d = ctx.alloc_device(L)
+            ctx.fill_payload(d, L // 8, SEED, first_word=0)
+            whole = crc32c.UpdateDevice(0, d, L, ctx)
+            ctx.timer_start()
+            for _ in range(3):
+                crc32c.UpdateDevice(0, d, L, ctx)
+            n1 = ctx.timer_stop() / 3
+            ctx.free_device(d)
+            out["golden_ok"] = bool(out["golden_ok"] and whole == int(g["crc32c"]))
+        rk.barrier()
+        if r == 0:
+            out["n1_ms_same_run"] = round(n1, 4)
+            out["efficiency_vs_n1"] = round(n1 / (W * ms), 4)
+    else:
+        out["efficiency_vs_n1"] = 1.0
+    return out
+
+
+def config5_block(rk, pkg, ctx):
+    """10^9 latency samples split over the ranks; bin counts / bracket counts all-reduced over NCCL."""
+    lat = pkg.latency
+    g = golden("config5.json")
+    N, W, r = int(g["samples"]), rk.world, rk.rank
+    lo, hi = N * r // W, N * (r + 1) // W
+    n = hi - lo
+    d = ctx.alloc_device(n * 8)
+    ctx.fill_latency_ns(d, n, SEED, first=lo)
+    rd = f"cuda:{rk.local}" if rk.dist is not None else None
+    kw = dict(ctx=ctx, reduce_device=rd)
+    calls = {"readme_histogram": lambda: lat.hist_readme(d, n, **kw),
+             "opencensus_distribution": lambda: lat.hist_opencensus(d, n, **kw),
+             "readme_and_opencensus_one_pass": lambda: lat.hist_readme_and_opencensus(d, n, **kw),
+             "ssd_test_seven_lines": lambda: lat.percentiles(d, n, lat.NS_PER_US, **kw)}
+    res, timing = {}, {}
+    reps = 3
+    for name, f in calls.items():
+        res[name] = f()  # warm-up: sizes the scratch buffers
+        rk.barrier()
+        tally0 = dict(lat._Reducer.tally)
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            f()
+        dt = (time.perf_counter() - t0) / reps * 1e3
+        rk.barrier()
+        ms, coll_ms = rk.reduce([dt, (lat._Reducer.tally["seconds"] - tally0["seconds"]) / reps * 1e3], "MAX")
+        timing[name] = {"ms": round(ms, 3), "GB/s": round(N * 8 / ms / 1e6, 1),
+                        "collectives": (lat._Reducer.tally["collectives"] - tally0["collectives"]) // reps,
+                        "collectives_ms": round(coll_ms, 3)}
+    ctx.free_device(d)
+    h, oc, (h2, oc2), p = (res[k] for k in calls)
+    gm, gu = g["ms"], g["us"]
+    ok = ([int(x) for x in h.counts] == gm["readme15_counts"] and h.dropped_below == gm["dropped_below"] and
+          h.dropped_above == gm["dropped_above"] and [int(x) for x in oc.counts] == gm["oc35_counts"] and
+          [int(x) for x in h2.counts] == gm["readme15_counts"] and [int(x) for x in oc2.counts] == gm["oc35_counts"] and
+          (h.count, h.min, h.max, h.sum, h.sumsq) == (N, gm["min"], gm["max"], gm["sum"], gm["sumsq"]) and
+          (oc.count, oc.sum) == (N, gm["sum"]) and
+          (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) ==
+          (gu["avg"], gu["p20"], gu["p50"], gu["p90"], gu["p99"], gu["min"], gu["max"]))
+    return {"workload": "config 5: 10^9 synthetic latency samples split over the ranks: README.md:21-32 histogram, "
+                        "metrics_exporter.go:28 distribution, ssd_test/main.go:147-163 lines", "scaling": "strong",
+            "samples": N, "n_gpus": W, "bytes_per_sample": 8, "golden_ok": bool(ok),
+            "reduction": "NCCL all-reduce of bin counts / moments / bracket ends and counts" if W > 1 else "none (one rank)",
+            "timing": f"wall clock around {reps} synchronous calls (each ends with a device->host copy of its result "
+                      "and, with several ranks, its all-reduces), max over ranks",
+            "calls": timing,
+            "us": {"avg": p.avg, "p20": p.p20, "p50": p.p50, "p90": p.p90, "p99": p.p99, "min": p.min, "max": p.max}}
+
+
 def run_b200(args):
     rank, world, local, dist = dist_setup(args.gpus)
+    rk = Ranks(dist, rank, world, local)
     affinity = bind_to_gpu_numa_node(local) if world > 1 else "single rank: not bound"
     pkg = importlib.import_module("custom-go-client-benchmark_b200")
+    import oracle  # the checker (and, at N=1, the timed CPU baseline); never on the GPU path
     crc32c = pkg.crc32c
     ctx = crc32c.Context([local])
+    multidev = multi_device_parity(rk)
     total = NOBJ * OBJ_BYTES
     d_arena = ctx.alloc_device(total)
     # rank r owns words [r*total/8, (r+1)*total/8) of the splitmix stream
@@ -267,60 +452,78 @@ def run_b200(args):
     off = np.arange(NOBJ, dtype=np.uint64) * OBJ_BYTES
     ln = np.full(NOBJ, OBJ_BYTES, dtype=np.uint64)
 
-    # expected checksums: first pass on the GPU (parity against the oracle is checked below on rank 0
-    # and exhaustively in tests/); the timed steps then VERIFY against them.
+    # expected checksums: first pass on the GPU; the timed steps then VERIFY against them.  Every rank checks a
+    # sample of ITS objects against the oracle on regenerated payload (rank 0 at N=1 checks all of them below).
     b0 = crc32c.DeviceBatch(off, ln, None, ctx)
     b0.run(d_arena)
     want, _, _ = b0.results()
     b0.close()
+    probe = [0, 1, 1234, NOBJ // 2, NOBJ - 1] + [int(x) for x in np.random.default_rng(rank).integers(0, NOBJ, 11)]
+    rank_ok = 1
+    for i in probe:
+        ref = oracle.crc32c(oracle.payload(OBJ_BYTES, seed=SEED, first_word=(rank * total + i * OBJ_BYTES) // 8))
+        rank_ok &= int(ref == int(want[i]))
+    rank_ok = int(rk.reduce([rank_ok], "MIN")[0])
+    assert rank_ok, "GPU CRCs differ from the CPU oracle on some rank"
     batch = crc32c.DeviceBatch(off, ln, want, ctx)
-
-    def barrier():
-        if dist is not None:
-            dist.barrier()
 
     for _ in range(max(args.warmup, 0)):
         batch.run(d_arena)
     batch.kernel_ms()  # reset the per-run event window
-    barrier()
+    rk.barrier()
     with ClockSampler(local) as clk:
         ctx.timer_start()
         for _ in range(args.steps):
             batch.run_async(d_arena)
         elapsed_ms = ctx.timer_stop()
-    barrier()
+    rk.barrier()
     got, ok, nbad = batch.results()
     assert nbad == 0 and (got == want).all(), "verification failed inside the timed region"
     _, rows_ms = batch.kernel_ms()
     launches = batch.launches() * args.steps
-    ms_per_step = elapsed_ms / args.steps
-    if dist is not None:
-        import torch
-        t = torch.tensor([ms_per_step, rows_ms], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_per_step, rows_ms = float(t[0]), float(t[1])
+    ms_per_step, rows_ms = rk.reduce([elapsed_ms / args.steps, rows_ms], "MAX")
     value = world * total / (ms_per_step * 1e-3) / 1e9
 
     # ---- e2e: host buffers through the C-ABI VerifyObjects entry point ---------------------------------
     h_arena = ctx.alloc_pinned(total)
     ctx.d2h(h_arena, d_arena)
+    # the ceiling first: a bare cudaMemcpy of the same pinned arena (no kernels), all ranks at once
+    ctx.h2d(d_arena, h_arena)
+    rk.barrier()
+    t0 = time.perf_counter()
+    for _ in range(2):
+        ctx.h2d(d_arena, h_arena)
+    h2d_ms = (time.perf_counter() - t0) / 2 * 1e3
+    rk.barrier()
     bufs = h_arena.reshape(NOBJ, OBJ_BYTES)  # one pinned 2 MiB buffer per object, as the read loop holds them
     e2e_steps = max(1, min(args.steps, 5))
     bad, g = crc32c.VerifyObjects(bufs, want, ctx)  # warm-up (allocates the slabs)
     assert bad == [] and (g == want).all()
-    barrier()
+    rk.barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
         bad, g = crc32c.VerifyObjects(bufs, want, ctx)
     e2e_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
-    barrier()
+    rk.barrier()
     assert bad == []
-    if dist is not None:
-        import torch
-        t = torch.tensor([e2e_ms], dtype=torch.float64, device=f"cuda:{local}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_ms = float(t[0])
+    # the same objects visited in shuffled order, so that no two neighbours are contiguous in host memory and
+    # every 2 MiB buffer is its own copy (a caller holding 4096 separately allocated buffers)
+    perm = np.random.default_rng(7).permutation(NOBJ)
+    ptrs = (h_arena.ctypes.data + perm.astype(np.uint64) * np.uint64(OBJ_BYTES)).astype(np.uint64)
+    bad, g = crc32c.VerifyObjectsAt(ptrs, ln, want[perm], ctx)
+    assert bad == [] and (g == want[perm]).all()
+    rk.barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        bad, g = crc32c.VerifyObjectsAt(ptrs, ln, want[perm], ctx)
+    sc_ms = (time.perf_counter() - t0) / e2e_steps * 1e3
+    rk.barrier()
+    assert bad == []
+    h2d_own_gbs = total / (h2d_ms * 1e-3) / 1e9
+    e2e_ms, sc_ms, h2d_ms = rk.reduce([e2e_ms, sc_ms, h2d_ms], "MAX")
+    h2d_per_rank = [x[0] / 1e3 for x in rk.gather_i64([int(h2d_own_gbs * 1e3)])]
     e2e_val = world * total / (e2e_ms * 1e-3) / 1e9
+    h2d_val = world * total / (h2d_ms * 1e-3) / 1e9
 
     line = None
     if rank == 0:
@@ -339,13 +542,25 @@ def run_b200(args):
                 "e2e": {"value": round(e2e_val, 2), "unit": UNIT, "h2d_bytes_per_step": total,
                         "d2h_bytes_per_step": NOBJ * 5 + 8, "steps": e2e_steps, "ms_per_step": round(e2e_ms, 3),
                         "api": "b200_crc32c_batch_host (VerifyObjects on pinned host buffers)",
+                        "h2d_only": {"value": round(h2d_val, 2), "unit": UNIT, "per_rank": [round(x, 2) for x in h2d_per_rank],
+                                     "what": "bare cudaMemcpy host->device of the same pinned 8 GiB arena, no kernels, "
+                                             "every rank at once (the PCIe / host-memory ceiling of this path)"},
+                        "frac_of_h2d": round(e2e_val / h2d_val, 4),
+                        "scattered": {"value": round(world * total / (sc_ms * 1e-3) / 1e9, 2), "unit": UNIT,
+                                      "ms_per_step": round(sc_ms, 3),
+                                      "what": "the same 4096 buffers in shuffled order: one cudaMemcpyAsync per 2 MiB "
+                                              "buffer, no merging of host-contiguous neighbours"},
                         "pcie_note": "PCIe Gen5 x16 bound (~64 GB/s raw per direction)", "cpu_affinity": affinity},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                              "frac": round(achieved / peak, 4), "traffic": traffic,
                              "frac_of_nominal_8TBps": round(achieved / 8000.0, 4), "kernel": "crc_fold_kernel",
                              "kernel_ms": round(rows_ms, 5), "algorithmic_bytes_per_launch": total,
-                             "peak_source": peak_src + " — of measured"}}
+                             "peak_source": peak_src + " — of measured"},
+                "oracle_check": f"every rank: {len(probe)} of its objects against the CPU oracle on regenerated payload"
+                                + ("; rank 0: all 4096" if world == 1 else ""),
+                "multi_device_parity": multidev if isinstance(multidev, str) else multidev.get("result"),
+                "multi_device_parity_detail": multidev}
         if world == 1:
             cores = os.cpu_count() or 1
             allc, got_cpu, reps = cpu_baseline_run(h_arena, off, ln, cores)
@@ -360,8 +575,17 @@ def run_b200(args):
     ctx.free_pinned(h_arena)
     ctx.free_device(d_arena)
     batch.close()
-    if line is not None and world == 1:
-        line["latency_reduction"] = latency_side_measurement(pkg, ctx)
+    side = {}
+    for name, f in (("config3", lambda: config3_block(rk, crc32c, ctx, oracle)),
+                    ("config5", lambda: config5_block(rk, pkg, ctx))):
+        try:
+            side[name] = f()
+        except Exception as e:  # a side block must not cost the headline line (every rank fails alike or not at all)
+            side[name] = {"error": f"{type(e).__name__}: {e}"[:300], "golden_ok": False}
+    if line is not None:
+        line.update(side)
+        if world == 1:
+            line["latency_reduction"] = latency_side_measurement(pkg, ctx)
     ctx.close()
     if dist is not None:
         dist.barrier()

@@ -260,6 +260,23 @@ def VerifyObjects(bufs, want: Optional[Sequence[int]], ctx: Optional[Context] = 
     return bad, got
 
 
+def VerifyObjectsAt(ptrs, lens, want, ctx: Optional[Context] = None, dev: Optional[int] = None):
+    """VerifyObjects on raw host addresses: ptrs[i] is the address of lens[i] bytes (what the cgo binding hands
+    over for a [][]byte).  Returns (bad []int, got []uint32).  The caller keeps the buffers alive."""
+    ctx = ctx or default_context()
+    ptrs = np.ascontiguousarray(ptrs, dtype=np.uint64)
+    lens = np.ascontiguousarray(lens, dtype=np.uint64)
+    n = ptrs.size
+    w = None if want is None else np.ascontiguousarray(want, dtype=np.uint32)
+    got = np.zeros(n, dtype=np.uint32)
+    ok = np.zeros(n, dtype=np.uint8)
+    nbad = C.c_uint64()
+    check(ctx._L.b200_crc32c_batch_host(ctx._h, ctx._dev(dev), ptrs.ctypes.data, lens.ctypes.data, n,
+                                        None if w is None else w.ctypes.data, got.ctypes.data, ok.ctypes.data,
+                                        C.byref(nbad)))
+    return [int(i) for i in np.nonzero(ok == 0)[0]], got
+
+
 class DeviceBatch:
     """A prepared VerifyObjects plan over a device-resident arena (BASELINE config 2)."""
 

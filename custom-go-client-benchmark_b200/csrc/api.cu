@@ -106,9 +106,11 @@ int HostSlab::reserve(size_t nobj) {
     }
     if (nobj <= cap) return 0;
     size_t c = std::max<size_t>(nobj * 2, 1024);
-    cudaFree(d_off); cudaFree(d_len); cudaFree(d_seg); cudaFree(d_want); cudaFree(d_got); cudaFree(d_ok);
-    cudaFreeHost(h_off); cudaFreeHost(h_len); cudaFreeHost(h_seg); cudaFreeHost(h_want); cudaFreeHost(h_got);
-    cudaFreeHost(h_ok);
+    // free AND forget: if one of the allocations below fails, a later reserve() / release() must not free these again
+    auto drop_dev = [](auto*& p) { cudaFree(p); p = nullptr; };
+    auto drop_host = [](auto*& p) { cudaFreeHost(p); p = nullptr; };
+    drop_dev(d_off); drop_dev(d_len); drop_dev(d_seg); drop_dev(d_want); drop_dev(d_got); drop_dev(d_ok);
+    drop_host(h_off); drop_host(h_len); drop_host(h_seg); drop_host(h_want); drop_host(h_got); drop_host(h_ok);
     cap = 0;
     CU(cudaMalloc(&d_off, c * 8));
     CU(cudaMalloc(&d_len, c * 8));
@@ -130,6 +132,7 @@ int HostSlab::reserve_tasks(size_t ntasks) {
     if (ntasks <= task_cap) return 0;
     size_t c = std::max<size_t>(ntasks * 2, 1 << 16);
     cudaFree(d_seg_raw);
+    d_seg_raw = nullptr;
     task_cap = 0;
     CU(cudaMalloc(&d_seg_raw, c * 4));
     task_cap = c;
@@ -182,6 +185,7 @@ uint32_t env_rows_per_seg() {  // test / tuning override, read once
 }
 
 constexpr uint32_t kShortRows = 256;  // short segments: 128 KB, 4 KB per lane in the fold kernel
+constexpr size_t kMaxBatchObjects = (size_t)1 << 29;  // task ids are 32-bit and an object has up to two non-long segments
 
 // The segmentation of a batch (see SegPlan in crc_kernels.h) and its task counts.
 struct HostPlan {
@@ -236,7 +240,9 @@ HostPlan make_plan(size_t nobj, RowsOf rows_of, int grid) {
             h.max_long = std::max(h.max_long, na);
         }
         h.ntasks = h.nlong + h.nshort + h.npartial;
-        if (h.ntasks <= (1u << 30)) break;
+        // doubling the long length shrinks nlong only; a batch whose partial / short segments alone exceed 2^30
+        // (more than 2^30 objects) is refused by the callers (kMaxBatchObjects), so this ends before p.a overflows
+        if (h.ntasks <= (1u << 30) || h.p.a >= (1u << 30)) break;
         h.p.a *= 2;
     }
     return h;
@@ -729,8 +735,8 @@ int b200_batch_free(b200_batch* b) {
 int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_t* len, size_t nobj,
                       const uint32_t* want, b200_batch** out) {
     DevState* d = get_dev(ctx, dev);
-    if (!d || !out || (nobj && (!off || !len)) || nobj > 0x7FFFFFFFu)
-        return fail(B200_ERR_INVALID, "b200_batch_create");
+    if (!d || !out || (nobj && (!off || !len))) return fail(B200_ERR_INVALID, "b200_batch_create");
+    if (nobj > kMaxBatchObjects) return fail(B200_ERR_TOO_LARGE, "b200_batch_create: more than 2^29 objects in one batch");
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
     b200_batch* b = new (std::nothrow) b200_batch;
@@ -925,7 +931,7 @@ int b200_crc32c_batch_host(b200_ctx* ctx, int dev, const void* const* bufs, cons
         // choose the objects of this slab
         size_t first = i, used = 0, staged = 0;
         size_t cnt = 0;
-        while (i < nobj && len[i] <= kSlabBytes) {
+        while (i < nobj && len[i] <= kSlabBytes && cnt < kMaxBatchObjects) {
             size_t start = (used + 15) & ~(size_t)15;
             if (start + len[i] > kSlabBytes) break;
             used = start + len[i];
@@ -1291,7 +1297,7 @@ int b200_hist_fixed_pair(b200_ctx* ctx, int dev, const int64_t* d_samples, size_
 
 int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t* mn, int64_t* mx) {
     DevState* d = get_dev(ctx, dev);
-    if (!d || !mn || !mx || (n && !d_samples)) return fail(B200_ERR_INVALID, "b200_minmax");
+    if (!d || !mn || !mx || (n && !d_samples) || ((uintptr_t)d_samples & 7)) return fail(B200_ERR_INVALID, "b200_minmax");
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
     CU(launch_minmax((const long long*)d_samples, n, d->lat, d->stream));
@@ -1306,7 +1312,8 @@ int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int6
 int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, uint64_t key_base, int shift,
                      int top, int nk, const uint64_t* prefix, uint64_t* counts) {
     DevState* d = get_dev(ctx, dev);
-    if (!d || !counts || (n && !d_samples) || nk < 1 || nk > B200_SELECT_MAX_K || shift < 0 || top <= shift ||
+    if (!d || !counts || (n && !d_samples) || ((uintptr_t)d_samples & 7) || nk < 1 || nk > B200_SELECT_MAX_K || shift < 0 ||
+        top <= shift ||
         top > 64 || top - shift > kRadixBits || (top < 64 && !prefix))
         return fail(B200_ERR_INVALID, "b200_radix_count");
     std::lock_guard<std::mutex> lk(d->mu);

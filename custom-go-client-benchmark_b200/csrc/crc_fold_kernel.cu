@@ -18,11 +18,13 @@
 // xor-reduced over the warp.
 //
 // Data movement.  A lane needs a CONTIGUOUS stream, which coalesced register loads cannot give; so the warp
-// stages it through shared memory with cp.async (LDGSTS, 16 B per lane, no registers): one instruction
-// moves four lanes' next 128 bytes fully coalesced (8 lanes x 16 B per row), eight instructions fill a
-// 32-row x 128-byte stage.  Rows are stored with a 128-byte XOR swizzle (chunk j of row l at chunk
-// j ^ (l & 7)) so both the copies and the per-lane 128-bit reads are bank-conflict free.  Three stages per
-// warp are in flight (commit/wait groups), 16 warps x 3 x 4 KB = 192 KB of shared memory.
+// stages it through shared memory with cp.async (LDGSTS, 16 B per lane, no registers).  In the shipped shape
+// <8 warps, 2 stages, 256 B per lane per stage> one instruction moves two lanes' next 256 bytes fully coalesced
+// (16 lanes x 16 B per row), sixteen instructions fill a 32-row x 256-byte stage (8 KB).  Rows are stored with
+// a 128-byte XOR swizzle (chunk j of row l at chunk j ^ (l & 7)), which keeps the per-lane 128-bit reads and
+// most of the copies off each other's banks (ncu: 5.9 % of the shared-memory wavefronts conflict).  Two stages
+// per warp are in flight (commit/wait groups): 8 warps x 2 x 8 KB + 4 KB of tables = 132 KB of shared memory.
+// The other shapes in kVariants (B200_FOLD_VARIANT) are kept for A/B runs; their measured rates are listed there.
 // (TMA bulk copies were tried first: UBLKCP takes uniform operands only, so per-lane copies serialise into a
 // 32-iteration loop per warp.)
 #include "crc_kernels.h"
@@ -109,7 +111,7 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
 
     const uint32_t rows_per_seg = kind == kSegLong ? plan.a : plan.b;  // this launch folds segments of this length
     const uint32_t lane_bytes = rows_per_seg * 16;   // S: bytes of the segment owned by one lane
-    const uint32_t nstage = lane_bytes / LANE_BYTES;  // rows_per_seg is a multiple of 16, so S is one of 256
+    const uint32_t nstage = lane_bytes / LANE_BYTES;  // exact: fold_enabled() admits only lengths with S % LANE_BYTES == 0
     // weight of this lane's register: the (31 - lane) lanes after it still have S bytes each to pass
     const uint32_t lane_k = gf2_xpow8((uint64_t)lane_bytes * (31 - lane), xsq);
     const uint32_t warp_stage = smem_u32(stage_base + (size_t)warp * STAGES * kWarpStageBytes);
@@ -237,6 +239,7 @@ const FoldVariant& fold_variant() {
 }  // namespace
 
 size_t fold_kernel_smem() { return fold_variant().smem(); }
+uint32_t fold_lane_bytes() { return (uint32_t)fold_variant().lane_bytes; }
 
 cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind) {
     const FoldVariant& fv = fold_variant();

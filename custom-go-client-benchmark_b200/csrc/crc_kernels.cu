@@ -83,7 +83,6 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
                 const uint32_t* __restrict__ col_k, const uint32_t* __restrict__ adv4_tab, uint32_t* __restrict__ seg_raw) {
     // skip_kinds: bit k set = segments of SegKind k are the fold kernel's, not ours
     // replicate the compact 4x256 table once per bank, at absolute shared address kTabAbs
-    const uint32_t smem_base = (uint32_t)__cvta_generic_to_shared(smem_raw);
     {
         uint32_t i = threadIdx.x;  // kRowsThreads == 4*256
         uint32_t t = i >> 8, v = i & 255;
@@ -93,7 +92,8 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
         for (int k = 0; k < 8; k++)
             asm volatile("st.shared.v4.u32 [%0], {%1,%1,%1,%1};" ::"r"(dst + 16 * k), "r"(val));
     }
-    if (smem_base > 1024) asm volatile("trap;");  // the dynamic window must cover [0x10000, 0x30000)
+    // (the dynamic window must cover [0x10000, 0x30000): it starts at most 1 KB up, which set-up has checked
+    // once per device with smem_base_probe — b200_init and the no-alloc entry point fail there otherwise)
     // the x^32 slicing tables for the segment epilogue live in the otherwise unused gap below the big tables
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(kAdv4Abs + threadIdx.x * 4), "r"(__ldg(adv4_tab + threadIdx.x)));
     __syncthreads();
@@ -358,13 +358,15 @@ __global__ void fill_latency_kernel(int64_t* __restrict__ dst, uint64_t first, s
 }  // namespace
 
 // dynamic shared memory: everything up to the end of the tables at absolute 0x10000 + 128 KB (the driver's
-// reserved 1 KB sits below the dynamic window; the kernel checks the window start at run time)
+// reserved 1 KB sits below the dynamic window; set-up checks the window start once per device)
 bool fold_enabled(uint32_t rows_per_seg) {
     static const bool disabled = [] {  // A/B switch, read once
         const char* e = getenv("B200_NO_FOLD");
         return e && *e && *e != '0';
     }();
-    return !disabled && rows_per_seg >= kFoldMinRows && rows_per_seg % 16 == 0;
+    // a lane owns rows_per_seg * 16 bytes of the segment and consumes them in whole stages
+    return !disabled && rows_per_seg >= kFoldMinRows && rows_per_seg % 16 == 0 &&
+           (rows_per_seg * 16u) % fold_lane_bytes() == 0;
 }
 
 size_t rows_kernel_smem() { return kTabAbs + kTabBytes; }

@@ -135,6 +135,7 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
                          cudaEvent_t ev_rows_begin, cudaEvent_t ev_rows_end, const SideStream* side = nullptr);
 
 size_t fold_kernel_smem();
+uint32_t fold_lane_bytes();  // bytes a lane consumes per stage in the variant in use; a lane's share of a segment must be a multiple
 // kind: kSegLong or kSegShort — which of the two full-segment lengths this launch folds
 cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind);
 

@@ -113,7 +113,7 @@ __device__ __noinline__ void slow_sample(long long v, const HistParams* __restri
 // Shared memory map of the histogram kernel, in ABSOLUTE shared addresses so that the hot loop addresses the
 // cell table and the counters as register + immediate (the compiler's own shared pointers carry a window base
 // it keeps recomputing under register pressure).  The driver's reserved 1 KB sits below the dynamic window;
-// the kernel checks the window start at run time.
+// lat_scratch_init checks the window start once per device (smem_base_probe).
 constexpr unsigned kSlowNAbs = 0x400;                                   // unsigned[kHistWarps]
 constexpr unsigned kSlowQAbs = 0x440;                                   // long long[kHistWarps][kSlowQueue]
 constexpr unsigned kFastAbs = kSlowQAbs + kHistWarps * kSlowQueue * 8;  // uint2 / uint4 [kFastCells]
@@ -137,8 +137,8 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     constexpr unsigned kCntAbs = kFast2Abs + (COLLECT ? kFastCells * 4 : 0);
     constexpr int kFastBias = (int)kFastAbs - kFastFirst * 8;   // cell address = bias + 8 * (bits >> 18)
     constexpr int kFast2Bias = (int)kFast2Abs - kFastFirst * 4;
+    // (set-up has checked once per device that the dynamic window starts at or below kSlowNAbs: smem_base_probe)
     const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
-    if (smem_base > kSlowNAbs) asm volatile("trap;");
     unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
     // Samples that need the generic path (>= 2^32 ns, negative, or a cell holding several thresholds) are rare
     // but would drag their whole warp through ~140 divergent instructions; they are parked in a per-warp queue
@@ -749,15 +749,20 @@ __global__ void smem_base_probe_kernel(unsigned long long* out) {
     *out = (unsigned long long)__cvta_generic_to_shared(probe_smem);
 }
 
+cudaError_t smem_base_probe(unsigned long long* d_tmp) {
+    unsigned long long base = ~0ull;
+    smem_base_probe_kernel<<<1, 1, 1024>>>(d_tmp);
+    const cudaError_t e = cudaMemcpy(&base, d_tmp, sizeof base, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) return e;
+    return base > 1024 ? cudaErrorInvalidConfiguration : cudaSuccess;  // see smem_base_probe_kernel
+}
+
 cudaError_t lat_scratch_init(LatScratch* s) {
     memset(s, 0, sizeof *s);
     cudaError_t e = cudaMalloc(&s->d_compact_n, sizeof(unsigned long long));
     if (e != cudaSuccess) return e;
-    unsigned long long base = ~0ull;
-    smem_base_probe_kernel<<<1, 1, 1024>>>(s->d_compact_n);
-    e = cudaMemcpy(&base, s->d_compact_n, sizeof base, cudaMemcpyDeviceToHost);
+    e = smem_base_probe(s->d_compact_n);
     if (e != cudaSuccess) return e;
-    if (base > 1024) return cudaErrorInvalidConfiguration;  // see smem_base_probe_kernel
     e = cudaMalloc(&s->d_params, sizeof(HistParams));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_counts, (kMaxThresholds + 1) * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_mom, sizeof(LatMoments));

@@ -91,6 +91,10 @@ struct LatScratch {
     size_t collect_cap;
 };
 
+// Where dynamic shared memory starts for a kernel without static shared memory.  The histogram and CRC row kernels
+// lay their tables out at ABSOLUTE shared addresses and need that to be at most 1 KB (the driver's reserved block);
+// cudaErrorInvalidConfiguration if it is not.  d_tmp: 8 bytes of device memory.  Asked once per device at set-up.
+cudaError_t smem_base_probe(unsigned long long* d_tmp);
 cudaError_t lat_scratch_init(LatScratch* s);
 void lat_scratch_free(LatScratch* s);
 

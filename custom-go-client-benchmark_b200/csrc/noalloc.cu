@@ -20,13 +20,18 @@
 //   * The first call on a given GPU also performs the one-time set-up for that GPU (it looks up the device
 //     address of the array and copies the constant tables into it).  Make that first call before you begin
 //     any stream capture.
-//   * Work is issued on the legacy default stream of the device and the call returns after the result has
-//     been copied back.
+//   * Work is issued on the legacy default stream of the device — a pageable-source cudaMemcpyAsync, the
+//     kernels, then a blocking cudaMemcpy of the result — and the call returns after the result has been
+//     copied back.  Legacy-stream work is not allowed while ANY thread of the process has a global-mode stream
+//     capture open, so no call at all (not only the first) may overlap such a capture: it would fail and
+//     invalidate the capture.
+//   * The calling thread's current device is put back to what it was before the call.
 #include <cstring>
 #include <mutex>
 
 #include "b200crc.h"
 #include "crc_kernels.h"
+#include "lat_kernels.h"
 
 using namespace b200;
 
@@ -62,6 +67,13 @@ int setup_device(int dev) {  // caller holds g_mu and has made `dev` current
         cudaGetLastError();
         return B200_ERR_CUDA;
     }
+    // the row kernel addresses its tables at absolute shared addresses: check once that this driver's dynamic
+    // shared-memory window starts where that layout assumes (8 bytes of the array serve as the probe's output)
+    e = smem_base_probe((unsigned long long*)(p + kOffNbad));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return B200_ERR_CUDA;
+    }
     uint32_t adv_row[1024], col_k[128], xsq[64], byte_tab[256], adv4[1024];
     host_build_adv_table(kRowBytes, adv_row);
     host_build_adv_table(4, adv4);
@@ -88,6 +100,14 @@ extern "C" int b200_crc32c_update_device_noalloc(int dev, uint32_t crc, const vo
     if (!out || (n && !dptr) || dev < 0 || dev >= kMaxDevices) return B200_ERR_INVALID;
     if (n > B200_NOALLOC_MAX_BYTES) return B200_ERR_TOO_LARGE;
     std::lock_guard<std::mutex> lk(g_mu);
+    struct RestoreDevice {  // leave the calling thread's current device as we found it
+        int prev = -1;
+        ~RestoreDevice() {
+            if (prev >= 0) cudaSetDevice(prev);
+            cudaGetLastError();
+        }
+    } restore;
+    if (cudaGetDevice(&restore.prev) != cudaSuccess) restore.prev = -1;
     if (cudaSetDevice(dev) != cudaSuccess) {
         cudaGetLastError();
         return B200_ERR_CUDA;

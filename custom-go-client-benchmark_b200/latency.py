@@ -78,6 +78,10 @@ def _signed(lo: int, hi: int) -> int:
 class _Reducer:
     """Sums small integer arrays over ranks.  No-op when not distributed."""
 
+    # how many collectives the reductions of this process issued and the wall-clock seconds spent in them
+    # (bench.py reports both beside the multi-rank timings)
+    tally = {"collectives": 0, "seconds": 0.0}
+
     def __init__(self, group=None, device=None):
         self.group, self.device = group, device
         try:
@@ -93,12 +97,18 @@ class _Reducer:
     def _run(self, arr: np.ndarray, op: str) -> np.ndarray:
         if not self.active:
             return arr
+        import time
+
         import torch
+        t0 = time.perf_counter()
         t = torch.from_numpy(arr.astype(np.int64, copy=True))
         if self.device is not None:
             t = t.to(self.device)
         self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op), group=self.group)
-        return t.cpu().numpy()
+        out = t.cpu().numpy()
+        _Reducer.tally["collectives"] += 1
+        _Reducer.tally["seconds"] += time.perf_counter() - t0
+        return out
 
     def sum_u64(self, arr: np.ndarray) -> np.ndarray:
         # split into 32-bit halves so the int64 all-reduce cannot overflow for < 2^31 ranks

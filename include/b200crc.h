@@ -81,7 +81,10 @@ int b200_crc32c_update_device(b200_ctx* ctx, int dev, uint32_t crc, const void* 
  *     keeps the previous call's contents; what must start at zero is cleared on every call.
  *   - The first call on a GPU also does that GPU's one-time set-up (resolves the array's device address,
  *     uploads the tables); make it before starting any stream capture.
- *   - Runs on the device's legacy default stream and returns once *out (host memory) holds the CRC. */
+ *   - Runs on the device's legacy default stream (a copy, the kernels, a blocking copy back) and returns once
+ *     *out (host memory) holds the CRC.  Because of that no call — not only the first — may be made while any
+ *     thread of the process has a global-mode stream capture open.
+ *   - The calling thread's current CUDA device is restored before returning. */
 #define B200_NOALLOC_MAX_BYTES (1ull << 35)
 int b200_crc32c_update_device_noalloc(int dev, uint32_t crc, const void* dptr, size_t n, uint32_t* out);
 

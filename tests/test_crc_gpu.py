@@ -398,58 +398,16 @@ def test_c_abi_argument_errors(ctx):
 
 
 def _ngpu():
-    import ctypes as C
-    n = C.c_int()
-    return n.value if pkg._lib.load().b200_device_count(C.byref(n)) == 0 else 0
+    import multidev_checks
+    return multidev_checks.ngpu()
 
 
-@pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs in one process")
+@pytest.mark.skipif(_ngpu() < 2, reason="needs two GPUs in one process (bench.py runs the same checks on multi-GPU boxes)")
 def test_sharded_object_over_two_devices_in_one_process():
-    """BASELINE config 3 in its one-process form: shards on different GPUs, host-side GF(2) fold."""
-    nd = min(_ngpu(), 4)
-    c = crc32c.Context(list(range(nd)))
-    total = (96 << 20) + 40
-    host = oracle.payload(total)
-    bounds = [total * i // nd // 8 * 8 for i in range(nd)] + [total]
-    ptrs, lens = [], []
-    for dev in range(nd):
-        a, b = bounds[dev], bounds[dev + 1]
-        p = c.alloc_device(b - a, dev)
-        c.h2d(p, host[a:b], dev)
-        ptrs.append(p)
-        lens.append(b - a)
-    assert crc32c.ShardedChecksum(ptrs, lens, c) == oracle.crc32c(host)
-    # the multi-device latency entry points on real distinct devices
-    import ctypes as C
-    lat = pkg.latency
-    n = 400_000
-    ns = oracle.latency_ns(n)
-    cuts = [n * i // nd for i in range(nd + 1)]
-    dptr = []
-    for dev in range(nd):
-        part = np.ascontiguousarray(ns[cuts[dev]:cuts[dev + 1]])
-        p = c.alloc_device(part.nbytes, dev)
-        c.h2d(p, part, dev)
-        dptr.append(p)
-    devs = (C.c_int * nd)(*range(nd))
-    pp = (C.c_void_p * nd)(*dptr)
-    sz = (C.c_size_t * nd)(*[cuts[i + 1] - cuts[i] for i in range(nd)])
-    counts = np.zeros(15, dtype=np.uint64)
-    st = pkg._lib.LatStats()
-    e = lat.README_EDGES
-    pkg._lib.check(c._L.b200_hist_fixed_multi(c._h, devs, pp, sz, nd, 1_000_000, e.ctypes.data, e.size, 0,
-                                              counts.ctypes.data, C.byref(st)))
-    ref, dropped = oracle.hist_numpy(oracle.ns_to_ms(ns).astype(np.float64))
-    assert list(counts) == list(ref) and st.count == n
-    ks = np.array([n // 5, n // 2, 9 * n // 10, 99 * n // 100], dtype=np.uint64)
-    out = np.zeros(4, dtype=np.int64)
-    pkg._lib.check(c._L.b200_select_kth_multi(c._h, devs, pp, sz, nd, 1000, ks.ctypes.data, 4, out.ctypes.data))
-    srt = np.sort(oracle.ns_to_us(ns))
-    assert list(out) == [int(srt[int(k)]) for k in ks]
-    for dev in range(nd):
-        c.free_device(ptrs[dev], dev)
-        c.free_device(dptr[dev], dev)
-    c.close()
+    """BASELINE config 3 in its one-process form (shards on different GPUs, host-side GF(2) fold) and the
+    multi-device latency entry points, on distinct devices: tests/multidev_checks.py."""
+    import multidev_checks
+    multidev_checks.multi_device_parity(min(_ngpu(), 4))
 
 
 def test_verify_objects_host_with_an_object_larger_than_a_slab(ctx):

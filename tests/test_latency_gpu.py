@@ -476,27 +476,51 @@ def test_golden_fixture(ctx):
     ctx.free_device(d)
 
 
-def test_large_sample_set_properties(ctx):
-    """1.25e8 samples (one GPU's share of BASELINE config 5), generated on the device.  Size-independent
-    checks: counts + dropped == n; each selected order statistic v_k satisfies
-    #(samples < v_k) <= k < #(samples <= v_k), counted by the histogram kernel with edges at v_k."""
+def test_large_sample_set_against_the_oracle(ctx):
+    """1.25e8 samples (one GPU's share of BASELINE config 5) on the library's DEFAULT route thresholds — far above
+    the 2^24 samples from which b200_select_kth takes the one-pass sampled route — against numpy.partition and
+    numpy's histogram rule on the oracle-generated samples."""
     n = 125_000_000
+    ns = oracle.latency_ns(n)
     d = ctx.alloc_device(n * 8)
     ctx.fill_latency_ns(d, n, oracle.SEED)
     h = lat.hist_readme(d, n, ctx=ctx)
-    assert int(h.counts.sum()) + h.dropped_below + h.dropped_above == n and h.count == n
+    ms = ns // 1_000_000
+    cnt = np.bincount(ms)
+    vals = np.nonzero(cnt)[0]
+    ref, _ = np.histogram(vals.astype(np.float64), lat.README_EDGES, weights=cnt[vals].astype(np.float64))
+    assert [int(x) for x in h.counts] == [int(x) for x in ref]
+    assert (h.dropped_below, h.dropped_above) == (int(cnt[:20].sum()), int(cnt[96:].sum()))
+    assert (h.count, h.min, h.max, h.sum) == (n, int(ms.min()), int(ms.max()), int(ms.sum()))
     oc = lat.hist_opencensus(d, n, ctx=ctx)
     assert int(oc.counts.sum()) == n
     ks = [n // 5, n // 2, 9 * n // 10, 99 * n // 100]
-    vs = lat.select_kth(d, n, lat.NS_PER_US, ks, ctx=ctx)
-    for k, v in zip(ks, vs):
-        c = lat.hist_fixed(d, n, lat.NS_PER_US, np.array([v, v + 1], dtype=np.float64), pkg._lib.HIST_OPENCENSUS,
-                           ctx=ctx).counts
-        less, equal = int(c[0]), int(c[1])
-        assert less <= k < less + equal, (k, v, less, equal)
-    # prefix cross-check against the oracle on the first 2e6 samples
-    m = 2_000_000
-    ref, dropped = oracle.hist_numpy(oracle.ns_to_ms(oracle.latency_ns(m)).astype(np.float64))
-    hp = lat.hist_readme(d, m, ctx=ctx)
-    assert list(hp.counts) == list(ref)
+    us = ns // 1000
+    del ns, ms
+    us_sum, us_min, us_max = int(us.sum()), int(us.min()), int(us.max())
+    us.partition(ks)
+    want = [int(us[k]) for k in ks]
+    assert lat.select_kth(d, n, lat.NS_PER_US, ks, ctx=ctx) == want
+    p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)
+    assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (us_sum // n, *want, us_min, us_max)
+    ctx.free_device(d)
+
+
+def test_default_routes_with_p99_beyond_32_bits(ctx):
+    """2^25 + 12345 samples on default thresholds, 3 % of them multi-second stalls (5 s .. 9 s): p99 lies beyond
+    2^32 ns, where the histogram pass leaves its 32-bit fast path.  Checked against numpy.partition."""
+    n = (1 << 25) + 12345
+    ns = oracle.latency_ns(n, seed=4242)
+    idx = np.arange(0, n, 33)
+    ns[idx] = 5_000_000_000 + (idx.astype(np.int64) * 7919) % 4_000_000_000
+    d = ctx.alloc_device(n * 8)
+    ctx.h2d(d, ns)
+    ks = [0, n // 5, n // 2, 9 * n // 10, 99 * n // 100, n - 1]
+    srt = np.partition(ns, ks)
+    assert int(srt[ks[4]]) > 1 << 32
+    assert lat.select_kth(d, n, 1, ks, ctx=ctx) == [int(srt[k]) for k in ks]
+    p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)
+    us = ns // 1000
+    assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (
+        int(us.sum()) // n, *[int(srt[k]) // 1000 for k in ks[1:5]], int(us.min()), int(us.max()))
     ctx.free_device(d)

@@ -1211,7 +1211,8 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
     CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
-    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32));
+    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, nullptr,
+                       P.qlut_ok != 0));
     unsigned long long c[kMaxThresholds + 1];
     LatMoments m;
     CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
@@ -1258,7 +1259,8 @@ int b200_hist_fixed_pair(b200_ctx* ctx, int dev, const int64_t* d_samples, size_
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
-        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, nullptr,
+                       P.qlut_ok != 0));
         CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
@@ -1756,7 +1758,7 @@ int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
-        CU(launch_hist((const long long*)d_samples, n, d->lat, true, d->stream, P.nthr + 1, P.mode32));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, true, d->stream, P.nthr + 1, P.mode32, nullptr, P.qlut_ok != 0));
         CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
     }

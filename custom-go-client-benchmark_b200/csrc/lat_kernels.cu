@@ -15,6 +15,8 @@
 #include "lat_kernels.h"
 
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 namespace b200 {
@@ -28,8 +30,8 @@ constexpr int kHistWarps = kHistThreads / 32;
 #endif
 constexpr int kHistCtasPerSm = B200_HIST_CTAS;  // 3 x 256 threads: 85 registers each, room for the prefetched tile
 constexpr int kRadixThreads = 512;
-constexpr int kTrashRows = 3;   // counter rows past the real bins: where parked samples' no-op updates land
-constexpr int kSlowQueue = 128;  // parked samples per warp; overflow falls back to the divergent path
+constexpr int kTrashRows = 2;   // counter rows past the real bins: the EVEN one of them is where the updates of
+                                // parked samples land (odd rows are the ones a collecting kernel keeps)
 
 struct U128 {
     unsigned long long lo, hi;
@@ -40,35 +42,6 @@ __device__ __forceinline__ void add128(U128& a, unsigned long long lo, unsigned 
     a.lo = s;
 }
 
-__device__ __forceinline__ unsigned long long udiv_magic(unsigned long long a, const HistParams& P) {
-    if (P.magic == 0) return a >> P.magic_shift;  // power of two divisor
-    unsigned long long t = __umul64hi(a, P.magic);
-    if (P.magic_add) t = ((a - t) >> 1) + t;
-    return t >> P.magic_shift;
-}
-
-__device__ __forceinline__ int classify(long long n, const long long* __restrict__ thr, int nthr,
-                                        const unsigned short* __restrict__ lut) {
-    int c;
-    if (n >= 0) {
-        unsigned long long u = (unsigned long long)n;
-        int idx;
-        if (u < 32) idx = (int)u;
-        else {
-            int e = 63 - __clzll((long long)u);
-            idx = (e - 4) * 32 + (int)((u >> (e - 5)) & 31);
-        }
-        unsigned cell = lut[idx];
-        c = cell >> 8;
-        int extra = cell & 0xFF;
-        int c0 = c;
-        for (int k = 0; k < extra; k++) c += (n >= thr[c0 + k]);
-    } else {
-        c = 0;
-        for (int j = 0; j < nthr; j++) c += (n >= thr[j]);
-    }
-    return c;
-}
 
 // Per-thread running moments.  Fast path values fit 32 bits, so their squares fit 64.
 struct SlowMoments {                                       // of generic-path samples: exact 128-bit
@@ -81,12 +54,32 @@ struct Moments {
     unsigned fsq_carry = 0;                                //   and q*q wraps at most once per add
 };
 
-// Generic path: any int64 sample.  Thresholds, LUT and the 64-bit magic are read from global memory and the
-// moments live in local memory: this runs for a handful of samples per million, and keeping it out of line
-// keeps the fast loop's registers and instruction cache to itself.
-__device__ __noinline__ void slow_sample(long long v, const HistParams* __restrict__ Pg, unsigned* mine,
+// What the generic path needs, copied to shared memory at kernel start: it runs with one or two lanes of a warp
+// active while the others wait, so its latency counts — a chain of dependent global loads (a microsecond each
+// under load) per sample made the whole kernel 7x slower; from shared memory the same chain is ~300 cycles.
+struct SlowParams {
+    long long thr[kMaxThresholds];
+    unsigned long long magic;
+    int nthr, magic_shift, magic_add, pad;
+};
+
+__device__ __forceinline__ unsigned long long udiv_magic(unsigned long long a, const SlowParams& P) {
+    if (P.magic == 0) return a >> P.magic_shift;  // power of two divisor
+    unsigned long long t = __umul64hi(a, P.magic);
+    if (P.magic_add) t = ((a - t) >> 1) + t;
+    return t >> P.magic_shift;
+}
+
+// Generic path: any int64 sample.  Out of line, so that the fast loop keeps its registers and instruction cache.
+// s == nullptr: count (and collect) only, no moments.
+__device__ __noinline__ void slow_sample(long long v, const SlowParams* __restrict__ P, unsigned* mine,
                                          SlowMoments* s, const HistCollect* col) {
-    const int c = classify(v, Pg->thr, Pg->nthr, Pg->lut);
+    int lo = 0, hi = P->nthr;  // c = #{j : thr[j] <= v}: thr[j] <= v for j < lo, thr[j] > v for j >= hi
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (P->thr[mid] <= v) lo = mid + 1; else hi = mid;
+    }
+    const int c = lo;
     mine[c * 32]++;
     if (col) {  // odd bins are kept; one global atomic for all the lanes that are here together
         const bool hit = c & 1;
@@ -103,33 +96,372 @@ __device__ __noinline__ void slow_sample(long long v, const HistParams* __restri
         s->mn = v < s->mn ? v : s->mn;
         s->mx = v > s->mx ? v : s->mx;
         const unsigned long long a = v < 0 ? 0ull - (unsigned long long)v : (unsigned long long)v;
-        const unsigned long long q = udiv_magic(a, *Pg);
+        const unsigned long long q = udiv_magic(a, *P);
         add128(s->sq, q * q, __umul64hi(q, q));
         if (v < 0) add128(s->sum, 0ull - q, q ? ~0ull : 0ull);
         else add128(s->sum, q, 0);
     }
 }
 
-// Shared memory map of the histogram kernel, in ABSOLUTE shared addresses so that the hot loop addresses the
+// every thread of the CTA: copy the generic path's parameters; the caller synchronises afterwards
+__device__ __forceinline__ void load_slow_params(SlowParams* sp, const HistParams* __restrict__ Pg) {
+    for (int i = threadIdx.x; i < kMaxThresholds; i += kHistThreads) sp->thr[i] = Pg->thr[i];
+    if (threadIdx.x == 0) {
+        sp->magic = Pg->magic;
+        sp->nthr = Pg->nthr;
+        sp->magic_shift = Pg->magic_shift;
+        sp->magic_add = Pg->magic_add;
+    }
+}
+
+// Shared memory map of the histogram kernels, in ABSOLUTE shared addresses so that the hot loop addresses the
 // cell table and the counters as register + immediate (the compiler's own shared pointers carry a window base
 // it keeps recomputing under register pressure).  The driver's reserved 1 KB sits below the dynamic window;
 // lat_scratch_init checks the window start once per device (smem_base_probe).
-constexpr unsigned kSlowNAbs = 0x400;                                   // unsigned[kHistWarps]
-constexpr unsigned kSlowQAbs = 0x440;                                   // long long[kHistWarps][kSlowQueue]
-constexpr unsigned kFastAbs = kSlowQAbs + kHistWarps * kSlowQueue * 8;  // uint2 / uint4 [kFastCells]
+constexpr unsigned kSlowAbs = 0x400;                                    // SlowParams
+constexpr int kParkCap = 128;                                           // parked samples per warp
+constexpr int kParkDrain = 64;                                           // drain from this many on
+constexpr unsigned kParkNAbs = kSlowAbs + 640;                          // unsigned[kHistWarps]
+constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long long[kHistWarps][kParkCap]
+constexpr unsigned kFastAbs = kParkQAbs + kHistWarps * kParkCap * 8;    // uint2 [kFastCells] (+ unsigned[kFastCells])
 // then unsigned[kHistWarps][rows][32] counters, then (collecting kernels) long long[kLaneQueue][kHistThreads]
 constexpr int kLaneQueue = 16;                                          // collected samples a lane can hold
 constexpr unsigned kLaneQueueStride = kHistThreads * 8;                 // bytes between a lane's slots
+constexpr unsigned kQLutAbs = kFastAbs;                                 // quotient kernel: unsigned char[kQLutSize]
+static_assert(sizeof(SlowParams) <= 640, "SlowParams slot");
+constexpr unsigned kQCntAbs = kQLutAbs + kQLutSize;                     //   then its counters
 
 extern __shared__ __align__(1024) unsigned char hist_smem_raw[];
 
+// ---- tile loop: a ring of tiles in shared memory, filled by 1-D bulk copies (TMA) ---------------------------
+// A CTA's tiles are contiguous 16 KB pieces of the sample array, so the operands of a bulk copy are uniform and
+// one thread can issue it.  Bandwidth here is (bytes in flight) / (loaded HBM latency, ~1.4 us): with the next
+// tile prefetched into registers a thread has 64 bytes in flight, 48 KB per SM, which is where the register
+// version stopped (4.85 TB/s; ncu: warps waiting on their loads, DRAM 54 %, issue 42 %).  The ring has nstages
+// tiles per CTA in flight and costs no registers: every round the threads copy their samples of the current
+// stage into registers, the LAST warp to have done so (a shared-memory counter per stage says who) re-arms the
+// stage's barrier and issues the copy of the tile nstages rounds on, and only then are the samples counted.
+// (An L2 bulk prefetch running ahead of register loads was measured too: slower than no prefetch at all.)
+constexpr int kTileBytes = 4 * kHistThreads * 16;  // 16 KB: four 128-bit pairs per thread
+constexpr int kMaxStages = 4;
+constexpr int kRingHeader = 128;                   // full barriers (8 B each), then the per-stage counters (4 B each)
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@!p bra WAIT_%=;\n\t}"
+        ::"r"(bar), "r"(parity) : "memory");
+}
+// this GPU's own memory only: a plain (non-multicast) bulk copy global -> this CTA's shared memory
+__device__ __forceinline__ void bulk_load(unsigned dst, const void* src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+__device__ __forceinline__ longlong2 lds_pair(unsigned addr) {
+    longlong2 v;
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+
+// Walks x[0, n): whole tiles of 4 x kHistThreads 128-bit pairs go to eight(a, b, c, d) — tile t belongs to CTA
+// t mod gridDim.x — everything else (unaligned head, remainder, odd tail) goes to one(v).  after_tile() runs once
+// per tile with the whole warp converged.  ring_abs: absolute shared address (128-byte aligned) of kRingHeader
+// bytes followed by nstages tile buffers.  Every thread of the CTA must call this (it synchronises the CTA once).
+template <typename Eight, typename One, typename AfterTile>
+__device__ __forceinline__ void for_each_sample(const long long* __restrict__ x, size_t n, unsigned ring_abs,
+                                                int nstages, Eight eight, One one, AfterTile after_tile) {
+    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
+    if (head > n) head = n;
+    const size_t tid = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
+    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
+    if (tid == 0 && head) one(x[0]);
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    constexpr size_t kTilePairs = 4 * kHistThreads;
+    const size_t ntiles = npairs / kTilePairs;
+    const unsigned mine = (size_t)blockIdx.x < ntiles ? (unsigned)((ntiles - 1 - blockIdx.x) / gridDim.x) + 1 : 0;
+    const unsigned full0 = ring_abs, cnt0 = ring_abs + 8 * kMaxStages, buf0 = ring_abs + kRingHeader;
+    const int lane = threadIdx.x & 31;
+    const unsigned char* const tile0 = reinterpret_cast<const unsigned char*>(x2) + (size_t)blockIdx.x * kTileBytes;
+    const size_t tile_step = (size_t)gridDim.x * kTileBytes;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < nstages; s++) {
+            mbar_init(full0 + 8 * s, 1);
+            asm volatile("st.shared.u32 [%0], %1;" ::"r"(cnt0 + 4 * s), "r"(0u) : "memory");
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (unsigned j = 0; j < (unsigned)nstages && j < mine; j++) {
+            mbar_expect_tx(full0 + 8 * j, kTileBytes);
+            bulk_load(buf0 + j * kTileBytes, tile0 + (size_t)j * tile_step, kTileBytes, full0 + 8 * j);
+        }
+    }
+    __syncthreads();
+    unsigned s = 0, ph = 0;  // tile j sits in stage j mod nstages, in that stage's (j div nstages)-th use
+    for (unsigned j = 0; j < mine; j++) {
+        mbar_wait(full0 + 8 * s, ph);
+        const unsigned at = buf0 + s * kTileBytes + threadIdx.x * 16;
+        const longlong2 a = lds_pair(at), b = lds_pair(at + 4096), c = lds_pair(at + 8192), d = lds_pair(at + 12288);
+        __syncwarp();
+        if (lane == 0) {
+            // the operands tie this atomic to the four loads above: it is issued once their data has arrived, so
+            // when the last warp's count shows up every thread of the CTA has its samples out of the stage
+            unsigned seen;
+            asm volatile("atom.shared.add.u32 %0, [%1], %2;"
+                         : "=r"(seen) : "r"(cnt0 + 4 * s), "r"(1u), "l"(a.x), "l"(b.x), "l"(c.x), "l"(d.x) : "memory");
+            if (seen == kHistWarps - 1) {
+                asm volatile("st.shared.u32 [%0], %1;" ::"r"(cnt0 + 4 * s), "r"(0u) : "memory");
+                if (j + nstages < mine) {
+                    mbar_expect_tx(full0 + 8 * s, kTileBytes);
+                    bulk_load(buf0 + s * kTileBytes, tile0 + (size_t)(j + nstages) * tile_step, kTileBytes, full0 + 8 * s);
+                }
+            }
+        }
+        if (++s == (unsigned)nstages) { s = 0; ph ^= 1; }
+        eight(a, b, c, d);
+        after_tile();
+    }
+    for (size_t i = ntiles * kTilePairs + tid; i < npairs; i += nthreads) {
+        const longlong2 a = __ldg(x2 + i);
+        one(a.x); one(a.y);
+    }
+    if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
+}
+
+// End of a histogram kernel: the CTA's private counters -> one 64-bit atomic per bin; the threads' moments -> the
+// device totals.  tbl: [kHistWarps][rows][32] counters.
+template <bool MOMENTS>
+__device__ __forceinline__ void hist_epilogue(const unsigned* tbl, int rows, int nbins, size_t n,
+                                              unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom,
+                                              long long mn, long long mx, U128 sum, U128 sq) {
+    const int lane = threadIdx.x & 31;
+    __syncthreads();
+    for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
+        unsigned long long t = 0;
+        for (int w = 0; w < kHistWarps; w++)
+            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * rows + b) * 32 + ((l + b) & 31)];
+        if (t) atomicAdd(counts + b, t);
+    }
+    if (MOMENTS) {
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
+            mn = omn < mn ? omn : mn;
+            mx = omx > mx ? omx : mx;
+            unsigned long long l1 = __shfl_xor_sync(0xFFFFFFFFu, sum.lo, d), h1 = __shfl_xor_sync(0xFFFFFFFFu, sum.hi, d);
+            add128(sum, l1, h1);
+            unsigned long long l2 = __shfl_xor_sync(0xFFFFFFFFu, sq.lo, d), h2 = __shfl_xor_sync(0xFFFFFFFFu, sq.hi, d);
+            add128(sq, l2, h2);
+        }
+        if (lane == 0) {
+            if (mn <= mx) {
+                atomicMin(&mom->min_ns, mn);
+                atomicMax(&mom->max_ns, mx);
+            }
+            unsigned long long old = atomicAdd(&mom->sum_lo, sum.lo);
+            unsigned long long carry = (old + sum.lo) < old;
+            atomicAdd(reinterpret_cast<unsigned long long*>(&mom->sum_hi), sum.hi + carry);
+            old = atomicAdd(&mom->sumsq_lo, sq.lo);
+            carry = (old + sq.lo) < old;
+            atomicAdd(&mom->sumsq_hi, sq.hi + carry);
+        }
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&mom->count, (unsigned long long)n);
+    }
+}
+
+// Samples that need the generic path — negative or >= 2^32 ns (a multi-second stall: about one in 200 of a
+// realistic run, so three warp rounds in four meet one somewhere, yet only one thread in 25 does), or in a cell
+// with more thresholds than the kernel compares with — are parked in their warp's queue and worked off 32 lanes
+// at a time; in the common code their place is taken by a SURROGATE the fast path can digest, whose effect is
+// taken out again at the end of the kernel (see the kernels).  What was measured on the way here: masks around
+// every fast-path update cost ~4.5 instructions per sample; doing the generic work where it is met, one or two
+// lanes active, made the kernel 7x slower; parking the whole group of eight kept the warps of a CTA out of step.
+// Returns false when the queue is full: the caller then takes the generic path on the spot.
+__device__ __forceinline__ bool park1(unsigned char* sm0, int warp, long long v) {
+    unsigned* const n = reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp;
+    const unsigned at = atomicAdd(n, 1u);
+    if (at >= (unsigned)kParkCap) return false;
+    reinterpret_cast<long long*>(sm0 + kParkQAbs)[(size_t)warp * kParkCap + at] = v;
+    return true;
+}
+// whole warp, converged: hand the parked samples to slow(v), 32 at a time
+template <typename Slow>
+__device__ __forceinline__ void drain_parked(unsigned char* sm0, int warp, int lane, Slow slow) {
+    unsigned* const n = reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp;
+    const long long* q = reinterpret_cast<const long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkCap;
+    __syncwarp();
+    const unsigned cnt = min(*n, (unsigned)kParkCap);
+    for (unsigned k = lane; k < cnt; k += 32) slow(q[k]);
+    __syncwarp();
+    if (lane == 0) *n = 0;
+    __syncwarp();
+}
+// after a tile round, warp converged: drain when the queue is filling up (every lane reads the same counter)
+template <typename Slow>
+__device__ __forceinline__ void maybe_drain(unsigned char* sm0, int warp, int lane, Slow slow) {
+    __syncwarp();
+    if (*(reinterpret_cast<const unsigned*>(sm0 + kParkNAbs) + warp) >= (unsigned)kParkDrain)
+        drain_parked(sm0, warp, lane, slow);
+}
+
+// the two halves of a sample, split where the compiler cannot merge the halves' arithmetic back into 64-bit
+// operations (an OR of eight high words must not become eight 64-bit ORs)
+__device__ __forceinline__ void split64(long long v, unsigned& lo, unsigned& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+}
+
+// the lane's private counter at absolute shared address `addr` += 1
+__device__ __forceinline__ void bump_abs(unsigned addr) {
+#ifdef B200_HIST_RED
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(1u) : "memory");
+    return;
+#endif
+    unsigned c;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
+    c += 1u;
+    asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+}
+
+// ---- quotient kernel ------------------------------------------------------------------------------------
+// When every threshold is a multiple of the divisor (edges given in the divisor's unit: the README bins and the
+// OpenCensus bounds in milliseconds) and the quotients of 32-bit samples are few (divisor >= 2^19), the bin is a
+// function of q = trunc(ns / divisor), which the moments need anyway: one byte-table look-up indexed by q
+// replaces the float-exponent cell, its compare and the masks.  Per sample: 3 instructions for q, 1 look-up,
+// 1 address, 3 for the counter, ~3 for the moments.  Samples outside 0 <= ns < 2^32 take slow_sample().
+template <bool MOMENTS>
+__global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
+hist_qlut_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
+                 unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, int nstages) {
+    const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
+    unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
+    unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kQCntAbs);  // [warp][bin][lane] private counters
+    SlowParams* const sp = reinterpret_cast<SlowParams*>(sm0 + kSlowAbs);
+    load_slow_params(sp, Pg);
+    if (threadIdx.x < kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
+    for (int i = threadIdx.x; i < kQLutSize / 4; i += kHistThreads)
+        reinterpret_cast<unsigned*>(sm0 + kQLutAbs)[i] = reinterpret_cast<const unsigned*>(Pg->qlut)[i];
+    const int nbins = Pg->nthr + 1, rows = nbins;
+    for (int i = threadIdx.x; i < kHistWarps * rows * 32; i += kHistThreads) tbl[i] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned* const mine = tbl + (size_t)warp * rows * 32 + lane;
+    const unsigned mine_abs = kQCntAbs + (unsigned)(warp * rows * 32 + lane) * 4u;
+    const unsigned magic32 = Pg->magic32;
+    const int shift32 = Pg->shift32, pre32 = Pg->pre32;
+    // q <= 8191: a thread's whole share of quotients sums in 32 bits (the launcher bounds n), eight squares too
+    unsigned mn32 = 0xFFFFFFFFu, mx32 = 0, fsum = 0;
+    unsigned long long fsq = 0;
+    SlowMoments sm_slow;
+    auto quotient = [&](unsigned u) -> unsigned { return __umulhi(u >> pre32, magic32) >> shift32; };
+    // (the table is read-only while the kernel counts: a plain asm, so that the eight look-ups of a round are
+    // issued together instead of each waiting for the previous sample's counter update)
+    auto bin_of = [&](unsigned q) -> unsigned {
+        unsigned b;
+        asm("ld.shared.u8 %0, [%1+%2];" : "=r"(b) : "r"(q), "n"(kQLutAbs));
+        return b;
+    };
+    auto bump_q = [&](unsigned q) { bump_abs(mine_abs + (bin_of(q) << 7)); };
+    // A sample outside 0 <= ns < 2^32 is parked; in the common code it is replaced by its clamp to that range (0
+    // or 2^32 - 1).  Such a surrogate lands in a known bin (nlo / nhi count how many this thread made; the bins are
+    // corrected at the end) and adds a known quotient to the sums (0, or qmax: subtracted at the end).  It cannot
+    // spoil the extremes either: a 0 can lower the minimum only when a negative sample exists, which is lower
+    // still, and 2^32 - 1 can raise the maximum only when a sample >= 2^32 exists; a thread that saw nothing but
+    // surrogates leaves its fast-path extremes out.
+    unsigned nlo = 0, nhi = 0, nproc = 0;
+    auto slow = [&](long long v) { slow_sample(v, sp, mine, MOMENTS ? &sm_slow : nullptr, nullptr); };
+    auto one = [&](long long v) {
+        if ((unsigned long long)v >> 32) {  // negative or >= 2^32 ns
+            slow(v);
+            return;
+        }
+        const unsigned u = (unsigned)v, q = quotient(u);
+        bump_q(q);
+        nproc++;
+        if (MOMENTS) {
+            mn32 = min(mn32, u);
+            mx32 = max(mx32, u);
+            fsum += q;
+            fsq += (unsigned long long)q * q;
+        }
+    };
+    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
+        const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+        unsigned u[8], hi[8], any = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            split64(v[k], u[k], hi[k]);
+            any |= hi[k];
+        }
+        if (any) {  // rare: a few lanes of three rounds in four
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                if (hi[k]) {
+                    if (!park1(sm0, warp, v[k])) slow(v[k]);
+                    const bool neg = (int)hi[k] < 0;
+                    u[k] = neg ? 0u : 0xFFFFFFFFu;
+                    nlo += neg;
+                    nhi += !neg;
+                }
+        }
+        nproc += 8;
+        unsigned q[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) q[k] = quotient(u[k]);
+        unsigned bin[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) bin[k] = bin_of(q[k]);
+#pragma unroll
+        for (int k = 0; k < 8; k++) bump_abs(mine_abs + (bin[k] << 7));
+        if (MOMENTS) {
+            unsigned s = 0, sq = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k += 2) {
+                mn32 = min(min(mn32, u[k]), u[k + 1]);
+                mx32 = max(max(mx32, u[k]), u[k + 1]);
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) {
+                s += q[k];
+                sq += q[k] * q[k];
+            }
+            fsum += s;
+            fsq += sq;
+        }
+    };
+    const unsigned ring_abs = (kQCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + 127u) & ~127u;
+    for_each_sample(x, n, ring_abs, nstages, eight, one, [&] { maybe_drain(sm0, warp, lane, slow); });
+    drain_parked(sm0, warp, lane, slow);
+
+    // take the surrogates out again: their bins, their quotients
+    const unsigned qhi = quotient(0xFFFFFFFFu);
+    mine[bin_of(0u) * 32] -= nlo;
+    mine[bin_of(qhi) * 32] -= nhi;
+    long long mn = sm_slow.mn, mx = sm_slow.mx;
+    if (nproc > nlo + nhi) {  // this thread saw genuine fast-path samples
+        mn = (long long)mn32 < mn ? (long long)mn32 : mn;
+        mx = (long long)mx32 > mx ? (long long)mx32 : mx;
+    }
+    U128 sum = sm_slow.sum, sq = sm_slow.sq;
+    add128(sum, (unsigned long long)fsum - (unsigned long long)nhi * qhi, 0);
+    add128(sq, fsq - (unsigned long long)nhi * qhi * qhi, 0);
+    hist_epilogue<MOMENTS>(tbl, rows, nbins, n, counts, mom, mn, mx, sum, sq);
+}
+
+// ---- cell kernel (any thresholds) ---------------------------------------------------------------------------
 // DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic with
 // the add fix-up, 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28.
 // COLLECT: cells may hold two thresholds and the samples of odd bins are appended to col.buf.
 template <bool MOMENTS, int DIVMODE, bool COLLECT>
 __global__ void __launch_bounds__(kHistThreads, (MOMENTS && COLLECT) ? kHistCtasPerSm - 1 : kHistCtasPerSm)
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
-            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, const HistCollect col) {
+            unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, const HistCollect col, int nstages) {
     // cell entries are 8 bytes; collecting kernels keep the cells' second compare values in a table of their own,
     // read (under a predicate) only by the lanes whose cell has one: 16-byte entries cost twice the shared-memory
     // wavefronts on every look-up and made the pass LSU-bound
@@ -137,16 +469,13 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     constexpr unsigned kCntAbs = kFast2Abs + (COLLECT ? kFastCells * 4 : 0);
     constexpr int kFastBias = (int)kFastAbs - kFastFirst * 8;   // cell address = bias + 8 * (bits >> 18)
     constexpr int kFast2Bias = (int)kFast2Abs - kFastFirst * 4;
-    // (set-up has checked once per device that the dynamic window starts at or below kSlowNAbs: smem_base_probe)
+    // (set-up has checked once per device that the dynamic window starts at or below kFastAbs: smem_base_probe)
     const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
     unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
-    // Samples that need the generic path (>= 2^32 ns, negative, or a cell holding several thresholds) are rare
-    // but would drag their whole warp through ~140 divergent instructions; they are parked in a per-warp queue
-    // and processed 32 at a time instead.
-    unsigned* const slow_n = reinterpret_cast<unsigned*>(sm0 + kSlowNAbs);
-    long long* const slow_q = reinterpret_cast<long long*>(sm0 + kSlowQAbs);
     unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kCntAbs);  // [warp][row][lane] private counters
-    if (threadIdx.x < kHistWarps) slow_n[threadIdx.x] = 0;
+    SlowParams* const sp = reinterpret_cast<SlowParams*>(sm0 + kSlowAbs);
+    load_slow_params(sp, Pg);
+    if (threadIdx.x < kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < kFastCells; i += kHistThreads) {
         const uint4 c = Pg->fast[i];
         // bit 3 of a collecting kernel's entry: the cell has a second compare value
@@ -169,25 +498,17 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     unsigned q_addr = q_base;
 
     SlowMoments sm_slow;
-    auto slow = [&](long long v) { slow_sample(v, Pg, mine, MOMENTS ? &sm_slow : nullptr, COLLECT ? &col : nullptr); };
-    auto park = [&](long long v) {
-        const unsigned at = atomicAdd(&slow_n[warp], 1u);
-        if (at < kSlowQueue) slow_q[warp * kSlowQueue + at] = v;
-        else slow(v);  // queue full: take the hit now
-    };
-    auto drain = [&]() {
-        __syncwarp();
-        const unsigned cnt = min(slow_n[warp], (unsigned)kSlowQueue);
-        for (unsigned k = lane; k < cnt; k += 32) slow(slow_q[warp * kSlowQueue + k]);
-        __syncwarp();
-        if (lane == 0) slow_n[warp] = 0;
-        __syncwarp();
+    // Generic path (slow_sample, 32 parked samples at a time): samples >= 2^32 ns or negative, and samples in a
+    // cell holding more thresholds than the kernel compares with.  The latter are ordinary for the moments — the
+    // fast path keeps those — and only their bin comes from the generic path (count_only).
+    auto slow = [&](long long v) {
+        const bool count_only = ((unsigned long long)v >> 32) == 0;
+        slow_sample(v, sp, mine, MOMENTS && !count_only ? &sm_slow : nullptr, COLLECT ? &col : nullptr);
     };
     // Fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), 32-bit arithmetic only.  lookup() fetches the sample's
-    // cell and says whether the sample has to be parked; bump() adds to one of the lane's private counters.
-    // (w.z is the cell's second compare value, used by collecting kernels only)
-    auto lookup = [&](long long v, uint4& w) -> unsigned {
-        const unsigned u = (unsigned)v, hi = (unsigned)((unsigned long long)v >> 32);
+    // cell (w.z is the cell's second compare value, used by collecting kernels only); bit 2 of w.y says the cell
+    // holds more thresholds than we compare with (its counter offset then points at a scratch row).
+    auto lookup = [&](unsigned u, uint4& w) {
         const unsigned bits = __float_as_uint(__uint2float_rz(u | 1u));
         const unsigned idx = (bits >> 15) & 0x3FFF8u;
         asm("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(w.x), "=r"(w.y) : "r"(idx), "n"(kFastBias));
@@ -195,19 +516,13 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\tmov.u32 %0, 0xFFFFFFFF;\n\t"
                 "@p ld.shared.u32 %0, [%1+%3];\n\t}"
                 : "=r"(w.z) : "r"(idx >> 1), "r"(w.y & 8u), "n"(kFast2Bias));
-            w.y &= ~8u;
         }
-        return hi | (w.y & 4u);  // >= 2^32 / negative, or more thresholds in the cell than we compare with
     };
     // returns the byte offset of the counter row: bit 7 = the sample's bin is odd
-    auto bump = [&](unsigned u, const uint4 w, unsigned inc) -> unsigned {
-        unsigned off = w.y + (u > w.x ? 128u : 0u);
+    auto bump = [&](unsigned u, const uint4 w) -> unsigned {
+        unsigned off = (COLLECT ? (w.y & ~8u) : w.y) + (u > w.x ? 128u : 0u);  // (flagged cells never get here)
         if (COLLECT) off += u > w.z ? 128u : 0u;
-        const unsigned addr = mine_abs + off;
-        unsigned c;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(c) : "r"(addr) : "memory");
-        c += inc;
-        asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
+        bump_abs(mine_abs + off);
         return off;
     };
     // keep the sample if `in` (0 or 128) is set: the slot is written under a predicate, the cursor moves by in * 16
@@ -250,44 +565,66 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         m.fsq_carry += sq < m.fsq;
         m.fsq = sq;
     };
+    // In the common code a parked sample is replaced by a surrogate: its clamp to [0, 2^32) when it lies outside
+    // (nlo / nhi count these: the quotient of 2^32 - 1 is taken out of the sums at the end; the extremes cannot be
+    // spoiled, see hist_qlut_kernel), itself when only its cell is the problem; either way its counter update is
+    // pointed at a scratch row, which is even and so never collected.
+    unsigned nlo = 0, nhi = 0, nproc = 0;
+    const unsigned scratch_row = (unsigned)((nbins + 1) & ~1) * 128u;  // even, past the last bin
     auto one = [&](long long v) {
-        uint4 w;
-        if (lookup(v, w)) { park(v); return; }
+        if ((unsigned long long)v >> 32) { slow(v); return; }
         const unsigned u = (unsigned)v;
-        const unsigned off = bump(u, w, 1u);
+        uint4 w;
+        lookup(u, w);
+        if (w.y & 4u) {
+            slow(v);  // count only
+            w = make_uint4(0xFFFFFFFFu, scratch_row, 0xFFFFFFFFu, 0);
+        }
+        const unsigned off = bump(u, w);
         if (COLLECT) collect(v, off & 128u);
+        nproc++;
         if (MOMENTS) {
             m.mn32 = min(m.mn32, u);
             m.mx32 = max(m.mx32, u);
             accumulate(quotient(u));
         }
     };
-    // Eight samples at a time, without a branch in the common work: a sample that has to be parked still walks
-    // through the counting code, but adds 0 to its counter and contributes the neutral element to every moment
-    // (its mask `keep` is 0).  Roughly one sample in 200 of a realistic run is such a sample (a multi-second
-    // stall), i.e. three warp iterations in four hold at least one, so a branch around the common work would
-    // be divergent most of the time.  Only the parking itself is conditional.
+    // Eight samples at a time.  Whether any of them needs the generic path is ONE test (the OR of the high words
+    // and of the cells' flag bits); the common work carries no masks.
     auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
         const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
         uint4 w[8];
-        unsigned keep[8], any = 0;
+        unsigned u[8], hi[8], any_hi = 0, any_y = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const unsigned rare = lookup(v[k], w[k]);
-            any |= rare;
-            keep[k] = rare ? 0u : 0xFFFFFFFFu;
+            split64(v[k], u[k], hi[k]);
+            lookup(u[k], w[k]);
+            any_hi |= hi[k];
+            any_y |= w[k].y;
         }
+        if (any_hi | (any_y & 4u)) {  // rare: a few lanes of three rounds in four
+#pragma unroll
+            for (int k = 0; k < 8; k++)
+                if (hi[k] | (w[k].y & 4u)) {
+                    if (!park1(sm0, warp, v[k])) slow(v[k]);
+                    if (hi[k]) {
+                        const bool neg = (int)hi[k] < 0;
+                        u[k] = neg ? 0u : 0xFFFFFFFFu;
+                        nlo += neg;
+                        nhi += !neg;
+                    }
+                    w[k] = make_uint4(0xFFFFFFFFu, scratch_row, 0xFFFFFFFFu, 0);
+                }
+        }
+        nproc += 8;
         unsigned s = 0;
         unsigned long long sq = 0;
 #pragma unroll
         for (int k = 0; k < 8; k++) {
-            const unsigned u = (unsigned)v[k];
-            const unsigned off = bump(u, w[k], keep[k] & 1u);
-            if (COLLECT) collect(v[k], off & keep[k] & 128u);
+            const unsigned off = bump(u[k], w[k]);
+            if (COLLECT) collect(v[k], off & 128u);
             if (MOMENTS) {
-                m.mn32 = min(m.mn32, u | ~keep[k]);
-                m.mx32 = max(m.mx32, u & keep[k]);
-                const unsigned q = quotient(u) & keep[k];
+                const unsigned q = quotient(u[k]);
                 if (DIVMODE == 3) {  // quotients < 2^28: eight of them fit 32 bits, eight squares fit 64
                     s += q;
                     sq += (unsigned long long)q * q;
@@ -296,99 +633,51 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
                 }
             }
         }
-        if (MOMENTS && DIVMODE == 3) {
-            m.fsum += s;
-            sq += m.fsq;
-            m.fsq_carry += sq < m.fsq;
-            m.fsq = sq;
-        }
-        if (any) {
+        if (MOMENTS) {
 #pragma unroll
-            for (int k = 0; k < 8; k++)
-                if (!keep[k]) park(v[k]);
+            for (int k = 0; k < 8; k += 2) {
+                m.mn32 = min(min(m.mn32, u[k]), u[k + 1]);
+                m.mx32 = max(max(m.mx32, u[k]), u[k + 1]);
+            }
+            if (DIVMODE == 3) {
+                m.fsum += s;
+                sq += m.fsq;
+                m.fsq_carry += sq < m.fsq;
+                m.fsq = sq;
+            }
         }
     };
-
-    // head (to 16-byte alignment), tiles of 16 KB per CTA, remainder, tail
-    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
-    if (head > n) head = n;
-    const size_t tid = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
-    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
-    if (tid == 0 && head) one(x[0]);
-    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
-    const size_t npairs = (n - head) / 2;
-    // A CTA takes whole tiles of 4 x kHistThreads pairs, so a thread's four 128-bit loads are a fixed 4 KB apart
-    // and the trip count is the same for every thread of the CTA (drain() synchronises warps).
-    constexpr size_t kTilePairs = 4 * kHistThreads;
-    const size_t ntiles = npairs / kTilePairs;
-    // The next tile's loads are issued before the current tile is counted (the kernel is otherwise bound by
-    // the latency of its own loads: 8 warps per scheduler do not cover ~1 us of HBM latency under load).
-    if ((size_t)blockIdx.x < ntiles) {
-        const longlong2* p = x2 + (size_t)blockIdx.x * kTilePairs + threadIdx.x;
-        longlong2 a = __ldg(p), b = __ldg(p + kHistThreads), c = __ldg(p + 2 * kHistThreads),
-                  d = __ldg(p + 3 * kHistThreads);
-        for (size_t t = blockIdx.x; t < ntiles; t += gridDim.x) {
-            const size_t tn = t + gridDim.x < ntiles ? t + gridDim.x : t;  // last round: reload (and ignore) the same tile
-            p = x2 + tn * kTilePairs + threadIdx.x;
-            const longlong2 na = __ldg(p), nb = __ldg(p + kHistThreads), nc = __ldg(p + 2 * kHistThreads),
-                            nd = __ldg(p + 3 * kHistThreads);
-            eight(a, b, c, d);
-            a = na; b = nb; c = nc; d = nd;
-            __syncwarp();
-            if (slow_n[warp] >= kSlowQueue / 2) drain();  // warp-uniform: everyone reads the same counter
-            // a round adds at most 8 samples to a lane's slots (7 + 8 < kLaneQueue), the tails after the loop at most 4
-            if (COLLECT && __any_sync(0xFFFFFFFFu, q_addr >= q_base + (kLaneQueue - 8) * kLaneQueueStride)) flush();
-        }
-    }
-    size_t i = ntiles * kTilePairs + tid;
-    for (; i < npairs; i += nthreads) {
-        longlong2 a = __ldg(x2 + i);
-        one(a.x); one(a.y);
-    }
-    if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
-    drain();
+    // Collecting kernels: a round adds at most 8 samples to a lane's slots (7 + 8 < kLaneQueue); the generic
+    // path appends to the output buffer directly.
+    const unsigned ring_abs = (kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u +
+                               (COLLECT ? (unsigned)kLaneQueue * kLaneQueueStride : 0u) + 127u) & ~127u;
+    for_each_sample(x, n, ring_abs, nstages, eight, one, [&] {
+        maybe_drain(sm0, warp, lane, slow);
+        if (COLLECT && __any_sync(0xFFFFFFFFu, q_addr >= q_base + (kLaneQueue - 8) * kLaneQueueStride)) flush();
+    });
+    drain_parked(sm0, warp, lane, slow);
     if (COLLECT) flush();
 
-    __syncthreads();
-    for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
-        unsigned long long t = 0;
-        for (int w = 0; w < kHistWarps; w++)
-            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * rows + b) * 32 + ((l + b) & 31)];
-        if (t) atomicAdd(counts + b, t);
+    long long mn = sm_slow.mn, mx = sm_slow.mx;
+    if (nproc > nlo + nhi) {  // this thread saw genuine fast-path samples
+        mn = (long long)m.mn32 < mn ? (long long)m.mn32 : mn;
+        mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
     }
-    if (MOMENTS) {
-        long long mn = sm_slow.mn, mx = sm_slow.mx;
-        if (m.mn32 <= m.mx32) {  // this thread saw fast-path samples
-            mn = (long long)m.mn32 < mn ? (long long)m.mn32 : mn;
-            mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
-        }
-        U128 sum = sm_slow.sum, sq = sm_slow.sq;
-        add128(sum, m.fsum, 0);
-        add128(sq, m.fsq, m.fsq_carry);
-#pragma unroll
-        for (int d = 16; d; d >>= 1) {
-            long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
-            mn = omn < mn ? omn : mn;
-            mx = omx > mx ? omx : mx;
-            unsigned long long l1 = __shfl_xor_sync(0xFFFFFFFFu, sum.lo, d), h1 = __shfl_xor_sync(0xFFFFFFFFu, sum.hi, d);
-            add128(sum, l1, h1);
-            unsigned long long l2 = __shfl_xor_sync(0xFFFFFFFFu, sq.lo, d), h2 = __shfl_xor_sync(0xFFFFFFFFu, sq.hi, d);
-            add128(sq, l2, h2);
-        }
-        if (lane == 0) {
-            if (mn <= mx) {
-                atomicMin(&mom->min_ns, mn);
-                atomicMax(&mom->max_ns, mx);
-            }
-            unsigned long long old = atomicAdd(&mom->sum_lo, sum.lo);
-            unsigned long long carry = (old + sum.lo) < old;
-            atomicAdd(reinterpret_cast<unsigned long long*>(&mom->sum_hi), sum.hi + carry);
-            old = atomicAdd(&mom->sumsq_lo, sq.lo);
-            carry = (old + sq.lo) < old;
-            atomicAdd(&mom->sumsq_hi, sq.hi + carry);
-        }
-        if (blockIdx.x == 0 && threadIdx.x == 0) atomicAdd(&mom->count, (unsigned long long)n);
+    U128 sum = sm_slow.sum, sq = sm_slow.sq;
+    add128(sum, m.fsum, 0);
+    add128(sq, m.fsq, m.fsq_carry);
+    if (MOMENTS && nhi) {  // take the surrogates of the samples >= 2^32 out of the sums again: nhi * q(2^32 - 1)
+        const unsigned long long qhi = quotient(0xFFFFFFFFu), q2 = qhi * qhi;
+        const unsigned long long s_lo = (unsigned long long)nhi * qhi;  // < 2^64
+        const unsigned long long p_lo = (unsigned long long)nhi * q2, p_hi = __umul64hi((unsigned long long)nhi, q2);
+        const unsigned long long b1 = sum.lo < s_lo;
+        sum.lo -= s_lo;
+        sum.hi -= b1;
+        const unsigned long long b2 = sq.lo < p_lo;
+        sq.lo -= p_lo;
+        sq.hi -= p_hi + b2;
     }
+    hist_epilogue<MOMENTS>(tbl, rows, nbins, n, counts, mom, mn, mx, sum, sq);
 }
 
 __global__ void __launch_bounds__(kHistThreads)
@@ -691,12 +980,32 @@ sel_scan_kernel(SelState* st, unsigned long long* __restrict__ hist) {
     }
 }
 
-// dynamic window: everything up to the end of the counters / lane slots (absolute address, see the map above)
-size_t hist_smem(int nbins, bool collect) {
+// dynamic window: everything up to the end of the counters / lane slots (absolute address, see the map above),
+// then the tile ring
+size_t hist_smem(int nbins, bool collect, int nstages) {
     size_t end = kFastAbs + (size_t)kFastCells * (collect ? 12 : 8) +
                  (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned);
     if (collect) end += (size_t)kLaneQueue * kLaneQueueStride;
-    return end;
+    return ((end + 127) & ~(size_t)127) + kRingHeader + (size_t)nstages * kTileBytes;
+}
+size_t hist_qlut_smem(int nbins, int nstages) {
+    const size_t end = kQCntAbs + (size_t)kHistWarps * nbins * 32 * sizeof(unsigned);
+    return ((end + 127) & ~(size_t)127) + kRingHeader + (size_t)nstages * kTileBytes;
+}
+// CTAs per SM and ring stages per CTA that fit the SM's 227 KB (plus 1 KB reserved per CTA): as many CTAs as the
+// registers allow with two stages each, then as many more stages as still fit
+void hist_shape(size_t smem_without_ring, int by_regs, int* per_sm, int* nstages) {
+    const size_t budget = 227 * 1024;
+    int c = by_regs, forced = 0;
+    if (const char* e = getenv("B200_HIST_SHAPE")) {  // tuning override: "<ctas per SM>,<stages>"
+        int cc = 0, ss = 0;
+        if (sscanf(e, "%d,%d", &cc, &ss) == 2 && cc >= 1 && ss >= 1 && ss <= kMaxStages) { c = cc; forced = ss; }
+    }
+    while (c > 1 && c * (smem_without_ring + 2 * (size_t)kTileBytes + 1024) > budget) c--;
+    int st = (int)((budget / c - 1024 - smem_without_ring) / kTileBytes);
+    if (forced && forced < st) st = forced;
+    *per_sm = c;
+    *nstages = st < 1 ? 1 : st > kMaxStages ? kMaxStages : st;
 }
 
 int sm_count() {
@@ -796,7 +1105,7 @@ static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
 }
 
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins, int mode32, const HistCollect* collect) {
+                        cudaStream_t stream, int nbins, int mode32, const HistCollect* collect, bool qlut) {
     cudaError_t e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     e = reset_moments(s, stream);
@@ -806,9 +1115,20 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
         if (e != cudaSuccess) return e;
     }
     if (!n) return cudaSuccess;
-    const size_t smem = hist_smem(nbins, collect != nullptr);
-    const int max_smem = (int)hist_smem(kMaxThresholds + 1, collect != nullptr);
-    using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*, HistCollect);
+    // the quotient kernel keeps a thread's whole sum of quotients (each <= 8191) in 32 bits: fine up to 2^35 samples
+    if (qlut && !collect && n < ((size_t)1 << 35)) {
+        int per_sm, nstages;
+        hist_shape(hist_qlut_smem(nbins, 0), kHistCtasPerSm, &per_sm, &nstages);
+        const size_t smem = hist_qlut_smem(nbins, nstages);
+        auto k = want_moments ? hist_qlut_kernel<true> : hist_qlut_kernel<false>;
+        e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) return e;
+        const size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
+        const int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
+        k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom, nstages);
+        return cudaGetLastError();
+    }
+    using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*, HistCollect, int);
     // without moments the quotient is never formed, so one instantiation serves all modes
     static const Kernel kernels[2][4] = {
         {hist_kernel<false, 0, false>, hist_kernel<false, 0, false>, hist_kernel<false, 0, false>,
@@ -821,17 +1141,18 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
         {hist_kernel<true, 0, true>, hist_kernel<true, 1, true>, hist_kernel<true, 2, true>,
          hist_kernel<true, 3, true>}};
     const Kernel k = (collect ? collecting : kernels)[want_moments ? 1 : 0][mode32];
-    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem);
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: kHistCtasPerSm by registers, fewer when the private counter tables are large
     // (the kernel that keeps moments AND collects needs more registers than a third of the file)
     const int by_regs = collect && want_moments ? kHistCtasPerSm - 1 : kHistCtasPerSm;
-    int per_sm = (int)std::min<size_t>(by_regs, (224 * 1024) / (smem + 1024));
-    if (per_sm < 1) per_sm = 1;
+    int per_sm, nstages;
+    hist_shape(hist_smem(nbins, collect != nullptr, 0), by_regs, &per_sm, &nstages);
+    const size_t smem = hist_smem(nbins, collect != nullptr, nstages);
     size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
     k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom,
-                                            collect ? *collect : HistCollect{nullptr, nullptr, 0});
+                                            collect ? *collect : HistCollect{nullptr, nullptr, 0}, nstages);
     return cudaGetLastError();
 }
 
@@ -1041,6 +1362,24 @@ void finish_hist_params(HistParams* P, long long divisor) {
                     break;
                 }
             }
+        }
+    }
+    // Quotient table (hist_qlut_kernel): usable when every threshold a 32-bit sample can reach is a multiple of
+    // the divisor — then the bin is a function of q = trunc(n / divisor) alone — and the quotients are few.
+    P->qlut_ok = 0;
+    if (P->mode32 == 3) {
+        const unsigned long long d32 = (unsigned long long)divisor, qmax = 0xFFFFFFFFull / d32;
+        bool aligned = qmax < (unsigned long long)kQLutSize;
+        for (int j = 0; j < m && aligned; j++)
+            if (P->thr[j] > 0 && P->thr[j] <= 0xFFFFFFFFll && (unsigned long long)P->thr[j] % d32 != 0) aligned = false;
+        if (aligned) {
+            int c = 0;
+            for (unsigned long long q = 0; q < (unsigned long long)kQLutSize; q++) {
+                if (q <= qmax)
+                    while (c < m && P->thr[c] <= (long long)(q * d32)) c++;
+                P->qlut[q] = (unsigned char)c;
+            }
+            P->qlut_ok = 1;
         }
     }
     // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)

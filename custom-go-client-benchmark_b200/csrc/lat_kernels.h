@@ -9,6 +9,7 @@ constexpr int kMaxThresholds = 66;      // B200_HIST_MAX_EDGES + slack
 constexpr int kLutCells = 2048;         // log-linear cells: 32 per power of two
 constexpr int kFastCells = 1024;        // fast path (0 <= n < 2^32): 32 cells per power of two
 constexpr int kFastFirst = 127 * 32;    // float bits >> 18 of 1.0f: the first cell's index
+constexpr int kQLutSize = 8192;         // quotient table: bins of q = trunc(n / divisor), q < 8192
 constexpr int kRadixBits = 12;
 constexpr int kRadixBins = 1 << kRadixBits;
 constexpr int kMaxSelect = 4;           // order statistics resolved per pass
@@ -46,6 +47,11 @@ struct HistParams {
     int pre32;                          //   3: q = umulhi(n >> pre32, magic32) >> shift32, and q < 2^28
     int mode32;
     long long divisor;
+    // Quotient table (valid when qlut_ok): every threshold within reach of a 32-bit sample is a multiple of the
+    // divisor and floor((2^32 - 1) / divisor) < kQLutSize, so the bin of such a sample is qlut[trunc(n / divisor)]
+    // (mode32 == 3 gives the quotient).  Edges given in the divisor's own unit always qualify.
+    int qlut_ok;
+    unsigned char qlut[kQLutSize];
 };
 
 // Optional output of the histogram pass: the samples that fall into an ODD bin (bins are numbered from 0; the
@@ -101,7 +107,7 @@ void lat_scratch_free(LatScratch* s);
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
                         cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */,
-                        const HistCollect* collect = nullptr);
+                        const HistCollect* collect = nullptr, bool qlut = false /* HistParams::qlut_ok */);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 // *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,

@@ -1210,9 +1210,7 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         return fail(B200_ERR_INVALID, "b200_hist_fixed: edges must be ascending, divisor >= 1");
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
-    CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
-    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, nullptr,
-                       P.qlut_ok != 0));
+    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P));
     unsigned long long c[kMaxThresholds + 1];
     LatMoments m;
     CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
@@ -1252,15 +1250,13 @@ int b200_hist_fixed_pair(b200_ctx* ctx, int dev, const int64_t* d_samples, size_
     if (mu > kMaxThresholds)
         return fail(B200_ERR_TOO_LARGE, "b200_hist_fixed_pair: more than 66 distinct thresholds between the two edge sets");
     HistParams P;
-    if (host_build_hist_params_thr(u, mu, divisor, &P)) return fail(B200_ERR_INVALID, "b200_hist_fixed_pair");
+    if (host_build_hist_params_thr(u, mu, divisor, false, &P)) return fail(B200_ERR_INVALID, "b200_hist_fixed_pair");
     unsigned long long c[kMaxThresholds + 1];
     LatMoments m;
     {
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
-        CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
-        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, nullptr,
-                       P.qlut_ok != 0));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P));
         CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
@@ -1601,7 +1597,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     HistParams P;
     // a bracket that starts at INT64_MIN leaves bin 0 empty, which the builder allows (thresholds stay ascending)
     // the divisor only matters to the moments (stats); the thresholds are raw nanoseconds
-    if (host_build_hist_params_thr(thr, 2 * nb, stats ? divisor : 1, &P)) return sampled_trace("skip: thresholds", 1);
+    if (host_build_hist_params_thr(thr, 2 * nb, stats ? divisor : 1, true, &P)) return sampled_trace("skip: thresholds", 1);
     // room for twice the expected number of samples inside the brackets, at least n/64; more than n/8 is not worth it
     const size_t expect = (size_t)nk * (2 * margin + 2) * stride;
     const size_t cap = std::min<size_t>(std::max<size_t>(2 * expect, n / 64), n / 8);
@@ -1611,9 +1607,8 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         std::unique_lock<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         if (!grow(&d->lat.d_collect, &d->lat.collect_cap, cap)) return sampled_trace("skip: no memory for the brackets", 1);
-        CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
         HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
-        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, &col));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P, &col));
         CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
         if (stats) CU(cudaMemcpyAsync(&mom, d->lat.d_mom, sizeof mom, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaMemcpyAsync(&kept, d->lat.d_compact_n, sizeof kept, cudaMemcpyDeviceToHost, d->stream));
@@ -1713,15 +1708,14 @@ int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n
         return fail(B200_ERR_INVALID, "b200_bracket_pass");
     HistParams P;
     static_assert(sizeof(long long) == sizeof(int64_t), "threshold type");
-    if (host_build_hist_params_thr((const long long*)thresholds, nthr, divisor, &P))
+    if (host_build_hist_params_thr((const long long*)thresholds, nthr, divisor, true, &P))
         return fail(B200_ERR_INVALID, "b200_bracket_pass: thresholds must be strictly ascending");
     std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
     if (cap && !grow(&d->lat.d_collect, &d->lat.collect_cap, (size_t)cap)) return fail(B200_ERR_NOMEM, "b200_bracket_pass");
-    CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
     HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
-    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P.nthr + 1, P.mode32, &col));
+    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P, &col));
     unsigned long long c[kMaxThresholds + 1], kept = 0;
     LatMoments m{};
     CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
@@ -1754,11 +1748,10 @@ int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size
     {
         HistParams P;
         const long long zero = 0;
-        if (host_build_hist_params_thr(&zero, 1, divisor, &P)) return fail(B200_ERR_INVALID, "b200_select_kth_stats");
+        if (host_build_hist_params_thr(&zero, 1, divisor, false, &P)) return fail(B200_ERR_INVALID, "b200_select_kth_stats");
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
-        CU(cudaMemcpyAsync(d->lat.d_params, &P, sizeof P, cudaMemcpyHostToDevice, d->stream));
-        CU(launch_hist((const long long*)d_samples, n, d->lat, true, d->stream, P.nthr + 1, P.mode32, nullptr, P.qlut_ok != 0));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, true, d->stream, P));
         CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
     }

@@ -14,6 +14,7 @@
 // (warp, lane) in shared memory so the skewed latency distribution causes no atomic contention.
 #include "lat_kernels.h"
 
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -23,15 +24,16 @@ namespace b200 {
 
 namespace {
 
-constexpr int kHistThreads = 256;
+#ifndef B200_HIST_THREADS
+#define B200_HIST_THREADS 256
+#endif
+constexpr int kHistThreads = B200_HIST_THREADS;
 constexpr int kHistWarps = kHistThreads / 32;
 #ifndef B200_HIST_CTAS
 #define B200_HIST_CTAS 3
 #endif
 constexpr int kHistCtasPerSm = B200_HIST_CTAS;  // 3 x 256 threads: 85 registers each, room for the prefetched tile
 constexpr int kRadixThreads = 512;
-constexpr int kTrashRows = 2;   // counter rows past the real bins: the EVEN one of them is where the updates of
-                                // parked samples land (odd rows are the ones a collecting kernel keeps)
 
 struct U128 {
     unsigned long long lo, hi;
@@ -70,26 +72,46 @@ __device__ __forceinline__ unsigned long long udiv_magic(unsigned long long a, c
     return t >> P.magic_shift;
 }
 
+// Kept samples of one warp on their way to the output buffer: staged in shared memory and flushed with ONE global
+// atomic per ~64 of them (a global atomic per handful, with the warp waiting for its return every time, is what
+// made the collecting pass slow).
+constexpr int kKeepCap = 96;
+struct KeepStage {
+    unsigned* n;     // shared: samples staged by this warp
+    long long* q;    // shared: [kKeepCap]
+};
+
 // Generic path: any int64 sample.  Out of line, so that the fast loop keeps its registers and instruction cache.
-// s == nullptr: count (and collect) only, no moments.
+// s == nullptr: count (and collect) only, no moments.  keep: this warp's staging (collecting kernels).
 __device__ __noinline__ void slow_sample(long long v, const SlowParams* __restrict__ P, unsigned* mine,
-                                         SlowMoments* s, const HistCollect* col) {
+                                         SlowMoments* s, const HistCollect* col, KeepStage keep) {
     int lo = 0, hi = P->nthr;  // c = #{j : thr[j] <= v}: thr[j] <= v for j < lo, thr[j] > v for j >= hi
     while (lo < hi) {
         const int mid = (lo + hi) >> 1;
         if (P->thr[mid] <= v) lo = mid + 1; else hi = mid;
     }
     const int c = lo;
-    mine[c * 32]++;
-    if (col) {  // odd bins are kept; one global atomic for all the lanes that are here together
+    mine[(c + 1) * 32]++;  // row 0 is the scratch row, bin c is row c + 1
+    if (col) {  // odd bins are kept: staged in shared memory; straight to the buffer when the staging is full
         const bool hit = c & 1;
         const unsigned peers = __ballot_sync(__activemask(), hit);
         if (hit) {
             const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
-            unsigned long long at = 0;
-            if (lane == leader) at = atomicAdd(col->count, (unsigned long long)__popc(peers));
-            at = __shfl_sync(peers, at, leader) + __popc(peers & ((1u << lane) - 1));
-            if (at < col->cap) col->buf[at] = v;
+            const unsigned cnt = __popc(peers), rank = __popc(peers & ((1u << lane) - 1));
+            unsigned pos = 0;
+            if (lane == leader) {
+                pos = *keep.n;
+                if (pos + cnt <= (unsigned)kKeepCap) *keep.n = pos + cnt; else pos = 0xFFFFFFFFu;
+            }
+            pos = __shfl_sync(peers, pos, leader);
+            if (pos != 0xFFFFFFFFu) {
+                keep.q[pos + rank] = v;
+            } else {
+                unsigned long long at = 0;
+                if (lane == leader) at = atomicAdd(col->count, (unsigned long long)cnt);
+                at = __shfl_sync(peers, at, leader) + rank;
+                if (at < col->cap) col->buf[at] = v;
+            }
         }
     }
     if (s) {
@@ -114,37 +136,44 @@ __device__ __forceinline__ void load_slow_params(SlowParams* sp, const HistParam
     }
 }
 
-// Shared memory map of the histogram kernels, in ABSOLUTE shared addresses so that the hot loop addresses the
-// cell table and the counters as register + immediate (the compiler's own shared pointers carry a window base
-// it keeps recomputing under register pressure).  The driver's reserved 1 KB sits below the dynamic window;
+// Shared memory map of the histogram kernel, in ABSOLUTE shared addresses so that the hot loop addresses the
+// look-up table and the counters as register + immediate (the compiler's own shared pointers carry a window
+// base it keeps recomputing under register pressure).  The driver's reserved 1 KB sits below the dynamic window;
 // lat_scratch_init checks the window start once per device (smem_base_probe).
 constexpr unsigned kSlowAbs = 0x400;                                    // SlowParams
-constexpr int kParkCap = 128;                                           // parked samples per warp
-constexpr int kParkDrain = 64;                                           // drain from this many on
-constexpr unsigned kParkNAbs = kSlowAbs + 640;                          // unsigned[kHistWarps]
-constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long long[kHistWarps][kParkCap]
-constexpr unsigned kFastAbs = kParkQAbs + kHistWarps * kParkCap * 8;    // uint2 [kFastCells] (+ unsigned[kFastCells])
-// then unsigned[kHistWarps][rows][32] counters, then (collecting kernels) long long[kLaneQueue][kHistThreads]
-constexpr int kLaneQueue = 16;                                          // collected samples a lane can hold
-constexpr unsigned kLaneQueueStride = kHistThreads * 8;                 // bytes between a lane's slots
-constexpr unsigned kQLutAbs = kFastAbs;                                 // quotient kernel: unsigned char[kQLutSize]
+constexpr unsigned kParkNAbs = kSlowAbs + 640;                          // unsigned[kHistWarps]: parked samples per warp
+constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long long[kHistWarps][park_cap(collect)]
+// a collecting pass parks ~1 % of the samples, the others ~0.5 %: queue slots per warp
+#ifndef B200_PARK_COLLECT
+#define B200_PARK_COLLECT 128
+#endif
+#ifndef B200_PARK_PLAIN
+#define B200_PARK_PLAIN 32
+#endif
+__host__ __device__ constexpr int park_cap(bool collect) { return collect ? B200_PARK_COLLECT : B200_PARK_PLAIN; }
+// unsigned char[lut_bytes], lut_bytes <= kLutSize
+__host__ __device__ constexpr unsigned lut_abs(bool collect) { return kParkQAbs + kHistWarps * park_cap(collect) * 8; }
+// then, at lut_abs + lut_bytes, unsigned[kHistWarps][rows][32] counters, then the tile ring, then (collecting) the
+// warps' staging for kept samples
 static_assert(sizeof(SlowParams) <= 640, "SlowParams slot");
-constexpr unsigned kQCntAbs = kQLutAbs + kQLutSize;                     //   then its counters
 
 extern __shared__ __align__(1024) unsigned char hist_smem_raw[];
 
-// ---- tile loop: a ring of tiles in shared memory, filled by 1-D bulk copies (TMA) ---------------------------
-// A CTA's tiles are contiguous 16 KB pieces of the sample array, so the operands of a bulk copy are uniform and
-// one thread can issue it.  Bandwidth here is (bytes in flight) / (loaded HBM latency, ~1.4 us): with the next
+// ---- tile loop: a ring of tiles per WARP in shared memory, filled by 1-D bulk copies (TMA) ---------------------
+// A warp's tiles are contiguous 2 KB pieces of the sample array, so the operands of a bulk copy are uniform and
+// one lane can issue it.  Bandwidth here is (bytes in flight) / (loaded HBM latency, ~1.4 us): with the next
 // tile prefetched into registers a thread has 64 bytes in flight, 48 KB per SM, which is where the register
-// version stopped (4.85 TB/s; ncu: warps waiting on their loads, DRAM 54 %, issue 42 %).  The ring has nstages
-// tiles per CTA in flight and costs no registers: every round the threads copy their samples of the current
-// stage into registers, the LAST warp to have done so (a shared-memory counter per stage says who) re-arms the
-// stage's barrier and issues the copy of the tile nstages rounds on, and only then are the samples counted.
+// version stopped (4.85 TB/s; ncu: warps waiting on their loads, DRAM 54 %, issue 42 %).  The ring keeps nstages
+// tiles per warp in flight and costs no registers: every round the lanes copy their samples of the current stage
+// into registers, lane 0 re-arms the stage's barrier and issues the copy of the tile nstages rounds on, and only
+// then are the samples counted.  The rings are per warp on purpose: one ring per CTA (16 KB tiles, refilled by
+// the last warp to have read a stage) keeps the CTA's warps in step, and a warp that is working its parked
+// samples off then stalls the other seven (ncu: a fifth of the stall samples at the barrier wait).
 // (An L2 bulk prefetch running ahead of register loads was measured too: slower than no prefetch at all.)
-constexpr int kTileBytes = 4 * kHistThreads * 16;  // 16 KB: four 128-bit pairs per thread
-constexpr int kMaxStages = 4;
-constexpr int kRingHeader = 128;                   // full barriers (8 B each), then the per-stage counters (4 B each)
+constexpr int kWarpTileBytes = 4 * 32 * 16;              // 2 KB: four 128-bit pairs per lane
+constexpr int kTileBytes = kHistWarps * kWarpTileBytes;  // ring bytes per stage and CTA
+constexpr int kMaxStages = 2;  // measured: a third stage per warp is slower (5.1 vs 5.5 TB/s), one stage much slower
+constexpr int kRingHeader = 8 * kHistWarps * kMaxStages;  // the barriers: [warp][stage], 8 B each
 
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
@@ -171,10 +200,10 @@ __device__ __forceinline__ longlong2 lds_pair(unsigned addr) {
     return v;
 }
 
-// Walks x[0, n): whole tiles of 4 x kHistThreads 128-bit pairs go to eight(a, b, c, d) — tile t belongs to CTA
-// t mod gridDim.x — everything else (unaligned head, remainder, odd tail) goes to one(v).  after_tile() runs once
-// per tile with the whole warp converged.  ring_abs: absolute shared address (128-byte aligned) of kRingHeader
-// bytes followed by nstages tile buffers.  Every thread of the CTA must call this (it synchronises the CTA once).
+// Walks x[0, n): whole warp tiles of 4 x 32 128-bit pairs go to eight(a, b, c, d) — tile t belongs to warp
+// t mod (warps in the grid) — everything else (unaligned head, remainder, odd tail) goes to one(v).  after_tile()
+// runs once per tile with the whole warp converged.  ring_abs: absolute shared address (128-byte aligned) of
+// kRingHeader bytes followed by nstages tile buffers per warp.
 template <typename Eight, typename One, typename AfterTile>
 __device__ __forceinline__ void for_each_sample(const long long* __restrict__ x, size_t n, unsigned ring_abs,
                                                 int nstages, Eight eight, One one, AfterTile after_tile) {
@@ -185,44 +214,36 @@ __device__ __forceinline__ void for_each_sample(const long long* __restrict__ x,
     if (tid == 0 && head) one(x[0]);
     const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
     const size_t npairs = (n - head) / 2;
-    constexpr size_t kTilePairs = 4 * kHistThreads;
+    constexpr size_t kTilePairs = 4 * 32;
     const size_t ntiles = npairs / kTilePairs;
-    const unsigned mine = (size_t)blockIdx.x < ntiles ? (unsigned)((ntiles - 1 - blockIdx.x) / gridDim.x) + 1 : 0;
-    const unsigned full0 = ring_abs, cnt0 = ring_abs + 8 * kMaxStages, buf0 = ring_abs + kRingHeader;
-    const int lane = threadIdx.x & 31;
-    const unsigned char* const tile0 = reinterpret_cast<const unsigned char*>(x2) + (size_t)blockIdx.x * kTileBytes;
-    const size_t tile_step = (size_t)gridDim.x * kTileBytes;
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < nstages; s++) {
-            mbar_init(full0 + 8 * s, 1);
-            asm volatile("st.shared.u32 [%0], %1;" ::"r"(cnt0 + 4 * s), "r"(0u) : "memory");
-        }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t gwarp = (size_t)blockIdx.x * kHistWarps + warp, nwarps = (size_t)gridDim.x * kHistWarps;
+    const unsigned mine = gwarp < ntiles ? (unsigned)((ntiles - 1 - gwarp) / nwarps) + 1 : 0;
+    const unsigned full0 = ring_abs + 8 * kMaxStages * warp;
+    const unsigned buf0 = ring_abs + kRingHeader + (unsigned)(warp * nstages) * kWarpTileBytes;
+    const unsigned char* const tile0 = reinterpret_cast<const unsigned char*>(x2) + gwarp * kWarpTileBytes;
+    const size_t tile_step = nwarps * kWarpTileBytes;
+    if (lane == 0) {
+        for (int s = 0; s < nstages; s++) mbar_init(full0 + 8 * s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         for (unsigned j = 0; j < (unsigned)nstages && j < mine; j++) {
-            mbar_expect_tx(full0 + 8 * j, kTileBytes);
-            bulk_load(buf0 + j * kTileBytes, tile0 + (size_t)j * tile_step, kTileBytes, full0 + 8 * j);
+            mbar_expect_tx(full0 + 8 * j, kWarpTileBytes);
+            bulk_load(buf0 + j * kWarpTileBytes, tile0 + (size_t)j * tile_step, kWarpTileBytes, full0 + 8 * j);
         }
     }
-    __syncthreads();
+    __syncwarp();
     unsigned s = 0, ph = 0;  // tile j sits in stage j mod nstages, in that stage's (j div nstages)-th use
     for (unsigned j = 0; j < mine; j++) {
         mbar_wait(full0 + 8 * s, ph);
-        const unsigned at = buf0 + s * kTileBytes + threadIdx.x * 16;
-        const longlong2 a = lds_pair(at), b = lds_pair(at + 4096), c = lds_pair(at + 8192), d = lds_pair(at + 12288);
+        const unsigned at = buf0 + s * kWarpTileBytes + lane * 16;
+        const longlong2 a = lds_pair(at), b = lds_pair(at + 512), c = lds_pair(at + 1024), d = lds_pair(at + 1536);
         __syncwarp();
-        if (lane == 0) {
-            // the operands tie this atomic to the four loads above: it is issued once their data has arrived, so
-            // when the last warp's count shows up every thread of the CTA has its samples out of the stage
-            unsigned seen;
-            asm volatile("atom.shared.add.u32 %0, [%1], %2;"
-                         : "=r"(seen) : "r"(cnt0 + 4 * s), "r"(1u), "l"(a.x), "l"(b.x), "l"(c.x), "l"(d.x) : "memory");
-            if (seen == kHistWarps - 1) {
-                asm volatile("st.shared.u32 [%0], %1;" ::"r"(cnt0 + 4 * s), "r"(0u) : "memory");
-                if (j + nstages < mine) {
-                    mbar_expect_tx(full0 + 8 * s, kTileBytes);
-                    bulk_load(buf0 + s * kTileBytes, tile0 + (size_t)(j + nstages) * tile_step, kTileBytes, full0 + 8 * s);
-                }
-            }
+        if (lane == 0 && j + nstages < mine) {
+            // the operands tie the re-arming to the four loads above: it is issued once their data has arrived (the
+            // other lanes' loads are the same instructions), and the copy after it
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                         ::"r"(full0 + 8 * s), "r"((unsigned)kWarpTileBytes), "l"(a.x), "l"(b.x), "l"(c.x), "l"(d.x) : "memory");
+            bulk_load(buf0 + s * kWarpTileBytes, tile0 + (size_t)(j + nstages) * tile_step, kWarpTileBytes, full0 + 8 * s);
         }
         if (++s == (unsigned)nstages) { s = 0; ph ^= 1; }
         eight(a, b, c, d);
@@ -246,7 +267,7 @@ __device__ __forceinline__ void hist_epilogue(const unsigned* tbl, int rows, int
     for (int b = threadIdx.x; b < nbins; b += kHistThreads) {
         unsigned long long t = 0;
         for (int w = 0; w < kHistWarps; w++)
-            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * rows + b) * 32 + ((l + b) & 31)];
+            for (int l = 0; l < 32; l++) t += tbl[((size_t)w * rows + b + 1) * 32 + ((l + b) & 31)];  // bin b is row b + 1
         if (t) atomicAdd(counts + b, t);
     }
     if (MOMENTS) {
@@ -283,32 +304,22 @@ __device__ __forceinline__ void hist_epilogue(const unsigned* tbl, int rows, int
 // taken out again at the end of the kernel (see the kernels).  What was measured on the way here: masks around
 // every fast-path update cost ~4.5 instructions per sample; doing the generic work where it is met, one or two
 // lanes active, made the kernel 7x slower; parking the whole group of eight kept the warps of a CTA out of step.
-// Returns false when the queue is full: the caller then takes the generic path on the spot.
-__device__ __forceinline__ bool park1(unsigned char* sm0, int warp, long long v) {
-    unsigned* const n = reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp;
-    const unsigned at = atomicAdd(n, 1u);
-    if (at >= (unsigned)kParkCap) return false;
-    reinterpret_cast<long long*>(sm0 + kParkQAbs)[(size_t)warp * kParkCap + at] = v;
-    return true;
-}
-// whole warp, converged: hand the parked samples to slow(v), 32 at a time
-template <typename Slow>
-__device__ __forceinline__ void drain_parked(unsigned char* sm0, int warp, int lane, Slow slow) {
-    unsigned* const n = reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp;
-    const long long* q = reinterpret_cast<const long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkCap;
+// (A full queue sends the sample down the generic path on the spot.  One queue reservation per thread and group of
+// four instead of one per sample was measured: the extra live values spill, slower.)
+// Whole warp, converged: hand the parked samples to slow(v), 32 at a time; before_step() runs, converged, before
+// every 32.
+template <typename Slow, typename BeforeStep>
+__device__ __forceinline__ void drain_parked(unsigned* n, const long long* q, unsigned cap, int lane, Slow slow,
+                                             BeforeStep before_step) {
     __syncwarp();
-    const unsigned cnt = min(*n, (unsigned)kParkCap);
-    for (unsigned k = lane; k < cnt; k += 32) slow(q[k]);
-    __syncwarp();
+    const unsigned cnt = min(*n, cap);
+    for (unsigned base = 0; base < cnt; base += 32) {
+        before_step();
+        if (base + lane < cnt) slow(q[base + lane]);
+        __syncwarp();
+    }
     if (lane == 0) *n = 0;
     __syncwarp();
-}
-// after a tile round, warp converged: drain when the queue is filling up (every lane reads the same counter)
-template <typename Slow>
-__device__ __forceinline__ void maybe_drain(unsigned char* sm0, int warp, int lane, Slow slow) {
-    __syncwarp();
-    if (*(reinterpret_cast<const unsigned*>(sm0 + kParkNAbs) + warp) >= (unsigned)kParkDrain)
-        drain_parked(sm0, warp, lane, slow);
 }
 
 // the two halves of a sample, split where the compiler cannot merge the halves' arithmetic back into 64-bit
@@ -329,227 +340,85 @@ __device__ __forceinline__ void bump_abs(unsigned addr) {
     asm volatile("st.shared.u32 [%0], %1;" ::"r"(addr), "r"(c) : "memory");
 }
 
-// ---- quotient kernel ------------------------------------------------------------------------------------
-// When every threshold is a multiple of the divisor (edges given in the divisor's unit: the README bins and the
-// OpenCensus bounds in milliseconds) and the quotients of 32-bit samples are few (divisor >= 2^19), the bin is a
-// function of q = trunc(ns / divisor), which the moments need anyway: one byte-table look-up indexed by q
-// replaces the float-exponent cell, its compare and the masks.  Per sample: 3 instructions for q, 1 look-up,
-// 1 address, 3 for the counter, ~3 for the moments.  Samples outside 0 <= ns < 2^32 take slow_sample().
-template <bool MOMENTS>
-__global__ void __launch_bounds__(kHistThreads, kHistCtasPerSm)
-hist_qlut_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
-                 unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, int nstages) {
-    const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
-    unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
-    unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kQCntAbs);  // [warp][bin][lane] private counters
-    SlowParams* const sp = reinterpret_cast<SlowParams*>(sm0 + kSlowAbs);
-    load_slow_params(sp, Pg);
-    if (threadIdx.x < kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
-    for (int i = threadIdx.x; i < kQLutSize / 4; i += kHistThreads)
-        reinterpret_cast<unsigned*>(sm0 + kQLutAbs)[i] = reinterpret_cast<const unsigned*>(Pg->qlut)[i];
-    const int nbins = Pg->nthr + 1, rows = nbins;
-    for (int i = threadIdx.x; i < kHistWarps * rows * 32; i += kHistThreads) tbl[i] = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned* const mine = tbl + (size_t)warp * rows * 32 + lane;
-    const unsigned mine_abs = kQCntAbs + (unsigned)(warp * rows * 32 + lane) * 4u;
-    const unsigned magic32 = Pg->magic32;
-    const int shift32 = Pg->shift32, pre32 = Pg->pre32;
-    // q <= 8191: a thread's whole share of quotients sums in 32 bits (the launcher bounds n), eight squares too
-    unsigned mn32 = 0xFFFFFFFFu, mx32 = 0, fsum = 0;
-    unsigned long long fsq = 0;
-    SlowMoments sm_slow;
-    auto quotient = [&](unsigned u) -> unsigned { return __umulhi(u >> pre32, magic32) >> shift32; };
-    // (the table is read-only while the kernel counts: a plain asm, so that the eight look-ups of a round are
-    // issued together instead of each waiting for the previous sample's counter update)
-    auto bin_of = [&](unsigned q) -> unsigned {
-        unsigned b;
-        asm("ld.shared.u8 %0, [%1+%2];" : "=r"(b) : "r"(q), "n"(kQLutAbs));
-        return b;
-    };
-    auto bump_q = [&](unsigned q) { bump_abs(mine_abs + (bin_of(q) << 7)); };
-    // A sample outside 0 <= ns < 2^32 is parked; in the common code it is replaced by its clamp to that range (0
-    // or 2^32 - 1).  Such a surrogate lands in a known bin (nlo / nhi count how many this thread made; the bins are
-    // corrected at the end) and adds a known quotient to the sums (0, or qmax: subtracted at the end).  It cannot
-    // spoil the extremes either: a 0 can lower the minimum only when a negative sample exists, which is lower
-    // still, and 2^32 - 1 can raise the maximum only when a sample >= 2^32 exists; a thread that saw nothing but
-    // surrogates leaves its fast-path extremes out.
-    unsigned nlo = 0, nhi = 0, nproc = 0;
-    auto slow = [&](long long v) { slow_sample(v, sp, mine, MOMENTS ? &sm_slow : nullptr, nullptr); };
-    auto one = [&](long long v) {
-        if ((unsigned long long)v >> 32) {  // negative or >= 2^32 ns
-            slow(v);
-            return;
-        }
-        const unsigned u = (unsigned)v, q = quotient(u);
-        bump_q(q);
-        nproc++;
-        if (MOMENTS) {
-            mn32 = min(mn32, u);
-            mx32 = max(mx32, u);
-            fsum += q;
-            fsq += (unsigned long long)q * q;
-        }
-    };
-    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
-        const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
-        unsigned u[8], hi[8], any = 0;
-#pragma unroll
-        for (int k = 0; k < 8; k++) {
-            split64(v[k], u[k], hi[k]);
-            any |= hi[k];
-        }
-        if (any) {  // rare: a few lanes of three rounds in four
-#pragma unroll
-            for (int k = 0; k < 8; k++)
-                if (hi[k]) {
-                    if (!park1(sm0, warp, v[k])) slow(v[k]);
-                    const bool neg = (int)hi[k] < 0;
-                    u[k] = neg ? 0u : 0xFFFFFFFFu;
-                    nlo += neg;
-                    nhi += !neg;
-                }
-        }
-        nproc += 8;
-        unsigned q[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) q[k] = quotient(u[k]);
-        unsigned bin[8];
-#pragma unroll
-        for (int k = 0; k < 8; k++) bin[k] = bin_of(q[k]);
-#pragma unroll
-        for (int k = 0; k < 8; k++) bump_abs(mine_abs + (bin[k] << 7));
-        if (MOMENTS) {
-            unsigned s = 0, sq = 0;
-#pragma unroll
-            for (int k = 0; k < 8; k += 2) {
-                mn32 = min(min(mn32, u[k]), u[k + 1]);
-                mx32 = max(max(mx32, u[k]), u[k + 1]);
-            }
-#pragma unroll
-            for (int k = 0; k < 8; k++) {
-                s += q[k];
-                sq += q[k] * q[k];
-            }
-            fsum += s;
-            fsq += sq;
-        }
-    };
-    const unsigned ring_abs = (kQCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + 127u) & ~127u;
-    for_each_sample(x, n, ring_abs, nstages, eight, one, [&] { maybe_drain(sm0, warp, lane, slow); });
-    drain_parked(sm0, warp, lane, slow);
+// resident CTAs per SM the registers allow (two CTAs with 128 registers were measured for the variants that form
+// 64-bit squares, which spill a little at 80: slower)
+constexpr int hist_ctas_by_regs(bool, bool) { return kHistCtasPerSm; }
 
-    // take the surrogates out again: their bins, their quotients
-    const unsigned qhi = quotient(0xFFFFFFFFu);
-    mine[bin_of(0u) * 32] -= nlo;
-    mine[bin_of(qhi) * 32] -= nhi;
-    long long mn = sm_slow.mn, mx = sm_slow.mx;
-    if (nproc > nlo + nhi) {  // this thread saw genuine fast-path samples
-        mn = (long long)mn32 < mn ? (long long)mn32 : mn;
-        mx = (long long)mx32 > mx ? (long long)mx32 : mx;
-    }
-    U128 sum = sm_slow.sum, sq = sm_slow.sq;
-    add128(sum, (unsigned long long)fsum - (unsigned long long)nhi * qhi, 0);
-    add128(sq, fsq - (unsigned long long)nhi * qhi * qhi, 0);
-    hist_epilogue<MOMENTS>(tbl, rows, nbins, n, counts, mom, mn, mx, sum, sq);
-}
-
-// ---- cell kernel (any thresholds) ---------------------------------------------------------------------------
-// DIVMODE: how the fast path divides a 32-bit sample by the divisor: 0 divisor is 1, 1 multiply-high magic with
-// the add fix-up, 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28.
-// COLLECT: cells may hold two thresholds and the samples of odd bins are appended to col.buf.
-template <bool MOMENTS, int DIVMODE, bool COLLECT>
-__global__ void __launch_bounds__(kHistThreads, (MOMENTS && COLLECT) ? kHistCtasPerSm - 1 : kHistCtasPerSm)
+// ---- the histogram kernel ---------------------------------------------------------------------------------
+// bin(n) = #{j : thr[j] <= n} for ascending thresholds.  For 0 <= n < 2^32 the bin comes from ONE byte look-up,
+// lut[index(n)], where index is either
+//   BYQ   the quotient q = trunc(n / divisor), which the moments need anyway, when the quotients of 32-bit samples
+//         number fewer than kLutSize (divisor >= 2^19: the README bins and OpenCensus bounds in milliseconds), or
+//   else  min(n >> lut_shift, kLutSize - 1), the shift chosen on the host so that the thresholds fall inside the
+//         table's reach (32 us cells for thresholds below 268 ms).
+// A table cell that holds a threshold — or, when the kernel also collects (HistCollect), lies inside a bin that is
+// kept — has no bin of its own: its entry is 0, the counter update lands in the scratch row 0, and the sample is
+// PARKED for the generic routine (binary search over the thresholds, collection).  With edges given in the
+// divisor's own unit no cell holds a threshold; the bracket pass of the select parks about as many samples as it
+// keeps (~1 %).  Samples outside 0 <= n < 2^32 are parked as well and replaced, in the common code, by their clamp
+// to that range: such a surrogate cannot spoil the extremes (a 0 lowers the minimum only when a negative sample
+// exists, which is lower still; 2^32 - 1 raises the maximum only when a sample >= 2^32 exists; a thread that saw
+// nothing but surrogates leaves its fast-path extremes out), and the quotient of 2^32 - 1 is taken out of the
+// sums at the end (nhi counts them).  So the common code carries no masks and no compares: per sample 1-3
+// instructions for the index, 1 look-up, 1 address, 3 for the counter, ~3 for the moments.
+// DIVMODE (how the fast path divides a 32-bit sample): 0 divisor is 1, 1 multiply-high magic with the add fix-up,
+// 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28; BYQ implies 3
+// with quotients < 2^13, whose sums of eight (and of a thread's whole share) fit 32 bits.
+template <bool MOMENTS, int DIVMODE, bool BYQ, bool COLLECT>
+__global__ void __launch_bounds__(kHistThreads, hist_ctas_by_regs(MOMENTS, BYQ))
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, const HistCollect col, int nstages) {
-    // cell entries are 8 bytes; collecting kernels keep the cells' second compare values in a table of their own,
-    // read (under a predicate) only by the lanes whose cell has one: 16-byte entries cost twice the shared-memory
-    // wavefronts on every look-up and made the pass LSU-bound
-    constexpr unsigned kFast2Abs = kFastAbs + kFastCells * 8;
-    constexpr unsigned kCntAbs = kFast2Abs + (COLLECT ? kFastCells * 4 : 0);
-    constexpr int kFastBias = (int)kFastAbs - kFastFirst * 8;   // cell address = bias + 8 * (bits >> 18)
-    constexpr int kFast2Bias = (int)kFast2Abs - kFastFirst * 4;
-    // (set-up has checked once per device that the dynamic window starts at or below kFastAbs: smem_base_probe)
+    static_assert(!BYQ || DIVMODE == 3, "the quotient index uses the pre-shift magic");
+    constexpr unsigned kLutAbs = lut_abs(COLLECT), kParkCap = park_cap(COLLECT);
+    constexpr bool collecting = COLLECT;
     const unsigned smem_base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
     unsigned char* const sm0 = hist_smem_raw - smem_base;  // generic pointer to absolute shared address 0
+    const unsigned lut_bytes = (unsigned)Pg->lut_bytes, kCntAbs = kLutAbs + lut_bytes;
     unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kCntAbs);  // [warp][row][lane] private counters
     SlowParams* const sp = reinterpret_cast<SlowParams*>(sm0 + kSlowAbs);
     load_slow_params(sp, Pg);
     if (threadIdx.x < kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
-    for (int i = threadIdx.x; i < kFastCells; i += kHistThreads) {
-        const uint4 c = Pg->fast[i];
-        // bit 3 of a collecting kernel's entry: the cell has a second compare value
-        reinterpret_cast<uint2*>(sm0 + kFastAbs)[i] =
-            COLLECT ? make_uint2(c.x, c.y | (c.z != 0xFFFFFFFFu && !(c.y & 4u) ? 8u : 0u)) : make_uint2(c.x, c.w);
-        if (COLLECT) reinterpret_cast<unsigned*>(sm0 + kFast2Abs)[i] = c.z;
-    }
-    const int nbins = Pg->nthr + 1, rows = nbins + kTrashRows;
+    for (int i = threadIdx.x; i < (int)lut_bytes / 4; i += kHistThreads)
+        reinterpret_cast<unsigned*>(sm0 + kLutAbs)[i] = reinterpret_cast<const unsigned*>(Pg->lut)[i];
+    const int nbins = Pg->nthr + 1, rows = nbins + 1;  // row 0: scratch
     for (int i = threadIdx.x; i < kHistWarps * rows * 32; i += kHistThreads) tbl[i] = 0;
     __syncthreads();
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     unsigned* const mine = tbl + (size_t)warp * rows * 32 + lane;
     const unsigned mine_abs = kCntAbs + (unsigned)(warp * rows * 32 + lane) * 4u;
-    Moments m;
     const unsigned magic32 = Pg->magic32;
-    const int shift32 = Pg->shift32, pre32 = Pg->pre32;
+    const int shift32 = Pg->shift32, pre32 = Pg->pre32, lut_shift = Pg->lut_shift;
 
-    // collecting kernels: a lane's pending samples sit in its own slots until some lane of the warp runs short
-    const unsigned q_base = kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + threadIdx.x * 8u;
-    unsigned q_addr = q_base;
-
+    Moments m;          // generic accumulation (64-bit sums with a carry count)
+    unsigned fsum32 = 0;  // BYQ: a thread's whole share of quotients (each < 2^13) sums in 32 bits (the launcher bounds n)
     SlowMoments sm_slow;
-    // Generic path (slow_sample, 32 parked samples at a time): samples >= 2^32 ns or negative, and samples in a
-    // cell holding more thresholds than the kernel compares with.  The latter are ordinary for the moments — the
-    // fast path keeps those — and only their bin comes from the generic path (count_only).
-    auto slow = [&](long long v) {
-        const bool count_only = ((unsigned long long)v >> 32) == 0;
-        slow_sample(v, sp, mine, MOMENTS && !count_only ? &sm_slow : nullptr, COLLECT ? &col : nullptr);
-    };
-    // Fast path: 0 <= v < 2^32 (4.29 s in nanoseconds), 32-bit arithmetic only.  lookup() fetches the sample's
-    // cell (w.z is the cell's second compare value, used by collecting kernels only); bit 2 of w.y says the cell
-    // holds more thresholds than we compare with (its counter offset then points at a scratch row).
-    auto lookup = [&](unsigned u, uint4& w) {
-        const unsigned bits = __float_as_uint(__uint2float_rz(u | 1u));
-        const unsigned idx = (bits >> 15) & 0x3FFF8u;
-        asm("ld.shared.v2.u32 {%0, %1}, [%2+%3];" : "=r"(w.x), "=r"(w.y) : "r"(idx), "n"(kFastBias));
-        if (COLLECT) {
-            asm("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %2, 0;\n\tmov.u32 %0, 0xFFFFFFFF;\n\t"
-                "@p ld.shared.u32 %0, [%1+%3];\n\t}"
-                : "=r"(w.z) : "r"(idx >> 1), "r"(w.y & 8u), "n"(kFast2Bias));
-        }
-    };
-    // returns the byte offset of the counter row: bit 7 = the sample's bin is odd
-    auto bump = [&](unsigned u, const uint4 w) -> unsigned {
-        unsigned off = (COLLECT ? (w.y & ~8u) : w.y) + (u > w.x ? 128u : 0u);  // (flagged cells never get here)
-        if (COLLECT) off += u > w.z ? 128u : 0u;
-        bump_abs(mine_abs + off);
-        return off;
-    };
-    // keep the sample if `in` (0 or 128) is set: the slot is written under a predicate, the cursor moves by in * 16
-    auto collect = [&](long long v, unsigned in) {
-        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %3, 0;\n\t@p st.shared.v2.u32 [%0], {%1, %2};\n\t}"
-                     ::"r"(q_addr), "r"((unsigned)v), "r"((unsigned)((unsigned long long)v >> 32)), "r"(in) : "memory");
-        static_assert(kLaneQueueStride == 128u << 4, "cursor step");
-        q_addr += in << 4;
-    };
-    auto flush = [&]() {  // whole warp: one global atomic for everything the 32 lanes hold
-        const unsigned cnt = (q_addr - q_base) / kLaneQueueStride;
-        unsigned incl = cnt;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const unsigned t = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-            if (lane >= d) incl += t;
-        }
-        const unsigned total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    unsigned nhi = 0, nsur = 0, nproc = 0;  // surrogates for samples >= 2^32; all surrogates; fast-path samples
+
+    // collecting kernels: the warp's staging for kept samples sits past the tile ring
+    const unsigned keep_abs = ((kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + 127u) & ~127u) + kRingHeader +
+                              (unsigned)nstages * kTileBytes;
+    KeepStage keep{reinterpret_cast<unsigned*>(sm0 + keep_abs) + warp,
+                   reinterpret_cast<long long*>(sm0 + keep_abs + 64) + (size_t)warp * kKeepCap};
+    // the warp's queue of parked samples: addressed from constants where it is used (no registers held for it)
+    auto park_n = [&]() -> unsigned* { return reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp; };
+    auto park_q = [&]() -> long long* { return reinterpret_cast<long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkCap; };
+    if (collecting && lane == 0) *keep.n = 0;
+    __syncwarp();
+    auto flush_keep = [&]() {  // whole warp, converged
+        __syncwarp();
+        const unsigned total = *keep.n;
         unsigned long long at = 0;
-        if (lane == 31 && total) at = atomicAdd(col.count, (unsigned long long)total);
-        at = __shfl_sync(0xFFFFFFFFu, at, 31) + (incl - cnt);
-        for (unsigned e = 0; e < cnt; e++) {
-            unsigned lo, hi;
-            asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(lo), "=r"(hi) : "r"(q_base + e * kLaneQueueStride) : "memory");
-            if (at + e < col.cap) col.buf[at + e] = (long long)(((unsigned long long)hi << 32) | lo);
-        }
-        q_addr = q_base;
+        if (lane == 0 && total) at = atomicAdd(col.count, (unsigned long long)total);
+        at = __shfl_sync(0xFFFFFFFFu, at, 0);
+        for (unsigned k = lane; k < total; k += 32)
+            if (at + k < col.cap) col.buf[at + k] = keep.q[k];
+        __syncwarp();
+        if (lane == 0) *keep.n = 0;
+        __syncwarp();
+    };
+    auto slow = [&](long long v) {  // parked: outside 32 bits -> everything; else its bin (and collection) only
+        const bool outside = ((unsigned long long)v >> 32) != 0;
+        slow_sample(v, sp, mine, MOMENTS && outside ? &sm_slow : nullptr, collecting ? &col : nullptr, keep);
     };
     auto quotient = [&](unsigned u) -> unsigned {
         if (DIVMODE == 1) {
@@ -559,112 +428,127 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         if (DIVMODE == 3) return __umulhi(u >> pre32, magic32) >> shift32;
         return DIVMODE == 0 ? u : 0u;
     };
+    const unsigned last_cell = lut_bytes - 1;
+    auto index_of = [&](unsigned u) -> unsigned { return BYQ ? quotient(u) : min(u >> lut_shift, last_cell); };
+    // (the table is read-only while the kernel counts: a plain asm, so that the eight look-ups of a round are
+    // issued together instead of each waiting for the previous sample's counter update)
+    auto row_of = [&](unsigned idx) -> unsigned {
+        unsigned r;
+        asm("ld.shared.u8 %0, [%1+%2];" : "=r"(r) : "r"(idx), "n"(kLutAbs));
+        return r;
+    };
     auto accumulate = [&](unsigned q) {  // running 64-bit sums; q*q wraps at most once per add
         m.fsum += q;
         const unsigned long long sq = (unsigned long long)q * q + m.fsq;
         m.fsq_carry += sq < m.fsq;
         m.fsq = sq;
     };
-    // In the common code a parked sample is replaced by a surrogate: its clamp to [0, 2^32) when it lies outside
-    // (nlo / nhi count these: the quotient of 2^32 - 1 is taken out of the sums at the end; the extremes cannot be
-    // spoiled, see hist_qlut_kernel), itself when only its cell is the problem; either way its counter update is
-    // pointed at a scratch row, which is even and so never collected.
-    unsigned nlo = 0, nhi = 0, nproc = 0;
-    const unsigned scratch_row = (unsigned)((nbins + 1) & ~1) * 128u;  // even, past the last bin
     auto one = [&](long long v) {
         if ((unsigned long long)v >> 32) { slow(v); return; }
-        const unsigned u = (unsigned)v;
-        uint4 w;
-        lookup(u, w);
-        if (w.y & 4u) {
-            slow(v);  // count only
-            w = make_uint4(0xFFFFFFFFu, scratch_row, 0xFFFFFFFFu, 0);
-        }
-        const unsigned off = bump(u, w);
-        if (COLLECT) collect(v, off & 128u);
+        const unsigned u = (unsigned)v, idx = index_of(u), row = row_of(idx);
+        if (row == 0) slow(v);  // its bin; the moments below are the fast path's
+        bump_abs(mine_abs + (row << 7));
         nproc++;
         if (MOMENTS) {
             m.mn32 = min(m.mn32, u);
             m.mx32 = max(m.mx32, u);
-            accumulate(quotient(u));
+            accumulate(BYQ ? idx : quotient(u));
         }
     };
-    // Eight samples at a time.  Whether any of them needs the generic path is ONE test (the OR of the high words
-    // and of the cells' flag bits); the common work carries no masks.
-    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
-        const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
-        uint4 w[8];
-        unsigned u[8], hi[8], any_hi = 0, any_y = 0;
+    // Four samples at a time (two such groups per round: eight at once keep too many values alive for the 80
+    // registers three CTAs per SM leave a thread).  Whether any of them must be parked is one test.
+    auto four = [&](const longlong2 a, const longlong2 b) {
+        constexpr int K = 4;
+        const long long v[K] = {a.x, a.y, b.x, b.y};
+        unsigned u[K], hi[K], q[K], row[K], any_hi = 0;
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
+        for (int k = 0; k < K; k++) {
             split64(v[k], u[k], hi[k]);
-            lookup(u[k], w[k]);
             any_hi |= hi[k];
-            any_y |= w[k].y;
         }
-        if (any_hi | (any_y & 4u)) {  // rare: a few lanes of three rounds in four
 #pragma unroll
-            for (int k = 0; k < 8; k++)
-                if (hi[k] | (w[k].y & 4u)) {
-                    if (!park1(sm0, warp, v[k])) slow(v[k]);
-                    if (hi[k]) {
+        for (int k = 0; k < K; k++) q[k] = index_of(u[k]);  // BYQ: the quotient itself
+#pragma unroll
+        for (int k = 0; k < K; k++) row[k] = row_of(q[k]);
+        const unsigned lowest = min(min(row[0], row[1]), min(row[2], row[3]));
+        if (any_hi != 0 || lowest == 0) {  // rare: a few lanes of most rounds
+#pragma unroll
+            for (int k = 0; k < K; k++)
+                if (hi[k] != 0 || row[k] == 0) {
+                    const unsigned at = atomicAdd(park_n(), 1u);
+                    if (at < kParkCap) park_q()[at] = v[k];
+                    else slow(v[k]);  // queue full: on the spot
+                    if (hi[k]) {  // the surrogate: clamp to [0, 2^32), counted in the scratch row
                         const bool neg = (int)hi[k] < 0;
                         u[k] = neg ? 0u : 0xFFFFFFFFu;
-                        nlo += neg;
+                        if (BYQ) q[k] = quotient(u[k]);
+                        row[k] = 0;
                         nhi += !neg;
+                        nsur++;
                     }
-                    w[k] = make_uint4(0xFFFFFFFFu, scratch_row, 0xFFFFFFFFu, 0);
                 }
         }
-        nproc += 8;
-        unsigned s = 0;
-        unsigned long long sq = 0;
 #pragma unroll
-        for (int k = 0; k < 8; k++) {
-            const unsigned off = bump(u[k], w[k]);
-            if (COLLECT) collect(v[k], off & 128u);
-            if (MOMENTS) {
-                const unsigned q = quotient(u[k]);
-                if (DIVMODE == 3) {  // quotients < 2^28: eight of them fit 32 bits, eight squares fit 64
-                    s += q;
-                    sq += (unsigned long long)q * q;
-                } else {
-                    accumulate(q);
-                }
-            }
-        }
+        for (int k = 0; k < K; k++) bump_abs(mine_abs + (row[k] << 7));
         if (MOMENTS) {
+            m.mn32 = min(min(m.mn32, u[0]), u[1]);
+            m.mn32 = min(min(m.mn32, u[2]), u[3]);
+            m.mx32 = max(max(m.mx32, u[0]), u[1]);
+            m.mx32 = max(max(m.mx32, u[2]), u[3]);
+            if (BYQ) {
+                unsigned s = 0, sq = 0;  // q < 2^13: the squares of a group fit 32 bits
 #pragma unroll
-            for (int k = 0; k < 8; k += 2) {
-                m.mn32 = min(min(m.mn32, u[k]), u[k + 1]);
-                m.mx32 = max(max(m.mx32, u[k]), u[k + 1]);
-            }
-            if (DIVMODE == 3) {
+                for (int k = 0; k < K; k++) {
+                    s += q[k];
+                    sq += q[k] * q[k];
+                }
+                fsum32 += s;
+                m.fsq += sq;  // cannot wrap: < 2^26 per sample
+            } else if (DIVMODE == 3) {  // quotients < 2^28: a group's sum fits 32 bits, its squares 64
+                unsigned s = 0;
+                unsigned long long sq = 0;
+#pragma unroll
+                for (int k = 0; k < K; k++) {
+                    const unsigned qq = quotient(u[k]);
+                    s += qq;
+                    sq += (unsigned long long)qq * qq;
+                }
                 m.fsum += s;
                 sq += m.fsq;
                 m.fsq_carry += sq < m.fsq;
                 m.fsq = sq;
+            } else {
+#pragma unroll
+                for (int k = 0; k < K; k++) accumulate(quotient(u[k]));
             }
         }
     };
-    // Collecting kernels: a round adds at most 8 samples to a lane's slots (7 + 8 < kLaneQueue); the generic
-    // path appends to the output buffer directly.
-    const unsigned ring_abs = (kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u +
-                               (COLLECT ? (unsigned)kLaneQueue * kLaneQueueStride : 0u) + 127u) & ~127u;
+    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
+        four(a, b);
+        four(c, d);
+        nproc += 8;
+    };
+    const unsigned ring_abs = (kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + 127u) & ~127u;
+    // a drain step stages at most 32 kept samples: flush before a step that might not fit
+    auto before_step = [&] {
+        if (collecting && *keep.n > (unsigned)(kKeepCap - 32)) flush_keep();
+    };
     for_each_sample(x, n, ring_abs, nstages, eight, one, [&] {
-        maybe_drain(sm0, warp, lane, slow);
-        if (COLLECT && __any_sync(0xFFFFFFFFu, q_addr >= q_base + (kLaneQueue - 8) * kLaneQueueStride)) flush();
+        __syncwarp();
+        if (*park_n() >= kParkCap / 2)  // every lane reads the same counter
+            drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step);
     });
-    drain_parked(sm0, warp, lane, slow);
-    if (COLLECT) flush();
+    drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step);
+    if (collecting) flush_keep();
 
     long long mn = sm_slow.mn, mx = sm_slow.mx;
-    if (nproc > nlo + nhi) {  // this thread saw genuine fast-path samples
+    if (nproc > nsur) {  // this thread saw genuine fast-path samples
         mn = (long long)m.mn32 < mn ? (long long)m.mn32 : mn;
         mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
     }
     U128 sum = sm_slow.sum, sq = sm_slow.sq;
     add128(sum, m.fsum, 0);
+    add128(sum, fsum32, 0);
     add128(sq, m.fsq, m.fsq_carry);
     if (MOMENTS && nhi) {  // take the surrogates of the samples >= 2^32 out of the sums again: nhi * q(2^32 - 1)
         const unsigned long long qhi = quotient(0xFFFFFFFFu), q2 = qhi * qhi;
@@ -680,7 +564,8 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     hist_epilogue<MOMENTS>(tbl, rows, nbins, n, counts, mom, mn, mx, sum, sq);
 }
 
-__global__ void __launch_bounds__(kHistThreads)
+constexpr int kMinmaxThreads = 256;
+__global__ void __launch_bounds__(kMinmaxThreads)
 minmax_kernel(const long long* __restrict__ x, size_t n, LatMoments* __restrict__ mom) {
     long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
     auto one = [&](long long v) {
@@ -689,8 +574,8 @@ minmax_kernel(const long long* __restrict__ x, size_t n, LatMoments* __restrict_
     };
     size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
     if (head > n) head = n;
-    const size_t tid = (size_t)blockIdx.x * kHistThreads + threadIdx.x;
-    const size_t nthreads = (size_t)gridDim.x * kHistThreads;
+    const size_t tid = (size_t)blockIdx.x * kMinmaxThreads + threadIdx.x;
+    const size_t nthreads = (size_t)gridDim.x * kMinmaxThreads;
     if (tid == 0 && head) one(x[0]);
     const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
     const size_t npairs = (n - head) / 2;
@@ -980,17 +865,11 @@ sel_scan_kernel(SelState* st, unsigned long long* __restrict__ hist) {
     }
 }
 
-// dynamic window: everything up to the end of the counters / lane slots (absolute address, see the map above),
-// then the tile ring
-size_t hist_smem(int nbins, bool collect, int nstages) {
-    size_t end = kFastAbs + (size_t)kFastCells * (collect ? 12 : 8) +
-                 (size_t)kHistWarps * (nbins + kTrashRows) * 32 * sizeof(unsigned);
-    if (collect) end += (size_t)kLaneQueue * kLaneQueueStride;
-    return ((end + 127) & ~(size_t)127) + kRingHeader + (size_t)nstages * kTileBytes;
-}
-size_t hist_qlut_smem(int nbins, int nstages) {
-    const size_t end = kQCntAbs + (size_t)kHistWarps * nbins * 32 * sizeof(unsigned);
-    return ((end + 127) & ~(size_t)127) + kRingHeader + (size_t)nstages * kTileBytes;
+// dynamic window: everything up to the end of the counters (absolute address, see the map above), then the tile ring
+size_t hist_smem(int nbins, int lut_bytes, int nstages, bool collect) {
+    const size_t end = lut_abs(collect) + (size_t)lut_bytes + (size_t)kHistWarps * (nbins + 1) * 32 * sizeof(unsigned);
+    return ((end + 127) & ~(size_t)127) + kRingHeader + (size_t)nstages * kTileBytes +
+           (collect ? 64 + (size_t)kHistWarps * kKeepCap * 8 : 0);
 }
 // CTAs per SM and ring stages per CTA that fit the SM's 227 KB (plus 1 KB reserved per CTA): as many CTAs as the
 // registers allow with two stages each, then as many more stages as still fit
@@ -1105,8 +984,10 @@ static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
 }
 
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins, int mode32, const HistCollect* collect, bool qlut) {
-    cudaError_t e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
+                        cudaStream_t stream, const HistParams& P, const HistCollect* collect) {
+    cudaError_t e = cudaMemcpyAsync(s.d_params, &P, sizeof P, cudaMemcpyHostToDevice, stream);
+    if (e != cudaSuccess) return e;
+    e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     e = reset_moments(s, stream);
     if (e != cudaSuccess) return e;
@@ -1115,52 +996,49 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
         if (e != cudaSuccess) return e;
     }
     if (!n) return cudaSuccess;
-    // the quotient kernel keeps a thread's whole sum of quotients (each <= 8191) in 32 bits: fine up to 2^35 samples
-    if (qlut && !collect && n < ((size_t)1 << 35)) {
-        int per_sm, nstages;
-        hist_shape(hist_qlut_smem(nbins, 0), kHistCtasPerSm, &per_sm, &nstages);
-        const size_t smem = hist_qlut_smem(nbins, nstages);
-        auto k = want_moments ? hist_qlut_kernel<true> : hist_qlut_kernel<false>;
-        e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        if (e != cudaSuccess) return e;
-        const size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
-        const int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
-        k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom, nstages);
-        return cudaGetLastError();
-    }
     using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*, HistCollect, int);
-    // without moments the quotient is never formed, so one instantiation serves all modes
-    static const Kernel kernels[2][4] = {
-        {hist_kernel<false, 0, false>, hist_kernel<false, 0, false>, hist_kernel<false, 0, false>,
-         hist_kernel<false, 0, false>},
-        {hist_kernel<true, 0, false>, hist_kernel<true, 1, false>, hist_kernel<true, 2, false>,
-         hist_kernel<true, 3, false>}};
-    static const Kernel collecting[2][4] = {
-        {hist_kernel<false, 0, true>, hist_kernel<false, 0, true>, hist_kernel<false, 0, true>,
-         hist_kernel<false, 0, true>},
-        {hist_kernel<true, 0, true>, hist_kernel<true, 1, true>, hist_kernel<true, 2, true>,
-         hist_kernel<true, 3, true>}};
-    const Kernel k = (collect ? collecting : kernels)[want_moments ? 1 : 0][mode32];
+    // without moments the quotient is only formed as the table index, so one instantiation serves all shift-indexed modes
+    static const Kernel by_shift[2][4] = {
+        {hist_kernel<false, 0, false, false>, hist_kernel<false, 0, false, false>, hist_kernel<false, 0, false, false>,
+         hist_kernel<false, 0, false, false>},
+        {hist_kernel<true, 0, false, false>, hist_kernel<true, 1, false, false>, hist_kernel<true, 2, false, false>,
+         hist_kernel<true, 3, false, false>}};
+    static const Kernel collecting[2][4] = {  // (a collecting pass is never indexed by quotient: its cells are parked)
+        {hist_kernel<false, 0, false, true>, hist_kernel<false, 0, false, true>, hist_kernel<false, 0, false, true>,
+         hist_kernel<false, 0, false, true>},
+        {hist_kernel<true, 0, false, true>, hist_kernel<true, 1, false, true>, hist_kernel<true, 2, false, true>,
+         hist_kernel<true, 3, false, true>}};
+    static const Kernel by_q[2] = {hist_kernel<false, 3, true, false>, hist_kernel<true, 3, true, false>};
+    if (collect && P.by_q) return cudaErrorInvalidValue;  // the builder never pairs the two
+    const Kernel k = collect ? collecting[want_moments ? 1 : 0][P.mode32]
+                             : P.by_q ? by_q[want_moments ? 1 : 0] : by_shift[want_moments ? 1 : 0][P.mode32];
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: kHistCtasPerSm by registers, fewer when the private counter tables are large
-    // (the kernel that keeps moments AND collects needs more registers than a third of the file)
-    const int by_regs = collect && want_moments ? kHistCtasPerSm - 1 : kHistCtasPerSm;
+    const int nbins = P.nthr + 1;
     int per_sm, nstages;
-    hist_shape(hist_smem(nbins, collect != nullptr, 0), by_regs, &per_sm, &nstages);
-    const size_t smem = hist_smem(nbins, collect != nullptr, nstages);
-    size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
-    int grid = (int)std::min<size_t>((size_t)sm_count() * per_sm, want_ctas ? want_ctas : 1);
-    k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom,
-                                            collect ? *collect : HistCollect{nullptr, nullptr, 0}, nstages);
+    hist_shape(hist_smem(nbins, P.lut_bytes, 0, collect != nullptr), hist_ctas_by_regs(want_moments, P.by_q != 0), &per_sm,
+               &nstages);
+    const size_t smem = hist_smem(nbins, P.lut_bytes, nstages, collect != nullptr);
+    const int max_grid = sm_count() * per_sm;
+    // The quotient-indexed kernel keeps a thread's whole sum of quotients (each < 2^13) in 32 bits: 2^18 samples
+    // per thread at most, so very long inputs go in pieces (counts and moments add up across launches)
+    const size_t piece = P.by_q ? (size_t)max_grid * kHistThreads * ((size_t)1 << 18) : n;
+    for (size_t done = 0; done < n; done += piece) {
+        const size_t m = std::min(piece, n - done);
+        const size_t want_ctas = (m / 2 + kHistThreads - 1) / kHistThreads;
+        const int grid = (int)std::min<size_t>((size_t)max_grid, want_ctas ? want_ctas : 1);
+        k<<<grid, kHistThreads, smem, stream>>>(d_samples + done, m, s.d_params, s.d_counts, s.d_mom,
+                                                collect ? *collect : HistCollect{nullptr, nullptr, 0}, nstages);
+    }
     return cudaGetLastError();
 }
 
 cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch& s, cudaStream_t stream) {
     cudaError_t e = reset_moments(s, stream);
     if (e != cudaSuccess || !n) return e;
-    int grid = (int)std::min<size_t>((size_t)sm_count() * 8, (n + kHistThreads - 1) / kHistThreads);
-    minmax_kernel<<<grid, kHistThreads, 0, stream>>>(d_samples, n, s.d_mom);
+    int grid = (int)std::min<size_t>((size_t)sm_count() * 8, (n + kMinmaxThreads - 1) / kMinmaxThreads);
+    minmax_kernel<<<grid, kMinmaxThreads, 0, stream>>>(d_samples, n, s.d_mom);
     return cudaGetLastError();
 }
 
@@ -1234,7 +1112,7 @@ long long first_n_with_quotient_at_least(double E, long long d) {
     return ((long long)E - 1) * d + 1;
 }
 
-void finish_hist_params(HistParams* P, long long divisor);
+void finish_hist_params(HistParams* P, long long divisor, bool collect);
 
 }  // namespace
 
@@ -1261,11 +1139,11 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
     const int m = host_edges_to_thresholds(edges, nedges, mode, divisor, P->thr);
     if (m < 0) return -1;
     P->nthr = m;
-    finish_hist_params(P, divisor);
+    finish_hist_params(P, divisor, false);
     return 0;
 }
 
-int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, HistParams* P) {
+int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, bool collect, HistParams* P) {
     memset(P, 0, sizeof *P);
     if (nthr < 1 || nthr > kMaxThresholds || divisor < 1) return -1;
     for (int j = 0; j < nthr; j++) {
@@ -1273,61 +1151,15 @@ int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor
         P->thr[j] = thr[j];
     }
     P->nthr = nthr;
-    finish_hist_params(P, divisor);
+    finish_hist_params(P, divisor, collect);
     return 0;
 }
 
 namespace {
 
-// thresholds (P->thr, P->nthr) -> cell tables and division magics
-void finish_hist_params(HistParams* P, long long divisor) {
+// thresholds (P->thr, P->nthr) -> look-up table and division magics
+void finish_hist_params(HistParams* P, long long divisor, bool collect) {
     const int m = P->nthr;
-    // log-linear LUT over n >= 0
-    for (int idx = 0; idx < kLutCells; idx++) {
-        unsigned long long lo, hi;
-        if (idx < 32) lo = hi = (unsigned long long)idx;
-        else {
-            int e = idx / 32 + 4, mant = idx % 32;
-            if (e > 62) { P->lut[idx] = (unsigned short)(m << 8); continue; }
-            lo = (1ull << e) + ((unsigned long long)mant << (e - 5));
-            hi = lo + (1ull << (e - 5)) - 1;
-        }
-        int base = 0, extra = 0;
-        for (int j = 0; j < m; j++) {
-            if (P->thr[j] <= (long long)lo) base++;
-            else if (P->thr[j] <= (long long)hi) extra++;
-        }
-        P->lut[idx] = (unsigned short)((base << 8) | (extra > 255 ? 255 : extra));
-    }
-    // fast-path cells (see HistParams::fast): the cell of n is read off float_rz(n | 1)
-    for (int t = 0; t < kFastCells; t++) {
-        unsigned long long lo, hi;
-        bool empty = false;
-        const int e = t / 32, mant = t % 32;
-        if (e >= 6) {  // bit 0 lies below the five mantissa bits: the | 1 does not move the cell
-            lo = (1ull << e) + ((unsigned long long)mant << (e - 5));
-            hi = lo + (1ull << (e - 5)) - 1;
-        } else {  // n | 1 is the odd number 2^e + (mant >> (5 - e)); the cell is that number and the even one below
-            const unsigned long long odd = (1ull << e) + (unsigned long long)(mant >> (5 - e));
-            empty = (mant & ((1 << (5 - e)) - 1)) != 0 || !(odd & 1);
-            lo = odd - 1;
-            hi = odd;
-        }
-        int base = 0, extra = 0;
-        for (int j = 0; j < m && !empty; j++) {
-            if (P->thr[j] <= (long long)lo) base++;
-            else if (P->thr[j] <= (long long)hi) extra++;
-        }
-        // thresholds inside a cell are > lo >= 0 and <= hi < 2^32, so thr - 1 fits 32 bits
-        P->fast[t].x = extra >= 1 ? (unsigned int)(P->thr[base] - 1) : 0xFFFFFFFFu;
-        P->fast[t].z = extra >= 2 ? (unsigned int)(P->thr[base + 1] - 1) : 0xFFFFFFFFu;
-        // A cell with more thresholds than the kernel compares with sends the sample to the generic path; its
-        // (no-op) counter update is pointed at the trash rows past the last bin, and bit 2 keeps the address
-        // word-aligned.
-        const unsigned int row = (unsigned int)base * 128u, generic = (unsigned int)(m + 1) * 128u | 4u;
-        P->fast[t].w = extra >= 2 ? generic : row;
-        P->fast[t].y = extra >= 3 ? generic : row;
-    }
     // 32-bit dividends (Granlund-Montgomery, N = 32): l = ceil(log2 d), m' = floor(2^32 (2^l - d) / d) + 1,
     // q = (t + ((n - t) >> 1)) >> (l - 1) with t = umulhi(m', n)
     if (divisor == 1) {
@@ -1364,23 +1196,47 @@ void finish_hist_params(HistParams* P, long long divisor) {
             }
         }
     }
-    // Quotient table (hist_qlut_kernel): usable when every threshold a 32-bit sample can reach is a multiple of
-    // the divisor — then the bin is a function of q = trunc(n / divisor) alone — and the quotients are few.
-    P->qlut_ok = 0;
-    if (P->mode32 == 3) {
-        const unsigned long long d32 = (unsigned long long)divisor, qmax = 0xFFFFFFFFull / d32;
-        bool aligned = qmax < (unsigned long long)kQLutSize;
-        for (int j = 0; j < m && aligned; j++)
-            if (P->thr[j] > 0 && P->thr[j] <= 0xFFFFFFFFll && (unsigned long long)P->thr[j] % d32 != 0) aligned = false;
-        if (aligned) {
-            int c = 0;
-            for (unsigned long long q = 0; q < (unsigned long long)kQLutSize; q++) {
-                if (q <= qmax)
-                    while (c < m && P->thr[c] <= (long long)(q * d32)) c++;
-                P->qlut[q] = (unsigned char)c;
+    // The look-up table (see hist_kernel).  Cell c covers the samples [lo_c, hi_c]; its entry is 1 + the number of
+    // thresholds <= lo_c — the counter row of every sample in the cell — unless a threshold lies inside (lo_c, hi_c]
+    // or, when collecting, that bin is odd (kept): then 0, the sample is parked.
+    auto fill = [&](auto cell_lo, auto cell_hi) {
+        int parked = 0, below = 0, inside = 0;  // thresholds <= lo of the current cell; inside it
+        for (int c = 0; c < kLutSize; c++) {
+            const unsigned long long lo = cell_lo(c), hi = cell_hi(c);
+            if (lo > 0xFFFFFFFFull) {  // beyond the reach of a 32-bit sample: never looked up
+                P->lut[c] = 0;
+                continue;
             }
-            P->qlut_ok = 1;
+            while (below < m && P->thr[below] <= (long long)lo) below++;
+            inside = 0;
+            while (below + inside < m && P->thr[below + inside] <= (long long)hi) inside++;
+            const bool park = inside > 0 || (collect && (below & 1));
+            P->lut[c] = park ? 0 : (unsigned char)(below + 1);
+            parked += park;
         }
+        return parked;
+    };
+    const unsigned long long d32 = (unsigned long long)divisor;
+    P->by_q = 0;
+    P->lut_bytes = kLutSize;
+    if (P->mode32 == 3 && 0xFFFFFFFFull / d32 < (unsigned long long)kLutSize) {
+        // index by quotient: exact (no parked cell) when every threshold in reach is a multiple of the divisor
+        const int parked = fill([&](int c) { return (unsigned long long)c * d32; },
+                                [&](int c) { return (unsigned long long)(c + 1) * d32 - 1; });
+        P->by_q = parked == 0 && !collect;
+        if (P->by_q) P->lut_bytes = (int)((0xFFFFFFFFull / d32 + 1 + 127) & ~127ull);  // only the quotients in reach
+    }
+    if (!P->by_q) {
+        // index by shift: the smallest shift that brings the largest threshold a 32-bit sample can reach inside the
+        // table (finer cells park fewer samples); at most 19, where the table spans all of 2^32
+        long long top = 0;
+        for (int j = 0; j < m; j++)
+            if (P->thr[j] <= 0xFFFFFFFFll) top = std::max(top, P->thr[j]);
+        int sh = 0;
+        while (sh < 19 && ((unsigned long long)top >> sh) >= (unsigned long long)kLutSize - 1) sh++;
+        P->lut_shift = sh;
+        fill([&](int c) { return (unsigned long long)c << sh; },
+             [&](int c) { return c == kLutSize - 1 ? 0xFFFFFFFFull : (((unsigned long long)c + 1) << sh) - 1; });
     }
     // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)
     P->divisor = divisor;

@@ -6,10 +6,7 @@
 namespace b200 {
 
 constexpr int kMaxThresholds = 66;      // B200_HIST_MAX_EDGES + slack
-constexpr int kLutCells = 2048;         // log-linear cells: 32 per power of two
-constexpr int kFastCells = 1024;        // fast path (0 <= n < 2^32): 32 cells per power of two
-constexpr int kFastFirst = 127 * 32;    // float bits >> 18 of 1.0f: the first cell's index
-constexpr int kQLutSize = 8192;         // quotient table: bins of q = trunc(n / divisor), q < 8192
+constexpr int kLutSize = 8192;          // cells of the histogram kernel's look-up table
 constexpr int kRadixBits = 12;
 constexpr int kRadixBins = 1 << kRadixBits;
 constexpr int kMaxSelect = 4;           // order statistics resolved per pass
@@ -27,19 +24,7 @@ struct LatMoments {
 struct HistParams {
     long long thr[kMaxThresholds];      // thresholds in raw ns, ascending: count(n) = #{j : thr[j] <= n}
     int nthr;
-    unsigned short lut[kLutCells];      // (base << 8) | extra for each log-linear cell of n >= 0 (generic path)
-    // Fast path (0 <= n < 2^32).  Cell t = (bits(float_rz(n | 1)) >> 18) - kFastFirst: the float's exponent and
-    // top five mantissa bits, i.e. 32 cells per power of two; below 64 a cell is the pair {2k, 2k+1}.
-    //   fast[t].x = (first threshold inside the cell) - 1, or 0xFFFFFFFF if none
-    //   fast[t].z = (second threshold inside the cell) - 1, or 0xFFFFFFFF
-    //   fast[t].w = 128 * #{thresholds <= low end of the cell}: byte offset of the counter row, for kernels that
-    //               compare with .x only; a cell holding two or more thresholds (generic path) has
-    //               128 * (nthr + 1) | 4 instead: bit 2 is the flag, the offset a scratch row
-    //   fast[t].y = the same for kernels that compare with .x and .z (flag from three thresholds up)
-    // so the sample's counter sits at byte offset .w + 128 * (n > .x)  [or .y + 128 * (n > .x) + 128 * (n > .z)]
-    // of the lane's column.
-    uint4 fast[kFastCells];
-    unsigned long long magic;           // division by `divisor` as multiply-high (see lat_kernels.cu)
+    unsigned long long magic;           // division by `divisor` as multiply-high, 64-bit dividends (generic path)
     int magic_shift;
     int magic_add;
     unsigned int magic32;               // the same for 32-bit dividends.  mode32: 0 = divisor 1, 2 = q is 0,
@@ -47,11 +32,14 @@ struct HistParams {
     int pre32;                          //   3: q = umulhi(n >> pre32, magic32) >> shift32, and q < 2^28
     int mode32;
     long long divisor;
-    // Quotient table (valid when qlut_ok): every threshold within reach of a 32-bit sample is a multiple of the
-    // divisor and floor((2^32 - 1) / divisor) < kQLutSize, so the bin of such a sample is qlut[trunc(n / divisor)]
-    // (mode32 == 3 gives the quotient).  Edges given in the divisor's own unit always qualify.
-    int qlut_ok;
-    unsigned char qlut[kQLutSize];
+    // Look-up table for samples 0 <= n < 2^32, indexed by the quotient (by_q: needs mode32 == 3 and fewer than
+    // kLutSize quotients; chosen when it parks nothing, i.e. the thresholds in reach are multiples of the divisor)
+    // or by min(n >> lut_shift, kLutSize - 1).  lut[c] = 1 + #{thresholds <= every sample of cell c}, the counter
+    // row of the cell's samples; 0 when the cell holds a threshold or (collecting) belongs to a kept bin: parked.
+    int by_q;
+    int lut_shift;
+    int lut_bytes;                      // table cells actually in use (a multiple of 128, <= kLutSize)
+    unsigned char lut[kLutSize];
 };
 
 // Optional output of the histogram pass: the samples that fall into an ODD bin (bins are numbered from 0; the
@@ -105,9 +93,9 @@ cudaError_t lat_scratch_init(LatScratch* s);
 void lat_scratch_free(LatScratch* s);
 
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
+// (uploads P to s.d_params first; P must have been built with collect == (collect != nullptr))
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
-                        cudaStream_t stream, int nbins, int mode32 /* HistParams::mode32 */,
-                        const HistCollect* collect = nullptr, bool qlut = false /* HistParams::qlut_ok */);
+                        cudaStream_t stream, const HistParams& P, const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 // *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
@@ -144,6 +132,6 @@ int host_build_hist_params(const double* edges, int nedges, int mode, long long 
 int host_edges_to_thresholds(const double* edges, int nedges, int mode, long long divisor, long long* thr);
 // The same from raw thresholds (strictly ascending int64 ns): bin(n) = #{j : thr[j] <= n}; the divisor only
 // scales the moments.
-int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, HistParams* out);
+int host_build_hist_params_thr(const long long* thr, int nthr, long long divisor, bool collect, HistParams* out);
 
 }  // namespace b200

@@ -1596,8 +1596,9 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     }
     HistParams P;
     // a bracket that starts at INT64_MIN leaves bin 0 empty, which the builder allows (thresholds stay ascending)
-    // the divisor only matters to the moments (stats); the thresholds are raw nanoseconds
-    if (host_build_hist_params_thr(thr, 2 * nb, stats ? divisor : 1, true, &P)) return sampled_trace("skip: thresholds", 1);
+    // the thresholds are raw nanoseconds; the divisor scales the moments (stats) and sets how far the kernel's fast
+    // path reaches (a divisor with a power-of-two part takes samples beyond 2^32 ns in its stride)
+    if (host_build_hist_params_thr(thr, 2 * nb, divisor, true, &P)) return sampled_trace("skip: thresholds", 1);
     // room for twice the expected number of samples inside the brackets, at least n/64; more than n/8 is not worth it
     const size_t expect = (size_t)nk * (2 * margin + 2) * stride;
     const size_t cap = std::min<size_t>(std::max<size_t>(2 * expect, n / 64), n / 8);

@@ -387,12 +387,16 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     unsigned* const mine = tbl + (size_t)warp * rows * 32 + lane;
     const unsigned mine_abs = kCntAbs + (unsigned)(warp * rows * 32 + lane) * 4u;
     const unsigned magic32 = Pg->magic32;
-    const int shift32 = Pg->shift32, pre32 = Pg->pre32, lut_shift = Pg->lut_shift;
+    // DIVMODE 3 works on u = n >> pre32 (the divisor's power-of-two part shifted out of both), so its fast path
+    // reaches n < 2^reach_bits with reach_bits up to 32 + pre32 (2^37 ns = 137 s for milliseconds): the shift is the
+    // funnel shift that splits the sample anyway.  Other modes: u = the low word, reach 2^32.
+    const int shift32 = Pg->shift32, pre = DIVMODE == 3 ? Pg->pre32 : 0, idx_shift = Pg->lut_shift - pre;
+    const int reach_bits = Pg->reach_bits, out_shift = reach_bits - 32;  // outside: (high word >> out_shift) != 0
+    const unsigned u_top = reach_bits - pre >= 32 ? 0xFFFFFFFFu : (1u << (reach_bits - pre)) - 1;  // largest fast-path u
 
-    Moments m;          // generic accumulation (64-bit sums with a carry count)
-    unsigned fsum32 = 0;  // BYQ: a thread's whole share of quotients (each < 2^13) sums in 32 bits (the launcher bounds n)
+    Moments m;          // 64-bit sums with a carry count
     SlowMoments sm_slow;
-    unsigned nhi = 0, nsur = 0, nproc = 0;  // surrogates for samples >= 2^32; all surrogates; fast-path samples
+    unsigned nhi = 0, nsur = 0, nproc = 0;  // surrogates for samples beyond the reach; all surrogates; fast-path samples
 
     // collecting kernels: the warp's staging for kept samples sits past the tile ring
     const unsigned keep_abs = ((kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + 127u) & ~127u) + kRingHeader +
@@ -416,8 +420,8 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         if (lane == 0) *keep.n = 0;
         __syncwarp();
     };
-    auto slow = [&](long long v) {  // parked: outside 32 bits -> everything; else its bin (and collection) only
-        const bool outside = ((unsigned long long)v >> 32) != 0;
+    auto slow = [&](long long v) {  // parked: outside the reach -> everything; else its bin (and collection) only
+        const bool outside = ((unsigned long long)v >> reach_bits) != 0;
         slow_sample(v, sp, mine, MOMENTS && outside ? &sm_slow : nullptr, collecting ? &col : nullptr, keep);
     };
     auto quotient = [&](unsigned u) -> unsigned {
@@ -425,11 +429,19 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             const unsigned t = __umulhi(magic32, u);
             return (t + ((u - t) >> 1)) >> shift32;
         }
-        if (DIVMODE == 3) return __umulhi(u >> pre32, magic32) >> shift32;
+        if (DIVMODE == 3) return __umulhi(u, magic32) >> shift32;  // u is already n >> pre32
         return DIVMODE == 0 ? u : 0u;
     };
     const unsigned last_cell = lut_bytes - 1;
-    auto index_of = [&](unsigned u) -> unsigned { return BYQ ? quotient(u) : min(u >> lut_shift, last_cell); };
+    // q: the quotient when BYQ (kept for the moments), else unused
+    auto index_of = [&](unsigned u, unsigned& q) -> unsigned {
+        if (BYQ) {
+            q = quotient(u);
+            return min(q, last_cell);
+        }
+        return min(u >> idx_shift, last_cell);
+    };
+    auto shifted = [&](unsigned lo, unsigned hi) -> unsigned { return DIVMODE == 3 ? __funnelshift_r(lo, hi, pre) : lo; };
     // (the table is read-only while the kernel counts: a plain asm, so that the eight look-ups of a round are
     // issued together instead of each waiting for the previous sample's counter update)
     auto row_of = [&](unsigned idx) -> unsigned {
@@ -444,15 +456,17 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         m.fsq = sq;
     };
     auto one = [&](long long v) {
-        if ((unsigned long long)v >> 32) { slow(v); return; }
-        const unsigned u = (unsigned)v, idx = index_of(u), row = row_of(idx);
+        if ((unsigned long long)v >> reach_bits) { slow(v); return; }
+        unsigned lo, hi, q = 0;
+        split64(v, lo, hi);
+        const unsigned u = shifted(lo, hi), row = row_of(index_of(u, q));
         if (row == 0) slow(v);  // its bin; the moments below are the fast path's
         bump_abs(mine_abs + (row << 7));
         nproc++;
         if (MOMENTS) {
             m.mn32 = min(m.mn32, u);
             m.mx32 = max(m.mx32, u);
-            accumulate(BYQ ? idx : quotient(u));
+            accumulate(BYQ ? q : quotient(u));
         }
     };
     // Four samples at a time (two such groups per round: eight at once keep too many values alive for the 80
@@ -460,27 +474,29 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     auto four = [&](const longlong2 a, const longlong2 b) {
         constexpr int K = 4;
         const long long v[K] = {a.x, a.y, b.x, b.y};
-        unsigned u[K], hi[K], q[K], row[K], any_hi = 0;
+        unsigned u[K], hi[K], q[K], idx[K], row[K], any_hi = 0;
 #pragma unroll
         for (int k = 0; k < K; k++) {
-            split64(v[k], u[k], hi[k]);
+            unsigned lo;
+            split64(v[k], lo, hi[k]);
+            u[k] = shifted(lo, hi[k]);
             any_hi |= hi[k];
         }
 #pragma unroll
-        for (int k = 0; k < K; k++) q[k] = index_of(u[k]);  // BYQ: the quotient itself
+        for (int k = 0; k < K; k++) idx[k] = index_of(u[k], q[k]);
 #pragma unroll
-        for (int k = 0; k < K; k++) row[k] = row_of(q[k]);
+        for (int k = 0; k < K; k++) row[k] = row_of(idx[k]);
         const unsigned lowest = min(min(row[0], row[1]), min(row[2], row[3]));
-        if (any_hi != 0 || lowest == 0) {  // rare: a few lanes of most rounds
+        if ((any_hi >> out_shift) != 0 || lowest == 0) {  // rare
 #pragma unroll
             for (int k = 0; k < K; k++)
-                if (hi[k] != 0 || row[k] == 0) {
+                if ((hi[k] >> out_shift) != 0 || row[k] == 0) {
                     const unsigned at = atomicAdd(park_n(), 1u);
                     if (at < kParkCap) park_q()[at] = v[k];
                     else slow(v[k]);  // queue full: on the spot
-                    if (hi[k]) {  // the surrogate: clamp to [0, 2^32), counted in the scratch row
+                    if (hi[k] >> out_shift) {  // the surrogate: clamp to the reach, counted in the scratch row
                         const bool neg = (int)hi[k] < 0;
-                        u[k] = neg ? 0u : 0xFFFFFFFFu;
+                        u[k] = neg ? 0u : u_top;
                         if (BYQ) q[k] = quotient(u[k]);
                         row[k] = 0;
                         nhi += !neg;
@@ -495,21 +511,12 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             m.mn32 = min(min(m.mn32, u[2]), u[3]);
             m.mx32 = max(max(m.mx32, u[0]), u[1]);
             m.mx32 = max(max(m.mx32, u[2]), u[3]);
-            if (BYQ) {
-                unsigned s = 0, sq = 0;  // q < 2^13: the squares of a group fit 32 bits
-#pragma unroll
-                for (int k = 0; k < K; k++) {
-                    s += q[k];
-                    sq += q[k] * q[k];
-                }
-                fsum32 += s;
-                m.fsq += sq;  // cannot wrap: < 2^26 per sample
-            } else if (DIVMODE == 3) {  // quotients < 2^28: a group's sum fits 32 bits, its squares 64
+            if (DIVMODE == 3) {  // quotients < 2^28: a group's sum fits 32 bits, its squares 64
                 unsigned s = 0;
                 unsigned long long sq = 0;
 #pragma unroll
                 for (int k = 0; k < K; k++) {
-                    const unsigned qq = quotient(u[k]);
+                    const unsigned qq = BYQ ? q[k] : quotient(u[k]);
                     s += qq;
                     sq += (unsigned long long)qq * qq;
                 }
@@ -543,15 +550,17 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
 
     long long mn = sm_slow.mn, mx = sm_slow.mx;
     if (nproc > nsur) {  // this thread saw genuine fast-path samples
-        mn = (long long)m.mn32 < mn ? (long long)m.mn32 : mn;
-        mx = (long long)m.mx32 > mx ? (long long)m.mx32 : mx;
+        // the extremes were kept of u = n >> pre: as nanoseconds, the bounds with the same quotients
+        const long long lo_ns = (long long)((unsigned long long)m.mn32 << pre);
+        const long long hi_ns = (long long)(((unsigned long long)m.mx32 << pre) | ((1ull << pre) - 1));
+        mn = lo_ns < mn ? lo_ns : mn;
+        mx = hi_ns > mx ? hi_ns : mx;
     }
     U128 sum = sm_slow.sum, sq = sm_slow.sq;
     add128(sum, m.fsum, 0);
-    add128(sum, fsum32, 0);
     add128(sq, m.fsq, m.fsq_carry);
-    if (MOMENTS && nhi) {  // take the surrogates of the samples >= 2^32 out of the sums again: nhi * q(2^32 - 1)
-        const unsigned long long qhi = quotient(0xFFFFFFFFu), q2 = qhi * qhi;
+    if (MOMENTS && nhi) {  // take the surrogates of the samples beyond the reach out of the sums again: nhi * q(u_top)
+        const unsigned long long qhi = quotient(u_top), q2 = qhi * qhi;
         const unsigned long long s_lo = (unsigned long long)nhi * qhi;  // < 2^64
         const unsigned long long p_lo = (unsigned long long)nhi * q2, p_hi = __umul64hi((unsigned long long)nhi, q2);
         const unsigned long long b1 = sum.lo < s_lo;
@@ -997,15 +1006,16 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
     }
     if (!n) return cudaSuccess;
     using Kernel = void (*)(const long long*, size_t, const HistParams*, unsigned long long*, LatMoments*, HistCollect, int);
-    // without moments the quotient is only formed as the table index, so one instantiation serves all shift-indexed modes
+    // without moments the quotient is only formed as the table index, so the shift-indexed modes share an
+    // instantiation — but for mode 3, whose samples are taken shifted by pre32 (longer reach)
     static const Kernel by_shift[2][4] = {
         {hist_kernel<false, 0, false, false>, hist_kernel<false, 0, false, false>, hist_kernel<false, 0, false, false>,
-         hist_kernel<false, 0, false, false>},
+         hist_kernel<false, 3, false, false>},
         {hist_kernel<true, 0, false, false>, hist_kernel<true, 1, false, false>, hist_kernel<true, 2, false, false>,
          hist_kernel<true, 3, false, false>}};
     static const Kernel collecting[2][4] = {  // (a collecting pass is never indexed by quotient: its cells are parked)
         {hist_kernel<false, 0, false, true>, hist_kernel<false, 0, false, true>, hist_kernel<false, 0, false, true>,
-         hist_kernel<false, 0, false, true>},
+         hist_kernel<false, 3, false, true>},
         {hist_kernel<true, 0, false, true>, hist_kernel<true, 1, false, true>, hist_kernel<true, 2, false, true>,
          hist_kernel<true, 3, false, true>}};
     static const Kernel by_q[2] = {hist_kernel<false, 3, true, false>, hist_kernel<true, 3, true, false>};
@@ -1021,16 +1031,10 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
                &nstages);
     const size_t smem = hist_smem(nbins, P.lut_bytes, nstages, collect != nullptr);
     const int max_grid = sm_count() * per_sm;
-    // The quotient-indexed kernel keeps a thread's whole sum of quotients (each < 2^13) in 32 bits: 2^18 samples
-    // per thread at most, so very long inputs go in pieces (counts and moments add up across launches)
-    const size_t piece = P.by_q ? (size_t)max_grid * kHistThreads * ((size_t)1 << 18) : n;
-    for (size_t done = 0; done < n; done += piece) {
-        const size_t m = std::min(piece, n - done);
-        const size_t want_ctas = (m / 2 + kHistThreads - 1) / kHistThreads;
-        const int grid = (int)std::min<size_t>((size_t)max_grid, want_ctas ? want_ctas : 1);
-        k<<<grid, kHistThreads, smem, stream>>>(d_samples + done, m, s.d_params, s.d_counts, s.d_mom,
-                                                collect ? *collect : HistCollect{nullptr, nullptr, 0}, nstages);
-    }
+    const size_t want_ctas = (n / 2 + kHistThreads - 1) / kHistThreads;
+    const int grid = (int)std::min<size_t>((size_t)max_grid, want_ctas ? want_ctas : 1);
+    k<<<grid, kHistThreads, smem, stream>>>(d_samples, n, s.d_params, s.d_counts, s.d_mom,
+                                            collect ? *collect : HistCollect{nullptr, nullptr, 0}, nstages);
     return cudaGetLastError();
 }
 
@@ -1173,25 +1177,30 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
         P->magic32 = (unsigned int)((((unsigned __int128)1 << 32) * ((1ull << l) - d32)) / d32 + 1);
         P->shift32 = l - 1;
         P->mode32 = 1;
-        // Cheaper when it exists: strip the divisor's trailing zero bits first (d = 2^pre * d'), then the dividend
-        // has only 32 - pre bits and a 32-bit magic M = ceil(2^k / d') without fix-up is exact as soon as
-        // (M d' - 2^k) (2^(32-pre) - 1) < 2^k.  Divisors >= 16 also bound the quotient below 2^28, which lets the
-        // kernel sum eight quotients in 32 bits and eight squares in 64.
+        // Cheaper when it exists: take the divisor's trailing zero bits out of divisor and dividend alike (d = 2^pre d',
+        // u = n >> pre, trunc(n / d) = trunc(u / d')); a 32-bit magic M = ceil(2^k / d') without fix-up is exact for all
+        // u < 2^B as soon as (M d' - 2^k) (2^B - 1) < 2^k.  The largest such B <= 32 is taken: the kernel's fast path
+        // then reaches n < 2^(B + pre) (2^37 ns = 137 s for milliseconds, 2^34 ns = 17 s for microseconds) instead of
+        // 2^32.  d' >= 16 also bounds the quotient below 2^28, which lets the kernel sum four quotients in 32 bits
+        // and four squares in 64.
         int pre = 0;
         while (!((d32 >> pre) & 1)) pre++;
         const unsigned long long dp = d32 >> pre;
-        if (d32 >= 16 && dp > 1) {
-            const unsigned __int128 nmax = ((unsigned __int128)1 << (32 - pre)) - 1;
-            for (int post = 0; post < 32; post++) {
-                const unsigned __int128 two_k = (unsigned __int128)1 << (32 + post);
-                const unsigned __int128 M = (two_k + dp - 1) / dp;
-                if (M >> 32) break;
-                if ((M * dp - two_k) * nmax < two_k) {
-                    P->magic32 = (unsigned int)M;
-                    P->shift32 = post;
-                    P->pre32 = pre;
-                    P->mode32 = 3;
-                    break;
+        if (dp >= 16) {
+            for (int B = 32; B >= 32 - pre && P->mode32 != 3; B--) {
+                const unsigned __int128 nmax = ((unsigned __int128)1 << B) - 1;
+                for (int post = 0; post < 32; post++) {
+                    const unsigned __int128 two_k = (unsigned __int128)1 << (32 + post);
+                    const unsigned __int128 M = (two_k + dp - 1) / dp;
+                    if (M >> 32) break;
+                    if ((M * dp - two_k) * nmax < two_k) {
+                        P->magic32 = (unsigned int)M;
+                        P->shift32 = post;
+                        P->pre32 = pre;
+                        P->mode32 = 3;
+                        P->reach_bits = B + pre;
+                        break;
+                    }
                 }
             }
         }
@@ -1199,11 +1208,13 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
     // The look-up table (see hist_kernel).  Cell c covers the samples [lo_c, hi_c]; its entry is 1 + the number of
     // thresholds <= lo_c — the counter row of every sample in the cell — unless a threshold lies inside (lo_c, hi_c]
     // or, when collecting, that bin is odd (kept): then 0, the sample is parked.
+    if (P->mode32 != 3) P->reach_bits = 32;
+    const unsigned long long reach = 1ull << P->reach_bits;  // the fast path takes 0 <= n < reach
     auto fill = [&](auto cell_lo, auto cell_hi) {
         int parked = 0, below = 0, inside = 0;  // thresholds <= lo of the current cell; inside it
         for (int c = 0; c < kLutSize; c++) {
-            const unsigned long long lo = cell_lo(c), hi = cell_hi(c);
-            if (lo > 0xFFFFFFFFull) {  // beyond the reach of a 32-bit sample: never looked up
+            const unsigned long long lo = cell_lo(c), hi = std::min<unsigned long long>(cell_hi(c), reach - 1);
+            if (lo >= reach) {  // beyond the reach of the fast path: never looked up
                 P->lut[c] = 0;
                 continue;
             }
@@ -1217,26 +1228,30 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
         return parked;
     };
     const unsigned long long d32 = (unsigned long long)divisor;
+    const unsigned long long kOpen = ~0ull;  // the last cell takes everything up to the reach
     P->by_q = 0;
     P->lut_bytes = kLutSize;
-    if (P->mode32 == 3 && 0xFFFFFFFFull / d32 < (unsigned long long)kLutSize) {
-        // index by quotient: exact (no parked cell) when every threshold in reach is a multiple of the divisor
+    if (P->mode32 == 3) {
+        // index by quotient (clamped to the last cell): no cell is parked when every threshold in reach is a multiple
+        // of the divisor and lies inside the table; thresholds beyond it (the OpenCensus bounds from 10 s up, in
+        // milliseconds) park the last cell only, i.e. the samples of 8.19 s and more — still the better table
         const int parked = fill([&](int c) { return (unsigned long long)c * d32; },
-                                [&](int c) { return (unsigned long long)(c + 1) * d32 - 1; });
-        P->by_q = parked == 0 && !collect;
-        if (P->by_q) P->lut_bytes = (int)((0xFFFFFFFFull / d32 + 1 + 127) & ~127ull);  // only the quotients in reach
+                                [&](int c) { return c == kLutSize - 1 ? kOpen : (unsigned long long)(c + 1) * d32 - 1; });
+        P->by_q = parked <= 1 && !collect;
+        if (P->by_q) P->lut_bytes = (int)std::min<unsigned long long>(kLutSize, ((reach - 1) / d32 + 1 + 127) & ~127ull);
     }
     if (!P->by_q) {
-        // index by shift: the smallest shift that brings the largest threshold a 32-bit sample can reach inside the
-        // table (finer cells park fewer samples); at most 19, where the table spans all of 2^32
+        // index by shift: the smallest shift (not below pre32: the kernel shifts the pre-shifted sample) that brings
+        // the largest threshold in reach inside the table — finer cells park fewer samples; at most reach_bits - 13,
+        // where the table spans the whole reach
         long long top = 0;
         for (int j = 0; j < m; j++)
-            if (P->thr[j] <= 0xFFFFFFFFll) top = std::max(top, P->thr[j]);
-        int sh = 0;
-        while (sh < 19 && ((unsigned long long)top >> sh) >= (unsigned long long)kLutSize - 1) sh++;
+            if (P->thr[j] >= 0 && (unsigned long long)P->thr[j] < reach) top = std::max(top, P->thr[j]);
+        int sh = P->mode32 == 3 ? P->pre32 : 0;
+        while (sh < P->reach_bits - 13 && ((unsigned long long)top >> sh) >= (unsigned long long)kLutSize - 1) sh++;
         P->lut_shift = sh;
         fill([&](int c) { return (unsigned long long)c << sh; },
-             [&](int c) { return c == kLutSize - 1 ? 0xFFFFFFFFull : (((unsigned long long)c + 1) << sh) - 1; });
+             [&](int c) { return c == kLutSize - 1 ? kOpen : (((unsigned long long)c + 1) << sh) - 1; });
     }
     // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)
     P->divisor = divisor;

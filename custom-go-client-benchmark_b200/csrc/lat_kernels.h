@@ -29,12 +29,13 @@ struct HistParams {
     int magic_add;
     unsigned int magic32;               // the same for 32-bit dividends.  mode32: 0 = divisor 1, 2 = q is 0,
     int shift32;                        //   1: q = (t + ((n - t) >> 1)) >> shift32, t = umulhi(magic32, n)
-    int pre32;                          //   3: q = umulhi(n >> pre32, magic32) >> shift32, and q < 2^28
-    int mode32;
+    int pre32;                          //   3: q = umulhi(n >> pre32, magic32) >> shift32, and q < 2^28,
+    int mode32;                         //      exact for n < 2^reach_bits
+    int reach_bits;                     // the kernel's fast path takes 0 <= n < 2^reach_bits (32; more in mode 3)
     long long divisor;
-    // Look-up table for samples 0 <= n < 2^32, indexed by the quotient (by_q: needs mode32 == 3 and fewer than
-    // kLutSize quotients; chosen when it parks nothing, i.e. the thresholds in reach are multiples of the divisor)
-    // or by min(n >> lut_shift, kLutSize - 1).  lut[c] = 1 + #{thresholds <= every sample of cell c}, the counter
+    // Look-up table for samples 0 <= n < 2^reach_bits, indexed by min(quotient, last cell) (by_q: needs mode32 == 3;
+    // chosen when it parks nothing, i.e. the thresholds in reach are multiples of the divisor and inside the table)
+    // or by min(n >> lut_shift, last cell), lut_shift >= pre32 in mode 3.  lut[c] = 1 + #{thresholds <= every sample of cell c}, the counter
     // row of the cell's samples; 0 when the cell holds a threshold or (collecting) belongs to a kept bin: parked.
     int by_q;
     int lut_shift;

@@ -158,10 +158,27 @@ def bind_to_gpu_numa_node(index: int):
     return "not bound"
 
 
+def pick_device(local_rank, world):
+    """Which visible GPU a rank takes.  The 8-GPU boxes of this pool feed GPUs 0-3 and GPUs 4-7 through two host
+    paths of ~115-140 GB/s each (profiles/r02_h2d_matrix_8gpu.json: any two GPUs copy at 55.5 GB/s each, GPUs 0-3
+    together at 28.8 each), so when fewer ranks than GPUs run they are dealt alternately to the two halves instead
+    of filling the first half.  With one rank, or as many ranks as GPUs, this changes nothing that matters."""
+    try:
+        import ctypes
+        n = ctypes.c_int()
+        lib = importlib.import_module("custom-go-client-benchmark_b200")._lib.load()
+        visible = n.value if lib.b200_device_count(ctypes.byref(n)) == 0 else 0
+    except Exception:
+        visible = 0
+    if world <= 1 or visible <= world or visible % 2:
+        return local_rank
+    return (local_rank % 2) * (visible // 2) + local_rank // 2
+
+
 def dist_setup(n_gpus):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
+    local = pick_device(int(os.environ.get("LOCAL_RANK", "0")), world)
     dist = None
     if world > 1:
         import torch
@@ -550,7 +567,9 @@ def run_b200(args):
                                       "ms_per_step": round(sc_ms, 3),
                                       "what": "the same 4096 buffers in shuffled order: one cudaMemcpyAsync per 2 MiB "
                                               "buffer, no merging of host-contiguous neighbours"},
-                        "pcie_note": "PCIe Gen5 x16 bound (~64 GB/s raw per direction)", "cpu_affinity": affinity},
+                        "pcie_note": "PCIe Gen5 x16 bound (~64 GB/s raw per direction)", "cpu_affinity": affinity,
+                        "cuda_device_of_rank0": local,
+                        "placement": "ranks dealt alternately to the two halves of the visible GPUs (pick_device)"},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                              "frac": round(achieved / peak, 4), "traffic": traffic,

@@ -1,6 +1,17 @@
 // Package crc32c is a drop-in for the part of hash/crc32 that cloud.google.com/go/storage's Reader uses
-// (crc32.New / Update / Checksum with the Castagnoli table), computed on an NVIDIA B200 through
+// (crc32.New / Update / Checksum / MakeTable with the Castagnoli polynomial), computed on an NVIDIA B200 through
 // libb200crc.so (C ABI: include/b200crc.h), plus the batched VerifyObjects and Combine.
+//
+// The hash/crc32 names keep their stdlib signatures, so a file that only uses the Castagnoli table switches over
+// by changing one import line:
+//
+//	import crc32 "github.com/raj-prince/custom-go-client-benchmark/b200/crc32c"
+//	...
+//	crc32cTable := crc32.MakeTable(crc32.Castagnoli)
+//	gotCRC = crc32.Update(gotCRC, crc32cTable, p[:n])
+//
+// As in the standard library these forms cannot return an error; a CUDA failure panics (exactly as Write does).
+// UpdateErr / ChecksumErr / NewErr are the same operations with an error result for callers that want one.
 //
 // NOT COMPILED IN THIS REPOSITORY'S CI: neither the build container nor the GPU box has a Go toolchain.
 // The file is the binding a maintainer adds; the same C entry points are exercised by the Python mirror
@@ -61,8 +72,52 @@ func context() (*C.b200_ctx, error) {
 	return ctx, ctxErr
 }
 
-// Update is crc32.Update(crc, crc32.MakeTable(crc32.Castagnoli), p).
-func Update(crc uint32, p []byte) (uint32, error) {
+// Table is crc32.Table for the one polynomial this package computes.  It carries no data: the tables live on
+// the GPU.
+type Table struct{ poly uint32 }
+
+var castagnoliTable = &Table{poly: Castagnoli}
+
+// MakeTable is crc32.MakeTable.  Only crc32.Castagnoli is available; any other polynomial panics, because a
+// silently different checksum would be worse.
+func MakeTable(poly uint32) *Table {
+	if poly != Castagnoli {
+		panic(fmt.Sprintf("b200crc: only the Castagnoli polynomial (%#x) is computed on the GPU, not %#x", Castagnoli, poly))
+	}
+	return castagnoliTable
+}
+
+func checkTable(tab *Table) {
+	if tab == nil || tab.poly != Castagnoli {
+		panic("b200crc: table must come from MakeTable(Castagnoli)")
+	}
+}
+
+// Update is crc32.Update(crc, tab, p): Update(Update(0, tab, a), tab, b) == Update(0, tab, a+b).
+func Update(crc uint32, tab *Table, p []byte) uint32 {
+	checkTable(tab)
+	out, err := UpdateErr(crc, p)
+	if err != nil {
+		panic(err)
+	}
+	return out
+}
+
+// Checksum is crc32.Checksum(data, tab).
+func Checksum(data []byte, tab *Table) uint32 { return Update(0, tab, data) }
+
+// New is crc32.New(tab): a hash.Hash32 computing CRC-32C.
+func New(tab *Table) hash.Hash32 {
+	checkTable(tab)
+	h, err := NewErr()
+	if err != nil {
+		panic(err)
+	}
+	return h
+}
+
+// UpdateErr is Update with the CUDA status as an error instead of a panic.
+func UpdateErr(crc uint32, p []byte) (uint32, error) {
 	c, err := context()
 	if err != nil {
 		return 0, err
@@ -76,8 +131,8 @@ func Update(crc uint32, p []byte) (uint32, error) {
 	return uint32(out), err
 }
 
-// Checksum is crc32.Checksum(p, castagnoliTable).
-func Checksum(p []byte) (uint32, error) { return Update(0, p) }
+// ChecksumErr is Checksum with an error result.
+func ChecksumErr(p []byte) (uint32, error) { return UpdateErr(0, p) }
 
 // Combine returns the CRC of A||B given crc(A), crc(B) and len(B).  Pure host arithmetic.
 func Combine(crc1, crc2 uint32, len2 int64) uint32 {
@@ -86,8 +141,8 @@ func Combine(crc1, crc2 uint32, len2 int64) uint32 {
 
 type digest struct{ h *C.b200_hasher }
 
-// New returns a hash.Hash32 computing CRC-32C, as crc32.New(crc32.MakeTable(crc32.Castagnoli)) does.
-func New() (hash.Hash32, error) {
+// NewErr is New with an error result.
+func NewErr() (hash.Hash32, error) {
 	c, err := context()
 	if err != nil {
 		return nil, err

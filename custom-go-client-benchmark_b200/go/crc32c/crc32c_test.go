@@ -26,7 +26,7 @@ func TestKnownAnswers(t *testing.T) {
 		in   string
 		want uint32
 	}{{"", 0}, {"a", 0xC1D04330}, {"123456789", 0xE3069283}} {
-		got, err := Checksum([]byte(c.in))
+		got, err := ChecksumErr([]byte(c.in))
 		if err != nil || got != c.want {
 			t.Fatalf("Checksum(%q) = %#x, %v; want %#x", c.in, got, err, c.want)
 		}
@@ -44,7 +44,7 @@ func TestUpdateMatchesStdlibOnAnySplit(t *testing.T) {
 			n = len(data) - off
 		}
 		var err error
-		if crc, err = Update(crc, data[off:off+n]); err != nil {
+		if crc, err = UpdateErr(crc, data[off:off+n]); err != nil {
 			t.Fatal(err)
 		}
 		off += n
@@ -55,7 +55,7 @@ func TestUpdateMatchesStdlibOnAnySplit(t *testing.T) {
 }
 
 func TestHash32Interface(t *testing.T) {
-	h, err := New()
+	h, err := NewErr()
 	if err != nil {
 		t.Fatal(err)
 	}
@@ -115,4 +115,33 @@ func TestXGoogHash(t *testing.T) {
 	if v, ok := DecodeXGoogHash("md5=XrY7u+Ae7tCTyyK7j1rNww==, crc32c=4waSgw=="); !ok || v != 0xE3069283 {
 		t.Fatalf("DecodeXGoogHash = %#x, %v", v, ok)
 	}
+}
+
+// The stdlib-shaped forms: the same expressions a caller of hash/crc32 writes, with this package under the
+// import alias crc32 (here: unqualified), must give what hash/crc32 gives.
+func TestStdlibSignatures(t *testing.T) {
+	tab := MakeTable(Castagnoli)
+	data := payload(3<<20+17, 7)
+	if got, want := Checksum(data, tab), crc32.Checksum(data, castagnoli); got != want {
+		t.Fatalf("Checksum = %#x, want %#x", got, want)
+	}
+	if got, want := Update(Update(0, tab, data[:1000]), tab, data[1000:]), crc32.Checksum(data, castagnoli); got != want {
+		t.Fatalf("Update chain = %#x, want %#x", got, want)
+	}
+	var h hash32 = New(tab)
+	h.Write(data)
+	if got, want := h.Sum32(), crc32.Checksum(data, castagnoli); got != want {
+		t.Fatalf("New(tab).Sum32 = %#x, want %#x", got, want)
+	}
+	defer func() {
+		if recover() == nil {
+			t.Fatal("MakeTable(IEEE) must panic: only Castagnoli is computed")
+		}
+	}()
+	MakeTable(crc32.IEEE)
+}
+
+type hash32 interface {
+	io.Writer
+	Sum32() uint32
 }

@@ -86,6 +86,8 @@ struct DevState {
     cudaEvent_t ev_timer[2] = {nullptr, nullptr};
     SideStream side{};  // second compute stream: row kernel next to the fold kernel
     LatScratch lat{};
+    unsigned long long* text_scratch = nullptr;  // b200_parse_latency_text: line ranks and start masks (grow-only)
+    size_t text_scratch_cap = 0;                 // in 64-bit words
     HostSlab slab[2];
 };
 
@@ -504,6 +506,7 @@ int b200_shutdown(b200_ctx* ctx) {
         cudaFree(d->d_nbad);
         cudaFreeHost(d->h_got);
         lat_scratch_free(&d->lat);
+        cudaFree(d->text_scratch);
         d->slab[0].release();
         d->slab[1].release();
         for (int b = 0; b < 2; b++) {
@@ -1777,17 +1780,29 @@ int b200_parse_latency_text(b200_ctx* ctx, int dev, const void* d_text, size_t n
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
     const size_t ntiles = text_tiles(nbytes);
-    unsigned long long *tiles = nullptr, *summary = nullptr;
-    CU(cudaMalloc(&tiles, (ntiles + 1) * sizeof(unsigned long long)));
-    cudaError_t e = cudaMalloc(&summary, 3 * sizeof(unsigned long long));
-    if (e == cudaSuccess)
-        e = launch_text_parse((const unsigned char*)d_text, nbytes, d_values, d_status, max_lines, tiles, summary, d->stream);
+    // scratch kept between calls (cudaMalloc + cudaFree of a few tens of MB cost more than the parse itself);
+    // three words in front hold the summary
+    const size_t need = 4 + text_scratch_words(nbytes);
+    if (need > d->text_scratch_cap) {
+        cudaFree(d->text_scratch);
+        d->text_scratch = nullptr;
+        d->text_scratch_cap = 0;
+        const size_t room = need + need / 4;
+        cudaError_t ea = cudaMalloc(&d->text_scratch, room * sizeof(unsigned long long));
+        if (ea == cudaErrorMemoryAllocation) {
+            cudaGetLastError();
+            return fail(B200_ERR_NOMEM, "b200_parse_latency_text: scratch");
+        }
+        CU(ea);
+        d->text_scratch_cap = room;
+    }
+    unsigned long long *summary = d->text_scratch, *tiles = d->text_scratch + 4;
+    cudaError_t e = launch_text_parse((const unsigned char*)d_text, nbytes, d_values, d_status, max_lines, tiles, summary,
+                                      d->stream);
     unsigned long long total = 0, sum3[3] = {~0ull, 0, 0};
     if (e == cudaSuccess) e = cudaMemcpyAsync(&total, tiles + ntiles, sizeof total, cudaMemcpyDeviceToHost, d->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(sum3, summary, sizeof sum3, cudaMemcpyDeviceToHost, d->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(d->stream);
-    cudaFree(tiles);
-    cudaFree(summary);
     if (e != cudaSuccess) return fail_cuda(e, "b200_parse_latency_text");
     if (nlines) *nlines = total;
     if (first_bad_line) *first_bad_line = sum3[0];

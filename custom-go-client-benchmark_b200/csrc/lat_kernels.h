@@ -117,9 +117,10 @@ cudaError_t launch_compact(const long long* d_samples, size_t n, unsigned long l
                            const LatScratch& s, cudaStream_t stream);
 
 // Latency text codec + float64 histogram (text_kernels.cu)
-size_t text_tiles(size_t nbytes);
+size_t text_tiles(size_t nbytes);          // the number of lines ends up in d_scratch[text_tiles(n)]
+size_t text_scratch_words(size_t nbytes);  // 64-bit words of scratch the parse needs
 cudaError_t launch_text_parse(const unsigned char* d_text, size_t n, double* d_values, unsigned char* d_status,
-                              size_t max_lines, unsigned long long* d_tiles /* text_tiles(n)+1 */,
+                              size_t max_lines, unsigned long long* d_scratch /* text_scratch_words(n) */,
                               unsigned long long* d_summary /* [3] */, cudaStream_t stream);
 int hist_f64_grid();
 cudaError_t launch_hist_f64(const double* d_x, size_t n, const double* edges, int nedges, int mode,

@@ -69,26 +69,70 @@ __device__ __forceinline__ bool line_ends_at(const Text& t, size_t n, size_t i) 
     return t[i] == '\n' || (t[i] == '\r' && (i + 1 >= n || t[i + 1] != '\n'));
 }
 
-// bit k of the result: a line starts at byte base + k (k < 16)
-template <typename Text>
-__device__ __forceinline__ unsigned start_mask(const Text& t, size_t n, size_t base) {
-    unsigned m = 0;
-    if (base >= n) return 0;
+// ---- line starts, sixteen bytes at a time (SWAR on four little-endian words) ----------------------------------
+// 0x80 in every byte of w that equals c (exact, no carries between bytes)
+__device__ __forceinline__ unsigned eq_flags(unsigned w, unsigned c4) {
+    const unsigned x = w ^ c4;
+    return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);
+}
+// Bit k of the result: a line starts at byte k of the window w[0..3] (Python's universal newlines: a line starts
+// after "\n", and after a "\r" that is not followed by "\n").  prev: the byte before the window (0x0A in front
+// of the very first byte of the text).  Only the first `valid` bytes count.
+__device__ __forceinline__ unsigned window_starts(const unsigned w[4], unsigned prev, int valid) {
+    unsigned nl[4], cr[4], anycr = 0;
 #pragma unroll
-    for (int k = 0; k < 16; k++) {
-        size_t i = base + k;
-        if (i < n && (i == 0 || line_ends_at(t, n, i - 1))) m |= 1u << k;
+    for (int j = 0; j < 4; j++) {
+        nl[j] = eq_flags(w[j], 0x0A0A0A0Au);
+        cr[j] = eq_flags(w[j], 0x0D0D0D0Du);
+        anycr |= cr[j];
     }
-    return m;
+    const unsigned pnl = prev == '\n' ? 0x80000000u : 0u, pcr = prev == '\r' ? 0x80000000u : 0u;
+    unsigned m = 0;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        // flags of the PREVIOUS byte, moved onto this byte's position
+        const unsigned nlp = __funnelshift_l(j ? nl[j - 1] : pnl, nl[j], 8);
+        unsigned st = nlp;
+        if (anycr | pcr) st |= __funnelshift_l(j ? cr[j - 1] : pcr, cr[j], 8) & ~nl[j];
+        // gather the four flag bits (7, 15, 23, 31) into a nibble: the products land on distinct bits
+        m |= ((((st >> 7) & 0x01010101u) * 0x00204081u >> 21) & 0xFu) << (4 * j);
+    }
+    return valid >= 16 ? m : (valid <= 0 ? 0u : m & ((1u << valid) - 1u));
+}
+// sixteen bytes of text at `base` as four words (zero beyond the end); g must be readable at [base, n)
+__device__ __forceinline__ void load_window(const unsigned char* __restrict__ g, size_t n, size_t base, unsigned w[4]) {
+    if (base + 16 <= n && ((reinterpret_cast<uintptr_t>(g) + base) & 15) == 0) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(g + base));
+        w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w;
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        w[j] = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const size_t i = base + 4 * j + k;
+            if (i < n) w[j] |= (unsigned)__ldg(g + i) << (8 * k);
+        }
+    }
 }
 
+// Pass 1: where the lines start.  One 16-bit mask per 16-byte window (kept for pass 3, which then need not look at
+// the bytes again to find its lines) and the number of line starts per tile.
 __global__ void __launch_bounds__(kTextThreads)
-text_count_kernel(const unsigned char* __restrict__ tg, size_t n, unsigned long long* __restrict__ tile_counts) {
+text_count_kernel(const unsigned char* __restrict__ tg, size_t n, unsigned long long* __restrict__ tile_counts,
+                  unsigned short* __restrict__ masks) {
     __shared__ unsigned wsum[kTextThreads / 32];
-    __shared__ __align__(16) unsigned char stage[kTileBytes + kHalo + 16];
-    const TextView t = stage_tile(tg, n, blockIdx.x, stage);
-    const size_t base = ((size_t)blockIdx.x * kTextThreads + threadIdx.x) * 16;
-    unsigned c = __popc(start_mask(t, n, base));
+    const size_t win = (size_t)blockIdx.x * kTextThreads + threadIdx.x, base = win * 16;
+    unsigned m = 0;
+    if (base < n) {
+        unsigned w[4];
+        load_window(tg, n, base, w);
+        const unsigned prev = base ? __ldg(tg + base - 1) : '\n';
+        m = window_starts(w, prev, (int)(n - base < 16 ? n - base : 16));
+    }
+    masks[win] = (unsigned short)m;
+    unsigned c = __popc(m);
 #pragma unroll
     for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xFFFFFFFFu, c, d);
     if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = c;
@@ -100,31 +144,59 @@ text_count_kernel(const unsigned char* __restrict__ tg, size_t n, unsigned long 
     }
 }
 
-// exclusive scan of tile counts in place (one CTA); total goes to tile_counts[ntiles]
-__global__ void __launch_bounds__(1024) text_scan_kernel(unsigned long long* __restrict__ tile_counts, size_t ntiles) {
-    __shared__ unsigned long long part[1024];
-    const size_t per = (ntiles + 1023) / 1024;
-    const size_t lo = (size_t)threadIdx.x * per, hi = lo + per < ntiles ? lo + per : ntiles;
-    unsigned long long s = 0;
-    for (size_t i = lo; i < hi; i++) s += tile_counts[i];
-    part[threadIdx.x] = s;
+// inclusive scan over the 1024 threads of a CTA; *excl_base receives the exclusive prefix of the caller's warp
+__device__ __forceinline__ unsigned long long block_scan_1024(unsigned long long v, unsigned long long* wtot,
+                                                              unsigned long long* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) wtot[warp] = incl;
     __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned long long run = 0;
-        for (int i = 0; i < 1024; i++) {
-            unsigned long long v = part[i];
-            part[i] = run;
-            run += v;
+    if (warp == 0) {
+        const unsigned long long t = wtot[lane];
+        unsigned long long in2 = t;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, in2, d);
+            if (lane >= d) in2 += o;
         }
-        tile_counts[ntiles] = run;
+        wtot[lane] = in2 - t;
+        if (lane == 31) *total = in2;
     }
     __syncthreads();
-    unsigned long long run = part[threadIdx.x];
-    for (size_t i = lo; i < hi; i++) {
-        unsigned long long v = tile_counts[i];
-        tile_counts[i] = run;
-        run += v;
+    return wtot[warp] + incl - v;  // exclusive
+}
+
+// Pass 2a: exclusive scan of the tile counts inside blocks of kScanBlock tiles (in place, coalesced); the block
+// totals go to aux[].  Pass 2b: one CTA scans aux[] (exclusive, in place) and leaves the number of lines in
+// *total.  The rank of a tile's first line is tile_counts[tile] + aux[tile / kScanBlock].
+constexpr int kScanBlock = 1024;
+__global__ void __launch_bounds__(kScanBlock)
+text_scan_local_kernel(unsigned long long* __restrict__ tile_counts, size_t ntiles, unsigned long long* __restrict__ aux) {
+    __shared__ unsigned long long wtot[32], tot;
+    const size_t i = (size_t)blockIdx.x * kScanBlock + threadIdx.x;
+    const unsigned long long v = i < ntiles ? tile_counts[i] : 0;
+    const unsigned long long excl = block_scan_1024(v, wtot, &tot);
+    if (i < ntiles) tile_counts[i] = excl;
+    if (threadIdx.x == 0) aux[blockIdx.x] = tot;
+}
+__global__ void __launch_bounds__(kScanBlock)
+text_scan_aux_kernel(unsigned long long* __restrict__ aux, size_t nblocks, unsigned long long* __restrict__ total) {
+    __shared__ unsigned long long wtot[32], tot;
+    unsigned long long carry = 0;
+    for (size_t c0 = 0; c0 < nblocks; c0 += kScanBlock) {  // 1024 blocks (a 4 GB text) per round
+        const size_t i = c0 + threadIdx.x;
+        const unsigned long long v = i < nblocks ? aux[i] : 0;
+        const unsigned long long excl = block_scan_1024(v, wtot, &tot);
+        if (i < nblocks) aux[i] = carry + excl;
+        carry += tot;
+        __syncthreads();  // tot and wtot are rewritten next round
     }
+    if (threadIdx.x == 0) *total = carry;
 }
 
 struct Parsed {
@@ -248,15 +320,89 @@ __device__ Parsed parse_float(const Text& t, size_t n, size_t s) {
     return r;
 }
 
+// bytes kept of a word holding k leading digits (k clamped to 0..4)
+__constant__ unsigned c_keep[5] = {0u, 0xFFu, 0xFFFFu, 0xFFFFFFu, 0xFFFFFFFFu};
+
+// 0x80 in every byte of w that is NOT an ASCII digit (w must be ASCII: no byte >= 0x80)
+__device__ __forceinline__ unsigned nondigit_flags(unsigned w) {
+    const unsigned x = w ^ 0x30303030u;  // digits -> 0..9
+    return (x + 0x76767676u) & 0x80808080u;  // x >= 10 (x <= 0x7F: no carry into the next byte)
+}
+// the number spelled by the four ASCII digits of w, first character in the low byte
+__device__ __forceinline__ unsigned four_digits(unsigned w) {
+    const unsigned d = w - 0x30303030u;
+    const unsigned t = d * 10u + (d >> 8);  // byte 0: d0*10 + d1, byte 2: d2*10 + d3 (each <= 99: no carries)
+    return (t & 0xFFu) * 100u + ((t >> 16) & 0xFFu);
+}
+
+// The common line, without a loop over its characters: [1-4 digits] [. 0-11 digits] [spaces] "\n", all inside
+// the 16 bytes w[0..3] that start at the line start (what Go's Duration.String() leaves after `tr 'ms' ' '` for
+// anything from 1 ms to 9 s).  The digits are taken four at a time (SWAR), the significand is the integer
+// int * 10^12 + fraction padded to twelve digits (< 2^53), and the value is that integer divided by 10^12: one
+// correctly rounded IEEE division of two exact doubles, hence the same double Python's float() gives.  tail(i):
+// byte i of the line, for the few bytes after the digits.  Returns false when the line is anything else (the
+// caller then takes the character-by-character parser).
+template <typename Tail>
+__device__ __forceinline__ bool parse_fast(const unsigned w[4], Tail tail, double* out) {
+    if ((w[0] | w[1] | w[2] | w[3]) & 0x80808080u) return false;  // not ASCII
+    const unsigned nd0 = nondigit_flags(w[0]);
+    int ni;  // digits before the first other character
+    if (nd0) ni = (__ffs(nd0) >> 3) - 1;
+    else if (nondigit_flags(w[1]) & 0x80u) ni = 4;
+    else return false;
+    if (ni < 1) return false;
+    const unsigned after = __funnelshift_rc(w[0], w[1], 8 * ni) & 0xFFu;  // the character after the integer part
+    const unsigned iw = __funnelshift_rc(0x30303030u, w[0], 8 * ni);       // its last four digits, '0'-padded in front
+    int end = ni;  // where the digits end
+    unsigned f0 = 0x30303030u, f1 = 0x30303030u, f2 = 0x30303030u;
+    if (after == '.') {
+        const int s = ni + 1;  // 2..5
+        const bool hiw = s >= 4;
+        const unsigned a0 = hiw ? w[1] : w[0], a1 = hiw ? w[2] : w[1], a2 = hiw ? w[3] : w[2], a3 = hiw ? 0u : w[3];
+        const int sh = 8 * (s & 3);
+        f0 = __funnelshift_r(a0, a1, sh);
+        f1 = __funnelshift_r(a1, a2, sh);
+        f2 = __funnelshift_r(a2, a3, sh);
+        const unsigned n0 = nondigit_flags(f0), n1 = nondigit_flags(f1), n2 = nondigit_flags(f2);
+        int nf;
+        if (n0) nf = (__ffs(n0) >> 3) - 1;
+        else if (n1) nf = 4 + (__ffs(n1) >> 3) - 1;
+        else if (n2) nf = 8 + (__ffs(n2) >> 3) - 1;
+        else return false;  // twelve or more fraction digits
+        const unsigned k0 = c_keep[min(nf, 4)], k1 = c_keep[min(max(nf - 4, 0), 4)], k2 = c_keep[min(max(nf - 8, 0), 4)];
+        f0 = (f0 & k0) | (0x30303030u & ~k0);
+        f1 = (f1 & k1) | (0x30303030u & ~k1);
+        f2 = (f2 & k2) | (0x30303030u & ~k2);
+        end = s + nf;
+    }
+    // after the digits: spaces, then the line feed (anything else, a carriage return included: the other parser)
+    for (int i = end;; i++) {
+        if (i >= 16) return false;
+        const unsigned c = tail(i);
+        if (c == '\n') break;
+        if (c != ' ') return false;
+    }
+    const unsigned ip = four_digits(iw);
+    if (ip >= 9007u) return false;  // the significand below must stay under 2^53
+    const unsigned hi8 = ip * 10000u + four_digits(f0);                // < 10^8
+    const unsigned lo8 = four_digits(f1) * 10000u + four_digits(f2);  // < 10^8
+    const unsigned long long mant = (unsigned long long)hi8 * 100000000ull + lo8;
+    *out = (double)mant / 1e12;
+    return true;
+}
+
 __global__ void __launch_bounds__(kTextThreads)
 text_parse_kernel(const unsigned char* __restrict__ tg, size_t n, const unsigned long long* __restrict__ tile_base,
+                  const unsigned long long* __restrict__ aux, const unsigned short* __restrict__ masks,
                   double* __restrict__ values, unsigned char* __restrict__ status, size_t max_lines,
                   unsigned long long* __restrict__ summary /* [0] first bad line, [1] bad count, [2] inexact count */) {
     __shared__ unsigned wsum[kTextThreads / 32];
+    __shared__ unsigned short starts[kTileBytes];  // offsets (from the tile's first byte) of the lines that start in it
     __shared__ __align__(16) unsigned char stage[kTileBytes + kHalo + 16];
     const TextView t = stage_tile(tg, n, blockIdx.x, stage);
-    const size_t base = ((size_t)blockIdx.x * kTextThreads + threadIdx.x) * 16;
-    const unsigned m = start_mask(t, n, base);
+    const size_t tbase = (size_t)blockIdx.x * kTileBytes;
+    const unsigned char* const tile = stage + (tbase - t.sbase);  // byte 0 of the tile in shared memory
+    const unsigned m = masks[(size_t)blockIdx.x * kTextThreads + threadIdx.x];  // this window's line starts (pass 1)
     const unsigned c = __popc(m);
     unsigned incl = c;
 #pragma unroll
@@ -266,23 +412,45 @@ text_parse_kernel(const unsigned char* __restrict__ tg, size_t n, const unsigned
     }
     if ((threadIdx.x & 31) == 31) wsum[threadIdx.x >> 5] = incl;
     __syncthreads();
-    unsigned wbase = 0;
-    for (int w = 0; w < (int)(threadIdx.x >> 5); w++) wbase += wsum[w];
-    unsigned long long rank = tile_base[blockIdx.x] + wbase + incl - c;
-    unsigned mm = m;
+    unsigned wbase = 0, total = 0;
+    for (int w = 0; w < kTextThreads / 32; w++) {
+        if (w < (int)(threadIdx.x >> 5)) wbase += wsum[w];
+        total += wsum[w];
+    }
+    // the line starts of the tile, in order: lines are then dealt to the threads evenly (a thread parsing the
+    // starts of its own window has none, one or two of them and the warp waits for the lane with the most)
+    unsigned at = wbase + incl - c, mm = m;
     while (mm) {
         const int k = __ffs(mm) - 1;
         mm &= mm - 1;
-        if (rank < max_lines) {
-            Parsed p = parse_float(t, n, base + k);
-            values[rank] = p.v;
-            if (status) status[rank] = p.status;
-            if (p.status) {
-                atomicMin(summary, rank);
-                atomicAdd(summary + (p.status == 1 ? 1 : 2), 1ull);
-            }
+        starts[at++] = (unsigned short)(threadIdx.x * 16 + k);
+    }
+    __syncthreads();
+    const unsigned long long rank0 = tile_base[blockIdx.x] + aux[blockIdx.x / kScanBlock];
+    const size_t staged_end = t.send;
+    for (unsigned l = threadIdx.x; l < total; l += kTextThreads) {
+        const unsigned long long rank = rank0 + l;
+        if (rank >= max_lines) break;
+        const unsigned off = starts[l];
+        const size_t pos = tbase + off;
+        Parsed p{0.0, 1};
+        bool done = false;
+        if (pos + 20 <= staged_end) {  // sixteen bytes from the line start, read as aligned words and shifted into place
+            const unsigned* aw = reinterpret_cast<const unsigned*>(tile + (off & ~3u));
+            const int sh = 8 * (off & 3);
+            unsigned w[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) w[j] = __funnelshift_r(aw[j], aw[j + 1], sh);
+            done = parse_fast(w, [&](int i) -> unsigned { return tile[off + i]; }, &p.v);
+            if (done) p.status = 0;
         }
-        rank++;
+        if (!done) p = parse_float(t, n, pos);
+        values[rank] = p.v;
+        if (status) status[rank] = p.status;
+        if (p.status) {
+            atomicMin(summary, rank);
+            atomicAdd(summary + (p.status == 1 ? 1 : 2), 1ull);
+        }
     }
 }
 
@@ -340,22 +508,31 @@ hist_f64_kernel(const double* __restrict__ x, size_t n, F64Params P, unsigned lo
 
 }  // namespace
 
+// scratch: [0, ntiles) tile counts / ranks, [ntiles] the number of lines, then the scan's block totals, then the
+// windows' line-start masks (16 bits per 16 bytes of text)
+size_t text_tiles(size_t nbytes) { return (nbytes + kTileBytes - 1) / kTileBytes; }
+size_t text_scratch_words(size_t nbytes) {
+    const size_t ntiles = text_tiles(nbytes), nblocks = (ntiles + kScanBlock - 1) / kScanBlock;
+    return ntiles + 1 + nblocks + (ntiles * kTextThreads * sizeof(unsigned short) + 7) / 8 + 1;
+}
+
 cudaError_t launch_text_parse(const unsigned char* d_text, size_t n, double* d_values, unsigned char* d_status,
-                              size_t max_lines, unsigned long long* d_tiles /* ntiles+1 */, unsigned long long* d_summary,
-                              cudaStream_t stream) {
-    const size_t ntiles = (n + kTileBytes - 1) / kTileBytes;
+                              size_t max_lines, unsigned long long* d_scratch /* text_scratch_words(n) */,
+                              unsigned long long* d_summary, cudaStream_t stream) {
+    const size_t ntiles = text_tiles(n), nblocks = (ntiles + kScanBlock - 1) / kScanBlock;
     unsigned long long init[3] = {~0ull, 0, 0};
     cudaError_t e = cudaMemcpyAsync(d_summary, init, sizeof init, cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
-    if (!ntiles) return cudaMemsetAsync(d_tiles, 0, sizeof(unsigned long long), stream);
-    text_count_kernel<<<(unsigned)ntiles, kTextThreads, 0, stream>>>(d_text, n, d_tiles);
-    text_scan_kernel<<<1, 1024, 0, stream>>>(d_tiles, ntiles);
-    text_parse_kernel<<<(unsigned)ntiles, kTextThreads, 0, stream>>>(d_text, n, d_tiles, d_values, d_status, max_lines,
-                                                                      d_summary);
+    if (!ntiles) return cudaMemsetAsync(d_scratch, 0, sizeof(unsigned long long), stream);
+    unsigned long long* const aux = d_scratch + ntiles + 1;
+    unsigned short* const masks = reinterpret_cast<unsigned short*>(aux + nblocks);
+    text_count_kernel<<<(unsigned)ntiles, kTextThreads, 0, stream>>>(d_text, n, d_scratch, masks);
+    text_scan_local_kernel<<<(unsigned)nblocks, kScanBlock, 0, stream>>>(d_scratch, ntiles, aux);
+    text_scan_aux_kernel<<<1, kScanBlock, 0, stream>>>(aux, nblocks, d_scratch + ntiles);
+    text_parse_kernel<<<(unsigned)ntiles, kTextThreads, 0, stream>>>(d_text, n, d_scratch, aux, masks, d_values, d_status,
+                                                                      max_lines, d_summary);
     return cudaGetLastError();
 }
-
-size_t text_tiles(size_t nbytes) { return (nbytes + kTileBytes - 1) / kTileBytes; }
 
 int hist_f64_grid() {
     int dev = 0, sms = 148;

@@ -4,9 +4,16 @@ distinct kernel past its warm-up launch.  usage: python tools/summarize_all_kern
 import csv, os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 rnd = sys.argv[1] if len(sys.argv) > 1 else "r02"
-rows = list(csv.reader(open(os.path.join(ROOT, "gpurun_out", f"{rnd}_all_raw.csv"))))
-hdr, vals = rows[0], rows[2:]
-col = {h: i for i, h in enumerate(hdr)}
+# one or two captures (the second, <round>_b_raw.csv, holds the kernels the first one's launch budget did not reach);
+# each row becomes a dict metric -> (value, unit)
+vals = []
+for name in (f"{rnd}_all_raw.csv", f"{rnd}_b_raw.csv"):
+    path = os.path.join(ROOT, "gpurun_out", name)
+    if os.path.exists(path):
+        rr = list(csv.reader(open(path)))
+        vals += [{h: (x, u) for h, x, u in zip(rr[0], r, rr[1])} for r in rr[2:]]
+col = {h: h for h in set().union(*[set(v) for v in vals])}
+rows = [None, {h: "" for h in col}]
 keep = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__throughput.avg.pct_of_peak_sustained_elapsed",
         "smsp__issue_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active",
@@ -20,7 +27,17 @@ keep = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
         "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio"]
-keep = [k for k in keep if k in col]
+keep = [k for k in keep if all(k in v for v in vals)]
+
+
+class Row(dict):  # v[col[m]] -> the value string
+    def __getitem__(self, m):
+        return dict.__getitem__(self, m)[0]
+
+
+units = {m: vals[0][m][1] for m in vals[0]}
+vals = [Row(v) for v in vals]
+rows[1] = units
 
 
 def short(n):
@@ -43,9 +60,10 @@ lines = ["| kernel (grid) | us | DRAM GB/s | DRAM % | L1/smem % | issue % | inst
          "|---|---|---|---|---|---|---|---|---|---|"]
 for k, v in picked:
     g = lambda m: float(v[col[m]].replace(",", "")) if m in col and v[col[m]] not in ("", "n/a") else float("nan")
-    tscale = {"ms": 1e3, "us": 1.0, "ns": 1e-3, "s": 1e6}[rows[1][col["gpu__time_duration.sum"]]]
+    unit_of = lambda m: dict.__getitem__(v, m)[1]
+    tscale = {"ms": 1e3, "us": 1.0, "ns": 1e-3, "s": 1e6}[unit_of("gpu__time_duration.sum")]
     us = g("gpu__time_duration.sum") * tscale
-    bscale = lambda m: {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[rows[1][col[m]]]
+    bscale = lambda m: {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[unit_of(m)]
     nbytes = g("dram__bytes_read.sum") * bscale("dram__bytes_read.sum") + g("dram__bytes_write.sum") * bscale("dram__bytes_write.sum")
     lines.append(f"| `{k}` | {us:.1f} | {nbytes / us / 1e3:.0f} | {g('gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'):.0f} | "
                  f"{g('l1tex__throughput.avg.pct_of_peak_sustained_elapsed'):.0f} | {g('smsp__issue_active.avg.pct_of_peak_sustained_active'):.0f} | "

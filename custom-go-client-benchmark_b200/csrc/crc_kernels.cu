@@ -19,6 +19,10 @@
 //   unaligned head and sub-row tail bytes, init/final inversion, comparison with want[].
 #include "crc_kernels.h"
 
+#ifdef B200_DEBUG_ASSERT
+#include <cassert>
+#endif
+
 #include <cstdlib>
 
 namespace b200 {
@@ -35,12 +39,26 @@ constexpr uint32_t kAdv4Abs = 0x1000;     // absolute shared address of the 4 KB
 
 extern __shared__ __align__(1024) uint8_t smem_raw[];
 
+// B200_DEBUG_ASSERT builds: the absolute shared-memory addresses of the table look-ups are checked against the
+// CTA's dynamic window (compute-sanitizer is closed on this pool).
+#ifdef B200_DEBUG_ASSERT
+__device__ __forceinline__ void check_tab(uint32_t addr) {
+    uint32_t size;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(size));
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(smem_raw);
+    assert(addr >= kTabAbs && addr + 4 <= kTabAbs + kTabBytes && addr + 4 <= base + size && (addr & 3) == 0);
+}
+#else
+__device__ __forceinline__ void check_tab(uint32_t) {}
+#endif
+
 // A^512 applied to a column register.  lanew = 0x00010000 | lane*4: byte 0 = lane*4, byte 2 = 1, byte 3 = 0.
 __device__ __forceinline__ uint32_t adv_row(uint32_t x, uint32_t lanew) {
     uint32_t o0 = __byte_perm(x, lanew, 0x7604);  // [lane*4, byte0(x), 0x01, 0x00]
     uint32_t o1 = __byte_perm(x, lanew, 0x7614);
     uint32_t o2 = __byte_perm(x, lanew, 0x7624);
     uint32_t o3 = __byte_perm(x, lanew, 0x7634);
+    check_tab(o0); check_tab(o1 + 128); check_tab(o2 + 65536); check_tab(o3 + 65664);
     uint32_t t0, t1, t2, t3;
     asm volatile("ld.shared.u32 %0, [%1];" : "=r"(t0) : "r"(o0));
     asm volatile("ld.shared.u32 %0, [%1+128];" : "=r"(t1) : "r"(o1));

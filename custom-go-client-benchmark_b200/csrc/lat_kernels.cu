@@ -14,6 +14,10 @@
 // (warp, lane) in shared memory so the skewed latency distribution causes no atomic contention.
 #include "lat_kernels.h"
 
+#ifdef B200_DEBUG_ASSERT
+#include <cassert>
+#endif
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -159,6 +163,20 @@ static_assert(sizeof(SlowParams) <= 640, "SlowParams slot");
 
 extern __shared__ __align__(1024) unsigned char hist_smem_raw[];
 
+// B200_DEBUG_ASSERT builds (compute-sanitizer is closed on this pool): every absolute shared-memory access of the
+// histogram kernel is checked against the CTA's dynamic window [base, base + %dynamic_smem_size).
+#ifdef B200_DEBUG_ASSERT
+__device__ __forceinline__ void check_abs(unsigned addr, unsigned bytes) {
+    unsigned size;
+    asm("mov.u32 %0, %%dynamic_smem_size;" : "=r"(size));
+    const unsigned base = (unsigned)__cvta_generic_to_shared(hist_smem_raw);
+    assert(addr >= base && addr + bytes <= base + size && addr % bytes == 0);
+}
+#else
+__device__ __forceinline__ void check_abs(unsigned, unsigned) {}
+#endif
+
+
 // ---- tile loop: a ring of tiles per WARP in shared memory, filled by 1-D bulk copies (TMA) ---------------------
 // A warp's tiles are contiguous 2 KB pieces of the sample array, so the operands of a bulk copy are uniform and
 // one lane can issue it.  Bandwidth here is (bytes in flight) / (loaded HBM latency, ~1.4 us): with the next
@@ -195,6 +213,7 @@ __device__ __forceinline__ void bulk_load(unsigned dst, const void* src, unsigne
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 __device__ __forceinline__ longlong2 lds_pair(unsigned addr) {
+    check_abs(addr, 16);
     longlong2 v;
     asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(v.x), "=l"(v.y) : "r"(addr) : "memory");
     return v;
@@ -330,6 +349,7 @@ __device__ __forceinline__ void split64(long long v, unsigned& lo, unsigned& hi)
 
 // the lane's private counter at absolute shared address `addr` += 1
 __device__ __forceinline__ void bump_abs(unsigned addr) {
+    check_abs(addr, 4);
 #ifdef B200_HIST_RED
     asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(addr), "r"(1u) : "memory");
     return;
@@ -446,6 +466,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     // issued together instead of each waiting for the previous sample's counter update)
     auto row_of = [&](unsigned idx) -> unsigned {
         unsigned r;
+        check_abs(idx + kLutAbs, 1);
         asm("ld.shared.u8 %0, [%1+%2];" : "=r"(r) : "r"(idx), "n"(kLutAbs));
         return r;
     };

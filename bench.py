@@ -281,6 +281,82 @@ def latency_side_measurement(pkg, ctx, n=500_000_000, reps=5):
         return {"error": f"{type(e).__name__}: {e}"[:300]}
 
 
+def small_objects_side(crc32c, ctx, oracle, d_arena, h_arena, total, reps=20):
+    """the row kernel's shapes — batches of many small or ragged objects resident in HBM — timed on
+    the device beside the headline (same arena), each with a sample of its objects checked against the oracle.
+    Never fails the bench."""
+    try:
+        rng = np.random.default_rng(SEED)
+        peak, _ = measured_peaks()
+        shapes = []
+        n = 1 << 20
+        shapes.append(("1Mi x 4 KiB", np.arange(n, dtype=np.uint64) * np.uint64(4096), np.full(n, 4096, dtype=np.uint64)))
+        shapes.append(("1Mi x U[0,8 KiB), unaligned",
+                       np.arange(n, dtype=np.uint64) * np.uint64(8192) + rng.integers(0, 16, size=n).astype(np.uint64),
+                       rng.integers(0, 8192, size=n).astype(np.uint64)))
+        ln = rng.integers(1, 4 << 20, size=4096).astype(np.uint64)
+        off = np.concatenate([[0], np.cumsum(ln[:-1] + rng.integers(0, 64, size=4095).astype(np.uint64))]).astype(np.uint64)
+        keep = off + ln <= np.uint64(total)
+        shapes.append(("ragged U[1,4 MiB], unaligned", off[keep], ln[keep]))
+        out = {}
+        for name, off, ln in shapes:
+            b = crc32c.DeviceBatch(off, ln, None, ctx)
+            for _ in range(3):
+                b.run(d_arena)
+            got = b.results()[0].copy()
+            ctx.timer_start()
+            for _ in range(reps):
+                b.run_async(d_arena)
+            ms = ctx.timer_stop() / reps
+            launches = b.launches()
+            b.close()
+            idx = rng.choice(len(ln), size=min(len(ln), 2048 if len(ln) > 5000 else 64), replace=False)
+            cpu, _, _ = oracle.verify_objects(h_arena, off[idx], ln[idx], None, threads=os.cpu_count() or 1)
+            nbytes = int(ln.sum())
+            gbs = nbytes / (ms * 1e-3) / 1e9
+            out[name] = {"objects": int(len(ln)), "bytes": nbytes, "ms": round(ms, 4), "GB/s": round(gbs, 1),
+                         "frac_of_hbm_peak": round(gbs / peak, 4), "launches": launches,
+                         "oracle_ok": bool((cpu == got[idx]).all()), "oracle_sample": int(len(idx))}
+        return out
+    except Exception as e:
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+
+def text_codec_side(pkg, ctx, nlines=20_000_000, reps=5):
+    """The text form of the samples (Go Duration.String() lines, what the README pipes to the histogram script)
+    parsed on the device: lines, bytes, ms and GB/s, the first block of values against Python's float()."""
+    try:
+        import ctypes as C
+        lat = pkg.latency
+        ns = np.random.default_rng(SEED + 1).integers(20_000_000, 95_000_000, size=200_000)
+        lines = [lat.go_duration_line(int(v)) for v in ns]
+        chunk = ("\n".join(lines) + "\n").encode()
+        data = np.frombuffer(chunk * (nlines // len(lines)), dtype=np.uint8)
+        dt = ctx.alloc_device(data.size)
+        ctx.h2d(dt, data)
+        dv = ctx.alloc_device(nlines * 8)
+        dst = ctx.alloc_device(nlines)
+        o = [C.c_uint64() for _ in range(4)]
+        call = lambda: pkg._lib.check(ctx._L.b200_parse_latency_text(ctx._h, 0, dt, data.size, dv, dst, nlines,
+                                                                      *[C.byref(x) for x in o]))
+        call()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            call()
+        ms = (time.perf_counter() - t0) / reps * 1e3
+        head = np.empty(len(lines), dtype=np.float64)
+        ctx.d2h(head, dv)
+        want = np.array([float(x.strip()) for x in lines])
+        for p in (dt, dv, dst):
+            ctx.free_device(p)
+        return {"lines": int(o[0].value), "bytes": int(data.size), "ms": round(ms, 3),
+                "GB/s": round(data.size / (ms * 1e-3) / 1e9, 1), "Mlines/s": round(o[0].value / ms / 1e3, 1),
+                "bad_lines": int(o[2].value), "first_block_equals_python_float": bool((head == want).all()),
+                "timing": "wall clock around the C-ABI call (ends with a device->host copy of the 4-word summary)"}
+    except Exception as e:
+        return {"error": f"{type(e).__name__}: {e}"[:300]}
+
+
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
@@ -591,6 +667,7 @@ def run_b200(args):
                                               "single_core: first 512 objects on 1 thread",
                                     "note": "oracle = C restatement of Go hash/crc32 amd64 Castagnoli "
                                             "(SSE4.2 crc32q, 3 lanes); Go unavailable on this box"}
+    small = small_objects_side(crc32c, ctx, oracle, d_arena, h_arena, total) if world == 1 else None
     ctx.free_pinned(h_arena)
     ctx.free_device(d_arena)
     batch.close()
@@ -605,6 +682,8 @@ def run_b200(args):
         line.update(side)
         if world == 1:
             line["latency_reduction"] = latency_side_measurement(pkg, ctx)
+            line["small_objects"] = small
+            line["text_codec"] = text_codec_side(pkg, ctx)
     ctx.close()
     if dist is not None:
         dist.barrier()

@@ -146,7 +146,7 @@ __device__ __forceinline__ void load_slow_params(SlowParams* sp, const HistParam
 // lat_scratch_init checks the window start once per device (smem_base_probe).
 constexpr unsigned kSlowAbs = 0x400;                                    // SlowParams
 constexpr unsigned kParkNAbs = kSlowAbs + 640;                          // unsigned[kHistWarps]: parked samples per warp
-constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long long[kHistWarps][park_cap(collect)]
+constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long long[kHistWarps][park_slots(collect)]
 // a collecting pass parks ~1 % of the samples, the others ~0.5 %: queue slots per warp
 #ifndef B200_PARK_COLLECT
 #define B200_PARK_COLLECT 128
@@ -155,8 +155,10 @@ constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long 
 #define B200_PARK_PLAIN 32
 #endif
 __host__ __device__ constexpr int park_cap(bool collect) { return collect ? B200_PARK_COLLECT : B200_PARK_PLAIN; }
+// a collecting kernel parks without a branch (park_if_zero): one more slot takes what does not fit
+__host__ __device__ constexpr int park_slots(bool collect) { return park_cap(collect) + (collect ? 1 : 0); }
 // unsigned char[lut_bytes], lut_bytes <= kLutSize
-__host__ __device__ constexpr unsigned lut_abs(bool collect) { return kParkQAbs + kHistWarps * park_cap(collect) * 8; }
+__host__ __device__ constexpr unsigned lut_abs(bool collect) { return kParkQAbs + kHistWarps * park_slots(collect) * 8; }
 // then, at lut_abs + lut_bytes, unsigned[kHistWarps][rows][32] counters, then the tile ring, then (collecting) the
 // warps' staging for kept samples
 static_assert(sizeof(SlowParams) <= 640, "SlowParams slot");
@@ -329,9 +331,9 @@ __device__ __forceinline__ void hist_epilogue(const unsigned* tbl, int rows, int
 // every 32.
 template <typename Slow, typename BeforeStep>
 __device__ __forceinline__ void drain_parked(unsigned* n, const long long* q, unsigned cap, int lane, Slow slow,
-                                             BeforeStep before_step) {
+                                             BeforeStep before_step, int shift = 0) {
     __syncwarp();
-    const unsigned cnt = min(*n, cap);
+    const unsigned cnt = min(*n >> shift, cap);  // (collecting kernels count the queue in bytes: shift 3)
     for (unsigned base = 0; base < cnt; base += 32) {
         before_step();
         if (base + lane < cnt) slow(q[base + lane]);
@@ -345,6 +347,23 @@ __device__ __forceinline__ void drain_parked(unsigned* n, const long long* q, un
 // operations (an OR of eight high words must not become eight 64-bit ORs)
 __device__ __forceinline__ void split64(long long v, unsigned& lo, unsigned& hi) {
     asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
+}
+
+// Collecting kernels park without a branch: about one sample in a hundred is parked (kept, or in a cell with a
+// threshold), so three groups of four in four meet one somewhere in the warp, and a divergent block there — ~50
+// warp instructions with its convergence barriers — was a quarter of the pass.  Predicated instead: when row == 0
+// the sample goes to the warp's queue at the byte offset an atomic add of 8 returns; offsets past the queue's cap
+// land in the spare slot behind it, and the caller, who looks at the count once per tile, redoes that tile.
+__device__ __forceinline__ void park_if_zero(unsigned row, long long v, unsigned count_abs, unsigned queue_abs,
+                                             unsigned cap_bytes) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t.reg .u32 at;\n\t"
+        "setp.eq.u32 p, %0, 0;\n\t"
+        "@p atom.shared.add.u32 at, [%1], 8;\n\t"
+        "@p min.u32 at, at, %4;\n\t"
+        "@p add.u32 at, at, %2;\n\t"
+        "@p st.shared.b64 [at], %3;\n\t}"
+        ::"r"(row), "r"(count_abs), "r"(queue_abs), "l"(v), "r"(cap_bytes) : "memory");
 }
 
 // the lane's private counter at absolute shared address `addr` += 1
@@ -397,7 +416,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kCntAbs);  // [warp][row][lane] private counters
     SlowParams* const sp = reinterpret_cast<SlowParams*>(sm0 + kSlowAbs);
     load_slow_params(sp, Pg);
-    if (threadIdx.x < kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
+    if (threadIdx.x < 2 * kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < (int)lut_bytes / 4; i += kHistThreads)
         reinterpret_cast<unsigned*>(sm0 + kLutAbs)[i] = reinterpret_cast<const unsigned*>(Pg->lut)[i];
     const int nbins = Pg->nthr + 1, rows = nbins + 1;  // row 0: scratch
@@ -425,7 +444,11 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
                    reinterpret_cast<long long*>(sm0 + keep_abs + 64) + (size_t)warp * kKeepCap};
     // the warp's queue of parked samples: addressed from constants where it is used (no registers held for it)
     auto park_n = [&]() -> unsigned* { return reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp; };
-    auto park_q = [&]() -> long long* { return reinterpret_cast<long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkCap; };
+    constexpr unsigned kParkSlots = park_slots(COLLECT);
+    auto park_q = [&]() -> long long* { return reinterpret_cast<long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkSlots; };
+    // collecting: the queue is counted in bytes, and the count at the start of the current tile is kept beside it
+    auto park_start = [&]() -> unsigned* { return reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + kHistWarps + warp; };
+    const unsigned park_n_abs = kParkNAbs + 4u * warp, park_q_abs = kParkQAbs + 8u * kParkSlots * warp;
     if (collecting && lane == 0) *keep.n = 0;
     __syncwarp();
     auto flush_keep = [&]() {  // whole warp, converged
@@ -507,8 +530,23 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         for (int k = 0; k < K; k++) idx[k] = index_of(u[k], q[k]);
 #pragma unroll
         for (int k = 0; k < K; k++) row[k] = row_of(idx[k]);
-        const unsigned lowest = min(min(row[0], row[1]), min(row[2], row[3]));
-        if ((any_hi >> out_shift) != 0 || lowest == 0) {  // rare
+        if constexpr (COLLECT) {
+#pragma unroll
+            for (int k = 0; k < K; k++) park_if_zero(row[k], v[k], park_n_abs, park_q_abs, kParkCap * 8u);
+            if ((any_hi >> out_shift) != 0) {  // beyond the reach: parked whatever its table entry said; surrogate
+#pragma unroll
+                for (int k = 0; k < K; k++)
+                    if ((hi[k] >> out_shift) != 0) {
+                        if (row[k] != 0) park_if_zero(0u, v[k], park_n_abs, park_q_abs, kParkCap * 8u);
+                        const bool neg = (int)hi[k] < 0;
+                        u[k] = neg ? 0u : u_top;
+                        if (BYQ) q[k] = quotient(u[k]);
+                        row[k] = 0;
+                        nhi += !neg;
+                        nsur++;
+                    }
+            }
+        } else if ((any_hi >> out_shift) != 0 || min(min(row[0], row[1]), min(row[2], row[3])) == 0) {  // rare
 #pragma unroll
             for (int k = 0; k < K; k++)
                 if ((hi[k] >> out_shift) != 0 || row[k] == 0) {
@@ -551,22 +589,59 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             }
         }
     };
-    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
-        four(a, b);
-        four(c, d);
-        nproc += 8;
-    };
     const unsigned ring_abs = (kCntAbs + (unsigned)(kHistWarps * rows * 32) * 4u + 127u) & ~127u;
     // a drain step stages at most 32 kept samples: flush before a step that might not fit
     auto before_step = [&] {
         if (collecting && *keep.n > (unsigned)(kKeepCap - 32)) flush_keep();
     };
+    auto drain = [&] {  // whole warp, converged
+        drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step, COLLECT ? 3 : 0);
+        if (COLLECT) {
+            if (lane == 0) *park_start() = 0;
+            __syncwarp();
+        }
+    };
+    auto eight = [&](const longlong2 a, const longlong2 b, const longlong2 c, const longlong2 d) {
+        four(a, b);
+        four(c, d);
+        nproc += 8;
+        if constexpr (COLLECT) {  // the queue, once per tile (every lane reads the same count)
+            __syncwarp();
+            const unsigned bytes = *park_n();
+            if (bytes > kParkCap * 8u) {
+                // more were parked in this tile than the queue had room for: forget this tile's entries, work the
+                // earlier ones off, and take this tile's parked samples one by one from the registers
+                const unsigned start = *park_start();
+                __syncwarp();
+                if (lane == 0) *park_n() = start;
+                drain();
+                const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    bool parked = ((unsigned long long)v[k] >> reach_bits) != 0;
+                    if (!parked) {
+                        unsigned lo, hi, q = 0;
+                        split64(v[k], lo, hi);
+                        parked = row_of(index_of(shifted(lo, hi), q)) == 0;
+                    }
+                    if (parked) slow(v[k]);
+                }
+                __syncwarp();
+            } else if (bytes >= kParkCap * 4u) {
+                drain();
+            } else if (lane == 0) {
+                *park_start() = bytes;
+            }
+        }
+    };
     for_each_sample(x, n, ring_abs, nstages, eight, one, [&] {
-        __syncwarp();
-        if (*park_n() >= kParkCap / 2)  // every lane reads the same counter
-            drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step);
+        if constexpr (!COLLECT) {
+            __syncwarp();
+            if (*park_n() >= kParkCap / 2)  // every lane reads the same counter
+                drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step);
+        }
     });
-    drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step);
+    drain();
     if (collecting) flush_keep();
 
     long long mn = sm_slow.mn, mx = sm_slow.mx;

@@ -524,3 +524,29 @@ def test_default_routes_with_p99_beyond_32_bits(ctx):
     assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (
         int(us.sum()) // n, *[int(srt[k]) // 1000 for k in ks[1:5]], int(us.min()), int(us.max()))
     ctx.free_device(d)
+
+
+@pytest.mark.parametrize("burst,heavy", [(6000, False), (0, True)])
+def test_bracket_pass_when_a_tile_parks_more_than_its_queue_holds(ctx, burst, heavy):
+    """The collecting pass parks kept samples in a per-warp queue of 128: a run of consecutive samples equal to the
+    median fills a tile's queue several times over (the tile is then redone one sample at a time), and an input that
+    is mostly one value does so everywhere (the brackets come out too heavy and the radix passes take over, but the
+    pass must still have counted every sample).  Checked against numpy.partition."""
+    n = (1 << 24) + 4321
+    ns = oracle.latency_ns(n, seed=99)
+    med = int(np.partition(ns, n // 2)[n // 2])
+    if burst:
+        for at in (12345, n // 3, n - burst - 7):
+            ns[at:at + burst] = med
+    if heavy:
+        ns[np.arange(n) % 5 != 0] = med
+    d = ctx.alloc_device(n * 8)
+    ctx.h2d(d, ns)
+    ks = [n // 5, n // 2, 9 * n // 10, 99 * n // 100]
+    srt = np.partition(ns, ks)
+    assert lat.select_kth(d, n, 1, ks, ctx=ctx) == [int(srt[k]) for k in ks]
+    p = lat.percentiles(d, n, lat.NS_PER_US, ctx=ctx)
+    us = ns // 1000
+    assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (
+        int(us.sum()) // n, *[int(srt[k]) // 1000 for k in ks], int(us.min()), int(us.max()))
+    ctx.free_device(d)

@@ -594,7 +594,11 @@ int b200_memcpy_h2d(b200_ctx* ctx, int dev, void* dptr, const void* host, size_t
     DevState* d = get_dev(ctx, dev);
     if (!d || (n && (!dptr || !host))) return fail(B200_ERR_INVALID, "b200_memcpy_h2d");
     CU(cudaSetDevice(dev));
-    CU(cudaMemcpy(dptr, host, n, cudaMemcpyHostToDevice));
+    // on the device's own stream and waited for: a plain cudaMemcpy from pageable memory may return with the last
+    // piece still on its way, and the kernels' non-blocking stream would not wait for it
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaMemcpyAsync(dptr, host, n, cudaMemcpyHostToDevice, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
     return 0;
 }
 
@@ -602,7 +606,9 @@ int b200_memcpy_d2h(b200_ctx* ctx, int dev, void* host, const void* dptr, size_t
     DevState* d = get_dev(ctx, dev);
     if (!d || (n && (!dptr || !host))) return fail(B200_ERR_INVALID, "b200_memcpy_d2h");
     CU(cudaSetDevice(dev));
-    CU(cudaMemcpy(host, dptr, n, cudaMemcpyDeviceToHost));
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaMemcpyAsync(host, dptr, n, cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
     return 0;
 }
 
@@ -1346,23 +1352,65 @@ size_t resident_select_max() {  // tuning / test override: B200_SELECT_RESIDENT_
     return v;
 }
 
+bool grow(long long** buf, size_t* cap, size_t want);  // below
+bool select_trace_on();
+
+// A stratified sample to take first, on the same stream and under the same lock: the select then runs over it
+// (d->lat.d_sample, n = its length) with the bounds the sampling kernel leaves behind.
+struct SampleFirst {
+    const int64_t* src;
+    size_t stride;
+    unsigned long long outside;  // out: samples of the sample outside [0, 2^32)
+};
+
+// have_bounds: 0 none, 1 [lo, hi] given.  approx_max > 0 (one-kernel select only; the separate launches give exact
+// ranks, which serve as well): out[i] is a bound on the rank's order statistic, from below — from above for the ranks
+// in ceil_of — within approx_max ranks.
 int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, bool have_bounds,
-                    int64_t lo, int64_t hi, const uint64_t* k, int nk, int64_t* out) {
+                    int64_t lo, int64_t hi, const uint64_t* k, int nk, int64_t* out, uint64_t approx_max = 0,
+                    const bool* ceil_of = nullptr, SampleFirst* first = nullptr) {
     DevState* d = get_dev(ctx, dev);
     if (!d) return fail(B200_ERR_INVALID, "b200_select_kth: unknown device");
     std::lock_guard<std::mutex> lk(d->mu);
     CU(cudaSetDevice(dev));
+    const bool fused = select_fused_grid() != 0;
+    int bounds = have_bounds ? 1 : 0;
+    if (first) {
+        if (!grow(&d->lat.d_sample, &d->lat.sample_cap, n)) return 1;  // (the caller takes another route)
+        CU(launch_sample((const long long*)first->src, first->stride, d->lat.d_sample, n, d->stream, d->lat.d_compact_n,
+                         fused ? d->lat.d_mom : nullptr));
+        d_samples = (const int64_t*)d->lat.d_sample;
+        bounds = fused ? 2 : 0;
+    }
     for (int g = 0; g < nk; g += kSelMax) {
         SelRanks r{};
         r.nk = std::min(kSelMax, nk - g);
         for (int i = 0; i < r.nk; i++) r.rank[i] = k[g + i];
-        CU(launch_select_resident((const long long*)d_samples, n, r, have_bounds, lo, hi, d->lat, d->stream));
+        if (fused) {
+            unsigned ceil_mask = 0;
+            for (int i = 0; i < r.nk && ceil_of; i++) ceil_mask |= ceil_of[g + i] ? 1u << i : 0u;
+            CU(launch_select_fused((const long long*)d_samples, n, r, bounds, lo, hi, approx_max, ceil_mask, d->lat,
+                                   d->stream));
+        } else {
+            CU(launch_select_resident((const long long*)d_samples, n, r, bounds == 1, lo, hi, d->lat, d->stream));
+        }
         SelState st;
         CU(cudaMemcpyAsync(&st, d->lat.d_sel, sizeof st, cudaMemcpyDeviceToHost, d->stream));
+        if (first && g == 0)
+            CU(cudaMemcpyAsync(&first->outside, d->lat.d_compact_n, sizeof first->outside, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
-        if (st.bad || st.top != 0)
+        if (st.bad || st.top != 0) {
+            if (select_trace_on()) fprintf(stderr, "b200 select: resident select failed: bad=%d top=%d n=%zu\n", st.bad, st.top, n);
             return fail(B200_ERR_INVALID, "b200_select_kth: samples outside the given [lo, hi] range");
+        }
         for (int i = 0; i < r.nk; i++) out[g + i] = st.result[i] / divisor;  // truncating division is monotone
+        if (fused && select_trace_on() && st.nstamp > 1) {
+            char msg[400];
+            int at = snprintf(msg, sizeof msg, "one-kernel select of %d ranks among %zu, CTA 0 phase ends (us):", r.nk, n);
+            for (int i = 1; i < st.nstamp && at < (int)sizeof msg - 12; i++)
+                at += snprintf(msg + at, sizeof msg - at, " %.1f", (double)(st.stamp[i] - st.stamp[0]) * 1e-3);
+            fprintf(stderr, "b200 select: %s\n", msg);
+        }
     }
     return 0;
 }
@@ -1493,12 +1541,16 @@ size_t sampled_select_min() {  // inputs at least this long try the sampled shor
     return v;
 }
 
-int sampled_trace(const char* what, int rc) {  // B200_SELECT_TRACE=1: say on stderr how a sampled select ended
+bool select_trace_on() {  // B200_SELECT_TRACE=1
     static const bool on = [] {
         const char* e = getenv("B200_SELECT_TRACE");
         return e && *e && *e != '0';
     }();
-    if (on) fprintf(stderr, "b200 select: sampled %s\n", what);
+    return on;
+}
+
+int sampled_trace(const char* what, int rc) {  // B200_SELECT_TRACE=1: say on stderr how a sampled select ended
+    if (select_trace_on()) fprintf(stderr, "b200 select: sampled %s\n", what);
     return rc;
 }
 
@@ -1549,7 +1601,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     // sample rank of an input rank r is about r / stride, with a standard deviation below sqrt(s) / 2
     const uint64_t margin = (uint64_t)(2.5 * std::sqrt((double)s)) + 2;
     uint64_t want[2 * kSelMax];
-    bool open_lo[kSelMax], open_hi[kSelMax];
+    bool open_lo[kSelMax], open_hi[kSelMax], is_hi[2 * kSelMax] = {};
     int nwant = 0, lo_at[kSelMax], hi_at[kSelMax];
     for (int i = 0; i < nk; i++) {
         const uint64_t c = k[i] / stride;
@@ -1557,25 +1609,30 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         open_hi[i] = c + margin + 1 >= s;
         lo_at[i] = hi_at[i] = -1;
         if (!open_lo[i]) { lo_at[i] = nwant; want[nwant++] = c - margin; }
-        if (!open_hi[i]) { hi_at[i] = nwant; want[nwant++] = c + margin + 1; }
+        if (!open_hi[i]) { hi_at[i] = nwant; is_hi[nwant] = true; want[nwant++] = c + margin + 1; }
     }
     int64_t got[2 * kSelMax];
-    {
+    unsigned long long outside = 0;
+    if (nwant) {
+        // bounds are enough here: a lower end at or below the sample's order statistic, an upper end at or above it,
+        // good to a sixteenth of the `margin` either side (s <= 2^22 + change: always the resident select).  The
+        // sampling kernel and the select run back to back on the stream: one host round trip for both.
+        SampleFirst first{d_samples, stride, 0};
+        const int rc = select_resident(ctx, dev, nullptr, s, 1, false, 0, 0, want, nwant, got,
+                                       std::max<uint64_t>(1, margin / 16), is_hi, &first);
+        if (rc) return rc < 0 ? rc : sampled_trace("skip: no memory for the sample", 1);
+        outside = first.outside;
+    } else {
         std::unique_lock<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         if (!grow(&d->lat.d_sample, &d->lat.sample_cap, s)) return sampled_trace("skip: no memory for the sample", 1);
         CU(launch_sample((const long long*)d_samples, stride, d->lat.d_sample, s, d->stream, d->lat.d_compact_n));
-        unsigned long long outside = 0;
         CU(cudaMemcpyAsync(&outside, d->lat.d_compact_n, sizeof outside, cudaMemcpyDeviceToHost, d->stream));
         CU(cudaStreamSynchronize(d->stream));
-        // the histogram pass takes negative samples and samples >= 2^32 ns one by one on its generic path: a
-        // multi-second tail is fine, a data set that mostly lives there (not latencies) is faster by radix passes
-        if (outside > s / 16) return sampled_trace("skip: too much of the input is outside the 32-bit fast path", 1);
     }
-    if (nwant) {
-        int rc = b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_sample, s, 1, want, nwant, got);
-        if (rc) return rc < 0 ? rc : 1;
-    }
+    // the histogram pass takes negative samples and samples >= 2^32 ns one by one on its generic path: a
+    // multi-second tail is fine, a data set that mostly lives there (not latencies) is faster by radix passes
+    if (outside > s / 16) return sampled_trace("skip: too much of the input is outside the 32-bit fast path", 1);
     const double ms_sample = ms_since(t0);
     // brackets, ascending and disjoint (overlapping or touching ones are merged)
     struct Bracket { int64_t lo, hi; };
@@ -1639,7 +1696,12 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         }
         rank_kept[i] = kept_before + (k[i] - below);
     }
-    int rc = b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, rank_kept, nk, out);
+    // the kept samples lie between the ends of the brackets: no min/max pass when those are finite
+    const bool bounded = br[0].lo != kMin && br[nb - 1].hi != kMax;
+    int rc = inside <= resident_select_max()
+                 ? select_resident(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, bounded,
+                                   bounded ? br[0].lo : 0, bounded ? br[nb - 1].hi : 0, rank_kept, nk, out)
+                 : b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, rank_kept, nk, out);
     if (rc) return rc < 0 ? rc : 1;
     if (stats) fill_stats(mom, divisor, stats);  // moments of the whole input, from the bracket pass
     char msg[160];

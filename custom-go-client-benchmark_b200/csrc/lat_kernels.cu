@@ -14,6 +14,8 @@
 // (warp, lane) in shared memory so the skewed latency distribution causes no atomic contention.
 #include "lat_kernels.h"
 
+#include <cooperative_groups.h>
+
 #ifdef B200_DEBUG_ASSERT
 #include <cassert>
 #endif
@@ -23,6 +25,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+
+namespace cg = cooperative_groups;
 
 namespace b200 {
 
@@ -970,6 +974,228 @@ sel_scan_kernel(SelState* st, unsigned long long* __restrict__ hist) {
     }
 }
 
+// ---- the same select in ONE kernel -----------------------------------------------------------------------------
+// The launches above cost more than their work on inputs of a few million samples (the sample of a sampled select,
+// the samples it keeps): min/max + init + six passes + six scans, ~12 us each with their gaps, for data that sits
+// in L2.  Here one cooperative grid (a CTA per SM, all resident) does the lot with grid-wide barriers: every round
+// the CTAs count their share into shared memory and add it to the global histograms; after the barrier CTA h scans
+// histogram h (one histogram for all ranks on the first round, one per rank afterwards), writes the ranks' new
+// prefixes into the state and clears the histogram; after a second barrier everyone reads the prefixes.
+// approx_max > 0: a rank stops being refined once its bucket holds at most approx_max samples, and the result is
+// the bucket's lowest key — or its highest for the ranks in ceil_mask — i.e. a bound on the order statistic good to
+// approx_max ranks, which is all the brackets of the sampled select need (one round less).
+constexpr int kFusedThreads = 1024, kScanBins = kRadixBins / kFusedThreads;
+__global__ void __launch_bounds__(kFusedThreads)
+sel_fused_kernel(const long long* __restrict__ x, size_t n, SelState* st, unsigned long long* __restrict__ hist,
+                 LatMoments* mom, SelRanks ranks, int have_bounds, long long lo, long long hi,
+                 unsigned long long approx_max, unsigned ceil_mask) {
+    static_assert(kRadixBins == kScanBins * kFusedThreads, "a thread scans kScanBins bins");
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) unsigned char sm[];
+    unsigned* hs = reinterpret_cast<unsigned*>(sm);  // [nhist][kRadixBins]
+    __shared__ unsigned long long pf[kSelMax];
+    __shared__ unsigned long long wtot[kFusedThreads / 32];
+    __shared__ unsigned flt[kRadixBins / 4];  // a byte per low-12-bit value of a prefix: the ranks it may belong to
+    static_assert(kSelMax == 8, "a byte of rank bits; copies of the first histogram");
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    int nstamp = 0;
+    auto stamp = [&] {  // CTA 0's clock at the end of a phase: where the time goes, for the trace
+        if (blockIdx.x == 0 && t == 0 && nstamp < 24) {
+            unsigned long long now;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+            st->stamp[nstamp++] = now;
+        }
+    };
+    stamp();
+    size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
+    if (head > n) head = n;
+    const size_t tid = (size_t)blockIdx.x * kFusedThreads + t, nthreads = (size_t)gridDim.x * kFusedThreads;
+    const longlong2* x2 = reinterpret_cast<const longlong2*>(x + head);
+    const size_t npairs = (n - head) / 2;
+    auto walk = [&](auto one) {
+        if (tid == 0 && head) one(x[0]);
+        size_t i = tid;
+        // (the data sits in L2 at best: what a pass costs is load latency, so four loads in flight per thread)
+        for (; i + 3 * nthreads < npairs; i += 4 * nthreads) {
+            const longlong2 a = __ldg(x2 + i), b = __ldg(x2 + i + nthreads), c = __ldg(x2 + i + 2 * nthreads),
+                            d = __ldg(x2 + i + 3 * nthreads);
+            one(a.x); one(a.y); one(b.x); one(b.y); one(c.x); one(c.y); one(d.x); one(d.y);
+        }
+        for (; i < npairs; i += nthreads) {
+            const longlong2 a = __ldg(x2 + i);
+            one(a.x); one(a.y);
+        }
+        if (tid == 0 && head + 2 * npairs < n) one(x[n - 1]);
+    };
+    if (!have_bounds) {  // mom: reset by the host before the launch
+        long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
+        walk([&](long long v) {
+            mn = v < mn ? v : mn;
+            mx = v > mx ? v : mx;
+        });
+#pragma unroll
+        for (int d = 16; d; d >>= 1) {
+            const long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
+            mn = omn < mn ? omn : mn;
+            mx = omx > mx ? omx : mx;
+        }
+        if (lane == 0 && mn <= mx) {
+            atomicMin(&mom->min_ns, mn);
+            atomicMax(&mom->max_ns, mx);
+        }
+        grid.sync();
+        stamp();
+    }
+    if (have_bounds != 1) {  // 2: an earlier kernel on the stream (the sampling) left them there
+        lo = __ldcg(&mom->min_ns);
+        hi = __ldcg(&mom->max_ns);
+    }
+    const unsigned long long kmin = (unsigned long long)lo ^ 0x8000000000000000ull,
+                             kmax = (unsigned long long)hi ^ 0x8000000000000000ull, range = kmax - kmin;
+    int top = lo > hi ? 0 : 64 - __clzll((long long)range);
+    const int nk = ranks.nk;
+    int bad = lo > hi;
+    for (int k = 0; k < nk; k++) bad |= ranks.rank[k] >= n;
+    if (blockIdx.x == 0 && t < kSelMax) {  // read by others only after the first barrier of a round
+        st->prefix[t] = 0;
+        st->rank[t] = t < nk ? ranks.rank[t] : 0;
+        st->more[t] = 0;
+        if (t == 0) st->bad = bad;
+    }
+    int nhist = 1, round = 0;
+    while (!bad && top > 0) {
+        const int shift = top > kRadixBits ? top - kRadixBits : 0, width = top - shift;
+        const unsigned mask = (1u << width) - 1;
+        // Round 0 has ONE histogram, and latencies crowd into a few of its bins (shared-memory atomics on one
+        // address serialise): kSelMax copies of it, a copy per four warps.  Later rounds have a histogram per rank
+        // that few samples reach: a byte per value of the prefix's low 12 bits says which ranks' prefixes end in
+        // them, so a sample that matches none — nearly all — costs one look-up instead of a compare per rank.
+        const int ncopies = round == 0 ? kSelMax : nhist;
+        for (int i = t; i < ncopies * kRadixBins; i += kFusedThreads) hs[i] = 0;
+        for (int i = t; i < kRadixBins / 4; i += kFusedThreads) flt[i] = 0;
+        if (t < kSelMax) pf[t] = t >= nk ? ~0ull : round == 0 ? 0ull : __ldcg(&st->prefix[t]);
+        __syncthreads();
+        if (round > 0 && t < nk) {
+            const unsigned slot = (unsigned)pf[t] & (kRadixBins - 1);
+            atomicOr(flt + (slot >> 2), (1u << t) << (8 * (slot & 3)));
+        }
+        __syncthreads();
+        if (round == 0) {
+            unsigned* const mine = hs + (warp & (kSelMax - 1)) * kRadixBins;  // (a copy per four warps)
+            walk([&](long long v) {
+                const unsigned long long key = ((unsigned long long)v ^ 0x8000000000000000ull) - kmin;
+                const unsigned dgt = (unsigned)(key >> shift) & mask;
+                const unsigned long long up = top >= 64 ? 0 : key >> top;
+                if (up == 0) atomicAdd(mine + dgt, 1u);  // (a sample outside given bounds has bits above `top`)
+            });
+        } else {
+            const unsigned char* const flt8 = reinterpret_cast<const unsigned char*>(flt);
+            walk([&](long long v) {
+                const unsigned long long key = ((unsigned long long)v ^ 0x8000000000000000ull) - kmin;
+                const unsigned long long up = key >> top;  // (top <= 52 after a round)
+                unsigned m = flt8[(unsigned)up & (kRadixBins - 1)];
+                while (m) {
+                    const int k = __ffs(m) - 1;
+                    m &= m - 1;
+                    if (up == pf[k]) atomicAdd(hs + k * kRadixBins + ((unsigned)(key >> shift) & mask), 1u);
+                }
+            });
+        }
+        __syncthreads();
+        if (round == 0) {
+            for (int i = t; i < kRadixBins; i += kFusedThreads) {
+                unsigned c = 0;
+#pragma unroll
+                for (int r = 0; r < kSelMax; r++) c += hs[r * kRadixBins + i];
+                if (c) atomicAdd(hist + i, (unsigned long long)c);
+            }
+        } else {
+            for (int i = t; i < nhist * kRadixBins; i += kFusedThreads) {
+                const unsigned c = hs[i];
+                if (c) atomicAdd(hist + i, (unsigned long long)c);
+            }
+        }
+        stamp();
+        grid.sync();
+        stamp();
+        for (int h = blockIdx.x; h < nhist; h += gridDim.x) {  // CTA h: histogram h (a small grid: several each)
+            unsigned long long* const H = hist + (size_t)h * kRadixBins + kScanBins * t;
+            unsigned long long c[kScanBins], sum = 0;
+#pragma unroll
+            for (int j = 0; j < kScanBins; j += 2) {
+                const ulonglong2 p = __ldcg(reinterpret_cast<const ulonglong2*>(H + j));
+                c[j] = p.x;
+                c[j + 1] = p.y;
+            }
+#pragma unroll
+            for (int j = 0; j < kScanBins; j++) sum += c[j];
+            unsigned long long incl = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned long long o = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+                if (lane >= d) incl += o;
+            }
+            // after the first round histogram h belongs to rank h alone; its rank and prefix are read by every thread
+            // BEFORE the barriers below, because the one thread that finds the bucket overwrites them
+            const unsigned long long r_own = round == 0 ? 0ull : __ldcg(&st->rank[h]),
+                                     p_own = round == 0 ? 0ull : __ldcg(&st->prefix[h]);
+            __syncthreads();  // (wtot: the previous histogram's readers are done)
+            if (lane == 31) wtot[warp] = incl;
+            __syncthreads();
+            unsigned long long before = incl - sum, total = 0;
+            for (int w = 0; w < kFusedThreads / 32; w++) {
+                if (w < warp) before += wtot[w];
+                total += wtot[w];
+            }
+            for (int k = 0; k < nk; k++) {
+                if (nhist != 1 && k != h) continue;
+                const unsigned long long r = round == 0 ? ranks.rank[k] : r_own;
+                if (r >= total) {
+                    if (t == 0) st->bad = 1;
+                } else if (r >= before && r < before + sum) {  // exactly one thread
+                    unsigned long long cum = before;
+                    int j = 0;
+#pragma unroll
+                    for (int jj = 0; jj < kScanBins - 1; jj++)
+                        if (j == jj && r >= cum + c[jj]) { cum += c[jj]; j++; }
+                    unsigned long long cj = c[0];
+#pragma unroll
+                    for (int jj = 1; jj < kScanBins; jj++) cj = j == jj ? c[jj] : cj;
+                    st->prefix[k] = (p_own << width) | (unsigned long long)(kScanBins * t + j);
+                    st->rank[k] = r - cum;
+                    if (cj > approx_max) st->more[round] = 1;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < kScanBins; j += 2) *reinterpret_cast<ulonglong2*>(H + j) = make_ulonglong2(0, 0);
+        }
+        stamp();
+        grid.sync();
+        stamp();
+        bad = __ldcg(&st->bad);
+        const int more = __ldcg(&st->more[round]);
+        top = shift;
+        nhist = nk;
+        round++;
+        if (approx_max && !more) break;
+    }
+    if (blockIdx.x == 0 && t < nk) {
+        unsigned long long key = round == 0 ? 0ull : __ldcg(&st->prefix[t]);
+        if (top > 0) {  // (only when approx_max stopped the rounds early: the bucket's ends)
+            key <<= top;
+            if ((ceil_mask >> t) & 1) key |= (1ull << top) - 1;
+        }
+        key = key < range ? key : range;
+        st->result[t] = (long long)((key + kmin) ^ 0x8000000000000000ull);
+    }
+    if (blockIdx.x == 0 && t == 0) {
+        st->top = 0;
+        st->nk = nk;
+        st->key_base = kmin;
+        st->nstamp = nstamp;
+    }
+}
+
 // dynamic window: everything up to the end of the counters (absolute address, see the map above), then the tile ring
 size_t hist_smem(int nbins, int lut_bytes, int nstages, bool collect) {
     const size_t end = lut_abs(collect) + (size_t)lut_bytes + (size_t)kHistWarps * (nbins + 1) * 32 * sizeof(unsigned);
@@ -1003,33 +1229,77 @@ int sm_count() {
 // position would alias with anything periodic in the data, e.g. 48 workers writing round-robin).
 __global__ void __launch_bounds__(256)
 sample_kernel(const long long* __restrict__ x, size_t stride, long long* __restrict__ out, size_t s,
-              unsigned long long* __restrict__ outside) {
-    const size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
-    bool wide = false;
-    if (i < s) {
+              unsigned long long* __restrict__ outside, LatMoments* __restrict__ bounds) {
+    long long mn = 0x7FFFFFFFFFFFFFFFll, mx = (long long)0x8000000000000000ull;
+    unsigned wide = 0;
+    auto where = [&](size_t i) -> const long long* {
         unsigned long long z = (i + 1) * 0x9E3779B97F4A7C15ull;
         z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
         z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
         z ^= z >> 31;
-        const long long v = __ldg(x + i * stride + z % stride);
+        return x + i * stride + z % stride;
+    };
+    auto take = [&](size_t i, long long v) {
         out[i] = v;
-        wide = ((unsigned long long)v >> 32) != 0;  // negative or >= 2^32: not on the histogram kernel's fast path
+        wide += ((unsigned long long)v >> 32) != 0;  // negative or >= 2^32: not on the histogram kernel's fast path
+        mn = v < mn ? v : mn;
+        mx = v > mx ? v : mx;
+    };
+    // every load is a DRAM access of its own with nothing to hide behind: four in flight per thread
+    const size_t step = (size_t)gridDim.x * 256;
+    size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    for (; i + 3 * step < s; i += 4 * step) {
+        const long long a = __ldg(where(i)), b = __ldg(where(i + step)), c = __ldg(where(i + 2 * step)),
+                        d = __ldg(where(i + 3 * step));
+        take(i, a); take(i + step, b); take(i + 2 * step, c); take(i + 3 * step, d);
     }
-    // how much of the sample the 32-bit fast path cannot take: the caller decides whether a histogram pass pays
-    const unsigned m = __ballot_sync(0xFFFFFFFFu, wide);
-    if (outside && m && (threadIdx.x & 31) == 0) atomicAdd(outside, (unsigned long long)__popc(m));
+    for (; i < s; i += step) take(i, __ldg(where(i)));
+    // how much of the sample the 32-bit fast path cannot take (the caller decides whether a histogram pass pays),
+    // and the sample's extremes (the bounds of the select that follows): one set of atomics per CTA
+    __shared__ long long smn[8], smx[8];
+    __shared__ unsigned swide[8];
+#pragma unroll
+    for (int d = 16; d; d >>= 1) {
+        const long long omn = __shfl_xor_sync(0xFFFFFFFFu, mn, d), omx = __shfl_xor_sync(0xFFFFFFFFu, mx, d);
+        mn = omn < mn ? omn : mn;
+        mx = omx > mx ? omx : mx;
+        wide += __shfl_xor_sync(0xFFFFFFFFu, wide, d);
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) { smn[warp] = mn; smx[warp] = mx; swide[warp] = wide; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; w++) {
+            mn = smn[w] < mn ? smn[w] : mn;
+            mx = smx[w] > mx ? smx[w] : mx;
+            wide += swide[w];
+        }
+        if (outside && wide) atomicAdd(outside, (unsigned long long)wide);
+        if (bounds && mn <= mx) {
+            atomicMin(&bounds->min_ns, mn);
+            atomicMax(&bounds->max_ns, mx);
+        }
+    }
 }
 
 }  // namespace
 
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
-                          unsigned long long* d_outside) {
+                          unsigned long long* d_outside, LatMoments* d_bounds) {
     if (d_outside) {
         cudaError_t e = cudaMemsetAsync(d_outside, 0, sizeof *d_outside, stream);
         if (e != cudaSuccess) return e;
     }
+    if (d_bounds) {
+        LatMoments init{};
+        init.min_ns = 0x7FFFFFFFFFFFFFFFll;
+        init.max_ns = (long long)0x8000000000000000ull;
+        cudaError_t e = cudaMemcpyAsync(d_bounds, &init, sizeof init, cudaMemcpyHostToDevice, stream);
+        if (e != cudaSuccess) return e;
+    }
     if (!s) return cudaSuccess;
-    sample_kernel<<<(unsigned)((s + 255) / 256), 256, 0, stream>>>(d_samples, stride, d_out, s, d_outside);
+    const unsigned grid = (unsigned)std::min<size_t>((s + 255) / 256, (size_t)sm_count() * 8);
+    sample_kernel<<<grid, 256, 0, stream>>>(d_samples, stride, d_out, s, d_outside, d_bounds);
     return cudaGetLastError();
 }
 
@@ -1169,6 +1439,51 @@ cudaError_t launch_select_resident(const long long* d_samples, size_t n, const S
         sel_scan_kernel<<<1, 1024, 0, stream>>>(s.d_sel, s.d_sel_hist);
     }
     return cudaGetLastError();
+}
+
+// 1 when this device can run the one-kernel select (cooperative launch, a CTA per SM with the histograms of
+// kSelMax ranks in shared memory), 0 when not or when B200_SELECT_FUSED=0 asks for the separate launches
+int select_fused_grid() {
+    static const int grid = [] {
+        const char* e = getenv("B200_SELECT_FUSED");
+        if (e && *e == '0') return 0;
+        int dev = 0, coop = 0, per_sm = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+        if (!coop) return 0;
+        const size_t smem = (size_t)kSelMax * kRadixBins * sizeof(unsigned);
+        if (cudaFuncSetAttribute(sel_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sel_fused_kernel, kFusedThreads, smem) != cudaSuccess ||
+            per_sm < 1) {
+            cudaGetLastError();
+            return 0;
+        }
+        return sm_count();  // (devices of one process are alike: B200s)
+    }();
+    return grid;
+}
+
+cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelRanks& ranks, int have_bounds,
+                                long long lo, long long hi, unsigned long long approx_max, unsigned ceil_mask,
+                                const LatScratch& s, cudaStream_t stream) {
+    // (the kernel leaves the histograms cleared; the memset makes that independent of how an earlier run ended)
+    cudaError_t e = cudaMemsetAsync(s.d_sel_hist, 0, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long), stream);
+    if (e != cudaSuccess) return e;
+    if (!have_bounds) {
+        e = reset_moments(s, stream);
+        if (e != cudaSuccess) return e;
+    }
+    const size_t want_ctas = (n / 4 + kFusedThreads - 1) / kFusedThreads;
+    const int grid = (int)std::min<size_t>((size_t)select_fused_grid(), want_ctas ? want_ctas : 1);
+    const size_t smem = (size_t)kSelMax * kRadixBins * sizeof(unsigned);
+    SelState* st = s.d_sel;
+    unsigned long long* hist = s.d_sel_hist;
+    LatMoments* mom = s.d_mom;
+    SelRanks r = ranks;
+    int hb = have_bounds;
+    void* args[] = {(void*)&d_samples, (void*)&n, (void*)&st, (void*)&hist, (void*)&mom, (void*)&r, (void*)&hb,
+                    (void*)&lo, (void*)&hi, (void*)&approx_max, (void*)&ceil_mask};
+    return cudaLaunchCooperativeKernel((const void*)sel_fused_kernel, dim3(grid), dim3(kFusedThreads), args, smem, stream);
 }
 
 cudaError_t launch_compact(const long long* d_samples, size_t n, unsigned long long key_base, int top, int nprefix,

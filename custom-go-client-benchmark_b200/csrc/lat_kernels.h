@@ -63,6 +63,9 @@ struct SelState {
     int top;                            // bits of key - key_base still unresolved
     int nk, nhist;                      // ranks; histograms the next pass fills (1 on the first pass)
     int bad;                            // a rank fell outside the counted samples
+    int more[kSelMax];                  // one-kernel select: round r left a bucket above approx_max
+    unsigned long long stamp[24];       // one-kernel select: %globaltimer of CTA 0 at its phase ends (B200_SELECT_TRACE)
+    int nstamp;
 };
 struct SelRanks {
     unsigned long long rank[kSelMax];
@@ -99,10 +102,21 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
                         cudaStream_t stream, const HistParams& P, const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 // *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32
+// d_bounds: when given, its min_ns / max_ns are reset and receive the extremes of the sample (the bounds of a select
+// over it that follows on the stream)
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
-                          unsigned long long* d_outside = nullptr);
+                          unsigned long long* d_outside = nullptr, LatMoments* d_bounds = nullptr);
 // All the passes of a radix select of up to kSelMax ranks over [lo, hi] (pass have_bounds = false to take the
 // bounds from a min/max pass first), queued on the stream; the answer lands in s.d_sel (result[], bad).
+// The same select in one cooperative kernel (select_fused_grid() != 0 says the device can).  approx_max > 0: stop
+// refining a rank once its bucket holds at most that many samples and give the bucket's lowest key (highest for the
+// ranks in ceil_mask): bounds on the order statistics, for the sampled select's brackets.
+int select_fused_grid();
+// have_bounds: 0 the kernel finds min and max itself, 1 [lo, hi] are given, 2 they are in s.d_mom already (left by
+// launch_sample with `bounds` on the same stream)
+cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelRanks& ranks, int have_bounds,
+                                long long lo, long long hi, unsigned long long approx_max, unsigned ceil_mask,
+                                const LatScratch& s, cudaStream_t stream);
 cudaError_t launch_select_resident(const long long* d_samples, size_t n, const SelRanks& ranks, bool have_bounds,
                                    long long lo, long long hi, const LatScratch& s, cudaStream_t stream);
 // One MSD radix pass over key' = (ns ^ 2^63) - key_base: for each k < nk count the digit

@@ -550,3 +550,31 @@ def test_bracket_pass_when_a_tile_parks_more_than_its_queue_holds(ctx, burst, he
     assert (p.avg, p.p20, p.p50, p.p90, p.p99, p.min, p.max) == (
         int(us.sum()) // n, *[int(srt[k]) // 1000 for k in ks], int(us.min()), int(us.max()))
     ctx.free_device(d)
+
+
+def test_one_kernel_select_against_numpy_many_shapes(ctx):
+    """The resident (one-kernel, cooperative) select on 80 random inputs of 1 .. 2.1 M samples: latency-like,
+    full-range int64, three distinct values, exponential with multi-second outliers; 1..8 ranks; both alignments.
+    (A rank re-read after its update made about 3 % of such calls fail before the fix this guards.)"""
+    rng = np.random.default_rng(7)
+    cap = 2_100_000
+    d = ctx.alloc_device(cap * 8 + 16)
+    for it in range(80):
+        n = int(rng.choice([1, 2, 3, 100, 4097, 65536, 1_000_000, 2_000_001])) if it % 3 else int(rng.integers(1, cap))
+        kind = it % 4
+        if kind == 0:
+            ns = rng.integers(20_000_000, 95_000_000, size=n)
+        elif kind == 1:
+            ns = rng.integers(-2**62, 2**62, size=n)
+        elif kind == 2:
+            ns = np.full(n, 57_000_000) + rng.integers(0, 3, size=n)
+        else:
+            ns = rng.exponential(5e7, size=n).astype(np.int64)
+            ns[rng.integers(0, n, size=max(1, n // 200))] = 9_000_000_000
+        ns = ns.astype(np.int64)
+        off = int(rng.integers(0, 2))
+        ctx.h2d(d + 8 * off, ns)
+        ks = sorted(int(x) for x in rng.integers(0, n, size=int(rng.integers(1, 9))))
+        want = [int(x) for x in np.partition(ns, ks)[ks]]
+        assert lat.select_kth(d + 8 * off, n, 1, ks, ctx=ctx) == want, (it, n, kind, off, ks)
+    ctx.free_device(d)

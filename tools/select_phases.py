@@ -9,6 +9,10 @@ crc32c, lat = pkg.crc32c, pkg.latency
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 500_000_000
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 ctx = crc32c.Context([0])
+if os.environ.get("B200_L2_FETCH"):  # experiment: the device's L2 fetch granularity (bytes)
+    from cuda import cudart
+    print("set limit:", cudart.cudaDeviceSetLimit(cudart.cudaLimit.cudaLimitMaxL2FetchGranularity, int(os.environ["B200_L2_FETCH"])),
+          cudart.cudaDeviceGetLimit(cudart.cudaLimit.cudaLimitMaxL2FetchGranularity))
 d = ctx.alloc_device(n * 8)
 ctx.fill_latency_ns(d, n, 0xC0FFEE)
 for _ in range(2):

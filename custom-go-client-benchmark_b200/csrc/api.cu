@@ -1222,9 +1222,10 @@ int b200_hist_fixed(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P));
     unsigned long long c[kMaxThresholds + 1];
     LatMoments m;
-    CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
-    CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+    CU(lat_read_results(d->lat, d->stream));
     CU(cudaStreamSynchronize(d->stream));
+    memcpy(c, d->lat.h_results->counts, sizeof c);
+    m = d->lat.h_results->mom;
     uint64_t below = 0, above = 0;
     if (mode == B200_HIST_NUMPY) {
         for (int i = 0; i < nedges - 1; i++) counts[i] = c[i + 1];
@@ -1266,9 +1267,10 @@ int b200_hist_fixed_pair(b200_ctx* ctx, int dev, const int64_t* d_samples, size_
         std::lock_guard<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P));
-        CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
-        CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+        CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
+        memcpy(c, d->lat.h_results->counts, sizeof c);
+        m = d->lat.h_results->mom;
     }
     // union bin g holds the samples with exactly g union thresholds <= them, i.e. those in [u[g-1], u[g]); the
     // number of a histogram's own thresholds <= such a sample is the number of them <= u[g-1]
@@ -1378,7 +1380,7 @@ int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     if (first) {
         if (!grow(&d->lat.d_sample, &d->lat.sample_cap, n)) return 1;  // (the caller takes another route)
         CU(launch_sample((const long long*)first->src, first->stride, d->lat.d_sample, n, d->stream, d->lat.d_compact_n,
-                         fused ? d->lat.d_mom : nullptr));
+                         fused ? d->lat.d_mom : nullptr, &d->lat.d_results_init->mom));
         d_samples = (const int64_t*)d->lat.d_sample;
         bounds = fused ? 2 : 0;
     }
@@ -1394,11 +1396,11 @@ int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         } else {
             CU(launch_select_resident((const long long*)d_samples, n, r, bounds == 1, lo, hi, d->lat, d->stream));
         }
-        SelState st;
-        CU(cudaMemcpyAsync(&st, d->lat.d_sel, sizeof st, cudaMemcpyDeviceToHost, d->stream));
-        if (first && g == 0)
-            CU(cudaMemcpyAsync(&first->outside, d->lat.d_compact_n, sizeof first->outside, cudaMemcpyDeviceToHost, d->stream));
+        CU(cudaMemcpyAsync(d->lat.h_sel, d->lat.d_sel, sizeof(SelState), cudaMemcpyDeviceToHost, d->stream));
+        if (first && g == 0) CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
+        const SelState& st = *d->lat.h_sel;
+        if (first && g == 0) first->outside = d->lat.h_results->compact_n;
         if (st.bad || st.top != 0) {
             if (select_trace_on()) fprintf(stderr, "b200 select: resident select failed: bad=%d top=%d n=%zu\n", st.bad, st.top, n);
             return fail(B200_ERR_INVALID, "b200_select_kth: samples outside the given [lo, hi] range");
@@ -1670,10 +1672,11 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         if (!grow(&d->lat.d_collect, &d->lat.collect_cap, cap)) return sampled_trace("skip: no memory for the brackets", 1);
         HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
         CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P, &col));
-        CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
-        if (stats) CU(cudaMemcpyAsync(&mom, d->lat.d_mom, sizeof mom, cudaMemcpyDeviceToHost, d->stream));
-        CU(cudaMemcpyAsync(&kept, d->lat.d_compact_n, sizeof kept, cudaMemcpyDeviceToHost, d->stream));
+        CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
+        memcpy(c, d->lat.h_results->counts, sizeof c);
+        mom = d->lat.h_results->mom;
+        kept = d->lat.h_results->compact_n;
     }
     const double ms_pass = ms_since(t0) - ms_sample;
     uint64_t inside = 0, total = 0;
@@ -1784,10 +1787,11 @@ int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n
     CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P, &col));
     unsigned long long c[kMaxThresholds + 1], kept = 0;
     LatMoments m{};
-    CU(cudaMemcpyAsync(c, d->lat.d_counts, sizeof c, cudaMemcpyDeviceToHost, d->stream));
-    CU(cudaMemcpyAsync(&kept, d->lat.d_compact_n, sizeof kept, cudaMemcpyDeviceToHost, d->stream));
-    if (stats) CU(cudaMemcpyAsync(&m, d->lat.d_mom, sizeof m, cudaMemcpyDeviceToHost, d->stream));
+    CU(lat_read_results(d->lat, d->stream));
     CU(cudaStreamSynchronize(d->stream));
+    memcpy(c, d->lat.h_results->counts, sizeof c);
+    kept = d->lat.h_results->compact_n;
+    m = d->lat.h_results->mom;
     for (int i = 0; i <= nthr; i++) counts[i] = c[i];
     *nkept = kept;
     *d_kept = (const int64_t*)d->lat.d_collect;

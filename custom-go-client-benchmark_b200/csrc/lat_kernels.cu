@@ -1285,16 +1285,13 @@ sample_kernel(const long long* __restrict__ x, size_t stride, long long* __restr
 }  // namespace
 
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
-                          unsigned long long* d_outside, LatMoments* d_bounds) {
+                          unsigned long long* d_outside, LatMoments* d_bounds, const LatMoments* d_bounds_init) {
     if (d_outside) {
         cudaError_t e = cudaMemsetAsync(d_outside, 0, sizeof *d_outside, stream);
         if (e != cudaSuccess) return e;
     }
-    if (d_bounds) {
-        LatMoments init{};
-        init.min_ns = 0x7FFFFFFFFFFFFFFFll;
-        init.max_ns = (long long)0x8000000000000000ull;
-        cudaError_t e = cudaMemcpyAsync(d_bounds, &init, sizeof init, cudaMemcpyHostToDevice, stream);
+    if (d_bounds && d_bounds_init) {
+        cudaError_t e = cudaMemcpyAsync(d_bounds, d_bounds_init, sizeof(LatMoments), cudaMemcpyDeviceToDevice, stream);
         if (e != cudaSuccess) return e;
     }
     if (!s) return cudaSuccess;
@@ -1322,28 +1319,46 @@ cudaError_t smem_base_probe(unsigned long long* d_tmp) {
 
 cudaError_t lat_scratch_init(LatScratch* s) {
     memset(s, 0, sizeof *s);
-    cudaError_t e = cudaMalloc(&s->d_compact_n, sizeof(unsigned long long));
+    cudaError_t e = cudaMalloc(&s->d_results, sizeof(LatResults));
     if (e != cudaSuccess) return e;
+    s->d_counts = s->d_results->counts;  // (addresses only: nothing is read through the device pointer here)
+    s->d_mom = &s->d_results->mom;
+    s->d_compact_n = &s->d_results->compact_n;
     e = smem_base_probe(s->d_compact_n);
     if (e != cudaSuccess) return e;
-    e = cudaMalloc(&s->d_params, sizeof(HistParams));
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_counts, (kMaxThresholds + 1) * sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_mom, sizeof(LatMoments));
+    e = cudaMalloc(&s->d_results_init, sizeof(LatResults));
+    if (e == cudaSuccess) e = cudaHostAlloc(&s->h_results, sizeof(LatResults), cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaHostAlloc(&s->h_params, sizeof(HistParams), cudaHostAllocDefault);
+    if (e == cudaSuccess) e = cudaHostAlloc(&s->h_sel, sizeof(SelState), cudaHostAllocDefault);
+    if (e == cudaSuccess) {
+        memset(s->h_results, 0, sizeof(LatResults));
+        s->h_results->mom.min_ns = 0x7FFFFFFFFFFFFFFFll;
+        s->h_results->mom.max_ns = (long long)0x8000000000000000ull;
+        e = cudaMemcpy(s->d_results_init, s->h_results, sizeof(LatResults), cudaMemcpyHostToDevice);
+    }
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_params, sizeof(HistParams));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel, sizeof(SelState));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
     return e;
 }
-
+cudaError_t lat_reset_results(const LatScratch& s, cudaStream_t stream) {
+    return cudaMemcpyAsync(s.d_results, s.d_results_init, sizeof(LatResults), cudaMemcpyDeviceToDevice, stream);
+}
+cudaError_t lat_read_results(const LatScratch& s, cudaStream_t stream) {
+    return cudaMemcpyAsync(s.h_results, s.d_results, sizeof(LatResults), cudaMemcpyDeviceToHost, stream);
+}
 void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_params);
-    cudaFree(s->d_counts);
-    cudaFree(s->d_mom);
+    cudaFree(s->d_results);
+    cudaFree(s->d_results_init);
+    cudaFreeHost(s->h_results);
+    cudaFreeHost(s->h_params);
+    cudaFreeHost(s->h_sel);
     cudaFree(s->d_radix);
     cudaFree(s->d_prefix);
     cudaFree(s->d_compact);
-    cudaFree(s->d_compact_n);
     cudaFree(s->d_sel);
     cudaFree(s->d_sel_hist);
     cudaFree(s->d_sample);
@@ -1352,21 +1367,19 @@ void lat_scratch_free(LatScratch* s) {
 }
 
 static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
-    LatMoments init{};
-    init.min_ns = 0x7FFFFFFFFFFFFFFFll;
-    init.max_ns = (long long)0x8000000000000000ull;
-    return cudaMemcpyAsync(s.d_mom, &init, sizeof init, cudaMemcpyHostToDevice, stream);
+    return cudaMemcpyAsync(s.d_mom, &s.d_results_init->mom, sizeof(LatMoments), cudaMemcpyDeviceToDevice, stream);
 }
 
 cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
                         cudaStream_t stream, const HistParams& P, const HistCollect* collect) {
-    cudaError_t e = cudaMemcpyAsync(s.d_params, &P, sizeof P, cudaMemcpyHostToDevice, stream);
+    // (the pinned staging is free again when the stream has been waited for, which every caller does before its
+    // next launch; the device's lock is held throughout)
+    memcpy(s.h_params, &P, sizeof P);
+    cudaError_t e = cudaMemcpyAsync(s.d_params, s.h_params, sizeof P, cudaMemcpyHostToDevice, stream);
     if (e != cudaSuccess) return e;
-    e = cudaMemsetAsync(s.d_counts, 0, (kMaxThresholds + 1) * sizeof(unsigned long long), stream);
+    e = lat_reset_results(s, stream);  // counts, moments and the collect counter (s.d_compact_n)
     if (e != cudaSuccess) return e;
-    e = reset_moments(s, stream);
-    if (e != cudaSuccess) return e;
-    if (collect) {
+    if (collect && collect->count != s.d_compact_n) {
         e = cudaMemsetAsync(collect->count, 0, sizeof(unsigned long long), stream);
         if (e != cudaSuccess) return e;
     }

@@ -72,8 +72,22 @@ struct SelRanks {
     int nk;
 };
 
+// What a histogram pass leaves behind, in ONE device block so that a call resets it with one device-to-device
+// copy (from a template held beside it) and reads it back with one copy into pinned memory: a pageable copy per
+// field and direction was ~10 us each, a sixth of a seven-line call.
+struct LatResults {
+    unsigned long long counts[kMaxThresholds + 1];
+    LatMoments mom;
+    unsigned long long compact_n;       // samples kept / compacted / outside the fast path (one counter, reused)
+};
+
 struct LatScratch {
     HistParams* d_params;
+    LatResults* d_results;              // the block; the three pointers below point into it
+    LatResults* d_results_init;         // the template: zero counts, min = INT64_MAX, max = INT64_MIN
+    LatResults* h_results;              // pinned: lat_read_results() copies the block here
+    HistParams* h_params;               // pinned staging of the parameter block
+    SelState* h_sel;                    // pinned: the resident select's state, read back
     unsigned long long* d_counts;       // [kMaxThresholds + 1]
     LatMoments* d_mom;
     unsigned long long* d_radix;        // [kMaxSelect][kRadixBins]
@@ -95,6 +109,9 @@ struct LatScratch {
 cudaError_t smem_base_probe(unsigned long long* d_tmp);
 cudaError_t lat_scratch_init(LatScratch* s);
 void lat_scratch_free(LatScratch* s);
+// counts = 0, moments = start values, compact_n = 0 (one device-to-device copy); the whole block -> s.h_results
+cudaError_t lat_reset_results(const LatScratch& s, cudaStream_t stream);
+cudaError_t lat_read_results(const LatScratch& s, cudaStream_t stream);
 
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
 // (uploads P to s.d_params first; P must have been built with collect == (collect != nullptr))
@@ -102,10 +119,11 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
                         cudaStream_t stream, const HistParams& P, const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 // *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32
-// d_bounds: when given, its min_ns / max_ns are reset and receive the extremes of the sample (the bounds of a select
-// over it that follows on the stream)
+// d_bounds: when given, it is reset from d_bounds_init (start values, on the device) and its min_ns / max_ns receive
+// the extremes of the sample (the bounds of a select over it that follows on the stream)
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
-                          unsigned long long* d_outside = nullptr, LatMoments* d_bounds = nullptr);
+                          unsigned long long* d_outside = nullptr, LatMoments* d_bounds = nullptr,
+                          const LatMoments* d_bounds_init = nullptr);
 // All the passes of a radix select of up to kSelMax ranks over [lo, hi] (pass have_bounds = false to take the
 // bounds from a min/max pass first), queued on the stream; the answer lands in s.d_sel (result[], bad).
 // The same select in one cooperative kernel (select_fused_grid() != 0 says the device can).  approx_max > 0: stop

@@ -89,6 +89,28 @@ struct KeepStage {
     long long* q;    // shared: [kKeepCap]
 };
 
+// A sample of a kept bin -> the warp's staging; straight to the buffer when the staging is full.  The lanes that
+// arrive here together share one reservation.  Out of line (called from the drain of parked samples).
+__device__ __noinline__ void keep_sample(long long v, const HistCollect* col, KeepStage keep) {
+    const unsigned peers = __activemask();
+    const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+    const unsigned cnt = __popc(peers), rank = __popc(peers & ((1u << lane) - 1));
+    unsigned pos = 0;
+    if (lane == leader) {
+        pos = *keep.n;
+        if (pos + cnt <= (unsigned)kKeepCap) *keep.n = pos + cnt; else pos = 0xFFFFFFFFu;
+    }
+    pos = __shfl_sync(peers, pos, leader);
+    if (pos != 0xFFFFFFFFu) {
+        keep.q[pos + rank] = v;
+    } else {
+        unsigned long long at = 0;
+        if (lane == leader) at = atomicAdd(col->count, (unsigned long long)cnt);
+        at = __shfl_sync(peers, at, leader) + rank;
+        if (at < col->cap) col->buf[at] = v;
+    }
+}
+
 // Generic path: any int64 sample.  Out of line, so that the fast loop keeps its registers and instruction cache.
 // s == nullptr: count (and collect) only, no moments.  keep: this warp's staging (collecting kernels).
 __device__ __noinline__ void slow_sample(long long v, const SlowParams* __restrict__ P, unsigned* mine,
@@ -100,28 +122,7 @@ __device__ __noinline__ void slow_sample(long long v, const SlowParams* __restri
     }
     const int c = lo;
     mine[(c + 1) * 32]++;  // row 0 is the scratch row, bin c is row c + 1
-    if (col) {  // odd bins are kept: staged in shared memory; straight to the buffer when the staging is full
-        const bool hit = c & 1;
-        const unsigned peers = __ballot_sync(__activemask(), hit);
-        if (hit) {
-            const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
-            const unsigned cnt = __popc(peers), rank = __popc(peers & ((1u << lane) - 1));
-            unsigned pos = 0;
-            if (lane == leader) {
-                pos = *keep.n;
-                if (pos + cnt <= (unsigned)kKeepCap) *keep.n = pos + cnt; else pos = 0xFFFFFFFFu;
-            }
-            pos = __shfl_sync(peers, pos, leader);
-            if (pos != 0xFFFFFFFFu) {
-                keep.q[pos + rank] = v;
-            } else {
-                unsigned long long at = 0;
-                if (lane == leader) at = atomicAdd(col->count, (unsigned long long)cnt);
-                at = __shfl_sync(peers, at, leader) + rank;
-                if (at < col->cap) col->buf[at] = v;
-            }
-        }
-    }
+    if (col && (c & 1)) keep_sample(v, col, keep);  // odd bins are kept
     if (s) {
         s->mn = v < s->mn ? v : s->mn;
         s->mx = v > s->mx ? v : s->mx;
@@ -159,7 +160,7 @@ constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long 
 #define B200_PARK_PLAIN 32
 #endif
 __host__ __device__ constexpr int park_cap(bool collect) { return collect ? B200_PARK_COLLECT : B200_PARK_PLAIN; }
-// a collecting kernel parks without a branch (park_if_zero): one more slot takes what does not fit
+// a collecting kernel parks without a branch (park_if_even): one more slot takes what does not fit
 __host__ __device__ constexpr int park_slots(bool collect) { return park_cap(collect) + (collect ? 1 : 0); }
 // unsigned char[lut_bytes], lut_bytes <= kLutSize
 __host__ __device__ constexpr unsigned lut_abs(bool collect) { return kParkQAbs + kHistWarps * park_slots(collect) * 8; }
@@ -355,14 +356,16 @@ __device__ __forceinline__ void split64(long long v, unsigned& lo, unsigned& hi)
 
 // Collecting kernels park without a branch: about one sample in a hundred is parked (kept, or in a cell with a
 // threshold), so three groups of four in four meet one somewhere in the warp, and a divergent block there — ~50
-// warp instructions with its convergence barriers — was a quarter of the pass.  Predicated instead: when row == 0
+// warp instructions with its convergence barriers — was a quarter of the pass.  Predicated instead: when the row is
+// even (0: the table has no bin for the cell; 2, 4, ...: a kept bin, counted on the fast path but still to be collected)
 // the sample goes to the warp's queue at the byte offset an atomic add of 8 returns; offsets past the queue's cap
 // land in the spare slot behind it, and the caller, who looks at the count once per tile, redoes that tile.
-__device__ __forceinline__ void park_if_zero(unsigned row, long long v, unsigned count_abs, unsigned queue_abs,
+__device__ __forceinline__ void park_if_even(unsigned row, long long v, unsigned count_abs, unsigned queue_abs,
                                              unsigned cap_bytes) {
     asm volatile(
         "{\n\t.reg .pred p;\n\t.reg .u32 at;\n\t"
-        "setp.eq.u32 p, %0, 0;\n\t"
+        "and.b32 at, %0, 1;\n\t"
+        "setp.eq.u32 p, at, 0;\n\t"
         "@p atom.shared.add.u32 at, [%1], 8;\n\t"
         "@p min.u32 at, at, %4;\n\t"
         "@p add.u32 at, at, %2;\n\t"
@@ -509,6 +512,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         split64(v, lo, hi);
         const unsigned u = shifted(lo, hi), row = row_of(index_of(u, q));
         if (row == 0) slow(v);  // its bin; the moments below are the fast path's
+        else if (COLLECT && !(row & 1)) keep_sample(v, &col, keep);  // a kept bin the table knows
         bump_abs(mine_abs + (row << 7));
         nproc++;
         if (MOMENTS) {
@@ -536,12 +540,12 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         for (int k = 0; k < K; k++) row[k] = row_of(idx[k]);
         if constexpr (COLLECT) {
 #pragma unroll
-            for (int k = 0; k < K; k++) park_if_zero(row[k], v[k], park_n_abs, park_q_abs, kParkCap * 8u);
+            for (int k = 0; k < K; k++) park_if_even(row[k], v[k], park_n_abs, park_q_abs, kParkCap * 8u);
             if ((any_hi >> out_shift) != 0) {  // beyond the reach: parked whatever its table entry said; surrogate
 #pragma unroll
                 for (int k = 0; k < K; k++)
                     if ((hi[k] >> out_shift) != 0) {
-                        if (row[k] != 0) park_if_zero(0u, v[k], park_n_abs, park_q_abs, kParkCap * 8u);
+                        if (row[k] & 1) park_if_even(0u, v[k], park_n_abs, park_q_abs, kParkCap * 8u);
                         const bool neg = (int)hi[k] < 0;
                         u[k] = neg ? 0u : u_top;
                         if (BYQ) q[k] = quotient(u[k]);
@@ -598,8 +602,21 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     auto before_step = [&] {
         if (collecting && *keep.n > (unsigned)(kKeepCap - 32)) flush_keep();
     };
+    // a queued sample of a collecting kernel: outside the reach or without a bin from the table -> the generic
+    // routine; in a kept bin the table knows (already counted) -> collected, nothing else
+    auto parked_one = [&](long long v) {
+        if (COLLECT && ((unsigned long long)v >> reach_bits) == 0) {
+            unsigned lo, hi, q = 0;
+            split64(v, lo, hi);
+            if (row_of(index_of(shifted(lo, hi), q)) != 0) {
+                keep_sample(v, &col, keep);
+                return;
+            }
+        }
+        slow(v);
+    };
     auto drain = [&] {  // whole warp, converged
-        drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step, COLLECT ? 3 : 0);
+        drain_parked(park_n(), park_q(), kParkCap, lane, parked_one, before_step, COLLECT ? 3 : 0);
         if (COLLECT) {
             if (lane == 0) *park_start() = 0;
             __syncwarp();
@@ -622,13 +639,15 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
                 const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
 #pragma unroll
                 for (int k = 0; k < 8; k++) {
-                    bool parked = ((unsigned long long)v[k] >> reach_bits) != 0;
-                    if (!parked) {
+                    bool outside = ((unsigned long long)v[k] >> reach_bits) != 0;
+                    unsigned row = 1;
+                    if (!outside) {
                         unsigned lo, hi, q = 0;
                         split64(v[k], lo, hi);
-                        parked = row_of(index_of(shifted(lo, hi), q)) == 0;
+                        row = row_of(index_of(shifted(lo, hi), q));
                     }
-                    if (parked) slow(v[k]);
+                    if (outside || row == 0) slow(v[k]);
+                    else if (!(row & 1)) keep_sample(v[k], &col, keep);
                 }
                 __syncwarp();
             } else if (bytes >= kParkCap * 4u) {
@@ -1630,8 +1649,8 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
         }
     }
     // The look-up table (see hist_kernel).  Cell c covers the samples [lo_c, hi_c]; its entry is 1 + the number of
-    // thresholds <= lo_c — the counter row of every sample in the cell — unless a threshold lies inside (lo_c, hi_c]
-    // or, when collecting, that bin is odd (kept): then 0, the sample is parked.
+    // thresholds <= lo_c — the counter row of every sample in the cell — unless a threshold lies inside (lo_c, hi_c]:
+    // then 0, the sample is parked.
     if (P->mode32 != 3) P->reach_bits = 32;
     const unsigned long long reach = 1ull << P->reach_bits;  // the fast path takes 0 <= n < reach
     auto fill = [&](auto cell_lo, auto cell_hi) {
@@ -1645,7 +1664,9 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
             while (below < m && P->thr[below] <= (long long)lo) below++;
             inside = 0;
             while (below + inside < m && P->thr[below + inside] <= (long long)hi) inside++;
-            const bool park = inside > 0 || (collect && (below & 1));
+            // (a collecting kernel also parks the cells of kept bins, which are the even rows: it tells them by the
+            // row's parity, and having the row it counts them on its fast path)
+            const bool park = inside > 0;
             P->lut[c] = park ? 0 : (unsigned char)(below + 1);
             parked += park;
         }

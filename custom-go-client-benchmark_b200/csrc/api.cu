@@ -1341,7 +1341,7 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
 namespace {
 
 int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
-                int64_t* out, b200_lat_stats* stats = nullptr);  // below, after the radix select it builds on
+                int64_t* out, b200_lat_stats* stats = nullptr, bool no_squares = false);  // below, after the radix select it builds on
 
 // Inputs up to this many samples are selected with all passes queued on the device (one host round trip);
 // longer ones that the sampled select did not settle take the host-driven passes with bucket compaction
@@ -1585,7 +1585,7 @@ bool grow(long long** buf, size_t* cap, size_t want) {
 //      samples, by the ordinary radix select.
 // The result is exact whenever it is given; a miss (returns 1) makes the caller take the radix passes.
 int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
-                   int nk, int64_t* out, b200_lat_stats* stats) {
+                   int nk, int64_t* out, b200_lat_stats* stats, bool no_squares) {
     DevState* d = get_dev(ctx, dev);
     if (!d || nk > kSelMax) return 1;
     std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
@@ -1671,7 +1671,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         CU(cudaSetDevice(dev));
         if (!grow(&d->lat.d_collect, &d->lat.collect_cap, cap)) return sampled_trace("skip: no memory for the brackets", 1);
         HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
-        CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P, &col));
+        CU(launch_hist((const long long*)d_samples, n, d->lat, stats ? (no_squares ? 2 : 1) : 0, d->stream, P, &col));
         CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
         memcpy(c, d->lat.h_results->counts, sizeof c);
@@ -1715,14 +1715,14 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
 
 // 0 = out[] is filled, 1 = not attempted or missed (take the radix passes), < 0 = error
 int try_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k, int nk,
-                int64_t* out, b200_lat_stats* stats) {
+                int64_t* out, b200_lat_stats* stats, bool no_squares) {
     if (g_sampled_depth != 0 || n < sampled_select_min() || !d_samples || ((uintptr_t)d_samples & 7)) return 1;
     for (int i = 0; i < nk; i++)
         if (k[i] >= n) return 1;  // the caller reports it
     // up to kSelMax ranks share a pass; more take one pass per group (the moments come from the first)
     for (int g = 0; g < nk; g += kSelMax) {
         const int rc = select_sampled(ctx, dev, d_samples, n, divisor, k + g, std::min(kSelMax, nk - g), out + g,
-                                      g == 0 ? stats : nullptr);
+                                      g == 0 ? stats : nullptr, no_squares);
         if (rc) return rc;  // a miss in any group: the caller redoes all of them by radix passes
     }
     return 0;
@@ -1799,8 +1799,29 @@ int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n
     return 0;
 }
 
+namespace {
+int select_kth_with_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
+                          int nk, int64_t* out, b200_lat_stats* stats, bool no_squares);
+}
+
 int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                           const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats) {
+    return select_kth_with_stats(ctx, dev, d_samples, n, divisor, k, nk, out, stats, false);
+}
+
+int b200_select_kth_avg(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                        const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats) {
+    const int rc = select_kth_with_stats(ctx, dev, d_samples, n, divisor, k, nk, out, stats, true);
+    if (rc == 0) stats->sumsq_lo = stats->sumsq_hi = 0;  // not part of this call's contract on any route
+    return rc;
+}
+
+}  // extern "C"
+
+namespace {
+
+int select_kth_with_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,
+                          int nk, int64_t* out, b200_lat_stats* stats, bool no_squares) {
     if (!k || !out || !stats || nk < 1 || divisor < 1 || !d_samples || ((uintptr_t)d_samples & 7))
         return fail(B200_ERR_INVALID, "b200_select_kth_stats");
     if (n == 0) return fail(B200_ERR_EMPTY, "b200_select_kth: no samples (the reference panics, ssd_test/main.go:157)");
@@ -1809,7 +1830,7 @@ int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size
     DevState* d = get_dev(ctx, dev);
     if (!d) return fail(B200_ERR_INVALID, "b200_select_kth: unknown device");
     {   // long inputs: moments and brackets in the same pass
-        const int rc = try_sampled(ctx, dev, d_samples, n, divisor, k, nk, out, stats);
+        const int rc = try_sampled(ctx, dev, d_samples, n, divisor, k, nk, out, stats, no_squares);
         if (rc <= 0) return rc;
     }
     // otherwise one pass for the moments (a histogram with a single threshold), then the radix select between
@@ -1832,7 +1853,7 @@ int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size
     return rc;
 }
 
-}  // extern "C"
+}  // namespace
 
 // ---- latency text codec + float64 histogram ----------------------------------------------------------------
 

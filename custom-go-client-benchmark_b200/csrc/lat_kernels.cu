@@ -410,8 +410,10 @@ constexpr int hist_ctas_by_regs(bool, bool) { return kHistCtasPerSm; }
 // DIVMODE (how the fast path divides a 32-bit sample): 0 divisor is 1, 1 multiply-high magic with the add fix-up,
 // 2 divisor >= 2^32 (quotient 0), 3 pre-shift + multiply-high without fix-up and quotient < 2^28; BYQ implies 3
 // with quotients < 2^13, whose sums of eight (and of a thread's whole share) fit 32 bits.
-template <bool MOMENTS, int DIVMODE, bool BYQ, bool COLLECT>
-__global__ void __launch_bounds__(kHistThreads, hist_ctas_by_regs(MOMENTS, BYQ))
+// MOMENTS: 0 none; 1 count, extremes, sum and sum of squares; 2 the same without the squares (what the seven
+// ssd_test lines need: three instructions per sample less)
+template <int MOMENTS, int DIVMODE, bool BYQ, bool COLLECT>
+__global__ void __launch_bounds__(kHistThreads, hist_ctas_by_regs(MOMENTS != 0, BYQ))
 hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restrict__ Pg,
             unsigned long long* __restrict__ counts, LatMoments* __restrict__ mom, const HistCollect col, int nstages) {
     static_assert(!BYQ || DIVMODE == 3, "the quotient index uses the pre-shift magic");
@@ -502,9 +504,11 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     };
     auto accumulate = [&](unsigned q) {  // running 64-bit sums; q*q wraps at most once per add
         m.fsum += q;
-        const unsigned long long sq = (unsigned long long)q * q + m.fsq;
-        m.fsq_carry += sq < m.fsq;
-        m.fsq = sq;
+        if (MOMENTS == 1) {
+            const unsigned long long sq = (unsigned long long)q * q + m.fsq;
+            m.fsq_carry += sq < m.fsq;
+            m.fsq = sq;
+        }
     };
     auto one = [&](long long v) {
         if ((unsigned long long)v >> reach_bits) { slow(v); return; }
@@ -585,12 +589,14 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
                 for (int k = 0; k < K; k++) {
                     const unsigned qq = BYQ ? q[k] : quotient(u[k]);
                     s += qq;
-                    sq += (unsigned long long)qq * qq;
+                    if (MOMENTS == 1) sq += (unsigned long long)qq * qq;
                 }
                 m.fsum += s;
-                sq += m.fsq;
-                m.fsq_carry += sq < m.fsq;
-                m.fsq = sq;
+                if (MOMENTS == 1) {
+                    sq += m.fsq;
+                    m.fsq_carry += sq < m.fsq;
+                    m.fsq = sq;
+                }
             } else {
 #pragma unroll
                 for (int k = 0; k < K; k++) accumulate(quotient(u[k]));
@@ -689,7 +695,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         sq.lo -= p_lo;
         sq.hi -= p_hi + b2;
     }
-    hist_epilogue<MOMENTS>(tbl, rows, nbins, n, counts, mom, mn, mx, sum, sq);
+    hist_epilogue<MOMENTS != 0>(tbl, rows, nbins, n, counts, mom, mn, mx, sum, sq);
 }
 
 constexpr int kMinmaxThreads = 256;
@@ -1389,7 +1395,7 @@ static cudaError_t reset_moments(const LatScratch& s, cudaStream_t stream) {
     return cudaMemcpyAsync(s.d_mom, &s.d_results_init->mom, sizeof(LatMoments), cudaMemcpyDeviceToDevice, stream);
 }
 
-cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
+cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, int want_moments,
                         cudaStream_t stream, const HistParams& P, const HistCollect* collect) {
     // (the pinned staging is free again when the stream has been waited for, which every caller does before its
     // next launch; the device's lock is held throughout)
@@ -1416,16 +1422,18 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
          hist_kernel<false, 3, false, true>},
         {hist_kernel<true, 0, false, true>, hist_kernel<true, 1, false, true>, hist_kernel<true, 2, false, true>,
          hist_kernel<true, 3, false, true>}};
+    static const Kernel collecting_no_squares[4] = {hist_kernel<2, 0, false, true>, hist_kernel<2, 1, false, true>,
+                                                    hist_kernel<2, 2, false, true>, hist_kernel<2, 3, false, true>};
     static const Kernel by_q[2] = {hist_kernel<false, 3, true, false>, hist_kernel<true, 3, true, false>};
     if (collect && P.by_q) return cudaErrorInvalidValue;  // the builder never pairs the two
-    const Kernel k = collect ? collecting[want_moments ? 1 : 0][P.mode32]
+    const Kernel k = collect ? (want_moments == 2 ? collecting_no_squares[P.mode32] : collecting[want_moments ? 1 : 0][P.mode32])
                              : P.by_q ? by_q[want_moments ? 1 : 0] : by_shift[want_moments ? 1 : 0][P.mode32];
     e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     if (e != cudaSuccess) return e;
     // resident CTAs per SM: kHistCtasPerSm by registers, fewer when the private counter tables are large
     const int nbins = P.nthr + 1;
     int per_sm, nstages;
-    hist_shape(hist_smem(nbins, P.lut_bytes, 0, collect != nullptr), hist_ctas_by_regs(want_moments, P.by_q != 0), &per_sm,
+    hist_shape(hist_smem(nbins, P.lut_bytes, 0, collect != nullptr), hist_ctas_by_regs(want_moments != 0, P.by_q != 0), &per_sm,
                &nstages);
     const size_t smem = hist_smem(nbins, P.lut_bytes, nstages, collect != nullptr);
     const int max_grid = sm_count() * per_sm;

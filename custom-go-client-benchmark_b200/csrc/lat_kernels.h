@@ -115,7 +115,8 @@ cudaError_t lat_read_results(const LatScratch& s, cudaStream_t stream);
 
 // counts[c] for c in 0..nthr, moments optional (want_moments).  Results stay on the device in scratch.
 // (uploads P to s.d_params first; P must have been built with collect == (collect != nullptr))
-cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, bool want_moments,
+// want_moments: 0 none, 1 all, 2 without the sum of squares (collecting passes only; elsewhere the same as 1)
+cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& s, int want_moments,
                         cudaStream_t stream, const HistParams& P, const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 // *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32

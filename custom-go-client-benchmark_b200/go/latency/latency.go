@@ -84,7 +84,7 @@ func ComputePercentiles(readTime []int64) (Percentiles, error) {
 	k := [4]C.uint64_t{C.uint64_t(size / 5), C.uint64_t(size / 2), C.uint64_t((9 * size) / 10), C.uint64_t((99 * size) / 100)}
 	var out [4]C.int64_t
 	var st C.b200_lat_stats
-	if err := status(C.b200_select_kth_stats(c, C.int(device), (*C.int64_t)(d), C.size_t(size), 1, &k[0], 4, &out[0], &st)); err != nil {
+	if err := status(C.b200_select_kth_avg(c, C.int(device), (*C.int64_t)(d), C.size_t(size), 1, &k[0], 4, &out[0], &st)); err != nil {
 		return Percentiles{}, err
 	}
 	sum := int64(st.sum) // the low 64 bits: what Go's `sum += readTime[i]` holds after wrapping

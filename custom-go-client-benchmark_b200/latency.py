@@ -463,10 +463,11 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
         karr = np.array([n // 5, n // 2, (9 * n) // 10, (99 * n) // 100], dtype=np.uint64)
         out = np.zeros(4, dtype=np.int64)
         st = LatStats()
-        check(ctx_._L.b200_select_kth_stats(ctx_._h, ctx_._dev(dev), d_samples_ns, n, divisor, karr.ctypes.data, 4,
-                                            out.ctypes.data, C.byref(st)))
+        # (the seven lines need the sum, not the sum of squares: b200_select_kth_avg)
+        check(ctx_._L.b200_select_kth_avg(ctx_._h, ctx_._dev(dev), d_samples_ns, n, divisor, karr.ctypes.data, 4,
+                                          out.ctypes.data, C.byref(st)))
         whole = merge_distribution(_Reducer(), np.zeros(0, dtype=np.uint64), st.count, st.min, st.max,
-                                   _signed(st.sum, st.sum_hi), (st.sumsq_hi << 64) | st.sumsq_lo, 0, 0)
+                                   _signed(st.sum, st.sum_hi), 0, 0, 0)
         return Percentiles(whole.avg_go_int, int(out[0]), int(out[1]), int(out[2]), int(out[3]), whole.min, whole.max)
     if dist is None:
         # several ranks: one sampled pass gives the ranks and the moments; the radix passes if it misses

@@ -191,6 +191,10 @@ int b200_select_kth(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
  * stats->dropped_* are 0. */
 int b200_select_kth_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                           const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats);
+/* The same without the sum of squares (stats->sumsq_* = 0): exactly what ssd_test/main.go:147-163 prints — the
+ * average needs the sum only — and the pass over long inputs is three instructions per sample shorter. */
+int b200_select_kth_avg(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                        const uint64_t* k, int nk, int64_t* out, b200_lat_stats* stats);
 /* Building blocks of the sampled select for the one-process-per-GPU form (custom-go-client-benchmark_b200/latency.py;
  * b200_select_kth runs the same steps itself on one device).
  * b200_select_sample: one sample per stratum of `stride` consecutive inputs, at a hashed position inside the

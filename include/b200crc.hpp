@@ -238,7 +238,7 @@ inline Percentiles ComputePercentiles(const Context& c, const int64_t* d_samples
     uint64_t ks[4] = {size / 5, size / 2, (9 * size) / 10, (99 * size) / 100};
     int64_t out[4];
     b200_lat_stats st;
-    check(b200_select_kth_stats(c.get(), dev < 0 ? c.device() : dev, d_samples_ns, n, divisor, ks, 4, out, &st));
+    check(b200_select_kth_avg(c.get(), dev < 0 ? c.device() : dev, d_samples_ns, n, divisor, ks, 4, out, &st));
     const int64_t sum = (int64_t)st.sum;  // Go's wrapping int64 sum
     return {sum / (int64_t)size, out[0], out[1], out[2], out[3], st.min, st.max};
 }

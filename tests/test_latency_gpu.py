@@ -578,3 +578,27 @@ def test_one_kernel_select_against_numpy_many_shapes(ctx):
         want = [int(x) for x in np.partition(ns, ks)[ks]]
         assert lat.select_kth(d + 8 * off, n, 1, ks, ctx=ctx) == want, (it, n, kind, off, ks)
     ctx.free_device(d)
+
+
+def test_select_kth_avg_is_select_kth_stats_without_the_squares(ctx):
+    """b200_select_kth_avg (what latency.percentiles calls): same ranks, count, sum, min, max as b200_select_kth_stats
+    on the sampled route (n >= 2^24) and on the short route; its sums of squares are 0 by contract."""
+    import ctypes as C
+    L, h = ctx._L, ctx._h
+    for n in ((1 << 24) + 77, 300_001):
+        ns = oracle.latency_ns(n, seed=n)
+        d = ctx.alloc_device(n * 8)
+        ctx.h2d(d, ns)
+        karr = np.array([n // 5, n // 2, 9 * n // 10, 99 * n // 100], dtype=np.uint64)
+        res = []
+        for fn in (L.b200_select_kth_stats, L.b200_select_kth_avg):
+            out, st = np.zeros(4, dtype=np.int64), pkg._lib.LatStats()
+            pkg._lib.check(fn(h, 0, d, n, 1000, karr.ctypes.data, 4, out.ctypes.data, C.byref(st)))
+            res.append((list(out), st.count, st.sum, st.sum_hi, st.min, st.max, st.sumsq_lo, st.sumsq_hi))
+        assert res[0][:6] == res[1][:6]
+        assert res[1][6:] == (0, 0) and res[0][6] != 0
+        us = ns // 1000
+        srt = np.partition(ns, [int(k) for k in karr])
+        assert res[1][0] == [int(srt[int(k)]) // 1000 for k in karr]
+        assert (res[1][1], res[1][2], res[1][4], res[1][5]) == (n, int(us.sum()), int(us.min()), int(us.max()))
+        ctx.free_device(d)

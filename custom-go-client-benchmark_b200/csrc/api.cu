@@ -1597,7 +1597,13 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     auto ms_since = [&](std::chrono::steady_clock::time_point t) {
         return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count();
     };
-    const size_t stride = std::max<size_t>(16, (n + ((size_t)1 << 22) - 1) >> 22);
+    // the sample: ~2^22 inputs (B200_SELECT_SAMPLE_LOG2 for tuning runs)
+    static const int sample_log2 = [] {
+        const char* e = getenv("B200_SELECT_SAMPLE_LOG2");
+        const int v = e && *e ? atoi(e) : 22;
+        return v < 16 ? 16 : v > 26 ? 26 : v;
+    }();
+    const size_t stride = std::max<size_t>(16, (n + ((size_t)1 << sample_log2) - 1) >> sample_log2);
     const size_t s = n / stride;
     if (s < 4096) return sampled_trace("skip: input too short", 1);
     // sample rank of an input rank r is about r / stride, with a standard deviation below sqrt(s) / 2

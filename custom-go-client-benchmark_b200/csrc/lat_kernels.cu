@@ -83,7 +83,7 @@ __device__ __forceinline__ unsigned long long udiv_magic(unsigned long long a, c
 // Kept samples of one warp on their way to the output buffer: staged in shared memory and flushed with ONE global
 // atomic per ~64 of them (a global atomic per handful, with the warp waiting for its return every time, is what
 // made the collecting pass slow).
-constexpr int kKeepCap = 96;
+constexpr int kKeepCap = 64;
 struct KeepStage {
     unsigned* n;     // shared: samples staged by this warp
     long long* q;    // shared: [kKeepCap]
@@ -151,19 +151,26 @@ __device__ __forceinline__ void load_slow_params(SlowParams* sp, const HistParam
 // lat_scratch_init checks the window start once per device (smem_base_probe).
 constexpr unsigned kSlowAbs = 0x400;                                    // SlowParams
 constexpr unsigned kParkNAbs = kSlowAbs + 640;                          // unsigned[kHistWarps]: parked samples per warp
-constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // long long[kHistWarps][park_slots(collect)]
-// a collecting pass parks ~1 % of the samples, the others ~0.5 %: queue slots per warp
-#ifndef B200_PARK_COLLECT
-#define B200_PARK_COLLECT 128
-#endif
+constexpr unsigned kParkQAbs = kParkNAbs + 64;                          // the parking area, see below
+// a plain pass parks ~0.5 % of the samples (multi-second stalls): queue slots per warp
 #ifndef B200_PARK_PLAIN
 #define B200_PARK_PLAIN 32
 #endif
-__host__ __device__ constexpr int park_cap(bool collect) { return collect ? B200_PARK_COLLECT : B200_PARK_PLAIN; }
-// a collecting kernel parks without a branch (park_if_even): one more slot takes what does not fit
-__host__ __device__ constexpr int park_slots(bool collect) { return park_cap(collect) + (collect ? 1 : 0); }
+__host__ __device__ constexpr int park_cap(bool) { return B200_PARK_PLAIN; }
+// A collecting pass parks ~1 % (everything it keeps).  Its lanes park into slots of their OWN — kLaneLevels entries
+// per lane, [level][lane], and one more level behind them that takes what does not fit — which costs four predicated
+// instructions per sample and no atomic; the warp moves the slots into its dense queue only when some lane holds
+// three, and works the dense queue off 32 entries at a time with every lane busy (hist_kernel).
+constexpr int kLaneLevels = 4;
+constexpr unsigned kLaneQBytes = (kLaneLevels + 1) * 32 * 8;            // per warp
+constexpr int kDenseCap = 64;                                           // per warp: < 32 left over + one level of 32
+constexpr unsigned kDenseAbs = kParkQAbs + kHistWarps * kLaneQBytes;    // long long[kHistWarps][kDenseCap]
+constexpr unsigned kLaneN0Abs = kDenseAbs + kHistWarps * kDenseCap * 8; // unsigned[kHistThreads]: a lane's slots at tile start
+__host__ __device__ constexpr unsigned park_bytes(bool collect) {
+    return collect ? kLaneN0Abs + kHistThreads * 4 - kParkQAbs : kHistWarps * park_cap(false) * 8;
+}
 // unsigned char[lut_bytes], lut_bytes <= kLutSize
-__host__ __device__ constexpr unsigned lut_abs(bool collect) { return kParkQAbs + kHistWarps * park_slots(collect) * 8; }
+__host__ __device__ constexpr unsigned lut_abs(bool collect) { return kParkQAbs + park_bytes(collect); }
 // then, at lut_abs + lut_bytes, unsigned[kHistWarps][rows][32] counters, then the tile ring, then (collecting) the
 // warps' staging for kept samples
 static_assert(sizeof(SlowParams) <= 640, "SlowParams slot");
@@ -354,23 +361,22 @@ __device__ __forceinline__ void split64(long long v, unsigned& lo, unsigned& hi)
     asm("mov.b64 {%0, %1}, %2;" : "=r"(lo), "=r"(hi) : "l"(v));
 }
 
-// Collecting kernels park without a branch: about one sample in a hundred is parked (kept, or in a cell with a
-// threshold), so three groups of four in four meet one somewhere in the warp, and a divergent block there — ~50
-// warp instructions with its convergence barriers — was a quarter of the pass.  Predicated instead: when the row is
-// even (0: the table has no bin for the cell; 2, 4, ...: a kept bin, counted on the fast path but still to be collected)
-// the sample goes to the warp's queue at the byte offset an atomic add of 8 returns; offsets past the queue's cap
-// land in the spare slot behind it, and the caller, who looks at the count once per tile, redoes that tile.
-__device__ __forceinline__ void park_if_even(unsigned row, long long v, unsigned count_abs, unsigned queue_abs,
-                                             unsigned cap_bytes) {
+// Collecting kernels park without a branch and without an atomic: about one sample in a hundred is parked (kept, or
+// in a cell with a threshold), so three groups of four in four meet one somewhere in the warp; a divergent block
+// there was a quarter of the pass, a predicated shared-memory atomic (which ptxas wraps in a branch) still seven
+// instructions per sample.  Here: when the row is even (0: the table has no bin for the cell; 2, 4, ...: a kept bin,
+// counted on the fast path but still to be collected) the sample is stored in the lane's next slot.  next: address
+// of the lane's next slot (levels are 256 bytes apart); at: where the next parked sample goes = min(next, lim), lim
+// the level behind the last, so a fifth sample lands there and next > lim says that something was lost.
+__device__ __forceinline__ void park_lane_if_even(unsigned row, long long v, unsigned& next, unsigned& at, unsigned lim) {
     asm volatile(
-        "{\n\t.reg .pred p;\n\t.reg .u32 at;\n\t"
-        "and.b32 at, %0, 1;\n\t"
-        "setp.eq.u32 p, at, 0;\n\t"
-        "@p atom.shared.add.u32 at, [%1], 8;\n\t"
-        "@p min.u32 at, at, %4;\n\t"
-        "@p add.u32 at, at, %2;\n\t"
-        "@p st.shared.b64 [at], %3;\n\t}"
-        ::"r"(row), "r"(count_abs), "r"(queue_abs), "l"(v), "r"(cap_bytes) : "memory");
+        "{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
+        "and.b32 t, %2, 1;\n\t"
+        "setp.eq.u32 p, t, 0;\n\t"
+        "@p st.shared.b64 [%1], %3;\n\t"
+        "@p add.u32 %0, %0, 256;\n\t"
+        "@p min.u32 %1, %0, %4;\n\t}"
+        : "+r"(next), "+r"(at) : "r"(row), "l"(v), "r"(lim) : "memory");
 }
 
 // the lane's private counter at absolute shared address `addr` += 1
@@ -425,7 +431,7 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     unsigned* const tbl = reinterpret_cast<unsigned*>(sm0 + kCntAbs);  // [warp][row][lane] private counters
     SlowParams* const sp = reinterpret_cast<SlowParams*>(sm0 + kSlowAbs);
     load_slow_params(sp, Pg);
-    if (threadIdx.x < 2 * kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
+    if (threadIdx.x < kHistWarps) reinterpret_cast<unsigned*>(sm0 + kParkNAbs)[threadIdx.x] = 0;
     for (int i = threadIdx.x; i < (int)lut_bytes / 4; i += kHistThreads)
         reinterpret_cast<unsigned*>(sm0 + kLutAbs)[i] = reinterpret_cast<const unsigned*>(Pg->lut)[i];
     const int nbins = Pg->nthr + 1, rows = nbins + 1;  // row 0: scratch
@@ -453,11 +459,14 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
                    reinterpret_cast<long long*>(sm0 + keep_abs + 64) + (size_t)warp * kKeepCap};
     // the warp's queue of parked samples: addressed from constants where it is used (no registers held for it)
     auto park_n = [&]() -> unsigned* { return reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + warp; };
-    constexpr unsigned kParkSlots = park_slots(COLLECT);
-    auto park_q = [&]() -> long long* { return reinterpret_cast<long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkSlots; };
-    // collecting: the queue is counted in bytes, and the count at the start of the current tile is kept beside it
-    auto park_start = [&]() -> unsigned* { return reinterpret_cast<unsigned*>(sm0 + kParkNAbs) + kHistWarps + warp; };
-    const unsigned park_n_abs = kParkNAbs + 4u * warp, park_q_abs = kParkQAbs + 8u * kParkSlots * warp;
+    auto park_q = [&]() -> long long* { return reinterpret_cast<long long*>(sm0 + kParkQAbs) + (size_t)warp * kParkCap; };
+    // collecting: the lane's own slots (level L at lane_base + 256 L), where its next parked sample goes, the warp's
+    // dense queue (counted in park_n) and the word that remembers the lane's slots at the start of the tile
+    const unsigned lane_base = kParkQAbs + kLaneQBytes * warp + 8u * lane, lane_lim = lane_base + 256u * kLaneLevels;
+    unsigned lane_next = lane_base, lane_at = lane_base;
+    long long* const dense = reinterpret_cast<long long*>(sm0 + kDenseAbs) + (size_t)warp * kDenseCap;
+    unsigned* const lane_n0 = reinterpret_cast<unsigned*>(sm0 + kLaneN0Abs) + threadIdx.x;
+    if (COLLECT) *lane_n0 = lane_base;
     if (collecting && lane == 0) *keep.n = 0;
     __syncwarp();
     auto flush_keep = [&]() {  // whole warp, converged
@@ -544,12 +553,12 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         for (int k = 0; k < K; k++) row[k] = row_of(idx[k]);
         if constexpr (COLLECT) {
 #pragma unroll
-            for (int k = 0; k < K; k++) park_if_even(row[k], v[k], park_n_abs, park_q_abs, kParkCap * 8u);
+            for (int k = 0; k < K; k++) park_lane_if_even(row[k], v[k], lane_next, lane_at, lane_lim);
             if ((any_hi >> out_shift) != 0) {  // beyond the reach: parked whatever its table entry said; surrogate
 #pragma unroll
                 for (int k = 0; k < K; k++)
                     if ((hi[k] >> out_shift) != 0) {
-                        if (row[k] & 1) park_if_even(0u, v[k], park_n_abs, park_q_abs, kParkCap * 8u);
+                        if (row[k] & 1) park_lane_if_even(0u, v[k], lane_next, lane_at, lane_lim);
                         const bool neg = (int)hi[k] < 0;
                         u[k] = neg ? 0u : u_top;
                         if (BYQ) q[k] = quotient(u[k]);
@@ -608,23 +617,73 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
     auto before_step = [&] {
         if (collecting && *keep.n > (unsigned)(kKeepCap - 32)) flush_keep();
     };
-    // a queued sample of a collecting kernel: outside the reach or without a bin from the table -> the generic
-    // routine; in a kept bin the table knows (already counted) -> collected, nothing else
-    auto parked_one = [&](long long v) {
-        if (COLLECT && ((unsigned long long)v >> reach_bits) == 0) {
+    // ---- collecting kernels: working the parked samples off ---------------------------------------------------
+    // work_off(count): the first `count` (<= 32) entries of the dense queue, one per lane, all lanes in step.  An
+    // entry in reach gets its exact bin from a branch-free binary search over the thresholds (the same trip count in
+    // every lane); if the table had no bin for its cell the fast path counted it in the scratch row, so its counter
+    // is bumped now; samples of kept (odd) bins are staged with one ballot.  Entries beyond the reach — rare — take
+    // the generic routine, which counts, sums and collects on its own.
+    auto work_off = [&](unsigned count) {
+        before_step();
+        const bool in = (unsigned)lane < count;
+        const long long v = in ? dense[lane] : 0;
+        const bool outside = in && ((unsigned long long)v >> reach_bits) != 0;
+        int c = 0;
+        for (int step = 64; step; step >>= 1) {  // kMaxThresholds <= 127
+            const int j = c + step;
+            if (j <= sp->nthr && sp->thr[j - 1] <= v) c = j;
+        }
+        bool kept = false;
+        if (in && !outside) {
             unsigned lo, hi, q = 0;
             split64(v, lo, hi);
-            if (row_of(index_of(shifted(lo, hi), q)) != 0) {
-                keep_sample(v, &col, keep);
-                return;
+            if (row_of(index_of(shifted(lo, hi), q)) == 0) mine[(c + 1) * 32]++;
+            kept = c & 1;
+        }
+        if (outside) slow(v);
+        __syncwarp();
+        const unsigned km = __ballot_sync(0xFFFFFFFFu, kept);
+        if (km) {
+            const unsigned pos = *keep.n;  // (room for 32: before_step)
+            if (kept) keep.q[pos + __popc(km & ((1u << lane) - 1))] = v;
+            __syncwarp();
+            if (lane == 0) *keep.n = pos + __popc(km);
+            __syncwarp();
+        }
+    };
+    // the lanes' slots -> the dense queue, level by level; every full group of 32 is worked off at once
+    auto compact = [&] {  // whole warp, converged
+        unsigned cnt = *park_n();
+#pragma unroll 1
+        for (unsigned level = lane_base; level != lane_lim; level += 256u) {
+            const bool has = lane_next > level;
+            const unsigned m = __ballot_sync(0xFFFFFFFFu, has);
+            if (!m) break;
+            if (has) dense[cnt + __popc(m & ((1u << lane) - 1))] = *reinterpret_cast<const long long*>(sm0 + level);
+            cnt += __popc(m);
+            __syncwarp();
+            if (cnt >= 32) {
+                work_off(32);
+                cnt -= 32;
+                const long long rest = (unsigned)lane < cnt ? dense[32 + lane] : 0;
+                __syncwarp();
+                if ((unsigned)lane < cnt) dense[lane] = rest;
+                __syncwarp();
             }
         }
-        slow(v);
+        lane_next = lane_at = lane_base;
+        if (lane == 0) *park_n() = cnt;
+        __syncwarp();
     };
-    auto drain = [&] {  // whole warp, converged
-        drain_parked(park_n(), park_q(), kParkCap, lane, parked_one, before_step, COLLECT ? 3 : 0);
-        if (COLLECT) {
-            if (lane == 0) *park_start() = 0;
+    auto drain = [&] {  // end of the kernel; whole warp, converged
+        if constexpr (!COLLECT) {
+            drain_parked(park_n(), park_q(), kParkCap, lane, slow, before_step);
+        } else {
+            compact();
+            const unsigned cnt = *park_n();
+            if (cnt) work_off(cnt);
+            __syncwarp();
+            if (lane == 0) *park_n() = 0;
             __syncwarp();
         }
     };
@@ -632,35 +691,31 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
         four(a, b);
         four(c, d);
         nproc += 8;
-        if constexpr (COLLECT) {  // the queue, once per tile (every lane reads the same count)
-            __syncwarp();
-            const unsigned bytes = *park_n();
-            if (bytes > kParkCap * 8u) {
-                // more were parked in this tile than the queue had room for: forget this tile's entries, work the
-                // earlier ones off, and take this tile's parked samples one by one from the registers
-                const unsigned start = *park_start();
-                __syncwarp();
-                if (lane == 0) *park_n() = start;
-                drain();
-                const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+        if constexpr (COLLECT) {
+            // once per tile: does some lane hold three?  (A lane with two can take two more; a lane that parks more
+            // in one tile than it had room for — a few times in 10^5 lane-tiles — forgets this tile's entries and
+            // takes its parked samples of the tile one by one from the registers.)
+            if (__any_sync(0xFFFFFFFFu, lane_next >= lane_base + 256u * (kLaneLevels - 1))) {
+                if (lane_next > lane_lim) {
+                    lane_next = *lane_n0;
+                    const long long v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
 #pragma unroll
-                for (int k = 0; k < 8; k++) {
-                    bool outside = ((unsigned long long)v[k] >> reach_bits) != 0;
-                    unsigned row = 1;
-                    if (!outside) {
-                        unsigned lo, hi, q = 0;
-                        split64(v[k], lo, hi);
-                        row = row_of(index_of(shifted(lo, hi), q));
+                    for (int k = 0; k < 8; k++) {
+                        const bool outside = ((unsigned long long)v[k] >> reach_bits) != 0;
+                        unsigned row = 1;
+                        if (!outside) {
+                            unsigned lo, hi, q = 0;
+                            split64(v[k], lo, hi);
+                            row = row_of(index_of(shifted(lo, hi), q));
+                        }
+                        if (outside || row == 0) slow(v[k]);
+                        else if (!(row & 1)) keep_sample(v[k], &col, keep);
                     }
-                    if (outside || row == 0) slow(v[k]);
-                    else if (!(row & 1)) keep_sample(v[k], &col, keep);
                 }
                 __syncwarp();
-            } else if (bytes >= kParkCap * 4u) {
-                drain();
-            } else if (lane == 0) {
-                *park_start() = bytes;
+                compact();
             }
+            *lane_n0 = lane_next;
         }
     };
     for_each_sample(x, n, ring_abs, nstages, eight, one, [&] {

@@ -1400,6 +1400,7 @@ int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         if (first && g == 0) CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
         const SelState& st = *d->lat.h_sel;
+        if (fused) *d->lat.sel_hist_clean = true;  // the kernel ran to its end: it leaves its histograms cleared
         if (first && g == 0) first->outside = d->lat.h_results->compact_n;
         if (st.bad || st.top != 0) {
             if (select_trace_on()) fprintf(stderr, "b200 select: resident select failed: bad=%d top=%d n=%zu\n", st.bad, st.top, n);

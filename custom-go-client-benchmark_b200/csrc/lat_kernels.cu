@@ -21,6 +21,7 @@
 #endif
 
 #include <algorithm>
+#include <new>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -1065,6 +1066,9 @@ sel_scan_kernel(SelState* st, unsigned long long* __restrict__ hist) {
 // the bucket's lowest key — or its highest for the ranks in ceil_mask — i.e. a bound on the order statistic good to
 // approx_max ranks, which is all the brackets of the sampled select need (one round less).
 constexpr int kFusedThreads = 1024, kScanBins = kRadixBins / kFusedThreads;
+// bounds (approx_max > 0) need not be finer than 2^kApproxBits key units (4 us for nanoseconds): identical samples
+// — a latency distribution has atoms — would otherwise keep a bucket above approx_max down to the last bit
+constexpr int kApproxBits = 12;
 __global__ void __launch_bounds__(kFusedThreads)
 sel_fused_kernel(const long long* __restrict__ x, size_t n, SelState* st, unsigned long long* __restrict__ hist,
                  LatMoments* mom, SelRanks ranks, int have_bounds, long long lo, long long hi,
@@ -1257,7 +1261,7 @@ sel_fused_kernel(const long long* __restrict__ x, size_t n, SelState* st, unsign
         top = shift;
         nhist = nk;
         round++;
-        if (approx_max && !more) break;
+        if (approx_max && (!more || top <= kApproxBits)) break;
     }
     if (blockIdx.x == 0 && t < nk) {
         unsigned long long key = round == 0 ? 0ull : __ldcg(&st->prefix[t]);
@@ -1421,6 +1425,10 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel, sizeof(SelState));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
+    if (e == cudaSuccess) {
+        s->sel_hist_clean = new (std::nothrow) bool(false);
+        if (!s->sel_hist_clean) e = cudaErrorMemoryAllocation;
+    }
     return e;
 }
 cudaError_t lat_reset_results(const LatScratch& s, cudaStream_t stream) {
@@ -1441,6 +1449,7 @@ void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_compact);
     cudaFree(s->d_sel);
     cudaFree(s->d_sel_hist);
+    delete s->sel_hist_clean;
     cudaFree(s->d_sample);
     cudaFree(s->d_collect);
     memset(s, 0, sizeof *s);
@@ -1561,9 +1570,14 @@ int select_fused_grid() {
 cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelRanks& ranks, int have_bounds,
                                 long long lo, long long hi, unsigned long long approx_max, unsigned ceil_mask,
                                 const LatScratch& s, cudaStream_t stream) {
-    // (the kernel leaves the histograms cleared; the memset makes that independent of how an earlier run ended)
-    cudaError_t e = cudaMemsetAsync(s.d_sel_hist, 0, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long), stream);
-    if (e != cudaSuccess) return e;
+    // the kernel leaves the histograms cleared: they are only cleared here after a run that did not end well
+    // (*s.sel_hist_clean is set by the caller once it has seen the run's result)
+    cudaError_t e = cudaSuccess;
+    if (!*s.sel_hist_clean) {
+        e = cudaMemsetAsync(s.d_sel_hist, 0, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long), stream);
+        if (e != cudaSuccess) return e;
+    }
+    *s.sel_hist_clean = false;
     if (!have_bounds) {
         e = reset_moments(s, stream);
         if (e != cudaSuccess) return e;

@@ -97,6 +97,7 @@ struct LatScratch {
     unsigned long long* d_compact_n;    // device counter
     SelState* d_sel;                    // device-resident select
     unsigned long long* d_sel_hist;     // [kSelMax][kRadixBins]
+    bool* sel_hist_clean;               // host: the last one-kernel select ended well, so d_sel_hist is all zero
     long long* d_sample;                // stratified sample of the input (sampled select, lazy)
     size_t sample_cap;
     long long* d_collect;               // samples inside the brackets (sampled select, lazy)

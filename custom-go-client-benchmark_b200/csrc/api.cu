@@ -1673,17 +1673,34 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
     const size_t cap = std::min<size_t>(std::max<size_t>(2 * expect, n / 64), n / 8);
     unsigned long long c[kMaxThresholds + 1], kept = 0;
     LatMoments mom{};
+    // The kept samples lie between the ends of the brackets: no min/max pass when those are finite — and then the
+    // select over them is queued right behind the pass, with its ranks worked out on the device from the pass's
+    // counts (bracket_ranks_kernel): one host round trip for both.  The host repeats the arithmetic on the counts it
+    // reads back and only then believes the result.
+    const bool bounded = br[0].lo != kMin && br[nb - 1].hi != kMax;
+    const bool chained = bounded && select_fused_grid() != 0 && cap <= resident_select_max();
+    SelState sel{};
     {
         std::unique_lock<std::mutex> lk(d->mu);
         CU(cudaSetDevice(dev));
         if (!grow(&d->lat.d_collect, &d->lat.collect_cap, cap)) return sampled_trace("skip: no memory for the brackets", 1);
         HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
         CU(launch_hist((const long long*)d_samples, n, d->lat, stats ? (no_squares ? 2 : 1) : 0, d->stream, P, &col));
+        if (chained) {
+            CU(launch_bracket_ranks(d->lat, nb, (const unsigned long long*)k, nk, cap, d->stream));
+            CU(launch_select_fused((const long long*)d->lat.d_collect, cap, SelRanks{}, 1, br[0].lo, br[nb - 1].hi, 0, 0,
+                                   d->lat, d->stream, true));
+            CU(cudaMemcpyAsync(d->lat.h_sel, d->lat.d_sel, sizeof(SelState), cudaMemcpyDeviceToHost, d->stream));
+        }
         CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
         memcpy(c, d->lat.h_results->counts, sizeof c);
         mom = d->lat.h_results->mom;
         kept = d->lat.h_results->compact_n;
+        if (chained) {
+            sel = *d->lat.h_sel;
+            *d->lat.sel_hist_clean = true;  // the select ran to its end (or did not start): its histograms are clear
+        }
     }
     const double ms_pass = ms_since(t0) - ms_sample;
     uint64_t inside = 0, total = 0;
@@ -1706,13 +1723,16 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         }
         rank_kept[i] = kept_before + (k[i] - below);
     }
-    // the kept samples lie between the ends of the brackets: no min/max pass when those are finite
-    const bool bounded = br[0].lo != kMin && br[nb - 1].hi != kMax;
-    int rc = inside <= resident_select_max()
-                 ? select_resident(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, bounded,
-                                   bounded ? br[0].lo : 0, bounded ? br[nb - 1].hi : 0, rank_kept, nk, out)
-                 : b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, rank_kept, nk, out);
-    if (rc) return rc < 0 ? rc : 1;
+    if (chained) {
+        if (sel.bad || sel.top != 0) return sampled_trace("miss: the select over the kept samples", 1);
+        for (int i = 0; i < nk; i++) out[i] = sel.result[i] / divisor;  // truncating division is monotone
+    } else {
+        int rc = inside <= resident_select_max()
+                     ? select_resident(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, bounded,
+                                       bounded ? br[0].lo : 0, bounded ? br[nb - 1].hi : 0, rank_kept, nk, out)
+                     : b200_select_kth(ctx, dev, (const int64_t*)d->lat.d_collect, (size_t)inside, divisor, rank_kept, nk, out);
+        if (rc) return rc < 0 ? rc : 1;
+    }
     if (stats) fill_stats(mom, divisor, stats);  // moments of the whole input, from the bracket pass
     char msg[160];
     snprintf(msg, sizeof msg, "ok (sample of %zu + brackets %.3f ms, pass %.3f ms, %llu kept + select %.3f ms)", s, ms_sample,

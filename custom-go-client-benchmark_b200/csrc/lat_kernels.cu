@@ -1070,9 +1070,24 @@ constexpr int kFusedThreads = 1024, kScanBins = kRadixBins / kFusedThreads;
 // — a latency distribution has atoms — would otherwise keep a bucket above approx_max down to the last bit
 constexpr int kApproxBits = 12;
 __global__ void __launch_bounds__(kFusedThreads)
-sel_fused_kernel(const long long* __restrict__ x, size_t n, SelState* st, unsigned long long* __restrict__ hist,
-                 LatMoments* mom, SelRanks ranks, int have_bounds, long long lo, long long hi,
-                 unsigned long long approx_max, unsigned ceil_mask) {
+sel_fused_kernel(const long long* __restrict__ x, size_t n_arg, SelState* st, unsigned long long* __restrict__ hist,
+                 LatMoments* mom, SelRanks ranks_arg, int have_bounds, long long lo, long long hi,
+                 unsigned long long approx_max, unsigned ceil_mask, const SelDeferred* __restrict__ in) {
+    // ranks and length either from the launch or from what the kernel before this one left (the same for every CTA)
+    size_t n = n_arg;
+    SelRanks ranks = ranks_arg;
+    if (in) {
+        if (in->miss) {
+            if (blockIdx.x == 0 && threadIdx.x == 0) {
+                st->bad = 1;
+                st->top = 0;
+                st->nstamp = 0;
+            }
+            return;
+        }
+        n = (size_t)in->n;
+        ranks = in->ranks;
+    }
     static_assert(kRadixBins == kScanBins * kFusedThreads, "a thread scans kScanBins bins");
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char sm[];
@@ -1424,6 +1439,7 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel, sizeof(SelState));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_in, sizeof(SelDeferred));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) {
         s->sel_hist_clean = new (std::nothrow) bool(false);
@@ -1448,6 +1464,7 @@ void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_prefix);
     cudaFree(s->d_compact);
     cudaFree(s->d_sel);
+    cudaFree(s->d_sel_in);
     cudaFree(s->d_sel_hist);
     delete s->sel_hist_clean;
     cudaFree(s->d_sample);
@@ -1545,6 +1562,46 @@ cudaError_t launch_select_resident(const long long* d_samples, size_t n, const S
     return cudaGetLastError();
 }
 
+namespace {
+
+struct WantedRanks {
+    unsigned long long k[kSelMax];
+};
+__global__ void bracket_ranks_kernel(const unsigned long long* __restrict__ counts, int nb, WantedRanks want, int nk,
+                                     unsigned long long cap, SelDeferred* __restrict__ out) {
+    if (threadIdx.x || blockIdx.x) return;
+    unsigned long long inside = 0, miss = 0;
+    for (int j = 0; j < nb; j++) inside += counts[2 * j + 1];
+    for (int i = 0; i < nk; i++) {
+        unsigned long long below = 0, kept_before = 0, rank = 0;
+        int j = 0;
+        for (;; j++) {
+            if (j == nb) { miss = 1; break; }            // beyond the last bracket
+            below += counts[2 * j];
+            if (want.k[i] < below) { miss = 1; break; }  // between brackets
+            if (want.k[i] < below + counts[2 * j + 1]) { rank = kept_before + (want.k[i] - below); break; }
+            below += counts[2 * j + 1];
+            kept_before += counts[2 * j + 1];
+        }
+        out->ranks.rank[i] = rank;
+    }
+    for (int i = nk; i < kSelMax; i++) out->ranks.rank[i] = 0;
+    out->ranks.nk = nk;
+    if (inside == 0 || inside > cap) miss = 1;
+    out->n = inside;
+    out->miss = miss;
+}
+
+}  // namespace
+
+cudaError_t launch_bracket_ranks(const LatScratch& s, int nbrackets, const unsigned long long* k, int nk,
+                                 unsigned long long cap, cudaStream_t stream) {
+    WantedRanks w{};
+    for (int i = 0; i < nk && i < kSelMax; i++) w.k[i] = k[i];
+    bracket_ranks_kernel<<<1, 32, 0, stream>>>(s.d_counts, nbrackets, w, nk, cap, s.d_sel_in);
+    return cudaGetLastError();
+}
+
 // 1 when this device can run the one-kernel select (cooperative launch, a CTA per SM with the histograms of
 // kSelMax ranks in shared memory), 0 when not or when B200_SELECT_FUSED=0 asks for the separate launches
 int select_fused_grid() {
@@ -1569,7 +1626,7 @@ int select_fused_grid() {
 
 cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelRanks& ranks, int have_bounds,
                                 long long lo, long long hi, unsigned long long approx_max, unsigned ceil_mask,
-                                const LatScratch& s, cudaStream_t stream) {
+                                const LatScratch& s, cudaStream_t stream, bool deferred) {
     // the kernel leaves the histograms cleared: they are only cleared here after a run that did not end well
     // (*s.sel_hist_clean is set by the caller once it has seen the run's result)
     cudaError_t e = cudaSuccess;
@@ -1590,8 +1647,9 @@ cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelR
     LatMoments* mom = s.d_mom;
     SelRanks r = ranks;
     int hb = have_bounds;
+    const SelDeferred* in = deferred ? s.d_sel_in : nullptr;
     void* args[] = {(void*)&d_samples, (void*)&n, (void*)&st, (void*)&hist, (void*)&mom, (void*)&r, (void*)&hb,
-                    (void*)&lo, (void*)&hi, (void*)&approx_max, (void*)&ceil_mask};
+                    (void*)&lo, (void*)&hi, (void*)&approx_max, (void*)&ceil_mask, (void*)&in};
     return cudaLaunchCooperativeKernel((const void*)sel_fused_kernel, dim3(grid), dim3(kFusedThreads), args, smem, stream);
 }
 

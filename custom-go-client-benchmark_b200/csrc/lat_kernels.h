@@ -81,8 +81,17 @@ struct LatResults {
     unsigned long long compact_n;       // samples kept / compacted / outside the fast path (one counter, reused)
 };
 
+// Input of a one-kernel select that an earlier kernel on the stream prepares (bracket_ranks_kernel after a bracket
+// pass): the host launches both without knowing the counts and checks them afterwards.
+struct SelDeferred {
+    SelRanks ranks;                     // ranks among the kept samples
+    unsigned long long n;               // kept samples (<= the buffer's capacity)
+    unsigned long long miss;            // a rank fell outside the brackets, or they hold too much / nothing: no select
+};
+
 struct LatScratch {
     HistParams* d_params;
+    SelDeferred* d_sel_in;
     LatResults* d_results;              // the block; the three pointers below point into it
     LatResults* d_results_init;         // the template: zero counts, min = INT64_MAX, max = INT64_MIN
     LatResults* h_results;              // pinned: lat_read_results() copies the block here
@@ -134,9 +143,14 @@ cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* 
 int select_fused_grid();
 // have_bounds: 0 the kernel finds min and max itself, 1 [lo, hi] are given, 2 they are in s.d_mom already (left by
 // launch_sample with `bounds` on the same stream)
+// in: ranks and n come from s.d_sel_in instead (n is then only an upper bound, for the grid)
 cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelRanks& ranks, int have_bounds,
                                 long long lo, long long hi, unsigned long long approx_max, unsigned ceil_mask,
-                                const LatScratch& s, cudaStream_t stream);
+                                const LatScratch& s, cudaStream_t stream, bool deferred = false);
+// After a bracket pass (thresholds lo0, hi0+1, lo1, hi1+1, ...: odd bins are the brackets), on the device: the ranks
+// of the wanted order statistics k[0..nk) among the kept samples -> s.d_sel_in, for the select that follows.
+cudaError_t launch_bracket_ranks(const LatScratch& s, int nbrackets, const unsigned long long* k, int nk,
+                                 unsigned long long cap, cudaStream_t stream);
 cudaError_t launch_select_resident(const long long* d_samples, size_t n, const SelRanks& ranks, bool have_bounds,
                                    long long lo, long long hi, const LatScratch& s, cudaStream_t stream);
 // One MSD radix pass over key' = (ns ^ 2^63) - key_base: for each k < nk count the digit

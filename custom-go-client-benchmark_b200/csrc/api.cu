@@ -1380,7 +1380,7 @@ int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
     if (first) {
         if (!grow(&d->lat.d_sample, &d->lat.sample_cap, n)) return 1;  // (the caller takes another route)
         CU(launch_sample((const long long*)first->src, first->stride, d->lat.d_sample, n, d->stream, d->lat.d_compact_n,
-                         fused ? d->lat.d_mom : nullptr, &d->lat.d_results_init->mom));
+                         fused ? d->lat.d_mom : nullptr, &d->lat));
         d_samples = (const int64_t*)d->lat.d_sample;
         bounds = fused ? 2 : 0;
     }
@@ -1396,10 +1396,9 @@ int select_resident(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, 
         } else {
             CU(launch_select_resident((const long long*)d_samples, n, r, bounds == 1, lo, hi, d->lat, d->stream));
         }
-        CU(cudaMemcpyAsync(d->lat.h_sel, d->lat.d_sel, sizeof(SelState), cudaMemcpyDeviceToHost, d->stream));
-        if (first && g == 0) CU(lat_read_results(d->lat, d->stream));
+        CU(lat_read_results(d->lat, d->stream));  // the select's state (and, after a sampling kernel, its counter)
         CU(cudaStreamSynchronize(d->stream));
-        const SelState& st = *d->lat.h_sel;
+        const SelState& st = d->lat.h_results->sel;
         if (fused) *d->lat.sel_hist_clean = true;  // the kernel ran to its end: it leaves its histograms cleared
         if (first && g == 0) first->outside = d->lat.h_results->compact_n;
         if (st.bad || st.top != 0) {
@@ -1690,7 +1689,6 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
             CU(launch_bracket_ranks(d->lat, nb, (const unsigned long long*)k, nk, cap, d->stream));
             CU(launch_select_fused((const long long*)d->lat.d_collect, cap, SelRanks{}, 1, br[0].lo, br[nb - 1].hi, 0, 0,
                                    d->lat, d->stream, true));
-            CU(cudaMemcpyAsync(d->lat.h_sel, d->lat.d_sel, sizeof(SelState), cudaMemcpyDeviceToHost, d->stream));
         }
         CU(lat_read_results(d->lat, d->stream));
         CU(cudaStreamSynchronize(d->stream));
@@ -1698,7 +1696,7 @@ int select_sampled(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, i
         mom = d->lat.h_results->mom;
         kept = d->lat.h_results->compact_n;
         if (chained) {
-            sel = *d->lat.h_sel;
+            sel = d->lat.h_results->sel;
             *d->lat.sel_hist_clean = true;  // the select ran to its end (or did not start): its histograms are clear
         }
     }

@@ -1384,13 +1384,12 @@ sample_kernel(const long long* __restrict__ x, size_t stride, long long* __restr
 }  // namespace
 
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
-                          unsigned long long* d_outside, LatMoments* d_bounds, const LatMoments* d_bounds_init) {
-    if (d_outside) {
-        cudaError_t e = cudaMemsetAsync(d_outside, 0, sizeof *d_outside, stream);
+                          unsigned long long* d_outside, LatMoments* d_bounds, const LatScratch* results) {
+    if (results) {  // outside counter and bounds both live in the results block: one copy resets them
+        cudaError_t e = lat_reset_results(*results, stream);
         if (e != cudaSuccess) return e;
-    }
-    if (d_bounds && d_bounds_init) {
-        cudaError_t e = cudaMemcpyAsync(d_bounds, d_bounds_init, sizeof(LatMoments), cudaMemcpyDeviceToDevice, stream);
+    } else if (d_outside) {
+        cudaError_t e = cudaMemsetAsync(d_outside, 0, sizeof *d_outside, stream);
         if (e != cudaSuccess) return e;
     }
     if (!s) return cudaSuccess;
@@ -1423,12 +1422,12 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     s->d_counts = s->d_results->counts;  // (addresses only: nothing is read through the device pointer here)
     s->d_mom = &s->d_results->mom;
     s->d_compact_n = &s->d_results->compact_n;
+    s->d_sel = &s->d_results->sel;
     e = smem_base_probe(s->d_compact_n);
     if (e != cudaSuccess) return e;
     e = cudaMalloc(&s->d_results_init, sizeof(LatResults));
     if (e == cudaSuccess) e = cudaHostAlloc(&s->h_results, sizeof(LatResults), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaHostAlloc(&s->h_params, sizeof(HistParams), cudaHostAllocDefault);
-    if (e == cudaSuccess) e = cudaHostAlloc(&s->h_sel, sizeof(SelState), cudaHostAllocDefault);
     if (e == cudaSuccess) {
         memset(s->h_results, 0, sizeof(LatResults));
         s->h_results->mom.min_ns = 0x7FFFFFFFFFFFFFFFll;
@@ -1438,7 +1437,6 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     if (e == cudaSuccess) e = cudaMalloc(&s->d_params, sizeof(HistParams));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_sel, sizeof(SelState));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_in, sizeof(SelDeferred));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) {
@@ -1459,11 +1457,9 @@ void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_results_init);
     cudaFreeHost(s->h_results);
     cudaFreeHost(s->h_params);
-    cudaFreeHost(s->h_sel);
     cudaFree(s->d_radix);
     cudaFree(s->d_prefix);
     cudaFree(s->d_compact);
-    cudaFree(s->d_sel);
     cudaFree(s->d_sel_in);
     cudaFree(s->d_sel_hist);
     delete s->sel_hist_clean;
@@ -1744,80 +1740,108 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
     const int m = P->nthr;
     // 32-bit dividends (Granlund-Montgomery, N = 32): l = ceil(log2 d), m' = floor(2^32 (2^l - d) / d) + 1,
     // q = (t + ((n - t) >> 1)) >> (l - 1) with t = umulhi(m', n)
-    if (divisor == 1) {
-        P->mode32 = 0;
-    } else if ((unsigned long long)divisor > 0xFFFFFFFFull) {
-        P->mode32 = 2;
-    } else {
-        unsigned long long d32 = (unsigned long long)divisor;
-        int l = 0;
-        while ((1ull << l) < d32) l++;
-        P->magic32 = (unsigned int)((((unsigned __int128)1 << 32) * ((1ull << l) - d32)) / d32 + 1);
-        P->shift32 = l - 1;
-        P->mode32 = 1;
-        // Cheaper when it exists: take the divisor's trailing zero bits out of divisor and dividend alike (d = 2^pre d',
-        // u = n >> pre, trunc(n / d) = trunc(u / d')); a 32-bit magic M = ceil(2^k / d') without fix-up is exact for all
-        // u < 2^B as soon as (M d' - 2^k) (2^B - 1) < 2^k.  The largest such B <= 32 is taken: the kernel's fast path
-        // then reaches n < 2^(B + pre) (2^37 ns = 137 s for milliseconds, 2^34 ns = 17 s for microseconds) instead of
-        // 2^32.  d' >= 16 also bounds the quotient below 2^28, which lets the kernel sum four quotients in 32 bits
-        // and four squares in 64.
-        int pre = 0;
-        while (!((d32 >> pre) & 1)) pre++;
-        const unsigned long long dp = d32 >> pre;
-        if (dp >= 16) {
-            for (int B = 32; B >= 32 - pre && P->mode32 != 3; B--) {
-                const unsigned __int128 nmax = ((unsigned __int128)1 << B) - 1;
-                for (int post = 0; post < 32; post++) {
-                    const unsigned __int128 two_k = (unsigned __int128)1 << (32 + post);
-                    const unsigned __int128 M = (two_k + dp - 1) / dp;
-                    if (M >> 32) break;
-                    if ((M * dp - two_k) * nmax < two_k) {
-                        P->magic32 = (unsigned int)M;
-                        P->shift32 = post;
-                        P->pre32 = pre;
-                        P->mode32 = 3;
-                        P->reach_bits = B + pre;
-                        break;
+    // (the search below is a few hundred 128-bit divisions: what it finds for a divisor is remembered)
+    struct Magic32 {
+        long long divisor = 0;
+        unsigned magic32 = 0;
+        int shift32 = 0, pre32 = 0, mode32 = 0, reach_bits = 32;
+    };
+    static thread_local Magic32 last;
+    if (last.divisor != divisor) {
+        Magic32 g;
+        g.divisor = divisor;
+        if (divisor == 1) {
+            g.mode32 = 0;
+        } else if ((unsigned long long)divisor > 0xFFFFFFFFull) {
+            g.mode32 = 2;
+        } else {
+            unsigned long long d32 = (unsigned long long)divisor;
+            int l = 0;
+            while ((1ull << l) < d32) l++;
+            g.magic32 = (unsigned int)((((unsigned __int128)1 << 32) * ((1ull << l) - d32)) / d32 + 1);
+            g.shift32 = l - 1;
+            g.mode32 = 1;
+            // Cheaper when it exists: take the divisor's trailing zero bits out of divisor and dividend alike (d = 2^pre
+            // d', u = n >> pre, trunc(n / d) = trunc(u / d')); a 32-bit magic M = ceil(2^k / d') without fix-up is exact
+            // for all u < 2^B as soon as (M d' - 2^k) (2^B - 1) < 2^k.  The largest such B <= 32 is taken: the kernel's
+            // fast path then reaches n < 2^(B + pre) (2^37 ns = 137 s for milliseconds, 2^34 ns = 17 s for
+            // microseconds) instead of 2^32.  d' >= 16 also bounds the quotient below 2^28, which lets the kernel sum
+            // four quotients in 32 bits and four squares in 64.
+            int pre = 0;
+            while (!((d32 >> pre) & 1)) pre++;
+            const unsigned long long dp = d32 >> pre;
+            if (dp >= 16) {
+                for (int B = 32; B >= 32 - pre && g.mode32 != 3; B--) {
+                    const unsigned __int128 nmax = ((unsigned __int128)1 << B) - 1;
+                    for (int post = 0; post < 32; post++) {
+                        const unsigned __int128 two_k = (unsigned __int128)1 << (32 + post);
+                        const unsigned __int128 M = (two_k + dp - 1) / dp;
+                        if (M >> 32) break;
+                        if ((M * dp - two_k) * nmax < two_k) {
+                            g.magic32 = (unsigned int)M;
+                            g.shift32 = post;
+                            g.pre32 = pre;
+                            g.mode32 = 3;
+                            g.reach_bits = B + pre;
+                            break;
+                        }
                     }
                 }
             }
         }
+        if (g.mode32 != 3) g.reach_bits = 32;
+        last = g;
     }
+    P->magic32 = last.magic32;
+    P->shift32 = last.shift32;
+    P->pre32 = last.pre32;
+    P->mode32 = last.mode32;
+    P->reach_bits = last.reach_bits;
     // The look-up table (see hist_kernel).  Cell c covers the samples [lo_c, hi_c]; its entry is 1 + the number of
     // thresholds <= lo_c — the counter row of every sample in the cell — unless a threshold lies inside (lo_c, hi_c]:
-    // then 0, the sample is parked.
-    if (P->mode32 != 3) P->reach_bits = 32;
+    // then 0, the sample is parked.  (A collecting kernel also parks the cells of kept bins, which are the even rows:
+    // it tells them by the row's parity, and having the row it counts them on its fast path.)
+    // Filled threshold by threshold — runs of equal entries between the cells that hold one — not cell by cell: this
+    // runs on the host before every launch.
     const unsigned long long reach = 1ull << P->reach_bits;  // the fast path takes 0 <= n < reach
-    auto fill = [&](auto cell_lo, auto cell_hi) {
-        int parked = 0, below = 0, inside = 0;  // thresholds <= lo of the current cell; inside it
-        for (int c = 0; c < kLutSize; c++) {
-            const unsigned long long lo = cell_lo(c), hi = std::min<unsigned long long>(cell_hi(c), reach - 1);
-            if (lo >= reach) {  // beyond the reach of the fast path: never looked up
-                P->lut[c] = 0;
-                continue;
-            }
-            while (below < m && P->thr[below] <= (long long)lo) below++;
-            inside = 0;
-            while (below + inside < m && P->thr[below + inside] <= (long long)hi) inside++;
-            // (a collecting kernel also parks the cells of kept bins, which are the even rows: it tells them by the
-            // row's parity, and having the row it counts them on its fast path)
-            const bool park = inside > 0;
-            P->lut[c] = park ? 0 : (unsigned char)(below + 1);
-            parked += park;
+    // cell_of(t) for 0 < t < reach: the cell t falls into and whether t is that cell's lowest sample
+    auto fill = [&](auto cell_of, auto cell_lo) {
+        int parked = 0, below = 0, pos = 0;  // cells [0, pos) are done
+        while (below < m && P->thr[below] <= 0) below++;
+        for (int j = below; j < m && (unsigned long long)P->thr[j] < reach; j++) {
+            bool exact;
+            const int ct = cell_of((unsigned long long)P->thr[j], &exact);
+            if (ct >= pos) {
+                memset(P->lut + pos, below + 1, (size_t)(ct - pos));
+                pos = ct;
+                if (!exact) {
+                    P->lut[ct] = 0;
+                    parked++;
+                    pos = ct + 1;
+                }
+            }  // (else: one more threshold in a cell that is parked already)
+            below++;
         }
+        if (pos < kLutSize) memset(P->lut + pos, below + 1, (size_t)(kLutSize - pos));
+        for (int c = kLutSize - 1; c >= 0 && cell_lo(c) >= reach; c--) P->lut[c] = 0;  // beyond the reach: never looked up
         return parked;
     };
     const unsigned long long d32 = (unsigned long long)divisor;
-    const unsigned long long kOpen = ~0ull;  // the last cell takes everything up to the reach
     P->by_q = 0;
     P->lut_bytes = kLutSize;
-    if (P->mode32 == 3) {
+    if (P->mode32 == 3 && !collect) {
         // index by quotient (clamped to the last cell): no cell is parked when every threshold in reach is a multiple
         // of the divisor and lies inside the table; thresholds beyond it (the OpenCensus bounds from 10 s up, in
-        // milliseconds) park the last cell only, i.e. the samples of 8.19 s and more — still the better table
-        const int parked = fill([&](int c) { return (unsigned long long)c * d32; },
-                                [&](int c) { return c == kLutSize - 1 ? kOpen : (unsigned long long)(c + 1) * d32 - 1; });
-        P->by_q = parked <= 1 && !collect;
+        // milliseconds) park the last cell only, i.e. the samples of 8.19 s and more — still the better table.  (A
+        // collecting pass is never indexed by quotient: its brackets are far narrower than a quotient.)
+        const int parked = fill(
+            [&](unsigned long long t, bool* exact) {
+                const unsigned long long c = t / d32;
+                *exact = c < (unsigned long long)kLutSize && t % d32 == 0;
+                return (int)std::min<unsigned long long>(c, kLutSize - 1);
+            },
+            [&](int c) { return (unsigned long long)c * d32; });
+        P->by_q = parked <= 1;
         if (P->by_q) P->lut_bytes = (int)std::min<unsigned long long>(kLutSize, ((reach - 1) / d32 + 1 + 127) & ~127ull);
     }
     if (!P->by_q) {
@@ -1830,8 +1854,13 @@ void finish_hist_params(HistParams* P, long long divisor, bool collect) {
         int sh = P->mode32 == 3 ? P->pre32 : 0;
         while (sh < P->reach_bits - 13 && ((unsigned long long)top >> sh) >= (unsigned long long)kLutSize - 1) sh++;
         P->lut_shift = sh;
-        fill([&](int c) { return (unsigned long long)c << sh; },
-             [&](int c) { return c == kLutSize - 1 ? kOpen : (((unsigned long long)c + 1) << sh) - 1; });
+        fill(
+            [&](unsigned long long t, bool* exact) {
+                const unsigned long long c = t >> sh;
+                *exact = c < (unsigned long long)kLutSize && (t & ((1ull << sh) - 1)) == 0;
+                return (int)std::min<unsigned long long>(c, kLutSize - 1);
+            },
+            [&](int c) { return (unsigned long long)c << sh; });
     }
     // division magic for unsigned 64-bit dividends (round-up method with optional add fix-up)
     P->divisor = divisor;

@@ -79,6 +79,7 @@ struct LatResults {
     unsigned long long counts[kMaxThresholds + 1];
     LatMoments mom;
     unsigned long long compact_n;       // samples kept / compacted / outside the fast path (one counter, reused)
+    SelState sel;                       // the resident select's state (its answer)
 };
 
 // Input of a one-kernel select that an earlier kernel on the stream prepares (bracket_ranks_kernel after a bracket
@@ -96,7 +97,6 @@ struct LatScratch {
     LatResults* d_results_init;         // the template: zero counts, min = INT64_MAX, max = INT64_MIN
     LatResults* h_results;              // pinned: lat_read_results() copies the block here
     HistParams* h_params;               // pinned staging of the parameter block
-    SelState* h_sel;                    // pinned: the resident select's state, read back
     unsigned long long* d_counts;       // [kMaxThresholds + 1]
     LatMoments* d_mom;
     unsigned long long* d_radix;        // [kMaxSelect][kRadixBins]
@@ -104,7 +104,7 @@ struct LatScratch {
     long long* d_compact;               // samples of the buckets still in play after the first radix pass (lazy)
     size_t compact_cap;                 // in samples
     unsigned long long* d_compact_n;    // device counter
-    SelState* d_sel;                    // device-resident select
+    SelState* d_sel;                    // device-resident select: &d_results->sel
     unsigned long long* d_sel_hist;     // [kSelMax][kRadixBins]
     bool* sel_hist_clean;               // host: the last one-kernel select ended well, so d_sel_hist is all zero
     long long* d_sample;                // stratified sample of the input (sampled select, lazy)
@@ -130,11 +130,12 @@ cudaError_t launch_hist(const long long* d_samples, size_t n, const LatScratch& 
                         cudaStream_t stream, const HistParams& P, const HistCollect* collect = nullptr);
 // out[i] = one sample of stratum i: x[i * stride + (hash(i) mod stride)], i < s, s * stride <= n
 // *d_outside (device, may be NULL) = how many of those samples are negative or >= 2^32
-// d_bounds: when given, it is reset from d_bounds_init (start values, on the device) and its min_ns / max_ns receive
-// the extremes of the sample (the bounds of a select over it that follows on the stream)
+// d_bounds: when given, its min_ns / max_ns receive the extremes of the sample (the bounds of a select over it that
+// follows on the stream).  results: the scratch whose block holds d_outside and d_bounds; it is reset first (without
+// it d_outside is cleared and d_bounds taken as it is).
 cudaError_t launch_sample(const long long* d_samples, size_t stride, long long* d_out, size_t s, cudaStream_t stream,
                           unsigned long long* d_outside = nullptr, LatMoments* d_bounds = nullptr,
-                          const LatMoments* d_bounds_init = nullptr);
+                          const LatScratch* results = nullptr);
 // All the passes of a radix select of up to kSelMax ranks over [lo, hi] (pass have_bounds = false to take the
 // bounds from a min/max pass first), queued on the stream; the answer lands in s.d_sel (result[], bad).
 // The same select in one cooperative kernel (select_fused_grid() != 0 says the device can).  approx_max > 0: stop

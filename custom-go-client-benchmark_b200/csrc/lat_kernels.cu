@@ -14,8 +14,6 @@
 // (warp, lane) in shared memory so the skewed latency distribution causes no atomic contention.
 #include "lat_kernels.h"
 
-#include <cooperative_groups.h>
-
 #ifdef B200_DEBUG_ASSERT
 #include <cassert>
 #endif
@@ -26,8 +24,6 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
-
-namespace cg = cooperative_groups;
 
 namespace b200 {
 
@@ -1066,13 +1062,35 @@ sel_scan_kernel(SelState* st, unsigned long long* __restrict__ hist) {
 // the bucket's lowest key — or its highest for the ranks in ceil_mask — i.e. a bound on the order statistic good to
 // approx_max ranks, which is all the brackets of the sampled select need (one round less).
 constexpr int kFusedThreads = 1024, kScanBins = kRadixBins / kFusedThreads;
+
+// Barrier over all CTAs of a grid that is resident as a whole (the launch is cooperative, which is what guarantees
+// that).  bar[0] counts arrivals and is cleared by the last to arrive, bar[1] is the generation it then advances:
+// both are left ready for the next barrier and the next launch (cleared once, at set-up).  The fences on either side
+// make what the CTAs wrote before the barrier visible to all of them after it.
+__device__ __forceinline__ void grid_barrier(unsigned* bar) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        const unsigned gen = *reinterpret_cast<volatile unsigned*>(bar + 1);
+        if (atomicAdd(bar, 1u) == gridDim.x - 1) {
+            *reinterpret_cast<volatile unsigned*>(bar) = 0;
+            __threadfence();
+            atomicAdd(bar + 1, 1u);
+        } else {
+            while (*reinterpret_cast<volatile unsigned*>(bar + 1) == gen) {
+            }
+        }
+        __threadfence();
+    }
+    __syncthreads();
+}
 // bounds (approx_max > 0) need not be finer than 2^kApproxBits key units (4 us for nanoseconds): identical samples
 // — a latency distribution has atoms — would otherwise keep a bucket above approx_max down to the last bit
 constexpr int kApproxBits = 12;
 __global__ void __launch_bounds__(kFusedThreads)
 sel_fused_kernel(const long long* __restrict__ x, size_t n_arg, SelState* st, unsigned long long* __restrict__ hist,
                  LatMoments* mom, SelRanks ranks_arg, int have_bounds, long long lo, long long hi,
-                 unsigned long long approx_max, unsigned ceil_mask, const SelDeferred* __restrict__ in) {
+                 unsigned long long approx_max, unsigned ceil_mask, const SelDeferred* __restrict__ in, unsigned* bar) {
     // ranks and length either from the launch or from what the kernel before this one left (the same for every CTA)
     size_t n = n_arg;
     SelRanks ranks = ranks_arg;
@@ -1089,7 +1107,6 @@ sel_fused_kernel(const long long* __restrict__ x, size_t n_arg, SelState* st, un
         ranks = in->ranks;
     }
     static_assert(kRadixBins == kScanBins * kFusedThreads, "a thread scans kScanBins bins");
-    cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(16) unsigned char sm[];
     unsigned* hs = reinterpret_cast<unsigned*>(sm);  // [nhist][kRadixBins]
     __shared__ unsigned long long pf[kSelMax];
@@ -1142,7 +1159,7 @@ sel_fused_kernel(const long long* __restrict__ x, size_t n_arg, SelState* st, un
             atomicMin(&mom->min_ns, mn);
             atomicMax(&mom->max_ns, mx);
         }
-        grid.sync();
+        grid_barrier(bar);
         stamp();
     }
     if (have_bounds != 1) {  // 2: an earlier kernel on the stream (the sampling) left them there
@@ -1215,7 +1232,7 @@ sel_fused_kernel(const long long* __restrict__ x, size_t n_arg, SelState* st, un
             }
         }
         stamp();
-        grid.sync();
+        grid_barrier(bar);
         stamp();
         for (int h = blockIdx.x; h < nhist; h += gridDim.x) {  // CTA h: histogram h (a small grid: several each)
             unsigned long long* const H = hist + (size_t)h * kRadixBins + kScanBins * t;
@@ -1269,7 +1286,7 @@ sel_fused_kernel(const long long* __restrict__ x, size_t n_arg, SelState* st, un
             for (int j = 0; j < kScanBins; j += 2) *reinterpret_cast<ulonglong2*>(H + j) = make_ulonglong2(0, 0);
         }
         stamp();
-        grid.sync();
+        grid_barrier(bar);
         stamp();
         bad = __ldcg(&st->bad);
         const int more = __ldcg(&st->more[round]);
@@ -1438,6 +1455,8 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_in, sizeof(SelDeferred));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_bar, 2 * sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemset(s->d_sel_bar, 0, 2 * sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_hist, (size_t)kSelMax * kRadixBins * sizeof(unsigned long long));
     if (e == cudaSuccess) {
         s->sel_hist_clean = new (std::nothrow) bool(false);
@@ -1461,6 +1480,7 @@ void lat_scratch_free(LatScratch* s) {
     cudaFree(s->d_prefix);
     cudaFree(s->d_compact);
     cudaFree(s->d_sel_in);
+    cudaFree(s->d_sel_bar);
     cudaFree(s->d_sel_hist);
     delete s->sel_hist_clean;
     cudaFree(s->d_sample);
@@ -1644,8 +1664,9 @@ cudaError_t launch_select_fused(const long long* d_samples, size_t n, const SelR
     SelRanks r = ranks;
     int hb = have_bounds;
     const SelDeferred* in = deferred ? s.d_sel_in : nullptr;
+    unsigned* bar = s.d_sel_bar;
     void* args[] = {(void*)&d_samples, (void*)&n, (void*)&st, (void*)&hist, (void*)&mom, (void*)&r, (void*)&hb,
-                    (void*)&lo, (void*)&hi, (void*)&approx_max, (void*)&ceil_mask, (void*)&in};
+                    (void*)&lo, (void*)&hi, (void*)&approx_max, (void*)&ceil_mask, (void*)&in, (void*)&bar};
     return cudaLaunchCooperativeKernel((const void*)sel_fused_kernel, dim3(grid), dim3(kFusedThreads), args, smem, stream);
 }
 

@@ -93,6 +93,7 @@ struct SelDeferred {
 struct LatScratch {
     HistParams* d_params;
     SelDeferred* d_sel_in;
+    unsigned* d_sel_bar;                // [2] the one-kernel select's grid barrier (count, generation)
     LatResults* d_results;              // the block; the three pointers below point into it
     LatResults* d_results_init;         // the template: zero counts, min = INT64_MAX, max = INT64_MIN
     LatResults* h_results;              // pinned: lat_read_results() copies the block here

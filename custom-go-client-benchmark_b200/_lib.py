@@ -80,6 +80,7 @@ SIGNATURES = {
     "b200_select_kth_avg": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp, _vp]),
     "b200_select_sample": (_int, [_vp, _int, _vp, _sz, _sz, _pp, C.POINTER(_sz)]),
     "b200_bracket_pass": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _u64, _vp, _pp, C.POINTER(_u64), _vp]),
+    "b200_bracket_pass_avg": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _u64, _vp, _pp, C.POINTER(_u64), _vp]),
     "b200_select_kth_range": (_int, [_vp, _int, _vp, _sz, _i64, _i64, _i64, _vp, _int, _vp]),
     "b200_hist_fixed_multi": (_int, [_vp, _vp, _vp, _vp, _int, _i64, _vp, _int, _int, _vp, C.POINTER(LatStats)]),
     "b200_select_kth_multi": (_int, [_vp, _vp, _vp, _vp, _int, _i64, _vp, _int, _vp]),
@@ -89,6 +90,7 @@ SIGNATURES = {
                                    C.POINTER(_u64), C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "b200_minmax": (_int, [_vp, _int, _vp, _sz, C.POINTER(_i64), C.POINTER(_i64)]),
     "b200_radix_count": (_int, [_vp, _int, _vp, _sz, _u64, _int, _int, _int, _vp, _vp]),
+    "b200_radix_count_based": (_int, [_vp, _int, _vp, _sz, _vp, _int, _int, _int, _vp, _vp]),
 }
 
 _lib = None

@@ -1336,6 +1336,27 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
     return 0;
 }
 
+int b200_radix_count_based(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, const uint64_t* key_bases,
+                           int shift, int top, int nk, const uint64_t* prefix, uint64_t* counts) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !counts || !key_bases || !prefix || (n && !d_samples) || ((uintptr_t)d_samples & 7) || nk < 1 ||
+        nk > B200_SELECT_MAX_K || shift < 0 || top <= shift || top >= 64 || top - shift > kRadixBits)
+        return fail(B200_ERR_INVALID, "b200_radix_count_based");
+    std::lock_guard<std::mutex> lk(d->mu);
+    CU(cudaSetDevice(dev));
+    uint64_t both[2 * kMaxSelect] = {};
+    for (int i = 0; i < nk; i++) {
+        both[i] = prefix[i];
+        both[kMaxSelect + i] = key_bases[i];
+    }
+    CU(cudaMemcpyAsync(d->lat.d_prefix, both, sizeof both, cudaMemcpyHostToDevice, d->stream));
+    CU(launch_radix_pass((const long long*)d_samples, n, 0, shift, top, nk, d->lat, d->stream, true));
+    CU(cudaMemcpyAsync(counts, d->lat.d_radix, (size_t)nk * kRadixBins * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+                       d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
 }  // extern "C"
 
 namespace {
@@ -1793,9 +1814,33 @@ int b200_select_sample(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t 
     return 0;
 }
 
+namespace {
+int bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const int64_t* thresholds,
+                 int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept, uint64_t* nkept, b200_lat_stats* stats,
+                 bool no_squares);
+}
+
 int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                       const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
                       uint64_t* nkept, b200_lat_stats* stats) {
+    return bracket_pass(ctx, dev, d_samples, n, divisor, thresholds, nthr, cap, counts, d_kept, nkept, stats, false);
+}
+
+int b200_bracket_pass_avg(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                          const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
+                          uint64_t* nkept, b200_lat_stats* stats) {
+    const int rc = bracket_pass(ctx, dev, d_samples, n, divisor, thresholds, nthr, cap, counts, d_kept, nkept, stats, true);
+    if (rc == 0 && stats) stats->sumsq_lo = stats->sumsq_hi = 0;
+    return rc;
+}
+
+}  // extern "C"
+
+namespace {
+
+int bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const int64_t* thresholds,
+                 int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept, uint64_t* nkept, b200_lat_stats* stats,
+                 bool no_squares) {
     DevState* d = get_dev(ctx, dev);
     if (!d || !thresholds || !counts || !d_kept || !nkept || nthr < 1 || nthr > B200_HIST_MAX_EDGES || divisor < 1 ||
         (n && !d_samples) || ((uintptr_t)d_samples & 7))
@@ -1809,7 +1854,7 @@ int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n
     CU(cudaSetDevice(dev));
     if (cap && !grow(&d->lat.d_collect, &d->lat.collect_cap, (size_t)cap)) return fail(B200_ERR_NOMEM, "b200_bracket_pass");
     HistCollect col{d->lat.d_collect, d->lat.d_compact_n, cap};
-    CU(launch_hist((const long long*)d_samples, n, d->lat, stats != nullptr, d->stream, P, &col));
+    CU(launch_hist((const long long*)d_samples, n, d->lat, stats ? (no_squares ? 2 : 1) : 0, d->stream, P, &col));
     unsigned long long c[kMaxThresholds + 1], kept = 0;
     LatMoments m{};
     CU(lat_read_results(d->lat, d->stream));
@@ -1823,6 +1868,10 @@ int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n
     if (stats) fill_stats(m, divisor, stats);
     return 0;
 }
+
+}  // namespace
+
+extern "C" {
 
 namespace {
 int select_kth_with_stats(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const uint64_t* k,

@@ -862,23 +862,28 @@ compact_kernel(const long long* __restrict__ x, size_t n, unsigned long long key
 
 __global__ void __launch_bounds__(kRadixThreads)
 radix_kernel(const long long* __restrict__ x, size_t n, unsigned long long key_base, int shift, int top, int nk,
-             const unsigned long long* __restrict__ prefix, unsigned long long* __restrict__ out) {
+             const unsigned long long* __restrict__ prefix, const unsigned long long* __restrict__ bases,
+             unsigned long long* __restrict__ out) {
     extern __shared__ __align__(16) unsigned char sm[];
     unsigned* hist = reinterpret_cast<unsigned*>(sm);  // [nk][kRadixBins]
     for (int i = threadIdx.x; i < nk * kRadixBins; i += kRadixThreads) hist[i] = 0;
-    __shared__ unsigned long long pf[kMaxSelect];
-    if (threadIdx.x < nk) pf[threadIdx.x] = top >= 64 ? 0 : prefix[threadIdx.x];
+    __shared__ unsigned long long pf[kMaxSelect], kb[kMaxSelect];  // prefix and key base of every histogram
+    if (threadIdx.x < nk) {
+        pf[threadIdx.x] = top >= 64 ? 0 : prefix[threadIdx.x];
+        kb[threadIdx.x] = bases ? bases[threadIdx.x] : key_base;
+    }
     __syncthreads();
     const unsigned mask = (top - shift >= kRadixBits) ? (kRadixBins - 1) : ((1u << (top - shift)) - 1);
     const bool all = top >= 64;
     const size_t nthreads = (size_t)gridDim.x * kRadixThreads;
     auto one = [&](long long v) {
-        unsigned long long key = ((unsigned long long)v ^ 0x8000000000000000ull) - key_base;
-        unsigned dgt = (unsigned)(key >> shift) & mask;
-        unsigned long long hi = all ? 0 : key >> top;
+        const unsigned long long raw = (unsigned long long)v ^ 0x8000000000000000ull;
 #pragma unroll
-        for (int k = 0; k < kMaxSelect; k++)
-            if (k < nk && hi == pf[k]) atomicAdd(hist + k * kRadixBins + dgt, 1u);
+        for (int k = 0; k < kMaxSelect; k++) {
+            if (k >= nk) break;
+            const unsigned long long key = raw - kb[k];
+            if (all || (key >> top) == pf[k]) atomicAdd(hist + k * kRadixBins + ((unsigned)(key >> shift) & mask), 1u);
+        }
     };
     size_t head = ((reinterpret_cast<uintptr_t>(x) & 15) ? 1 : 0);
     if (head > n) head = n;
@@ -1453,7 +1458,7 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     }
     if (e == cudaSuccess) e = cudaMalloc(&s->d_params, sizeof(HistParams));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, kMaxSelect * sizeof(unsigned long long));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, 2 * kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_in, sizeof(SelDeferred));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_bar, 2 * sizeof(unsigned));
     if (e == cudaSuccess) e = cudaMemset(s->d_sel_bar, 0, 2 * sizeof(unsigned));
@@ -1681,7 +1686,7 @@ cudaError_t launch_compact(const long long* d_samples, size_t n, unsigned long l
 }
 
 cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned long long key_base, int shift, int top,
-                              int nk, const LatScratch& s, cudaStream_t stream) {
+                              int nk, const LatScratch& s, cudaStream_t stream, bool own_bases) {
     cudaError_t e = cudaMemsetAsync(s.d_radix, 0, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long), stream);
     if (e != cudaSuccess || !n) return e;
     size_t smem = (size_t)nk * kRadixBins * sizeof(unsigned);
@@ -1690,7 +1695,8 @@ cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned lon
     if (e != cudaSuccess) return e;
     size_t want_ctas = (n / 2 + kRadixThreads - 1) / kRadixThreads;
     int grid = (int)std::min<size_t>((size_t)sm_count() * 2, want_ctas ? want_ctas : 1);
-    radix_kernel<<<grid, kRadixThreads, smem, stream>>>(d_samples, n, key_base, shift, top, nk, s.d_prefix, s.d_radix);
+    radix_kernel<<<grid, kRadixThreads, smem, stream>>>(d_samples, n, key_base, shift, top, nk, s.d_prefix,
+                                                        own_bases ? s.d_prefix + kMaxSelect : nullptr, s.d_radix);
     return cudaGetLastError();
 }
 

@@ -101,7 +101,7 @@ struct LatScratch {
     unsigned long long* d_counts;       // [kMaxThresholds + 1]
     LatMoments* d_mom;
     unsigned long long* d_radix;        // [kMaxSelect][kRadixBins]
-    unsigned long long* d_prefix;       // [kMaxSelect]
+    unsigned long long* d_prefix;       // [2][kMaxSelect]: prefixes, then (optionally) a key base per histogram
     long long* d_compact;               // samples of the buckets still in play after the first radix pass (lazy)
     size_t compact_cap;                 // in samples
     unsigned long long* d_compact_n;    // device counter
@@ -159,7 +159,8 @@ cudaError_t launch_select_resident(const long long* d_samples, size_t n, const S
 // (key' >> shift) & (2^(top-shift) - 1) over the samples with key' >> top == d_prefix[k] (all samples when
 // top >= 64).  top - shift <= kRadixBits.
 cudaError_t launch_radix_pass(const long long* d_samples, size_t n, unsigned long long key_base, int shift, int top,
-                              int nk, const LatScratch& s, cudaStream_t stream);
+                              int nk, const LatScratch& s, cudaStream_t stream,
+                              bool own_bases = false);  // own_bases: histogram k's keys are taken from s.d_prefix[kMaxSelect + k]
 cudaError_t launch_minmax(const long long* d_samples, size_t n, const LatScratch& s, cudaStream_t stream);
 // Append to s.d_compact every sample whose key' >> top equals one of the nprefix (distinct) values in
 // s.d_prefix; the count lands in *s.d_compact_n.  At most s.compact_cap samples are written.

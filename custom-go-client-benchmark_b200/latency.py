@@ -81,6 +81,7 @@ class _Reducer:
     # how many collectives the reductions of this process issued and the wall-clock seconds spent in them
     # (bench.py reports both beside the multi-rank timings)
     tally = {"collectives": 0, "seconds": 0.0}
+    _buffers: dict = {}
 
     def __init__(self, group=None, device=None):
         self.group, self.device = group, device
@@ -110,6 +111,46 @@ class _Reducer:
         _Reducer.tally["seconds"] += time.perf_counter() - t0
         return out
 
+    def gather(self, values) -> list:
+        """Every rank's list of Python ints (each within 64 bits, signed or unsigned; all lists equally long), as
+        a list of lists of ints in [0, 2^64) — ONE collective (all_gather), from which sums, minima and maxima of
+        any width are then formed locally.  Not distributed: [values]."""
+        vals = [int(v) & _M64 for v in values]
+        if not self.active:
+            return [vals]
+        import time
+
+        import torch
+        t0 = time.perf_counter()
+        world = self.dist.get_world_size(self.group)
+        arr = np.array(vals, dtype=np.uint64).view(np.int64)
+        if self.device is None:
+            mine = torch.from_numpy(arr.copy())
+            out = torch.empty(world * mine.numel(), dtype=torch.int64)
+            self.dist.all_gather_into_tensor(out, mine, group=self.group)
+            rows = out.numpy().view(np.uint64).reshape(world, -1)
+        else:
+            # pinned staging and device buffers are kept per (device, length): a collective of a few hundred bytes
+            # is all overhead, and allocating four tensors was a good part of it
+            key = (str(self.device), arr.size, world)
+            buf = _Reducer._buffers.get(key)
+            if buf is None:
+                buf = (torch.empty(arr.size, dtype=torch.int64).pin_memory(),
+                       torch.empty(arr.size, dtype=torch.int64, device=self.device),
+                       torch.empty(world * arr.size, dtype=torch.int64, device=self.device),
+                       torch.empty(world * arr.size, dtype=torch.int64).pin_memory())
+                _Reducer._buffers[key] = buf
+            pin_in, dev_in, dev_out, pin_out = buf
+            pin_in.numpy()[:] = arr
+            dev_in.copy_(pin_in, non_blocking=True)
+            self.dist.all_gather_into_tensor(dev_out, dev_in, group=self.group)
+            pin_out.copy_(dev_out, non_blocking=True)
+            torch.cuda.current_stream(dev_out.device).synchronize()
+            rows = pin_out.numpy().view(np.uint64).reshape(world, -1)
+        _Reducer.tally["collectives"] += 1
+        _Reducer.tally["seconds"] += time.perf_counter() - t0
+        return [[int(x) for x in r] for r in rows]
+
     def sum_u64(self, arr: np.ndarray) -> np.ndarray:
         # split into 32-bit halves so the int64 all-reduce cannot overflow for < 2^31 ranks
         a = arr.astype(np.uint64)
@@ -135,25 +176,38 @@ class _Reducer:
         return int(r[0]), ~int(r[1])
 
 
+def _moment_words(counts, cnt, mn, mx, total, sumsq, below, above) -> list:
+    """One rank's exact partials as 64-bit words for _Reducer.gather: counts..., cnt, below, above, the signed
+    128-bit sum (two words, two's complement), the 128-bit sum of squares (two words), min, max."""
+    t = int(total) & ((1 << 128) - 1)
+    q = int(sumsq)
+    return ([int(c) for c in counts] + [int(cnt), int(below), int(above), t & _M64, t >> 64, q & _M64, q >> 64,
+                                        int(mn), int(mx)])
+
+
+def _merge_moment_words(rows, nb: int):
+    """The ranks' _moment_words -> (counts, cnt, mn, mx, total, sumsq, below, above) of all of them."""
+    s64 = lambda w: w - (1 << 64) if w >= _SIGN else w
+    counts = np.array([sum(r[i] for r in rows) for i in range(nb)], dtype=np.uint64)
+    cnt, below, above = (sum(r[nb + i] for r in rows) for i in range(3))
+    total = 0
+    for r in rows:
+        t = r[nb + 3] | (r[nb + 4] << 64)
+        total += t - (1 << 128) if t >> 127 else t
+    sumsq = sum(r[nb + 5] | (r[nb + 6] << 64) for r in rows)
+    have = [r for r in rows if r[nb]]  # ranks that hold samples
+    mn = min((s64(r[nb + 7]) for r in have), default=(1 << 63) - 1)
+    mx = max((s64(r[nb + 8]) for r in have), default=-(1 << 63))
+    return counts, cnt, mn, mx, total, sumsq, below, above
+
+
 def merge_distribution(red: _Reducer, counts: np.ndarray, cnt: int, mn: int, mx: int, total: int, sumsq: int,
                        below: int, above: int) -> Distribution:
     """Combine one rank's exact integer partials with the other ranks' (sum / min / max all-reduces)."""
     nb = counts.size
     if red.active:
-        # 128-bit quantities travel as four 32-bit limbs each (the signed sum is offset to be non-negative)
-        off = 1 << 100
-        limbs = lambda v: [(v >> (32 * i)) & 0xFFFFFFFF for i in range(4)]
-        vec = np.array([int(c) for c in counts] + [cnt, below, above] + limbs(total + off) + limbs(sumsq),
-                       dtype=np.uint64)
-        r = red.sum_u64(vec)
-        world = red.dist.get_world_size(red.group)
-        counts = np.array([int(x) for x in r[:nb]], dtype=np.uint64)
-        had = cnt > 0
-        cnt, below, above = int(r[nb]), int(r[nb + 1]), int(r[nb + 2])
-        total = sum(int(r[nb + 3 + i]) << (32 * i) for i in range(4)) - world * off
-        sumsq = sum(int(r[nb + 7 + i]) << (32 * i) for i in range(4))
-        big = (1 << 63) - 1
-        mn, mx = red.minmax_i64(mn if had else big, mx if had else -big - 1)
+        rows = red.gather(_moment_words(counts, cnt, mn, mx, total, sumsq, below, above))  # ONE collective
+        counts, cnt, mn, mx, total, sumsq, below, above = _merge_moment_words(rows, nb)
     wrapped = total & _M64
     wrapped = wrapped - (1 << 64) if wrapped >= _SIGN else wrapped
     return Distribution(cnt, mn, mx, total, wrapped, sumsq, counts, below, above)
@@ -291,30 +345,86 @@ def locate_in_brackets(counts, k: int):
     return None
 
 
-def sampled_select(red: _Reducer, n_local: int, n_global: int, divisor: int, ks: Sequence[int], sample_fn,
-                   sample_select_fn, bracket_fn, kept_count_fn, kept_minmax_fn):
+def locate_bracket(counts, k: int):
+    """As locate_in_brackets, but (bracket index, 0-based rank of global rank k among that bracket's samples)."""
+    below = 0
+    for j in range((len(counts) - 1) // 2):
+        below += int(counts[2 * j])
+        if k < below:
+            return None
+        inside = int(counts[2 * j + 1])
+        if k < below + inside:
+            return j, k - below
+        below += inside
+    return None
+
+
+def bracket_radix_select(red: _Reducer, count_fn, brackets, located, divisor: int):
+    """The order statistics among the kept samples, each resolved INSIDE its own bracket: keys are taken relative to
+    the bracket's lower end, so they are as many bits wide as the widest bracket (~18 for 10^9 latencies) and two
+    12-bit passes settle them — against three over the span of all brackets together.  located[i] = (bracket
+    index, rank inside that bracket).  A pass is one local count (count_fn with a LIST of key bases, one per wanted
+    rank; up to SELECT_MAX_K per call) and ONE all-reduce of the digit counts.  (A key range is the width of the
+    widest bracket rounded up to a power of two: what it takes in beyond a bracket's upper end is larger than every
+    sample of the bracket and cannot change a rank inside it; what lies below the lower end wraps to a huge key.)"""
+    m = len(located)
+    kbase = [(int(brackets[j][0]) + _SIGN) & _M64 for j, _ in located]
+    top = max((int(brackets[j][1]) - int(brackets[j][0])).bit_length() for j, _ in located)
+    prefix, rank = [0] * m, [int(r) for _, r in located]
+    while top > 0:
+        shift = max(top - 12, 0)
+        width = top - shift
+        parts = [np.asarray(count_fn(kbase[g:g + SELECT_MAX_K], shift, top, prefix[g:g + SELECT_MAX_K]),
+                            dtype=np.uint64).reshape(-1) for g in range(0, m, SELECT_MAX_K)]
+        tot = red.sum_counts(np.concatenate(parts))
+        for i in range(m):
+            cs = np.cumsum(tot[i * RADIX_BINS: i * RADIX_BINS + (1 << width)])
+            dgt = int(np.searchsorted(cs, rank[i], side="right"))
+            if dgt == 1 << width:
+                raise RuntimeError("inconsistent radix counts")
+            rank[i] -= int(cs[dgt - 1]) if dgt else 0
+            prefix[i] = (prefix[i] << width) | dgt
+        top = shift
+    res = []
+    for i in range(m):
+        ns = ((prefix[i] + kbase[i]) & _M64) - _SIGN
+        q = abs(ns) // divisor  # Go's truncating division
+        res.append(q if ns >= 0 else -q)
+    return res
+
+
+def sampled_select(red: _Reducer, n_local: int, n_global: Optional[int], divisor: int, ks: Sequence[int], sample_fn,
+                   sample_select_fn, bracket_fn, kept_count_fn, kept_minmax_fn, fractions=None, extra_fn=None,
+                   min_total: int = 0):
     """One pass over every rank's samples instead of min/max + three radix passes (the multi-rank form of what
-    b200_select_kth does on one device).  Collectives carry a few dozen integers only.
+    b200_select_kth does on one device).  FOUR collectives of a few dozen integers (the last two a few
+    thousand): the brackets, the bracket-pass counts, two radix passes inside the brackets.
 
       sample_fn(stride) -> s                 this rank's stratified sample (one input per `stride`), its size
       sample_select_fn(ranks) -> values      order statistics of that sample (local, exact)
       bracket_fn(thresholds, cap) -> (counts, nkept, stats)   the histogram pass that keeps the odd bins
       kept_count_fn / kept_minmax_fn         radix-select building blocks over the kept samples
+      fractions                              [(num, den)]: the wanted ranks are n_global * num // den; n_global may
+                                             then be None (it comes out of the first collective) and ks is ignored
+      extra_fn(stats) -> [ints]              words gathered from every rank along with the counts (the caller's
+                                             moments): returned as one list per rank
+      min_total                              None is returned (by every rank alike) when the ranks hold fewer
 
     Every rank brackets each wanted quantile with ITS sample, a few standard deviations either side; the union of
     the ranks' brackets (min of the lower ends, max of the upper ends) holds the global order statistic whenever
     every local bracket holds the local quantile, whatever the ranks' distributions are - it is just wide when
-    they differ, and then (or on a ~1e-6 tail event) the exact counts of the pass say so and None is returned:
-    the caller takes the radix passes.  Returns (values, stats) otherwise."""
-    ks = [int(k) for k in ks]
-    nk = len(ks)
-    stride = max(16, -(-n_global // (1 << 22)))
+    they differ, and then (or on a rare tail event) the exact counts of the pass say so and None is returned:
+    the caller takes the radix passes.  Returns (values, stats, extra rows) otherwise."""
+    world = red.dist.get_world_size(red.group) if red.active else 1
+    nk = len(fractions) if fractions is not None else len(ks)
+    # (without the total, ranks are taken to hold about equal shares: it only sizes the sample)
+    stride = max(16, -(-(n_global if n_global is not None else n_local * world) // (1 << 22)))
     s = sample_fn(stride)
     ok = s >= 1024
     margin = int(2.5 * np.sqrt(max(s, 1))) + 2
     want, where = [], []
-    for k in ks:
-        c = k * s // n_global
+    for i in range(nk):
+        c = fractions[i][0] * s // fractions[i][1] if fractions is not None else int(ks[i]) * s // n_global
         lo_at = hi_at = None
         if ok and c >= margin:
             lo_at = len(want); want.append(c - margin)
@@ -322,13 +432,19 @@ def sampled_select(red: _Reducer, n_local: int, n_global: int, divisor: int, ks:
             hi_at = len(want); want.append(c + margin + 1)
         where.append((lo_at, hi_at))
     got = sample_select_fn(want) if want else []
-    vec = [1 if ok else 0]
+    s64 = lambda w: w - (1 << 64) if w >= _SIGN else w
+    vec = [int(n_local), 1 if ok else 0]
     vec += [_I64_MIN if a is None else int(got[a]) for a, _ in where]
-    vec += [-(_I64_MAX - 1) if b is None else -min(int(got[b]), _I64_MAX - 1) for _, b in where]
-    g = [int(x) for x in red._run(np.array(vec, dtype=np.int64), "MIN")]
-    if g[0] == 0:
+    vec += [_I64_MAX - 1 if b is None else min(int(got[b]), _I64_MAX - 1) for _, b in where]
+    rows = red.gather(vec)                                                                   # collective 1
+    n_all = sum(r[0] for r in rows)
+    if n_global is not None and n_all != n_global:
+        raise ValueError("sampled_select: n_global is not the sum of the ranks' sample counts")
+    n_global = n_all
+    if not all(r[1] for r in rows) or n_global == 0 or n_global < min_total:
         return None  # some rank holds too few samples to bracket anything
-    br = merge_brackets([(g[1 + i], -g[1 + nk + i]) for i in range(nk)])
+    ks = [n_global * num // den for num, den in fractions] if fractions is not None else [int(k) for k in ks]
+    br = merge_brackets([(min(s64(r[2 + i]) for r in rows), max(s64(r[2 + nk + i]) for r in rows)) for i in range(nk)])
     thr = []
     for lo, hi in br:
         thr += [lo, hi + 1]
@@ -337,21 +453,29 @@ def sampled_select(red: _Reducer, n_local: int, n_global: int, divisor: int, ks:
     expect = nk * (2 * margin + 2) * stride
     cap = max(min(max(8 * expect, n_local // 64), n_local // 8), 1024)
     counts, nkept, stats = bracket_fn(thr, cap)
-    tot = red.sum_counts(np.array([int(c) for c in counts] + [int(nkept), 1 if nkept > cap else 0], dtype=np.uint64))
-    gc = [int(x) for x in tot[:len(thr) + 1]]
+    extra = [int(x) for x in extra_fn(stats)] if extra_fn is not None else []
+    nc = len(thr) + 1
+    rows = red.gather([int(c) for c in counts] + [int(nkept), 1 if nkept > cap else 0] + extra)  # collective 2
+    gc = [sum(r[i] for r in rows) for i in range(nc)]
+    kept_all, overflow = sum(r[nc] for r in rows), sum(r[nc + 1] for r in rows)
+    extra_rows = [r[nc + 2:] for r in rows]
     inside = sum(gc[1::2])
-    if int(tot[-1]) or sum(gc) != n_global or int(tot[-2]) != inside or inside == 0:
+    if overflow or sum(gc) != n_global or kept_all != inside or inside == 0:
         return None  # brackets too heavy for the buffers (heavy duplicates, ranks with very different data)
-    rank_kept = [locate_in_brackets(gc, k) for k in ks]
-    if any(r is None for r in rank_kept):
+    located = [locate_bracket(gc, k) for k in ks]
+    if any(x is None for x in located):
         return None
-    open_ended = br[0][0] == _I64_MIN or br[-1][1] == _I64_MAX - 1
-    vals = radix_select(red, int(nkept), kept_minmax_fn, kept_count_fn, divisor, rank_kept, n_global=inside,
-                        global_bounds=None if open_ended else (br[0][0], br[-1][1]))
-    return vals, stats
+    if br[0][0] == _I64_MIN or br[-1][1] == _I64_MAX - 1:
+        # a bracket open at an end is as wide as int64: the passes run over all kept samples between their extremes
+        rank_kept = [locate_in_brackets(gc, k) for k in ks]
+        vals = radix_select(red, int(nkept), kept_minmax_fn, kept_count_fn, divisor, rank_kept, n_global=inside)
+    else:
+        vals = bracket_radix_select(red, kept_count_fn, br, located, divisor)              # collectives 3, 4
+    return vals, stats, extra_rows
 
 
-def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, want_stats):
+def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, want_stats, fractions=None,
+                           extra_fn=None, min_total=0):
     """sampled_select over this rank's device samples through the C ABI building blocks."""
     state = {}
 
@@ -372,8 +496,10 @@ def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, wa
         tarr = np.array(thr, dtype=np.int64)
         counts = np.zeros(tarr.size + 1, dtype=np.uint64)
         p, nkept, st = C.c_void_p(), C.c_uint64(), LatStats()
-        check(L.b200_bracket_pass(h, d, d_samples, n, divisor, tarr.ctypes.data, tarr.size, cap, counts.ctypes.data,
-                                  C.byref(p), C.byref(nkept), C.byref(st) if want_stats else None))
+        # want_stats == "avg": without the sum of squares (the seven lines need the sum only)
+        fn = L.b200_bracket_pass_avg if want_stats == "avg" else L.b200_bracket_pass
+        check(fn(h, d, d_samples, n, divisor, tarr.ctypes.data, tarr.size, cap, counts.ctypes.data,
+                 C.byref(p), C.byref(nkept), C.byref(st) if want_stats else None))
         state["kept"] = (p.value, min(nkept.value, cap))
         return counts, nkept.value, (st if want_stats else None)
 
@@ -381,7 +507,13 @@ def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, wa
         p, cnt = state["kept"]
         counts = np.zeros(len(prefixes) * RADIX_BINS, dtype=np.uint64)
         parr = np.array(prefixes, dtype=np.uint64)
-        check(L.b200_radix_count(h, d, p, cnt, key_base, shift, top, len(prefixes), parr.ctypes.data, counts.ctypes.data))
+        if isinstance(key_base, (list, tuple)):  # a key base per histogram (bracket_radix_select)
+            barr = np.array(key_base, dtype=np.uint64)
+            check(L.b200_radix_count_based(h, d, p, cnt, barr.ctypes.data, shift, top, len(prefixes), parr.ctypes.data,
+                                           counts.ctypes.data))
+        else:
+            check(L.b200_radix_count(h, d, p, cnt, key_base, shift, top, len(prefixes), parr.ctypes.data,
+                                     counts.ctypes.data))
         return counts
 
     def kept_minmax_fn():
@@ -391,12 +523,12 @@ def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, wa
         return mn.value, mx.value
 
     return sampled_select(red, n, n_global, divisor, ks, sample_fn, sample_select_fn, bracket_fn, kept_count_fn,
-                          kept_minmax_fn)
+                          kept_minmax_fn, fractions=fractions, extra_fn=extra_fn, min_total=min_total)
 
 
 def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Optional[Context] = None,
                dev: Optional[int] = None, group=None, reduce_device=None, n_global: Optional[int] = None,
-               bounds_ns: Optional[tuple] = None):
+               bounds_ns: Optional[tuple] = None, try_sampled: bool = True):
     """k-th smallest (0-based) of trunc(sample/divisor) over all ranks' samples (sorted[k] of
     ssd_test/main.go:158-163) without sorting.  bounds_ns = (lo, hi) with lo <= every sample <= hi on every
     rank skips the min/max pass."""
@@ -414,7 +546,8 @@ def select_kth(d_samples: int, n: int, divisor: int, ks: Sequence[int], ctx: Opt
         return [int(x) for x in out]
 
     ntot = n_global if n_global is not None else int(red.sum_u64(np.array([n], dtype=np.uint64))[0])
-    if ntot >= SAMPLED_SELECT_MIN and all(0 <= int(k) < ntot for k in ks) and 0 < len(ks) <= 2 * SELECT_MAX_K:
+    if (try_sampled and ntot >= SAMPLED_SELECT_MIN and all(0 <= int(k) < ntot for k in ks)
+            and 0 < len(ks) <= 2 * SELECT_MAX_K):
         r = _sampled_select_on_gpu(red, L, h, d, d_samples, n, ntot, divisor, ks, False)
         if r is not None:
             return r[0]
@@ -473,15 +606,23 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
         # several ranks: one sampled pass gives the ranks and the moments; the radix passes if it misses
         red = _Reducer(group, reduce_device)
         ctx_ = ctx or default_context()
-        size = int(red.sum_u64(np.array([n], dtype=np.uint64))[0])
-        if size >= SAMPLED_SELECT_MIN:
-            ks = [size // 5, size // 2, (9 * size) // 10, (99 * size) // 100]
-            r = _sampled_select_on_gpu(red, ctx_._L, ctx_._h, ctx_._dev(dev), d_samples_ns, n, size, divisor, ks, True)
-            if r is not None:
-                (p20, p50, p90, p99), st = r
-                whole = merge_distribution(red, np.zeros(0, dtype=np.uint64), st.count, st.min, st.max,
-                                           _signed(st.sum, st.sum_hi), (st.sumsq_hi << 64) | st.sumsq_lo, 0, 0)
-                return Percentiles(whole.avg_go_int, p20, p50, p90, p99, whole.min, whole.max)
+        # (whether the ranks together hold enough samples for this route comes out of its first collective: every
+        # rank takes the same decision)
+        r = _sampled_select_on_gpu(red, ctx_._L, ctx_._h, ctx_._dev(dev), d_samples_ns, n, None, divisor, None, "avg",
+                                   fractions=[(1, 5), (1, 2), (9, 10), (99, 100)],
+                                   extra_fn=lambda st: _moment_words([], st.count, st.min, st.max,
+                                                                     _signed(st.sum, st.sum_hi),
+                                                                     (st.sumsq_hi << 64) | st.sumsq_lo, 0, 0),
+                                   min_total=SAMPLED_SELECT_MIN)
+        if r is not None:  # ranks, and every rank's moments from the same two collectives
+            (p20, p50, p90, p99), _, rows = r
+            _, cnt, mn, mx, total, sumsq, _, _ = _merge_moment_words(rows, 0)
+            if cnt == 0:
+                raise ZeroDivisionError("percentiles of an empty sample set (Go panics at ssd_test/main.go:157)")
+            wrapped = total & _M64
+            whole = Distribution(cnt, mn, mx, total, wrapped - (1 << 64) if wrapped >= _SIGN else wrapped, sumsq,
+                                 np.zeros(0, dtype=np.uint64), 0, 0)
+            return Percentiles(whole.avg_go_int, p20, p50, p90, p99, whole.min, whole.max)
     dist_ = dist if dist is not None else hist_fixed(d_samples_ns, n, divisor, OC_DEFAULT_LATENCY_BOUNDS,
                                                      HIST_OPENCENSUS, ctx=ctx, dev=dev, group=group,
                                                      reduce_device=reduce_device)
@@ -493,8 +634,10 @@ def percentiles(d_samples_ns: int, n: int, divisor: int = NS_PER_US, ctx: Option
     lo = dist_.min * divisor if dist_.min > 0 else (dist_.min - 1) * divisor + 1
     hi = (dist_.max + 1) * divisor - 1 if dist_.max >= 0 else dist_.max * divisor
     lo, hi = max(lo, -(1 << 63)), min(hi, (1 << 63) - 1)
+    # (a sampled pass was tried above when the ranks hold enough samples: not again)
     p20, p50, p90, p99 = select_kth(d_samples_ns, n, divisor, ks, ctx=ctx, dev=dev, group=group,
-                                    reduce_device=reduce_device, n_global=size, bounds_ns=(lo, hi))
+                                    reduce_device=reduce_device, n_global=size, bounds_ns=(lo, hi),
+                                    try_sampled=dist is not None)
     return Percentiles(dist_.avg_go_int, p20, p50, p90, p99, dist_.min, dist_.max)
 
 

@@ -203,12 +203,16 @@ int b200_select_kth_avg(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t
  *   thresholds <= sample; the samples of ODD c (the brackets, when the thresholds are lo0, hi0+1, lo1, hi1+1, ...)
  *   are kept, in no particular order, in a library-owned device buffer *d_kept; *nkept is their number, of which
  *   only the first `cap` are stored.  stats (may be NULL): moments of trunc(sample/divisor) over all n samples.
+ * b200_bracket_pass_avg: the same without the sum of squares (stats->sumsq_* = 0), as b200_select_kth_avg.
  * Both buffers stay valid until the next b200_select_* / b200_bracket_pass call on the same device. */
 int b200_select_sample(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, size_t stride,
                        const int64_t** d_sample, size_t* nsample);
 int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                       const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
                       uint64_t* nkept, b200_lat_stats* stats);
+int b200_bracket_pass_avg(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
+                          const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
+                          uint64_t* nkept, b200_lat_stats* stats);
 /* The same when the caller already knows bounds lo_ns <= every sample <= hi_ns (for instance from the min/max
  * of a previous b200_hist_fixed): saves the min/max pass of the radix select.  The bounds must be true: a
  * sample outside them is either reported as B200_ERR_INVALID (radix select) or ranked like any other
@@ -225,6 +229,10 @@ int b200_select_kth_range(b200_ctx* ctx, int dev, const int64_t* d_samples, size
 int b200_minmax(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t* min, int64_t* max);
 int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, uint64_t key_base, int shift,
                      int top, int nk, const uint64_t* prefix, uint64_t* counts);
+/* b200_radix_count with a key base per histogram (key_bases[i] instead of one key_base; top < 64): the order
+ * statistics of a multi-rank sampled select are each resolved inside their own bracket, relative to its lower end. */
+int b200_radix_count_based(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, const uint64_t* key_bases,
+                           int shift, int top, int nk, const uint64_t* prefix, uint64_t* counts);
 
 /* One process driving several devices (the other multi-GPU form is one process per GPU with the counts
  * all-reduced over NCCL by the caller, latency.py): device devs[i] holds n[i] samples at d_samples[i]; the

@@ -30,10 +30,12 @@ def _np_count_fn(samples):
     keys = (samples.astype(np.int64).view(np.uint64) ^ np.uint64(SIGN))
 
     def count_fn(key_base, shift, top, prefixes):
-        k = (keys - np.uint64(key_base)).astype(np.uint64)
+        # key_base: one for all histograms (b200_radix_count) or a list, one each (b200_radix_count_based)
+        bases = key_base if isinstance(key_base, (list, tuple)) else [key_base] * len(prefixes)
         out = np.zeros((len(prefixes), lat.RADIX_BINS), dtype=np.uint64)
         width = top - shift
         for i, p in enumerate(prefixes):
+            k = (keys - np.uint64(bases[i])).astype(np.uint64)
             sel = k if top >= 64 else k[(k >> np.uint64(top)) == np.uint64(p)]
             dg = ((sel >> np.uint64(shift)) & np.uint64((1 << width) - 1)).astype(np.int64)
             out[i] = np.bincount(dg, minlength=lat.RADIX_BINS).astype(np.uint64)
@@ -131,6 +133,21 @@ def _worker(rank, world, port, q):
             assert r is not None, "the brackets should catch the ranks on spread-out data"
             srt = np.sort(ns_all // 1000)
             assert r[0] == [int(srt[k]) for k in ks], r[0]
+        # the same by fractions (the total comes out of the first collective), with words of the caller's riding
+        # along in the second: what latency.percentiles does across ranks — four collectives in all
+        ns = ns_all[:n // 3] if rank == 0 else ns_all[n // 3:]
+        before = lat._Reducer.tally["collectives"]
+        r = lat.sampled_select(red, ns.size, None, 1000, None, *_np_sampled_fns(ns, 1000, rank),
+                               fractions=[(1, 5), (1, 2), (9, 10), (99, 100)], extra_fn=lambda st: [rank + 1, ns.size],
+                               min_total=1 << 20)
+        used = lat._Reducer.tally["collectives"] - before
+        assert r is not None and used in (4, 5), (r is None, used)  # (a wide p99 bracket takes a third radix pass)
+        srt = np.sort(ns_all // 1000)
+        assert r[0] == [int(srt[n * a // b]) for a, b in ((1, 5), (1, 2), (9, 10), (99, 100))]
+        assert r[2] == [[1, n // 3], [2, n - n // 3]]
+        # too few samples for the route: every rank says so after the first collective
+        assert lat.sampled_select(red, ns.size, None, 1000, None, *_np_sampled_fns(ns, 1000, rank),
+                                  fractions=[(1, 2)], min_total=n + 1) is None
         # extreme ranks open the brackets at the ends; ranks whose data differ widen them: exact or a clean miss
         shifted = ns_all[:n // 2] if rank == 0 else ns_all[n // 2:] + 3_000_000
         both = np.concatenate([ns_all[:n // 2], ns_all[n // 2:] + 3_000_000])

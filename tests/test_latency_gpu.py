@@ -602,3 +602,28 @@ def test_select_kth_avg_is_select_kth_stats_without_the_squares(ctx):
         assert res[1][0] == [int(srt[int(k)]) // 1000 for k in karr]
         assert (res[1][1], res[1][2], res[1][4], res[1][5]) == (n, int(us.sum()), int(us.min()), int(us.max()))
         ctx.free_device(d)
+
+
+def test_radix_count_with_a_key_base_per_histogram(ctx):
+    """b200_radix_count_based against numpy: three histograms over the same samples, each with its own key base
+    (the lower end of its bracket), a common 20-bit key range; first pass (prefix 0) and a second pass."""
+    n = 300_007
+    ns = oracle.latency_ns(n, seed=5)
+    d = ctx.alloc_device(n * 8)
+    ctx.h2d(d, ns)
+    keys = ns.view(np.uint64) ^ np.uint64(1 << 63)
+    bases = [int(np.uint64(b) ^ np.uint64(1 << 63)) for b in (20_000_000, 47_000_000, 71_500_000)]
+    top = 20
+    for shift, prefixes in ((8, [0, 0, 0]), (0, [5, 300, 4095])):
+        barr, parr = np.array(bases, dtype=np.uint64), np.array(prefixes, dtype=np.uint64)
+        counts = np.zeros(3 * lat.RADIX_BINS, dtype=np.uint64)
+        t = top if shift else 8
+        pkg._lib.check(ctx._L.b200_radix_count_based(ctx._h, 0, d, n, barr.ctypes.data, shift, t, 3, parr.ctypes.data,
+                                                     counts.ctypes.data))
+        for i in range(3):
+            k = keys - np.uint64(bases[i])
+            sel = k[(k >> np.uint64(t)) == np.uint64(prefixes[i])]
+            dg = ((sel >> np.uint64(shift)) & np.uint64((1 << (t - shift)) - 1)).astype(np.int64)
+            want = np.bincount(dg, minlength=lat.RADIX_BINS).astype(np.uint64)
+            assert (counts[i * lat.RADIX_BINS:(i + 1) * lat.RADIX_BINS] == want).all(), (shift, i)
+    ctx.free_device(d)

@@ -94,7 +94,9 @@ func ComputePercentiles(readTime []int64) (Percentiles, error) {
 
 // ReadmeHistogram is numpy.histogram(x, range(20, 100, 5)) of README.md:21-23,32 over per-read durations in
 // nanoseconds, each taken as Duration.Milliseconds() first (main.go:146): 15 bins [20,25) ... [90,95], and the
-// number of samples outside [20, 95], which the script silently drops.
+// number of samples outside [20, 95], which the script silently drops.  Integer milliseconds: on fractional
+// Duration strings the script bins the fractions (95.3 ms is dropped there, counted in [90, 95] here); the C ABI's
+// b200_parse_latency_text + b200_hist_fixed_f64 reproduce that form.
 func ReadmeHistogram(durationsNs []int64) (counts [15]uint64, dropped uint64, err error) {
 	if len(durationsNs) == 0 {
 		return

@@ -248,13 +248,17 @@ def hist_fixed_pair(d_samples: int, n: int, divisor: int, edges_a, mode_a: int, 
 
 
 def hist_readme_and_opencensus(d_samples_ns: int, n: int, **kw):
-    """README.md:21-23,32 and metrics_exporter.go:28 on per-read milliseconds, from one pass."""
+    """README.md:21-23,32 and metrics_exporter.go:28 on per-read milliseconds, from one pass.  (Integer milliseconds,
+    as main.go:146 records them: see hist_readme.)"""
     return hist_fixed_pair(d_samples_ns, n, NS_PER_MS, README_EDGES, HIST_NUMPY, OC_DEFAULT_LATENCY_BOUNDS,
                            HIST_OPENCENSUS, **kw)
 
 
 def hist_readme(d_samples_ns: int, n: int, **kw) -> Distribution:
-    """README.md:21-23,32 on per-read milliseconds (main.go:146)."""
+    """README.md:21-23,32 on per-read milliseconds as main.go:146 records them: trunc(ns / 10^6), INTEGER
+    milliseconds.  That is the script's answer when its input lines are whole milliseconds; on the fractional
+    Duration strings of execute_pb.sh the script bins float(line) instead — a sample of 95.3 ms is dropped there and
+    lands in the closed last bin [90, 95] here — and that form is parse_latency_text + hist_fixed_f64."""
     return hist_fixed(d_samples_ns, n, NS_PER_MS, README_EDGES, HIST_NUMPY, **kw)
 
 

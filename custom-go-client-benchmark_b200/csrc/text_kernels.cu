@@ -49,11 +49,20 @@ __device__ __forceinline__ TextView stage_tile(const unsigned char* __restrict__
     if (send > n) send = n;
     const size_t len = send > sbase ? send - sbase : 0;
     if ((reinterpret_cast<uintptr_t>(t) & 15) == 0) {
-        const size_t nvec = len / 16;
+        // at most kTileBytes + kHalo + 16 bytes = 273 vectors for kTextThreads threads: one each and a few second
+        // ones, written out with 32-bit indices (as a generic size_t loop this copy was 14 % of the parse kernel)
+        const unsigned nvec = (unsigned)(len / 16);
         const uint4* src = reinterpret_cast<const uint4*>(t + sbase);
         uint4* dst = reinterpret_cast<uint4*>(sm);
-        for (size_t i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = __ldg(src + i);
-        for (size_t i = nvec * 16 + threadIdx.x; i < len; i += blockDim.x) sm[i] = __ldg(t + sbase + i);
+        static_assert((kTileBytes + kHalo + 16) / 16 <= 2 * kTextThreads, "two vectors per thread cover the staging");
+        const unsigned i0 = threadIdx.x, i1 = threadIdx.x + kTextThreads;
+        uint4 v0 = make_uint4(0, 0, 0, 0), v1 = v0;
+        if (i0 < nvec) v0 = __ldg(src + i0);
+        if (i1 < nvec) v1 = __ldg(src + i1);
+        if (i0 < nvec) dst[i0] = v0;
+        if (i1 < nvec) dst[i1] = v1;
+        const unsigned tail = nvec * 16 + threadIdx.x;  // the last, incomplete vector of the text (< 16 bytes)
+        if (tail < (unsigned)len) sm[tail] = __ldg(t + sbase + tail);
     } else {
         for (size_t i = threadIdx.x; i < len; i += blockDim.x) sm[i] = __ldg(t + sbase + i);
     }

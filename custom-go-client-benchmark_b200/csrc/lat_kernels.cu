@@ -366,6 +366,10 @@ __device__ __forceinline__ void split64(long long v, unsigned& lo, unsigned& hi)
 // of the lane's next slot (levels are 256 bytes apart); at: where the next parked sample goes = min(next, lim), lim
 // the level behind the last, so a fifth sample lands there and next > lim says that something was lost.
 __device__ __forceinline__ void park_lane_if_even(unsigned row, long long v, unsigned& next, unsigned& at, unsigned lim) {
+    check_abs(at, 8);
+#ifdef B200_DEBUG_ASSERT
+    assert(at <= lim && next >= at);
+#endif
     asm volatile(
         "{\n\t.reg .pred p;\n\t.reg .u32 t;\n\t"
         "and.b32 t, %2, 1;\n\t"
@@ -656,6 +660,10 @@ hist_kernel(const long long* __restrict__ x, size_t n, const HistParams* __restr
             const bool has = lane_next > level;
             const unsigned m = __ballot_sync(0xFFFFFFFFu, has);
             if (!m) break;
+            check_abs(level, 8);
+#ifdef B200_DEBUG_ASSERT
+            assert(cnt + __popc(m) <= (unsigned)kDenseCap);
+#endif
             if (has) dense[cnt + __popc(m & ((1u << lane) - 1))] = *reinterpret_cast<const long long*>(sm0 + level);
             cnt += __popc(m);
             __syncwarp();

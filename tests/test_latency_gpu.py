@@ -380,11 +380,17 @@ def test_multi_rank_sampled_select_building_blocks(ctx):
         ks = [m // 5, m // 2, 9 * m // 10, 99 * m // 100]
         r = lat._sampled_select_on_gpu(red, ctx._L, ctx._h, 0, d + 8 * start, m, m, div, ks, True)
         assert r is not None
-        vals, st = r
+        vals, st, _ = r
         v = part // div
         srt = np.sort(v)
         assert vals == [int(srt[k]) for k in ks]
         assert (st.count, st.min, st.max, st.sum) == (m, int(v.min()), int(v.max()), int(v.sum()))
+        # by fractions, the total left to the first collective, the moments riding along (latency.percentiles' form)
+        r = lat._sampled_select_on_gpu(red, ctx._L, ctx._h, 0, d + 8 * start, m, None, div, None, "avg",
+                                       fractions=[(1, 5), (1, 2), (9, 10), (99, 100)],
+                                       extra_fn=lambda s: [s.count, s.min, s.max, s.sum, s.sumsq_lo])
+        assert r is not None and r[0] == vals
+        assert r[2] == [[m, int(v.min()) & (2**64 - 1), int(v.max()), int(v.sum()) & (2**64 - 1), 0]]
     # the building blocks directly: strata and odd-bin bookkeeping
     import ctypes as C
     p, cnt = C.c_void_p(), C.c_size_t()

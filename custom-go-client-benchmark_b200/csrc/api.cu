@@ -714,6 +714,8 @@ struct b200_batch {
     unsigned long long* d_nbad = nullptr;
     HostPlan plan;
     uint32_t small_objects = 0;
+    uint64_t uniform_off0 = 0;  // equal blocks back to back (BatchArgs::uniform_*), found at creation
+    uint32_t uniform_len = 0, uniform_objs = 0;
     static constexpr int kRing = 256;  // per-run CUDA event triples: begin, row kernel end, all end
     cudaEvent_t ev[kRing][3] = {};
     uint64_t runs = 0, timed_from = 0;
@@ -758,6 +760,18 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     std::vector<uint32_t> seg_start(3 * (nobj + 1));
     fill_task_prefix(nobj, rows_of, b->plan.p, seg_start.data());
     b->small_objects = (nobj >= 1024 && b->plan.max_long <= 16) ? 1 : 0;
+    // equal blocks back to back (block-wise verification: pages, ssd_test's blocks)?  Then the fold kernel can take
+    // them a lane per object (launch_batch decides, once it knows the arena's alignment).
+    if (nobj >= 64 && len[0] >= 1024 && len[0] <= 32768 && len[0] % 512 == 0 && b->plan.nlong == 0 && b->plan.nshort == 0 &&
+        b->plan.npartial == nobj) {
+        bool uniform = true;
+        for (size_t i = 0; i < nobj && uniform; i++) uniform = len[i] == len[0] && off[i] == off[0] + i * len[0];
+        if (uniform) {
+            b->uniform_off0 = off[0];
+            b->uniform_len = (uint32_t)len[0];
+            b->uniform_objs = (uint32_t)(nobj / 32 * 32);
+        }
+    }
     int rc = 0;
     auto dev_alloc = [&](void** p, size_t bytes) -> int {
         if (rc) return rc;
@@ -813,6 +827,9 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     if (int rc = apply_plan(d, b->plan, &a)) return rc;
     a.nobj = (uint32_t)b->nobj;
     a.small_objects = b->small_objects;
+    a.uniform_off0 = b->uniform_off0;
+    a.uniform_len = b->uniform_len;
+    a.uniform_objs = b->uniform_objs;
     a.init_crc = 0;
     cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];
     CU(launch_batch(a, d->tabs, d->grid, d->stream, ev[0], ev[1], &d->side));

@@ -97,7 +97,13 @@ __global__ void __launch_bounds__(WARPS * 32, 1)
 crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
                 TaskTable tt, SegPlan plan, uint32_t kind,
                 uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv4_tab,
-                const uint32_t* __restrict__ xsq, uint32_t* __restrict__ seg_raw) {
+                const uint32_t* __restrict__ xsq, uint32_t* __restrict__ seg_raw, uint32_t block_rows,
+                uint32_t block_tasks, uint32_t block_raw_base) {
+    // block_rows != 0: a lane per OBJECT.  The batch is equal blocks of block_rows * 16 bytes back to back from
+    // base + single_off; a task is 32 consecutive blocks, lane l folds block 32 * task + l exactly as it folds its
+    // share of a segment, and its raw register goes to seg_raw[block_raw_base + 32 * task + l] unweighted (what the
+    // row kernel would have written for that object's only segment).  A million 4 KiB blocks then cost 256 table
+    // look-ups per object instead of the row kernel's 4096.
     constexpr int kThreads = WARPS * 32;
     constexpr int kWarpStageBytes = 32 * LANE_BYTES;
     constexpr int kLanesPerRow = LANE_BYTES / 16;      // copy role: this many lanes move one row's stage
@@ -109,7 +115,7 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     for (uint32_t i = threadIdx.x; i < 1024; i += kThreads) tab[i] = __ldg(adv4_tab + i);
     __syncthreads();
 
-    const uint32_t rows_per_seg = kind == kSegLong ? plan.a : plan.b;  // this launch folds segments of this length
+    const uint32_t rows_per_seg = block_rows ? block_rows : kind == kSegLong ? plan.a : plan.b;  // this launch's length
     const uint32_t lane_bytes = rows_per_seg * 16;   // S: bytes of the segment owned by one lane
     const uint32_t nstage = lane_bytes / LANE_BYTES;  // exact: fold_enabled() admits only lengths with S % LANE_BYTES == 0
     // weight of this lane's register: the (31 - lane) lanes after it still have S bytes each to pass
@@ -121,21 +127,26 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     const uint32_t nwarps = gridDim.x * WARPS;
     // this launch's tasks: the segments of kind `kind`, numbered 0..ntasks-1 over the whole batch, dealt round
     // robin so every warp gets the same number (+-1)
-    const uint32_t ntasks = tt.count[kind], raw_base = tt.base(kind);
-    const uint32_t* __restrict__ seg_start = off ? tt.prefix(kind) : nullptr;
+    const uint32_t ntasks = block_rows ? block_tasks : tt.count[kind], raw_base = block_rows ? 0 : tt.base(kind);
+    const uint32_t* __restrict__ seg_start = off && !block_rows ? tt.prefix(kind) : nullptr;
 
     for (uint32_t task = warp * gridDim.x + blockIdx.x; task < ntasks; task += nwarps) {
-        uint32_t seg = task;
-        uint64_t o = single_off, n = single_len;
-        if (off) {
-            const uint32_t obj = find_object2(seg_start, tt.nobj, task);
-            seg = task - __ldg(seg_start + obj);
-            o = __ldg(off + obj);
-            n = __ldg(len + obj);
+        const uint8_t* src;  // lane l's stream starts at src + l*S
+        if (block_rows) {
+            src = base + single_off + (size_t)task * 32 * lane_bytes;
+        } else {
+            uint32_t seg = task;
+            uint64_t o = single_off, n = single_len;
+            if (seg_start) {
+                const uint32_t obj = find_object2(seg_start, tt.nobj, task);
+                seg = task - __ldg(seg_start + obj);
+                o = __ldg(off + obj);
+                n = __ldg(len + obj);
+            }
+            const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
+            const Seg sg = seg_of(cut.rows, plan, kind, seg);
+            src = base + o + cut.head + sg.row0 * kRowBytes;
         }
-        const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
-        const Seg sg = seg_of(cut.rows, plan, kind, seg);
-        const uint8_t* src = base + o + cut.head + sg.row0 * kRowBytes;  // lane l's stream starts at src + l*S
         const uint8_t* csrc = src + (size_t)crow * lane_bytes + cchunk * 16;
 
         uint32_t r[64];
@@ -203,6 +214,10 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
             const uint32_t x = reg ^ r[k];
             reg = tab[x & 0xFF] ^ tab[256 + ((x >> 8) & 0xFF)] ^ tab[512 + ((x >> 16) & 0xFF)] ^ tab[768 + (x >> 24)];
         }
+        if (block_rows) {
+            seg_raw[block_raw_base + 32 * task + lane] = reg;
+            continue;
+        }
         uint32_t s = gf2_mul(lane_k, reg);
 #pragma unroll
         for (int d = 16; d; d >>= 1) s ^= __shfl_xor_sync(0xFFFFFFFFu, s, d);
@@ -213,7 +228,7 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
 struct FoldVariant {
     int warps, stages, lane_bytes;
     void (*kernel)(const uint8_t*, const uint64_t*, const uint64_t*, TaskTable, SegPlan, uint32_t, uint64_t, uint64_t,
-                   const uint32_t*, const uint32_t*, uint32_t*);
+                   const uint32_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t, uint32_t);
     size_t smem() const { return kFoldSmemTab + (size_t)warps * stages * 32 * lane_bytes; }
 };
 // Measured on B200 (4096 x 2 MiB, 300 back-to-back steps, GB/s): <8,2,256> 6878 | <7,2,256> 6796 | <4,3,512> 6780 |
@@ -241,8 +256,7 @@ const FoldVariant& fold_variant() {
 size_t fold_kernel_smem() { return fold_variant().smem(); }
 uint32_t fold_lane_bytes() { return (uint32_t)fold_variant().lane_bytes; }
 
-cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind) {
-    const FoldVariant& fv = fold_variant();
+static cudaError_t fold_attr(const FoldVariant& fv) {
     static thread_local int attr_dev = -1;
     int dev = 0;
     cudaGetDevice(&dev);
@@ -251,12 +265,41 @@ cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cud
         if (e != cudaSuccess) return e;
         attr_dev = dev;
     }
+    return cudaSuccess;
+}
+
+cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind) {
+    const FoldVariant& fv = fold_variant();
+    if (cudaError_t e = fold_attr(fv)) return e;
     const TaskTable tt{a.seg_start, a.nobj, {a.nfull_tasks, a.nshort_tasks, a.npartial_tasks}};
     if (!tt.count[kind]) return cudaSuccess;
     uint32_t need = (tt.count[kind] + fv.warps - 1) / fv.warps;
     int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
     fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, a.off, a.len, tt, SegPlan{a.rows_per_seg, a.rows_per_seg2},
-                                                       kind, a.single_off, a.single_len, t.adv4, t.xpow8_sq, a.seg_raw);
+                                                       kind, a.single_off, a.single_len, t.adv4, t.xpow8_sq, a.seg_raw,
+                                                       0, 0, 0);
+    return cudaGetLastError();
+}
+
+bool fold_lane_block_ok(uint32_t block_bytes) {
+    // whole 512-byte rows (no tail for a finalize kernel to pick up), whole stages per lane, and long enough that the
+    // 256 look-ups of the final reduction are a minor part (1 KiB: a quarter of the row kernel's look-ups)
+    return fold_enabled(kFoldMinRows) && block_bytes >= 1024 && block_bytes <= 32768 && block_bytes % 512 == 0 &&
+           block_bytes % fold_lane_bytes() == 0;
+}
+
+cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs,
+                                 uint32_t raw_base) {
+    const FoldVariant& fv = fold_variant();
+    if (cudaError_t e = fold_attr(fv)) return e;
+    const uint32_t tasks = nobjs / 32;
+    if (!tasks) return cudaSuccess;
+    const TaskTable tt{a.seg_start, a.nobj, {a.nfull_tasks, a.nshort_tasks, a.npartial_tasks}};
+    uint32_t need = (tasks + fv.warps - 1) / fv.warps;
+    int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
+    fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, nullptr, nullptr, tt, SegPlan{a.rows_per_seg, a.rows_per_seg2},
+                                                       kSegPartial, a.uniform_off0, (uint64_t)nobjs * a.uniform_len, t.adv4,
+                                                       t.xpow8_sq, a.seg_raw, a.uniform_len / 16, tasks, raw_base);
     return cudaGetLastError();
 }
 

@@ -98,8 +98,10 @@ __global__ void __launch_bounds__(kRowsThreads, 1)
 crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
                 TaskTable tt, SegPlan plan,
                 uint64_t single_off, uint64_t single_len, uint32_t skip_kinds, const uint32_t* __restrict__ adv_tab,
-                const uint32_t* __restrict__ col_k, const uint32_t* __restrict__ adv4_tab, uint32_t* __restrict__ seg_raw) {
-    // skip_kinds: bit k set = segments of SegKind k are the fold kernel's, not ours
+                const uint32_t* __restrict__ col_k, const uint32_t* __restrict__ adv4_tab, uint32_t* __restrict__ seg_raw,
+                uint32_t partial_first) {
+    // skip_kinds: bit k set = segments of SegKind k are the fold kernel's, not ours; partial_first: so are the
+    // partial segments below this task number (equal blocks hashed a lane per object)
     // replicate the compact 4x256 table once per bank, at absolute shared address kTabAbs
     {
         uint32_t i = threadIdx.x;  // kRowsThreads == 4*256
@@ -128,12 +130,13 @@ crc_rows_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     const uint32_t gw = warp * gridDim.x + blockIdx.x;
     for (uint32_t kind = 0; kind < 3; kind++) {
     if ((skip_kinds >> kind) & 1) continue;  // these segments belong to the fold kernel
-    const uint32_t ntasks = tt.count[kind];
+    const uint32_t first = kind == kSegPartial ? partial_first : 0u;
+    const uint32_t ntasks = tt.count[kind] > first ? tt.count[kind] - first : 0u;  // ours: [first, count)
     const uint32_t* __restrict__ seg_start = off ? tt.prefix(kind) : nullptr;
     const uint32_t raw_base = tt.base(kind);
-    const uint32_t task_lo = (uint32_t)((uint64_t)ntasks * gw / nwarps);
-    const uint32_t task_hi = (uint32_t)((uint64_t)ntasks * (gw + 1) / nwarps);
-    uint32_t obj = 0, obj_first = 0, obj_next = ntasks;  // tasks [obj_first, obj_next) belong to obj
+    const uint32_t task_lo = first + (uint32_t)((uint64_t)ntasks * gw / nwarps);
+    const uint32_t task_hi = first + (uint32_t)((uint64_t)ntasks * (gw + 1) / nwarps);
+    uint32_t obj = 0, obj_first = 0, obj_next = first + ntasks;  // tasks [obj_first, obj_next) belong to obj
     if (off && task_lo < task_hi) {
         obj = find_object(seg_start, tt.nobj, task_lo);
         obj_first = __ldg(seg_start + obj);
@@ -414,7 +417,13 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     const bool fold_long = !a.no_fold && fold_enabled(plan.a) && a.nfull_tasks > 0;
     const bool fold_short = !a.no_fold && plan.b && fold_enabled(plan.b) && a.nshort_tasks > 0;
     const uint32_t skip_kinds = (fold_long ? 1u << kSegLong : 0u) | (fold_short ? 1u << kSegShort : 0u);
-    const bool rows = a.ntasks && (a.npartial_tasks > 0 || (!fold_long && a.nfull_tasks > 0) ||
+    // equal blocks back to back, one partial segment each: a lane per object on the fold kernel for every whole
+    // group of 32 (the row kernel pays a table look-up per byte and ~450 instructions of set-up and epilogue per object)
+    uint32_t lane_objs = 0;
+    if (!a.no_fold && a.off && a.uniform_objs && a.nfull_tasks == 0 && a.nshort_tasks == 0 && a.npartial_tasks == a.nobj &&
+        fold_lane_block_ok(a.uniform_len) && ((uintptr_t)(a.base + a.uniform_off0) & 15) == 0)
+        lane_objs = a.uniform_objs;
+    const bool rows = a.ntasks && (a.npartial_tasks > lane_objs || (!fold_long && a.nfull_tasks > 0) ||
                                    (!fold_short && a.nshort_tasks > 0));
     // The long segments run on `stream`; the short ones and the row kernel run next to them on the side stream
     // (when there is one), so that their CTAs fill the SMs the long fold kernel's tail leaves idle.
@@ -434,14 +443,21 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
         e = launch_fold(a, t, grid, second, kSegShort);
         if (e != cudaSuccess) return e;
     }
+    if (lane_objs) {
+        e = launch_fold_per_lane(a, t, grid, second, lane_objs, tt.base(kSegPartial));
+        if (e != cudaSuccess) return e;
+    }
     if (rows) {
         uint32_t mine = 0;  // tasks of the kinds the row kernel takes
-        for (uint32_t k = 0; k < 3; k++)
-            if (!((skip_kinds >> k) & 1)) mine = mine > tt.count[k] ? mine : tt.count[k];
+        for (uint32_t k = 0; k < 3; k++) {
+            const uint32_t cnt = k == kSegPartial ? tt.count[k] - lane_objs : tt.count[k];
+            if (!((skip_kinds >> k) & 1)) mine = mine > cnt ? mine : cnt;
+        }
         uint32_t need = (mine + kRowsWarps - 1) / kRowsWarps;
         int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
         crc_rows_kernel<<<g ? g : 1, kRowsThreads, rows_kernel_smem(), second>>>(
-            a.base, a.off, a.len, tt, plan, a.single_off, a.single_len, skip_kinds, t.adv_row, t.col_k, t.adv4, a.seg_raw);
+            a.base, a.off, a.len, tt, plan, a.single_off, a.single_len, skip_kinds, t.adv_row, t.col_k, t.adv4, a.seg_raw,
+            lane_objs);
     }
     if (forked) {  // join
         e = cudaEventRecord(side->join, second);

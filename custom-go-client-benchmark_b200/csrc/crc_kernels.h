@@ -117,6 +117,12 @@ struct BatchArgs {
     // every object has at most a few full segments and there are many objects: finalize one object per THREAD
     uint32_t small_objects;
     uint32_t no_fold;           // keep every segment on the row kernel (the caller has no tables for the fold kernel)
+    // Equal blocks back to back (object i = base[uniform_off0 + i * uniform_len ..), uniform_len a multiple of 512
+    // between 1 and 32 KiB, every object one partial segment): the first uniform_objs objects (a multiple of 32) may
+    // be hashed by the fold kernel with ONE LANE PER OBJECT when base + uniform_off0 is 16-byte aligned; 0 = not so.
+    uint64_t uniform_off0;
+    uint32_t uniform_len;
+    uint32_t uniform_objs;
 };
 
 // true when launch_batch will give full segments of this length to the fold kernel
@@ -138,6 +144,11 @@ size_t fold_kernel_smem();
 uint32_t fold_lane_bytes();  // bytes a lane consumes per stage in the variant in use; a lane's share of a segment must be a multiple
 // kind: kSegLong or kSegShort — which of the two full-segment lengths this launch folds
 cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind);
+// The fold kernel with a lane per object: objects [0, nobjs) of a.uniform_* (nobjs a multiple of 32), raw registers to
+// a.seg_raw[raw_base + object].  True when block_bytes suits it (fold_lane_block_ok).
+bool fold_lane_block_ok(uint32_t block_bytes);
+cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs,
+                                 uint32_t raw_base);
 
 cudaError_t launch_fill_payload(uint64_t* dst, uint64_t first_word, size_t nwords, uint64_t seed, cudaStream_t s);
 cudaError_t launch_fill_latency(int64_t* dst, uint64_t first, size_t n, uint64_t seed, cudaStream_t s);

@@ -154,6 +154,23 @@ def test_batch_many_tiny_objects(ctx, arena):
     _batch_check(ctx, host, d, off, ln)
 
 
+@pytest.mark.parametrize("block,nobj,off0", [(4096, 4096, 0), (1024, 1000, 16), (512 * 3, 333, 4096 + 48),
+                                             (32768, 100, 32), (4096, 63, 0), (4096, 70, 8), (2048, 4097, 1 << 20)])
+def test_batch_of_equal_blocks_back_to_back(ctx, arena, block, nobj, off0):
+    """Equal blocks back to back (pages, ssd_test's blocks): whole groups of 32 go to the fold kernel a lane per
+    object, the rest and every case it does not take (fewer than 64 objects, an arena offset that is not 16-byte
+    aligned) to the row kernel; a corrupt block in either part is the one that is flagged."""
+    host, d = arena
+    off = np.uint64(off0) + np.arange(nobj, dtype=np.uint64) * np.uint64(block)
+    ln = np.full(nobj, block, dtype=np.uint64)
+    want = _batch_check(ctx, host, d, off, ln)
+    for bad_at in (5, nobj - 1):
+        w = want.copy()
+        w[bad_at] ^= 0x80
+        got, ok, nbad = crc32c.VerifyObjectsDevice(d, off, ln, w, ctx=ctx)
+        assert nbad == 1 and not ok[bad_at] and ok.sum() == nobj - 1 and (got == want).all()
+
+
 def test_batch_empty(ctx, arena):
     host, d = arena
     got, ok, nbad = crc32c.VerifyObjectsDevice(d, np.zeros(0, np.uint64), np.zeros(0, np.uint64), None, ctx=ctx)

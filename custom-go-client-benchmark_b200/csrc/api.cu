@@ -892,8 +892,12 @@ int b200_batch_launches(const b200_batch* b, int* launches_per_run) {
     const HostPlan& h = b->plan;  // mirrors launch_batch
     const bool fold_long = fold_enabled(h.p.a) && h.nlong > 0;
     const bool fold_short = h.p.b && fold_enabled(h.p.b) && h.nshort > 0;
-    const bool rows = h.ntasks && (h.npartial > 0 || (!fold_long && h.nlong > 0) || (!fold_short && h.nshort > 0));
-    *launches_per_run = (fold_long ? 1 : 0) + (fold_short ? 1 : 0) + (rows ? 1 : 0) + (b->nobj ? 1 : 0);
+    // equal blocks on the fold kernel, a lane per object, finished there (taken when the arena is 16-byte aligned
+    // at run time, which the count assumes)
+    const uint64_t lane_objs = b->small_objects && b->uniform_objs && fold_lane_block_ok(b->uniform_len) ? b->uniform_objs : 0;
+    const bool rows = h.ntasks && (h.npartial > lane_objs || (!fold_long && h.nlong > 0) || (!fold_short && h.nshort > 0));
+    const bool finalize = b->nobj > lane_objs;
+    *launches_per_run = (fold_long ? 1 : 0) + (fold_short ? 1 : 0) + (lane_objs ? 1 : 0) + (rows ? 1 : 0) + (finalize ? 1 : 0);
     return 0;
 }
 

@@ -35,6 +35,15 @@ namespace b200 {
 
 namespace {
 
+// lane-per-object mode: where a lane leaves its object's checksum and verdict
+struct BlockOut {
+    const uint32_t* want;
+    uint32_t* got;
+    uint8_t* ok;
+    unsigned long long* nbad;
+    uint32_t init_crc;
+};
+
 constexpr int kFoldSmemTab = 4 * 256 * 4;  // A^4 slicing tables for the final reduction (not replicated)
 
 extern __shared__ __align__(1024) uint8_t fold_smem[];
@@ -98,12 +107,13 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
                 TaskTable tt, SegPlan plan, uint32_t kind,
                 uint64_t single_off, uint64_t single_len, const uint32_t* __restrict__ adv4_tab,
                 const uint32_t* __restrict__ xsq, uint32_t* __restrict__ seg_raw, uint32_t block_rows,
-                uint32_t block_tasks, uint32_t block_raw_base) {
+                uint32_t block_tasks, BlockOut bo) {
     // block_rows != 0: a lane per OBJECT.  The batch is equal blocks of block_rows * 16 bytes back to back from
     // base + single_off; a task is 32 consecutive blocks, lane l folds block 32 * task + l exactly as it folds its
-    // share of a segment, and its raw register goes to seg_raw[block_raw_base + 32 * task + l] unweighted (what the
-    // row kernel would have written for that object's only segment).  A million 4 KiB blocks then cost 256 table
-    // look-ups per object instead of the row kernel's 4096.
+    // share of a segment; its raw register, unweighted, is what the row kernel would have written for that object's
+    // only segment, and since the object is nothing but that segment the lane finishes it on the spot (BlockOut):
+    // crc = ~(x^(8 len) * ~init ^ raw), compared with want[], no seg_raw round trip and no finalize launch.  A
+    // million 4 KiB blocks then cost 256 table look-ups per object instead of the row kernel's 4096.
     constexpr int kThreads = WARPS * 32;
     constexpr int kWarpStageBytes = 32 * LANE_BYTES;
     constexpr int kLanesPerRow = LANE_BYTES / 16;      // copy role: this many lanes move one row's stage
@@ -120,6 +130,8 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
     const uint32_t nstage = lane_bytes / LANE_BYTES;  // exact: fold_enabled() admits only lengths with S % LANE_BYTES == 0
     // weight of this lane's register: the (31 - lane) lanes after it still have S bytes each to pass
     const uint32_t lane_k = gf2_xpow8((uint64_t)lane_bytes * (31 - lane), xsq);
+    // lane-per-object mode: the initial register carried over the block, the same for every block
+    const uint32_t block_init = block_rows ? gf2_mul(gf2_xpow8((uint64_t)lane_bytes, xsq), ~bo.init_crc) : 0u;
     const uint32_t warp_stage = smem_u32(stage_base + (size_t)warp * STAGES * kWarpStageBytes);
     const uint32_t my_row = warp_stage + lane * LANE_BYTES;  // this lane's row inside a stage
     const uint32_t sw = (lane & 7) << 4;                     // its swizzle (chunk j lives at chunk j ^ (row & 7))
@@ -215,7 +227,11 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
             reg = tab[x & 0xFF] ^ tab[256 + ((x >> 8) & 0xFF)] ^ tab[512 + ((x >> 16) & 0xFF)] ^ tab[768 + (x >> 24)];
         }
         if (block_rows) {
-            seg_raw[block_raw_base + 32 * task + lane] = reg;
+            const uint32_t obj = 32 * task + lane, crc = ~(block_init ^ reg);
+            bo.got[obj] = crc;
+            const bool good = bo.want ? crc == __ldg(bo.want + obj) : true;
+            bo.ok[obj] = good ? 1 : 0;
+            if (!good) atomicAdd(bo.nbad, 1ull);
             continue;
         }
         uint32_t s = gf2_mul(lane_k, reg);
@@ -228,7 +244,7 @@ crc_fold_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ o
 struct FoldVariant {
     int warps, stages, lane_bytes;
     void (*kernel)(const uint8_t*, const uint64_t*, const uint64_t*, TaskTable, SegPlan, uint32_t, uint64_t, uint64_t,
-                   const uint32_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t, uint32_t);
+                   const uint32_t*, const uint32_t*, uint32_t*, uint32_t, uint32_t, BlockOut);
     size_t smem() const { return kFoldSmemTab + (size_t)warps * stages * 32 * lane_bytes; }
 };
 // Measured on B200 (4096 x 2 MiB, 300 back-to-back steps, GB/s): <8,2,256> 6878 | <7,2,256> 6796 | <4,3,512> 6780 |
@@ -277,7 +293,7 @@ cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cud
     int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
     fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, a.off, a.len, tt, SegPlan{a.rows_per_seg, a.rows_per_seg2},
                                                        kind, a.single_off, a.single_len, t.adv4, t.xpow8_sq, a.seg_raw,
-                                                       0, 0, 0);
+                                                       0, 0, BlockOut{});
     return cudaGetLastError();
 }
 
@@ -288,8 +304,7 @@ bool fold_lane_block_ok(uint32_t block_bytes) {
            block_bytes % fold_lane_bytes() == 0;
 }
 
-cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs,
-                                 uint32_t raw_base) {
+cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs) {
     const FoldVariant& fv = fold_variant();
     if (cudaError_t e = fold_attr(fv)) return e;
     const uint32_t tasks = nobjs / 32;
@@ -299,7 +314,8 @@ cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int 
     int g = (int)(need < (uint32_t)grid ? need : (uint32_t)grid);
     fv.kernel<<<g, fv.warps * 32, fv.smem(), stream>>>(a.base, nullptr, nullptr, tt, SegPlan{a.rows_per_seg, a.rows_per_seg2},
                                                        kSegPartial, a.uniform_off0, (uint64_t)nobjs * a.uniform_len, t.adv4,
-                                                       t.xpow8_sq, a.seg_raw, a.uniform_len / 16, tasks, raw_base);
+                                                       t.xpow8_sq, a.seg_raw, a.uniform_len / 16, tasks,
+                                                       BlockOut{a.want, a.got, a.ok, a.nbad, a.init_crc});
     return cudaGetLastError();
 }
 

@@ -285,13 +285,14 @@ crc_finalize_small_kernel(const uint8_t* __restrict__ base, const uint64_t* __re
                           const uint32_t* __restrict__ adv_seg, const uint32_t* __restrict__ adv_seg2,
                           const uint32_t* __restrict__ xsq, const uint32_t* __restrict__ byte_tab,
                           const uint32_t* __restrict__ adv4_tab, SegPlan plan, uint32_t init_crc, uint32_t nobj,
-                          uint32_t* __restrict__ got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
+                          uint32_t* __restrict__ got, uint8_t* __restrict__ ok, unsigned long long* nbad,
+                          uint32_t first_obj) {  // objects below first_obj were finished by the kernel that hashed them
     __shared__ uint32_t bt[256];
     __shared__ uint32_t w4[1024];  // x^32 slicing tables: a whole tail word per step instead of four byte steps
     for (int i = threadIdx.x; i < 256; i += kFinalThreads) bt[i] = __ldg(byte_tab + i);
     for (int i = threadIdx.x; i < 1024; i += kFinalThreads) w4[i] = __ldg(adv4_tab + i);
     __syncthreads();
-    const uint32_t obj = blockIdx.x * kFinalThreads + threadIdx.x;
+    const uint32_t obj = first_obj + blockIdx.x * kFinalThreads + threadIdx.x;
     if (obj >= nobj) return;
     const uint64_t o = off[obj], n = len[obj];
     const ObjectCut cut = cut_object((uint64_t)(uintptr_t)base + o, n);
@@ -420,7 +421,8 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     // equal blocks back to back, one partial segment each: a lane per object on the fold kernel for every whole
     // group of 32 (the row kernel pays a table look-up per byte and ~450 instructions of set-up and epilogue per object)
     uint32_t lane_objs = 0;
-    if (!a.no_fold && a.off && a.uniform_objs && a.nfull_tasks == 0 && a.nshort_tasks == 0 && a.npartial_tasks == a.nobj &&
+    if (!a.no_fold && a.off && a.small_objects && a.uniform_objs && a.nfull_tasks == 0 && a.nshort_tasks == 0 &&
+        a.npartial_tasks == a.nobj &&
         fold_lane_block_ok(a.uniform_len) && ((uintptr_t)(a.base + a.uniform_off0) & 15) == 0)
         lane_objs = a.uniform_objs;
     const bool rows = a.ntasks && (a.npartial_tasks > lane_objs || (!fold_long && a.nfull_tasks > 0) ||
@@ -444,7 +446,7 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
         if (e != cudaSuccess) return e;
     }
     if (lane_objs) {
-        e = launch_fold_per_lane(a, t, grid, second, lane_objs, tt.base(kSegPartial));
+        e = launch_fold_per_lane(a, t, grid, second, lane_objs);
         if (e != cudaSuccess) return e;
     }
     if (rows) {
@@ -465,11 +467,12 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
         if (e != cudaSuccess) return e;
     }
     if (ev_end) cudaEventRecord(ev_end, stream);
-    if (a.nobj && a.off && a.small_objects)
-        crc_finalize_small_kernel<<<(a.nobj + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, stream>>>(
-            a.base, a.off, a.len, tt, a.want, a.seg_raw, a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, t.adv4, plan,
-            a.init_crc, a.nobj, a.got, a.ok, a.nbad);
-    else if (a.nobj)
+    if (a.nobj && a.off && a.small_objects) {
+        if (a.nobj > lane_objs)
+            crc_finalize_small_kernel<<<(a.nobj - lane_objs + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, stream>>>(
+                a.base, a.off, a.len, tt, a.want, a.seg_raw, a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, t.adv4, plan,
+                a.init_crc, a.nobj, a.got, a.ok, a.nbad, lane_objs);
+    } else if (a.nobj)
         crc_finalize_kernel<<<a.nobj, kFinalThreads, 0, stream>>>(a.base, a.off, a.len, tt, a.want, a.seg_raw,
                                                                   a.adv_seg, a.adv_seg2, t.xpow8_sq, t.byte_tab, plan,
                                                                   a.init_crc, a.init_ptr, a.single_off, a.single_len, a.got,

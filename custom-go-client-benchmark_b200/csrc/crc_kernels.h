@@ -144,11 +144,10 @@ size_t fold_kernel_smem();
 uint32_t fold_lane_bytes();  // bytes a lane consumes per stage in the variant in use; a lane's share of a segment must be a multiple
 // kind: kSegLong or kSegShort — which of the two full-segment lengths this launch folds
 cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind);
-// The fold kernel with a lane per object: objects [0, nobjs) of a.uniform_* (nobjs a multiple of 32), raw registers to
-// a.seg_raw[raw_base + object].  True when block_bytes suits it (fold_lane_block_ok).
+// The fold kernel with a lane per object: objects [0, nobjs) of a.uniform_* (nobjs a multiple of 32), finished on the
+// spot (a.got / a.ok / a.nbad against a.want).  fold_lane_block_ok: block_bytes suits it.
 bool fold_lane_block_ok(uint32_t block_bytes);
-cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs,
-                                 uint32_t raw_base);
+cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs);
 
 cudaError_t launch_fill_payload(uint64_t* dst, uint64_t first_word, size_t nwords, uint64_t seed, cudaStream_t s);
 cudaError_t launch_fill_latency(int64_t* dst, uint64_t first, size_t n, uint64_t seed, cudaStream_t s);

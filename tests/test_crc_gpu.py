@@ -154,12 +154,14 @@ def test_batch_many_tiny_objects(ctx, arena):
     _batch_check(ctx, host, d, off, ln)
 
 
-@pytest.mark.parametrize("block,nobj,off0", [(4096, 4096, 0), (1024, 1000, 16), (512 * 3, 333, 4096 + 48),
-                                             (32768, 100, 32), (4096, 63, 0), (4096, 70, 8), (2048, 4097, 1 << 20)])
+@pytest.mark.parametrize("block,nobj,off0", [(4096, 4096, 0), (1024, 2000, 16), (512 * 3, 1333, 4096 + 48),
+                                             (32768, 1100, 32), (4096, 63, 0), (4096, 1030, 8), (2048, 4097, 1 << 20),
+                                             (4096, 1000, 0), (512, 3000, 0)])
 def test_batch_of_equal_blocks_back_to_back(ctx, arena, block, nobj, off0):
     """Equal blocks back to back (pages, ssd_test's blocks): whole groups of 32 go to the fold kernel a lane per
-    object, the rest and every case it does not take (fewer than 64 objects, an arena offset that is not 16-byte
-    aligned) to the row kernel; a corrupt block in either part is the one that is flagged."""
+    object and are finished there, the rest and every case it does not take (fewer than 1024 objects, blocks under
+    1 KiB, an arena offset that is not 16-byte aligned) go to the row kernel; a corrupt block in either part is the one
+    that is flagged."""
     host, d = arena
     off = np.uint64(off0) + np.arange(nobj, dtype=np.uint64) * np.uint64(block)
     ln = np.full(nobj, block, dtype=np.uint64)

@@ -18,6 +18,9 @@ rng = np.random.default_rng(0)
 n = 1 << 20
 b = crc32c.DeviceBatch(np.arange(n, dtype=np.uint64) * 4096, np.full(n, 4096, dtype=np.uint64), None, ctx)
 b.run(d); b.run(d); b.close()
+# the same blocks 8 bytes off a 16-byte boundary: the row kernel's shape (the aligned ones above go to the fold kernel)
+b = crc32c.DeviceBatch(np.arange(n - 1, dtype=np.uint64) * 4096 + 8, np.full(n - 1, 4096, dtype=np.uint64), None, ctx)
+b.run(d); b.run(d); b.close()
 # ragged
 ln = rng.integers(1, 4 << 20, size=2048).astype(np.uint64)
 off = np.concatenate([[0], np.cumsum(ln[:-1] + rng.integers(0, 64, size=2047).astype(np.uint64))]).astype(np.uint64)

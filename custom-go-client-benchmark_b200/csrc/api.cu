@@ -433,6 +433,8 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
     host_build_col_k(col_k);
     host_build_xpow8_sq(xsq);
     host_build_byte_tab(byte_tab);
+    std::vector<uint32_t> xpow128(kXpow128Entries);
+    host_build_xpow128(xpow128.data());
     for (int i = 0; i < ndev; i++) {
         int dev = devs ? devs[i] : i;
         if (dev < 0 || dev >= have) {
@@ -472,6 +474,7 @@ int b200_init(int ndev, const int* devs, b200_ctx** out) {
         if (!rc) rc = upload(&d->tabs.xpow8_sq, xsq, 64);
         if (!rc) rc = upload(&d->tabs.byte_tab, byte_tab, 256);
         if (!rc) rc = upload(&d->tabs.adv4, adv4, 1024);
+        if (!rc) rc = upload(&d->tabs.xpow128, xpow128.data(), xpow128.size());
         if (!rc) {
             const cudaError_t e = lat_scratch_init(&d->lat);
             if (e == cudaErrorInvalidConfiguration)
@@ -500,6 +503,7 @@ int b200_shutdown(b200_ctx* ctx) {
         cudaFree(d->tabs.xpow8_sq);
         cudaFree(d->tabs.byte_tab);
         cudaFree(d->tabs.adv4);
+        cudaFree(d->tabs.xpow128);
         cudaFree(d->seg_raw);
         cudaFree(d->d_got);
         cudaFree(d->d_ok);
@@ -716,6 +720,8 @@ struct b200_batch {
     uint32_t small_objects = 0;
     uint64_t uniform_off0 = 0;  // equal blocks back to back (BatchArgs::uniform_*), found at creation
     uint32_t uniform_len = 0, uniform_objs = 0;
+    uint32_t lane_objects = 0;  // many small objects, none above 32 KiB (BatchArgs::lane_objects)
+    uint32_t* d_order = nullptr;  // ... sorted by the length of their streams (BatchArgs::lane_order)
     static constexpr int kRing = 256;  // per-run CUDA event triples: begin, row kernel end, all end
     cudaEvent_t ev[kRing][3] = {};
     uint64_t runs = 0, timed_from = 0;
@@ -732,6 +738,7 @@ int b200_batch_free(b200_batch* b) {
     cudaFree(b->d_seg_start);
     cudaFree(b->d_want);
     cudaFree(b->d_seg_raw);
+    cudaFree(b->d_order);
     cudaFree(b->d_got);
     cudaFree(b->d_ok);
     cudaFree(b->d_nbad);
@@ -784,7 +791,30 @@ int b200_batch_create(b200_ctx* ctx, int dev, const uint64_t* off, const uint64_
     dev_alloc((void**)&b->d_len, nobj * 8);
     dev_alloc((void**)&b->d_seg_start, 3 * (nobj + 1) * 4);
     if (want) dev_alloc((void**)&b->d_want, nobj * 4);
-    dev_alloc((void**)&b->d_seg_raw, (size_t)b->plan.ntasks * 4);
+    // many small objects of any shape, none above 32 KiB: candidates for the fold kernel's lane-per-object form, which
+    // leaves one word per object in seg_raw
+    if (b->small_objects && !b->uniform_objs) {
+        uint64_t longest = 0;
+        for (size_t i = 0; i < nobj; i++) longest = std::max<uint64_t>(longest, len[i]);
+        b->lane_objects = longest <= 32768 ? 1 : 0;
+    }
+    dev_alloc((void**)&b->d_seg_raw, std::max<size_t>(b->plan.ntasks, b->lane_objects ? nobj : 0) * 4);
+    if (b->lane_objects) {
+        // counting sort by stream length in 256-byte stages (the arena is 16-byte aligned, so an object's head follows
+        // from its offset): the 32 lanes of a task then run the same number of stages
+        constexpr uint32_t kBuckets = 32768 / 256 + 2;
+        std::vector<uint32_t> start(kBuckets + 1, 0), order(nobj);
+        auto stages_of = [&](size_t i) {
+            const uint64_t h = (16 - (off[i] & 15)) & 15, head = h < len[i] ? h : len[i];
+            return (uint32_t)((((len[i] - head) & ~(uint64_t)15) + 255) / 256);
+        };
+        for (size_t i = 0; i < nobj; i++) start[stages_of(i) + 1]++;
+        for (uint32_t k = 0; k < kBuckets; k++) start[k + 1] += start[k];
+        for (size_t i = 0; i < nobj; i++) order[start[stages_of(i)]++] = (uint32_t)i;
+        dev_alloc((void**)&b->d_order, nobj * 4);
+        if (!rc && cudaMemcpy(b->d_order, order.data(), nobj * 4, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = fail(B200_ERR_CUDA, "upload order");
+    }
     dev_alloc((void**)&b->d_got, nobj * 4);
     dev_alloc((void**)&b->d_ok, nobj);
     dev_alloc((void**)&b->d_nbad, 8);
@@ -830,6 +860,8 @@ int b200_batch_run_async(b200_batch* b, const void* base) {
     a.uniform_off0 = b->uniform_off0;
     a.uniform_len = b->uniform_len;
     a.uniform_objs = b->uniform_objs;
+    a.lane_objects = b->lane_objects;
+    a.lane_order = b->d_order;
     a.init_crc = 0;
     cudaEvent_t* ev = b->ev[b->runs % b200_batch::kRing];
     CU(launch_batch(a, d->tabs, d->grid, d->stream, ev[0], ev[1], &d->side));
@@ -894,6 +926,10 @@ int b200_batch_launches(const b200_batch* b, int* launches_per_run) {
     const bool fold_short = h.p.b && fold_enabled(h.p.b) && h.nshort > 0;
     // equal blocks on the fold kernel, a lane per object, finished there (taken when the arena is 16-byte aligned
     // at run time, which the count assumes)
+    if (b->lane_objects && fold_enabled(kFoldMinRows)) {  // ragged small objects: one fold launch + one finalize
+        *launches_per_run = 2;
+        return 0;
+    }
     const uint64_t lane_objs = b->small_objects && b->uniform_objs && fold_lane_block_ok(b->uniform_len) ? b->uniform_objs : 0;
     const bool rows = h.ntasks && (h.npartial > lane_objs || (!fold_long && h.nlong > 0) || (!fold_short && h.nshort > 0));
     const bool finalize = b->nobj > lane_objs;

@@ -207,6 +207,48 @@ __device__ __forceinline__ uint32_t adv_tab4(const uint32_t* __restrict__ t, uin
            __ldg(t + 768 + (s >> 24));
 }
 
+// After crc_fold_objects_kernel: a thread per object adds what the stream of whole 16-byte words left out — the
+// head up to the first 16-byte boundary, the tail of fewer than 16 bytes — and the initial value, and gives the
+// verdict.  s <- bytes(head); s <- x^(8 m) s ^ raw; s <- bytes(tail).
+__global__ void __launch_bounds__(kFinalThreads)
+crc_finalize_objects_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off,
+                            const uint64_t* __restrict__ len, const uint32_t* __restrict__ want,
+                            const uint32_t* __restrict__ raw, const uint32_t* __restrict__ xpow128,
+                            const uint32_t* __restrict__ byte_tab, uint32_t init_crc, uint32_t nobj,
+                            uint32_t* __restrict__ got, uint8_t* __restrict__ ok, unsigned long long* nbad) {
+    __shared__ uint32_t bt[256];
+    for (int i = threadIdx.x; i < 256; i += kFinalThreads) bt[i] = __ldg(byte_tab + i);
+    __syncthreads();
+    const uint32_t obj = blockIdx.x * kFinalThreads + threadIdx.x;
+    if (obj >= nobj) return;
+    const uint64_t o = off[obj], n = len[obj];
+    const uint8_t* p = base + o;
+    const uint64_t h = (16 - (reinterpret_cast<uintptr_t>(p) & 15)) & 15;
+    const uint32_t head = (uint32_t)(h < n ? h : n);
+    const uint64_t m = (n - head) & ~(uint64_t)15;
+    const uint32_t tail = (uint32_t)(n - head - m);
+    // (an aligned 16-byte word that holds a byte of the object cannot cross a page: reading all of it is safe)
+    auto bytes_of = [&](const uint4& q, uint32_t from, uint32_t count, uint32_t st) {
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (uint32_t k = 0; k < 16; k++)
+            if (k >= from && k < from + count) st = (st >> 8) ^ bt[(st ^ (w[k >> 2] >> (8 * (k & 3)))) & 0xFF];
+        return st;
+    };
+    uint4 hq = make_uint4(0, 0, 0, 0), tq = hq;
+    if (head) hq = __ldg(reinterpret_cast<const uint4*>(reinterpret_cast<uintptr_t>(p) & ~(uintptr_t)15));
+    if (tail) tq = __ldg(reinterpret_cast<const uint4*>(p + head + m));
+    uint32_t s = ~init_crc;
+    if (head) s = bytes_of(hq, (uint32_t)(reinterpret_cast<uintptr_t>(p) & 15), head, s);
+    if (m) s = gf2_mul(__ldg(xpow128 + (m >> 4)), s) ^ raw[obj];  // (m <= 32 KiB: the shift comes from a table)
+    if (tail) s = bytes_of(tq, 0, tail, s);
+    const uint32_t crc = ~s;
+    got[obj] = crc;
+    const bool good = want ? (crc == want[obj]) : true;
+    ok[obj] = good ? 1 : 0;
+    if (!good) atomicAdd(nbad, 1ull);
+}
+
 // One CTA per object.
 __global__ void __launch_bounds__(kFinalThreads)
 crc_finalize_kernel(const uint8_t* __restrict__ base, const uint64_t* __restrict__ off, const uint64_t* __restrict__ len,
@@ -413,6 +455,16 @@ cudaError_t launch_batch(const BatchArgs& a, const DeviceTables& t, int grid, cu
     cudaError_t e = cudaMemsetAsync(a.nbad, 0, sizeof(unsigned long long), stream);
     if (e != cudaSuccess) return e;
     if (ev_begin) cudaEventRecord(ev_begin, stream);
+    if (!a.no_fold && a.off && a.lane_objects && a.small_objects && !a.uniform_objs && t.xpow128 &&
+        fold_enabled(kFoldMinRows)) {
+        // many small ragged objects: a lane per object on the fold kernel, then a thread per object for heads and tails
+        e = launch_fold_objects(a.base, a.off, a.len, a.nobj, a.lane_order, t, a.seg_raw, grid, stream);
+        if (e != cudaSuccess) return e;
+        if (ev_end) cudaEventRecord(ev_end, stream);
+        crc_finalize_objects_kernel<<<(a.nobj + kFinalThreads - 1) / kFinalThreads, kFinalThreads, 0, stream>>>(
+            a.base, a.off, a.len, a.want, a.seg_raw, t.xpow128, t.byte_tab, a.init_crc, a.nobj, a.got, a.ok, a.nbad);
+        return cudaGetLastError();
+    }
     const SegPlan plan{a.rows_per_seg, a.rows_per_seg2};
     const TaskTable tt{a.seg_start, a.nobj, {a.nfull_tasks, a.nshort_tasks, a.npartial_tasks}};
     const bool fold_long = !a.no_fold && fold_enabled(plan.a) && a.nfull_tasks > 0;

@@ -84,7 +84,10 @@ struct DeviceTables {
     uint32_t* xpow8_sq;  // [64]  x^(8*2^k)
     uint32_t* byte_tab;  // [256] classic one-byte table
     uint32_t* adv4;      // [4][256] multiply-by-x^32 slicing tables (fold kernel's final reduction)
+    uint32_t* xpow128;   // [kXpow128Entries] x^(8*16*j): the shift over a stream of j 16-byte words (objects up to
+                         // 32 KiB, crc_finalize_objects_kernel); null where the lane-per-object path is not offered
 };
+constexpr uint32_t kXpow128Entries = 32768 / 16 + 1;
 
 struct BatchArgs {
     const uint8_t* base;        // device arena, 16-byte aligned
@@ -123,6 +126,10 @@ struct BatchArgs {
     uint64_t uniform_off0;
     uint32_t uniform_len;
     uint32_t uniform_objs;
+    // many small objects of any offset and length (all of them at most 32 KiB, seg_raw has room for one word per
+    // object): the fold kernel may take them a lane per object, crc_finalize_objects_kernel finishes them
+    uint32_t lane_objects;
+    const uint32_t* lane_order;  // [nobj] device: the objects sorted by stream length (may be null)
 };
 
 // true when launch_batch will give full segments of this length to the fold kernel
@@ -146,6 +153,11 @@ uint32_t fold_lane_bytes();  // bytes a lane consumes per stage in the variant i
 cudaError_t launch_fold(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t kind);
 // The fold kernel with a lane per object: objects [0, nobjs) of a.uniform_* (nobjs a multiple of 32), finished on the
 // spot (a.got / a.ok / a.nbad against a.want).  fold_lane_block_ok: block_bytes suits it.
+// Ragged small objects, a lane per object (crc_fold_kernel.cu): raw[object] = raw register of the object's stream of
+// whole 16-byte words (what lies between its head, up to the next 16-byte boundary, and its tail of < 16 bytes).
+// order: nullptr, or the object numbers sorted by stream length (lanes of a task then finish together).
+cudaError_t launch_fold_objects(const uint8_t* base, const uint64_t* off, const uint64_t* len, uint32_t nobj,
+                                const uint32_t* order, const DeviceTables& t, uint32_t* raw, int grid, cudaStream_t stream);
 bool fold_lane_block_ok(uint32_t block_bytes);
 cudaError_t launch_fold_per_lane(const BatchArgs& a, const DeviceTables& t, int grid, cudaStream_t stream, uint32_t nobjs);
 
@@ -157,6 +169,7 @@ void host_build_adv_table(uint64_t nbytes, uint32_t out[4 * 256]);
 void host_build_col_k(uint32_t out[128]);
 void host_build_xpow8_sq(uint32_t out[64]);
 void host_build_byte_tab(uint32_t out[256]);
+void host_build_xpow128(uint32_t* out /* [kXpow128Entries] */);
 uint32_t host_xpow8(uint64_t nbytes);
 
 

@@ -41,6 +41,12 @@ void host_build_col_k(uint32_t out[128]) {
     for (int c = 0; c < kRowWords; c++) out[c] = host_xpow8(4ull * (kRowWords - c));
 }
 
+void host_build_xpow128(uint32_t* out) {
+    const uint32_t step = host_xpow8(16);
+    out[0] = kXpow0;
+    for (uint32_t j = 1; j < kXpow128Entries; j++) out[j] = gf2_mul(out[j - 1], step);
+}
+
 void host_build_byte_tab(uint32_t out[256]) {
     for (uint32_t v = 0; v < 256; v++) out[v] = crc_step_byte(0, v);
 }

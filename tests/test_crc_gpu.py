@@ -173,6 +173,26 @@ def test_batch_of_equal_blocks_back_to_back(ctx, arena, block, nobj, off0):
         assert nbad == 1 and not ok[bad_at] and ok.sum() == nobj - 1 and (got == want).all()
 
 
+@pytest.mark.parametrize("longest", [700, 8192, 32768, 40000])
+def test_batch_of_many_ragged_small_objects(ctx, arena, longest):
+    """1024 or more objects of any offset and length, none above 32 KiB, go to the fold kernel a lane per object
+    (sorted by stream length, right-aligned by zeros), heads and tails to a thread per object; with one object above
+    32 KiB the row kernel takes the batch as before.  Lengths around every boundary of the cut (0, < 16, multiples of
+    16 and of 256, one more, one less) are in; a corrupt object is the one that is flagged."""
+    host, d = arena
+    rng = np.random.default_rng(longest)
+    n = 3000
+    ln = rng.integers(0, longest + 1, size=n).astype(np.uint64)
+    ln[:24] = [0, 1, 15, 16, 17, 31, 32, 33, 255, 256, 257, 271, 272, 511, 512, 513, 4095, 4096, 4097, 2, 3, 0, 16, longest]
+    off = rng.integers(0, (64 << 20) - longest - 64, size=n).astype(np.uint64)  # overlapping, any alignment
+    off[:4] = [0, 1, 15, 16]
+    want = _batch_check(ctx, host, d, off, ln)
+    w = want.copy()
+    w[1234] ^= 1
+    got, ok, nbad = crc32c.VerifyObjectsDevice(d, off, ln, w, ctx=ctx)
+    assert nbad == 1 and not ok[1234] and ok.sum() == n - 1 and (got == want).all()
+
+
 def test_batch_empty(ctx, arena):
     host, d = arena
     got, ok, nbad = crc32c.VerifyObjectsDevice(d, np.zeros(0, np.uint64), np.zeros(0, np.uint64), None, ctx=ctx)

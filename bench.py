@@ -21,9 +21,13 @@ Beside the headline line's keys, at EVERY N:
             [r*L/N, (r+1)*L/N), the (crc, len) pairs are all-gathered and folded with the GF(2) combine on the host;
             strong scaling; the CRC is compared with tests/golden/config3.json (made on the CPU).
 `config5` : BASELINE config 5 — 10^9 latency samples split over the N ranks: README histogram, OpenCensus buckets and
-            the seven ssd_test lines with the counts all-reduced over NCCL; compared with tests/golden/config5.json.
+            the seven ssd_test lines with the counts gathered / all-reduced over NCCL (collectives counted); compared with tests/golden/config5.json.
 `e2e.h2d_only` : a bare cudaMemcpy of the same pinned arena on every rank at once — the ceiling of the host-buffer path.
 `multi_device_parity` : the one-process multi-GPU entry points checked on distinct devices (tests/multidev_checks.py).
+At N = 1 also: `small_objects` (a million 4 KiB blocks, a million ragged objects under 8 KiB, 4096 ragged
+objects up to 4 MiB; device-timed, a sample of each checked against the oracle), `text_codec` (20 M lines of latency
+text parsed on the device, the first block against Python's float()), `latency_reduction` (5*10^8 samples: README
+histogram with moments, the seven ssd_test lines).
 """
 from __future__ import annotations
 

@@ -21,6 +21,11 @@ b.run(d); b.run(d); b.close()
 # the same blocks 8 bytes off a 16-byte boundary: the row kernel's shape (the aligned ones above go to the fold kernel)
 b = crc32c.DeviceBatch(np.arange(n - 1, dtype=np.uint64) * 4096 + 8, np.full(n - 1, 4096, dtype=np.uint64), None, ctx)
 b.run(d); b.run(d); b.close()
+# a million ragged objects under 8 KiB, unaligned: the fold kernel a lane per object + the thread-per-object finish
+ln_t = rng.integers(0, 8192, size=n).astype(np.uint64)
+off_t = np.arange(n, dtype=np.uint64) * np.uint64(4096 - 16) + rng.integers(0, 16, size=n).astype(np.uint64)
+b = crc32c.DeviceBatch(off_t, np.minimum(ln_t, 4000), None, ctx)
+b.run(d); b.run(d); b.close()
 # ragged
 ln = rng.integers(1, 4 << 20, size=2048).astype(np.uint64)
 off = np.concatenate([[0], np.cumsum(ln[:-1] + rng.integers(0, 64, size=2047).astype(np.uint64))]).astype(np.uint64)

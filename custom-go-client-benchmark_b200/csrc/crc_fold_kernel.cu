@@ -308,6 +308,16 @@ crc_fold_objects_kernel(const uint8_t* __restrict__ base, const uint64_t* __rest
         info[lane].vbase = p + head - (size_t)(nstage * LANE_BYTES - m);
         __syncwarp();
 
+        // the sixteen rows this lane copies for (its chunk of each), kept in registers for the whole task: where the
+        // lane's chunk of the row's NEXT stage lies, and how many zero bytes the row still has in front of it
+        const uint8_t* src_of[kCopyInstrs];
+        uint32_t zeros_of[kCopyInstrs];
+#pragma unroll
+        for (int k = 0; k < kCopyInstrs; k++) {
+            const RowInfo ri = info[crow + kRowsPerInstr * k];
+            src_of[k] = ri.vbase + cchunk * 16;
+            zeros_of[k] = ri.zeros;
+        }
         uint32_t r[64];
 #pragma unroll
         for (int k = 0; k < 64; k++) r[k] = 0;
@@ -320,11 +330,11 @@ crc_fold_objects_kernel(const uint8_t* __restrict__ base, const uint64_t* __rest
 #pragma unroll
                 for (int k = 0; k < kCopyInstrs; k++) {
                     const uint32_t row = crow + kRowsPerInstr * k;
-                    const RowInfo ri = info[row];
-                    const bool real = u >= ri.zeros;
+                    const bool real = u >= zeros_of[k];
                     const uint32_t dst = buf + row * LANE_BYTES + ((cchunk ^ (row & 7)) << 4);
                     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst),
-                                 "l"(real ? ri.vbase + u : base), "r"(real ? 16u : 0u) : "memory");
+                                 "l"(real ? src_of[k] : base), "r"(real ? 16u : 0u) : "memory");
+                    src_of[k] += LANE_BYTES;
                 }
             }
             cp_async_commit();

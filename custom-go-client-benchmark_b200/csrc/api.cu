@@ -1387,9 +1387,10 @@ int b200_radix_count(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n,
     if (top < 64)
         CU(cudaMemcpyAsync(d->lat.d_prefix, prefix, nk * sizeof(uint64_t), cudaMemcpyHostToDevice, d->stream));
     CU(launch_radix_pass((const long long*)d_samples, n, key_base, shift, top, nk, d->lat, d->stream));
-    CU(cudaMemcpyAsync(counts, d->lat.d_radix, (size_t)nk * kRadixBins * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+    CU(cudaMemcpyAsync(d->lat.h_radix, d->lat.d_radix, (size_t)nk * kRadixBins * sizeof(uint64_t), cudaMemcpyDeviceToHost,
                        d->stream));
     CU(cudaStreamSynchronize(d->stream));
+    memcpy(counts, d->lat.h_radix, (size_t)nk * kRadixBins * sizeof(uint64_t));
     return 0;
 }
 
@@ -1408,9 +1409,10 @@ int b200_radix_count_based(b200_ctx* ctx, int dev, const int64_t* d_samples, siz
     }
     CU(cudaMemcpyAsync(d->lat.d_prefix, both, sizeof both, cudaMemcpyHostToDevice, d->stream));
     CU(launch_radix_pass((const long long*)d_samples, n, 0, shift, top, nk, d->lat, d->stream, true));
-    CU(cudaMemcpyAsync(counts, d->lat.d_radix, (size_t)nk * kRadixBins * sizeof(uint64_t), cudaMemcpyDeviceToHost,
+    CU(cudaMemcpyAsync(d->lat.h_radix, d->lat.d_radix, (size_t)nk * kRadixBins * sizeof(uint64_t), cudaMemcpyDeviceToHost,
                        d->stream));
     CU(cudaStreamSynchronize(d->stream));
+    memcpy(counts, d->lat.h_radix, (size_t)nk * kRadixBins * sizeof(uint64_t));
     return 0;
 }
 

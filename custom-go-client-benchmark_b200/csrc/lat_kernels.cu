@@ -1466,6 +1466,8 @@ cudaError_t lat_scratch_init(LatScratch* s) {
     }
     if (e == cudaSuccess) e = cudaMalloc(&s->d_params, sizeof(HistParams));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long));
+    if (e == cudaSuccess)
+        e = cudaHostAlloc(&s->h_radix, (size_t)kMaxSelect * kRadixBins * sizeof(unsigned long long), cudaHostAllocDefault);
     if (e == cudaSuccess) e = cudaMalloc(&s->d_prefix, 2 * kMaxSelect * sizeof(unsigned long long));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_in, sizeof(SelDeferred));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_sel_bar, 2 * sizeof(unsigned));
@@ -1490,6 +1492,7 @@ void lat_scratch_free(LatScratch* s) {
     cudaFreeHost(s->h_results);
     cudaFreeHost(s->h_params);
     cudaFree(s->d_radix);
+    cudaFreeHost(s->h_radix);
     cudaFree(s->d_prefix);
     cudaFree(s->d_compact);
     cudaFree(s->d_sel_in);

@@ -101,6 +101,7 @@ struct LatScratch {
     unsigned long long* d_counts;       // [kMaxThresholds + 1]
     LatMoments* d_mom;
     unsigned long long* d_radix;        // [kMaxSelect][kRadixBins]
+    unsigned long long* h_radix;        // pinned: the same, read back (a pageable copy of 128 KB was ~40 us)
     unsigned long long* d_prefix;       // [2][kMaxSelect]: prefixes, then (optionally) a key base per histogram
     long long* d_compact;               // samples of the buckets still in play after the first radix pass (lazy)
     size_t compact_cap;                 // in samples

@@ -102,11 +102,26 @@ class _Reducer:
 
         import torch
         t0 = time.perf_counter()
-        t = torch.from_numpy(arr.astype(np.int64, copy=True))
-        if self.device is not None:
-            t = t.to(self.device)
-        self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op), group=self.group)
-        out = t.cpu().numpy()
+        a = np.ascontiguousarray(arr).astype(np.int64, copy=False)
+        if self.device is None:
+            t = torch.from_numpy(a.copy())
+            self.dist.all_reduce(t, op=getattr(self.dist.ReduceOp, op), group=self.group)
+            out = t.numpy()
+        else:
+            # pinned staging and a device buffer kept per (device, length): see gather()
+            key = (str(self.device), a.size, "reduce")
+            buf = _Reducer._buffers.get(key)
+            if buf is None:
+                buf = (torch.empty(a.size, dtype=torch.int64).pin_memory(),
+                       torch.empty(a.size, dtype=torch.int64, device=self.device))
+                _Reducer._buffers[key] = buf
+            pin, dev = buf
+            pin.numpy()[:] = a.reshape(-1)
+            dev.copy_(pin, non_blocking=True)
+            self.dist.all_reduce(dev, op=getattr(self.dist.ReduceOp, op), group=self.group)
+            pin.copy_(dev, non_blocking=True)
+            torch.cuda.current_stream(dev.device).synchronize()
+            out = pin.numpy().copy().reshape(a.shape)
         _Reducer.tally["collectives"] += 1
         _Reducer.tally["seconds"] += time.perf_counter() - t0
         return out

@@ -329,8 +329,6 @@ __device__ Parsed parse_float(const Text& t, size_t n, size_t s) {
     return r;
 }
 
-// bytes kept of a word holding k leading digits (k clamped to 0..4)
-__constant__ unsigned c_keep[5] = {0u, 0xFFu, 0xFFFFu, 0xFFFFFFu, 0xFFFFFFFFu};
 
 // 0x80 in every byte of w that is NOT an ASCII digit (w must be ASCII: no byte >= 0x80)
 __device__ __forceinline__ unsigned nondigit_flags(unsigned w) {
@@ -378,7 +376,10 @@ __device__ __forceinline__ bool parse_fast(const unsigned w[4], Tail tail, doubl
         else if (n1) nf = 4 + (__ffs(n1) >> 3) - 1;
         else if (n2) nf = 8 + (__ffs(n2) >> 3) - 1;
         else return false;  // twelve or more fraction digits
-        const unsigned k0 = c_keep[min(nf, 4)], k1 = c_keep[min(max(nf - 4, 0), 4)], k2 = c_keep[min(max(nf - 8, 0), 4)];
+        // bytes kept of each word: the first nf, nf - 4, nf - 8 (clamped to 0..4) — a clamping funnel shift of ones
+        const unsigned k0 = __funnelshift_rc(0xFFFFFFFFu, 0u, 32 - 8 * min(nf, 4)),
+                       k1 = __funnelshift_rc(0xFFFFFFFFu, 0u, 32 - 8 * min(max(nf - 4, 0), 4)),
+                       k2 = __funnelshift_rc(0xFFFFFFFFu, 0u, 32 - 8 * min(max(nf - 8, 0), 4));
         f0 = (f0 & k0) | (0x30303030u & ~k0);
         f1 = (f1 & k1) | (0x30303030u & ~k1);
         f2 = (f2 & k2) | (0x30303030u & ~k2);
@@ -436,15 +437,16 @@ text_parse_kernel(const unsigned char* __restrict__ tg, size_t n, const unsigned
     }
     __syncthreads();
     const unsigned long long rank0 = tile_base[blockIdx.x] + aux[blockIdx.x / kScanBlock];
-    const size_t staged_end = t.send;
-    for (unsigned l = threadIdx.x; l < total; l += kTextThreads) {
-        const unsigned long long rank = rank0 + l;
-        if (rank >= max_lines) break;
+    // per-line quantities in 32 bits, relative to the tile: the lines this tile may write, the staged bytes past its start
+    const unsigned mine = rank0 >= max_lines ? 0u : (unsigned)min((unsigned long long)total, (unsigned long long)max_lines - rank0);
+    const unsigned staged_len = (unsigned)(t.send - tbase);
+    double* const vout = values + rank0;
+    unsigned char* const sout = status ? status + rank0 : nullptr;
+    for (unsigned l = threadIdx.x; l < mine; l += kTextThreads) {
         const unsigned off = starts[l];
-        const size_t pos = tbase + off;
         Parsed p{0.0, 1};
         bool done = false;
-        if (pos + 20 <= staged_end) {  // sixteen bytes from the line start, read as aligned words and shifted into place
+        if (off + 20 <= staged_len) {  // sixteen bytes from the line start, read as aligned words and shifted into place
             const unsigned* aw = reinterpret_cast<const unsigned*>(tile + (off & ~3u));
             const int sh = 8 * (off & 3);
             unsigned w[4];
@@ -453,11 +455,11 @@ text_parse_kernel(const unsigned char* __restrict__ tg, size_t n, const unsigned
             done = parse_fast(w, [&](int i) -> unsigned { return tile[off + i]; }, &p.v);
             if (done) p.status = 0;
         }
-        if (!done) p = parse_float(t, n, pos);
-        values[rank] = p.v;
-        if (status) status[rank] = p.status;
+        if (!done) p = parse_float(t, n, tbase + off);
+        vout[l] = p.v;
+        if (sout) sout[l] = p.status;
         if (p.status) {
-            atomicMin(summary, rank);
+            atomicMin(summary, rank0 + l);
             atomicAdd(summary + (p.status == 1 ? 1 : 2), 1ull);
         }
     }

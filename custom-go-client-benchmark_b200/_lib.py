@@ -79,6 +79,7 @@ SIGNATURES = {
     "b200_select_kth_stats": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp, _vp]),
     "b200_select_kth_avg": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _vp, _vp]),
     "b200_select_sample": (_int, [_vp, _int, _vp, _sz, _sz, _pp, C.POINTER(_sz)]),
+    "b200_select_sample_bounds": (_int, [_vp, _int, _vp, _sz, _sz, _vp, _vp, _int, _u64, _vp, C.POINTER(_sz)]),
     "b200_bracket_pass": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _u64, _vp, _pp, C.POINTER(_u64), _vp]),
     "b200_bracket_pass_avg": (_int, [_vp, _int, _vp, _sz, _i64, _vp, _int, _u64, _vp, _pp, C.POINTER(_u64), _vp]),
     "b200_select_kth_range": (_int, [_vp, _int, _vp, _sz, _i64, _i64, _i64, _vp, _int, _vp]),

@@ -1873,6 +1873,26 @@ int b200_select_sample(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t 
     return 0;
 }
 
+int b200_select_sample_bounds(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, size_t stride,
+                              const uint64_t* ranks, const uint8_t* upper, int nranks, uint64_t slack, int64_t* out,
+                              size_t* nsample) {
+    DevState* d = get_dev(ctx, dev);
+    if (!d || !ranks || !out || !nsample || nranks < 1 || nranks > 2 * kSelMax || stride < 1 || !d_samples ||
+        ((uintptr_t)d_samples & 7))
+        return fail(B200_ERR_INVALID, "b200_select_sample_bounds");
+    const size_t s = n / stride;
+    for (int i = 0; i < nranks; i++)
+        if (ranks[i] >= s) return fail(B200_ERR_INVALID, "b200_select_sample_bounds: rank >= n / stride");
+    std::lock_guard<std::recursive_mutex> sel_lock(d->select_mu);
+    bool up[2 * kSelMax] = {};
+    for (int i = 0; i < nranks && upper; i++) up[i] = upper[i] != 0;
+    SampleFirst first{d_samples, stride, 0};
+    const int rc = select_resident(ctx, dev, nullptr, s, 1, false, 0, 0, ranks, nranks, out, slack, up, &first);
+    if (rc > 0) return fail(B200_ERR_NOMEM, "b200_select_sample_bounds");
+    if (rc == 0) *nsample = s;
+    return rc;
+}
+
 namespace {
 int bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor, const int64_t* thresholds,
                  int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept, uint64_t* nkept, b200_lat_stats* stats,

@@ -420,7 +420,8 @@ def sampled_select(red: _Reducer, n_local: int, n_global: Optional[int], divisor
     thousand): the brackets, the bracket-pass counts, two radix passes inside the brackets.
 
       sample_fn(stride) -> s                 this rank's stratified sample (one input per `stride`), its size
-      sample_select_fn(ranks) -> values      order statistics of that sample (local, exact)
+      sample_select_fn(ranks, upper, slack) -> values   order statistics of that sample (local), or bounds on them
+                                             to within `slack` sample ranks: from below, from above where upper[i]
       bracket_fn(thresholds, cap) -> (counts, nkept, stats)   the histogram pass that keeps the odd bins
       kept_count_fn / kept_minmax_fn         radix-select building blocks over the kept samples
       fractions                              [(num, den)]: the wanted ranks are n_global * num // den; n_global may
@@ -441,16 +442,17 @@ def sampled_select(red: _Reducer, n_local: int, n_global: Optional[int], divisor
     s = sample_fn(stride)
     ok = s >= 1024
     margin = int(2.5 * np.sqrt(max(s, 1))) + 2
-    want, where = [], []
+    want, upper, where = [], [], []
     for i in range(nk):
         c = fractions[i][0] * s // fractions[i][1] if fractions is not None else int(ks[i]) * s // n_global
         lo_at = hi_at = None
         if ok and c >= margin:
-            lo_at = len(want); want.append(c - margin)
+            lo_at = len(want); want.append(c - margin); upper.append(False)
         if ok and c + margin + 1 < s:
-            hi_at = len(want); want.append(c + margin + 1)
+            hi_at = len(want); want.append(c + margin + 1); upper.append(True)
         where.append((lo_at, hi_at))
-    got = sample_select_fn(want) if want else []
+    # (bounds good to a sixteenth of the margin are enough for bracket ends, and a radix round cheaper)
+    got = sample_select_fn(want, upper, max(1, margin // 16)) if want else []
     s64 = lambda w: w - (1 << 64) if w >= _SIGN else w
     vec = [int(n_local), 1 if ok else 0]
     vec += [_I64_MIN if a is None else int(got[a]) for a, _ in where]
@@ -498,17 +500,17 @@ def _sampled_select_on_gpu(red, L, h, d, d_samples, n, n_global, divisor, ks, wa
     """sampled_select over this rank's device samples through the C ABI building blocks."""
     state = {}
 
-    def sample_fn(stride):
-        p, cnt = C.c_void_p(), C.c_size_t()
-        check(L.b200_select_sample(h, d, d_samples, n, stride, C.byref(p), C.byref(cnt)))
-        state["sample"] = (p.value, cnt.value)
-        return cnt.value
+    def sample_fn(stride):  # (the sample is taken together with its order statistics, below: one call, one round trip)
+        state["stride"] = stride
+        return n // stride
 
-    def sample_select_fn(ranks):
-        p, cnt = state["sample"]
+    def sample_select_fn(ranks, upper=None, slack=0):
         karr = np.array(ranks, dtype=np.uint64)
+        uarr = np.array([1 if u else 0 for u in (upper or [0] * karr.size)], dtype=np.uint8)
         out = np.zeros(karr.size, dtype=np.int64)
-        check(L.b200_select_kth(h, d, p, cnt, 1, karr.ctypes.data, karr.size, out.ctypes.data))
+        cnt = C.c_size_t()
+        check(L.b200_select_sample_bounds(h, d, d_samples, n, state["stride"], karr.ctypes.data, uarr.ctypes.data, karr.size,
+                                          int(slack), out.ctypes.data, C.byref(cnt)))
         return [int(x) for x in out]
 
     def bracket_fn(thr, cap):

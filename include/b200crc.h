@@ -207,6 +207,13 @@ int b200_select_kth_avg(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t
  * Both buffers stay valid until the next b200_select_* / b200_bracket_pass call on the same device. */
 int b200_select_sample(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, size_t stride,
                        const int64_t** d_sample, size_t* nsample);
+/* Sampling and the order statistics of the sample in ONE call (one device round trip): out[i] bounds the ranks[i]-th
+ * smallest (0-based) of the same stratified sample — from below, or from above where upper[i] != 0 (upper may be
+ * NULL) — to within `slack` sample ranks (0 = the order statistic itself); bounds are all the brackets of a sampled
+ * select need and cost a pass less.  nranks <= 16, ranks[i] < n / stride = *nsample. */
+int b200_select_sample_bounds(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, size_t stride,
+                              const uint64_t* ranks, const uint8_t* upper, int nranks, uint64_t slack, int64_t* out,
+                              size_t* nsample);
 int b200_bracket_pass(b200_ctx* ctx, int dev, const int64_t* d_samples, size_t n, int64_t divisor,
                       const int64_t* thresholds, int nthr, uint64_t cap, uint64_t* counts, const int64_t** d_kept,
                       uint64_t* nkept, b200_lat_stats* stats);

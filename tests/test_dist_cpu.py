@@ -54,7 +54,7 @@ def _np_sampled_fns(samples, divisor, seed):
         st["sample"] = np.sort(samples[np.arange(s) * stride + rng.integers(0, stride, size=s)]) if s else samples[:0]
         return s
 
-    def sample_select_fn(ranks):
+    def sample_select_fn(ranks, upper=None, slack=0):  # (exact order statistics are bounds with no slack)
         return [int(st["sample"][r]) for r in ranks]
 
     def bracket_fn(thr, cap):

@@ -633,3 +633,41 @@ def test_radix_count_with_a_key_base_per_histogram(ctx):
             want = np.bincount(dg, minlength=lat.RADIX_BINS).astype(np.uint64)
             assert (counts[i * lat.RADIX_BINS:(i + 1) * lat.RADIX_BINS] == want).all(), (shift, i)
     ctx.free_device(d)
+
+
+def test_sample_and_bounds_in_one_call(ctx):
+    """b200_select_sample_bounds: the same stratified sample as b200_select_sample; with slack 0 its order statistics
+    exactly, with slack > 0 bounds from below / above that are off by at most `slack` sample ranks or 4096 ns."""
+    import ctypes as C
+    n, stride = 6_000_003, 16
+    ns = oracle.latency_ns(n, seed=17)
+    d = upload(ctx, ns)
+    L, h = ctx._L, ctx._h
+    p, cnt = C.c_void_p(), C.c_size_t()
+    assert L.b200_select_sample(h, 0, d, n, stride, C.byref(p), C.byref(cnt)) == 0
+    s = cnt.value
+    sample = np.empty(s, dtype=np.int64)
+    ctx.d2h(sample, p.value)
+    srt = np.sort(sample)
+    ranks = np.array([0, 7, s // 5, s // 2, s // 2 + 1, 9 * s // 10, 99 * s // 100, s - 1, 3, 4], dtype=np.uint64)
+    upper = np.array([0, 1, 0, 1, 0, 1, 0, 1, 1, 0], dtype=np.uint8)
+    for slack in (0, 40):
+        out = np.zeros(ranks.size, dtype=np.int64)
+        got_s = C.c_size_t()
+        pkg._lib.check(L.b200_select_sample_bounds(h, 0, d, n, stride, ranks.ctypes.data, upper.ctypes.data, ranks.size,
+                                                   slack, out.ctypes.data, C.byref(got_s)))
+        assert got_s.value == s
+        for r, u, v in zip(ranks, upper, out):
+            exact = int(srt[int(r)])
+            if slack == 0:
+                assert int(v) == exact
+            elif u:
+                between = int(np.searchsorted(srt, v, "right")) - int(r) - 1
+                assert v >= exact and (v - exact < 4096 or between <= slack), (r, v, exact, between)
+            else:
+                between = int(r) - int(np.searchsorted(srt, v, "left"))
+                assert v <= exact and (exact - v < 4096 or between <= slack), (r, v, exact, between)
+    bad = np.array([s], dtype=np.uint64)
+    assert L.b200_select_sample_bounds(h, 0, d, n, stride, bad.ctypes.data, None, 1, 0, out.ctypes.data,
+                                       C.byref(got_s)) == pkg._lib.ERR_INVALID
+    ctx.free_device(d)

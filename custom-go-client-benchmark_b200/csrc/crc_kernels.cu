@@ -17,6 +17,8 @@
 //   x^(32*(128-c)) and xor-reduced over the warp into one raw register per segment.
 // Finalize kernel: per object, Horner over the segment registers with the per-segment shift constant,
 //   unaligned head and sub-row tail bytes, init/final inversion, comparison with want[].
+// Whole segments of large objects, and batches of many small objects (a lane per object), are the fold kernel's:
+//   crc_fold_kernel.cu.  launch_batch below picks the road for a batch.
 #include "crc_kernels.h"
 
 #ifdef B200_DEBUG_ASSERT

@@ -8,10 +8,14 @@
 //   percentiles benchmark-script/ssd_test/main.go:147-163  sorted[size/2] etc.
 // Both bin rules are monotone step functions of the raw nanosecond value, so the host turns the float
 // edges into ascending int64 nanosecond thresholds and the kernel only counts thresholds <= n; no
-// per-sample division or float compare is needed for binning.  A log-linear LUT (32 cells per power of
-// two) gives the count at the low end of the sample's cell plus the 0..few thresholds inside it.
-// All kernels are HBM-bound streams of 8 bytes per sample with 128-bit loads; counters are private per
-// (warp, lane) in shared memory so the skewed latency distribution causes no atomic contention.
+// per-sample division or float compare is needed for binning.  One byte look-up in an 8 KB table (indexed by
+// the sample's quotient or by its high bits) gives the counter row; the few samples whose cell holds a threshold
+// are parked and resolved by a search over the thresholds (hist_kernel).
+// All kernels stream 8 bytes per sample — the histogram family through per-warp rings of 2 KB tiles filled by
+// bulk copies — and keep their counters private per (warp, lane) in shared memory, so the skewed latency
+// distribution causes no atomic contention.  Order statistics: a stratified sample brackets the wanted ranks, one
+// collecting histogram pass counts below the brackets and keeps what is inside, and a one-kernel radix select
+// (sel_fused_kernel) settles the ranks among the kept samples; api.cu holds the host side of that.
 #include "lat_kernels.h"
 
 #ifdef B200_DEBUG_ASSERT

@@ -199,3 +199,42 @@ def test_radix_select_single_process_matches_sort():
         lat.radix_select(red, 0, lambda: (0, 0), _np_count_fn(v[:0]), 1, [0])
     with pytest.raises(ValueError):
         lat.radix_select(red, v.size, lambda: (int(v.min()), int(v.max())), _np_count_fn(v), 1, [5000])
+
+
+def test_moment_words_round_trip_and_merge():
+    """The 64-bit words a rank contributes to the one-collective merges: negative 128-bit sums, sums of squares
+    above 2^64, extremes across ranks, a rank without samples (its extremes must not count)."""
+    a = lat._moment_words([3, 0, 7], 10, -5, 40, -(1 << 70) - 3, (1 << 100) + 9, 1, 2)
+    b = lat._moment_words([1, 1, 1], 3, -9, 12, (1 << 70) + 1, (1 << 64) - 1, 0, 5)
+    empty = lat._moment_words([0, 0, 0], 0, (1 << 63) - 1, -(1 << 63), 0, 0, 0, 0)
+    assert all(0 <= w < 1 << 64 for w in [int(x) & ((1 << 64) - 1) for x in a + b + empty])
+    rows = [[int(x) & ((1 << 64) - 1) for x in r] for r in (a, empty, b)]  # what _Reducer.gather hands back
+    counts, cnt, mn, mx, total, sumsq, below, above = lat._merge_moment_words(rows, 3)
+    assert list(counts) == [4, 1, 8] and (cnt, below, above) == (13, 1, 7)
+    assert (mn, mx) == (-9, 40)
+    assert total == -2 and sumsq == (1 << 100) + 9 + (1 << 64) - 1
+    # nobody holds a sample
+    _, cnt, mn, mx, _, _, _, _ = lat._merge_moment_words([rows[1], rows[1]], 3)
+    assert cnt == 0 and mn == (1 << 63) - 1 and mx == -(1 << 63)
+    # not distributed: gather is the identity on one row
+    assert lat._Reducer().gather([1, -1, (1 << 64) - 1]) == [[1, (1 << 64) - 1, (1 << 64) - 1]]
+
+
+def test_bracket_radix_select_single_process():
+    """Order statistics resolved inside their own brackets (keys relative to the bracket's lower end, one key base per
+    wanted rank): against a sort, with brackets of different widths, touching key ranges and a one-value bracket."""
+    rng = np.random.default_rng(3)
+    v = np.concatenate([rng.integers(1000, 1400, 3000), rng.integers(5000, 5001, 50), rng.integers(70_000, 90_000, 2000),
+                        rng.integers(-500, -100, 700)]).astype(np.int64)
+    brackets = [(-500, -101), (1000, 1399), (5000, 5000), (70_000, 89_999)]
+    srt = np.sort(v)
+    red = lat._Reducer()
+    located, want = [], []
+    for j, (lo, hi) in enumerate(brackets):
+        inside = srt[(srt >= lo) & (srt <= hi)]
+        for r in (0, inside.size // 2, inside.size - 1):
+            located.append((j, r))
+            want.append(int(inside[r]))
+    for divisor in (1, 7):
+        got = lat.bracket_radix_select(red, _np_count_fn(v), brackets, located, divisor)
+        assert got == [abs(w) // divisor * (1 if w >= 0 else -1) for w in want]
